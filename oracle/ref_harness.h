@@ -1,0 +1,121 @@
+/* TEST INFRASTRUCTURE — C API of oracle/_ref/libpim_ref.so.
+ *
+ * libpim_ref.so = the reference's own src/rendering/path_tracer.c,
+ * src/rendering/lightmap.c, src/math/{dist1d,sphgauss,pcg,lighting}.c compiled
+ * unmodified from /root/reference, over the CPU ray-query restatement
+ * (cpu_bvh.c, standing in for the absent Embree 3.13.5 binary) and the engine
+ * stubs (ref_stubs.c). Only tests/, __graft_entry__.smoke() and bench.py's CPU
+ * baseline may load it. Everything here is plain pointers and sizes for ctypes.
+ */
+#ifndef ORACLE_REF_HARNESS_H
+#define ORACLE_REF_HARNESS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* RNG streams: work item i of Task_Run call number c inside oracle_begin(stream, pass)
+ * starts from Prng_Get() state Pcg4(i, pass, seed, (stream<<4)|c) and path-tracer
+ * context state Pcg4(i, pass, seed, ((stream<<4)|c) ^ 0x80000000).            */
+enum
+{
+    ORACLE_STREAM_SCENE = 1,   /* call 0: CalcEmissionPdfFn, call 1: SetupLightGridFn */
+    ORACLE_STREAM_TRACE = 2,   /* call 0: UpdateDistsFn, call 1: TraceFn */
+    ORACLE_STREAM_RAYGEN = 3,  /* call 0: UpdateDistsFn, call 1: RayGenFn */
+    ORACLE_STREAM_BAKE = 4,    /* call 0: UpdateDistsFn, call 1: BakeFn */
+    ORACLE_STREAM_LUT = 5,     /* call 0: BakeBrdfFn */
+    ORACLE_STREAM_RAYS = 6,    /* call 0: harness Pt_TraceRay batch */
+};
+
+void oracle_set_threads(int n);
+int oracle_get_threads(void);
+void oracle_set_seed(uint32_t seed);
+void oracle_begin(uint32_t stream, uint32_t pass);
+void oracle_frame_end(void);
+void oracle_set_pt_dist_meters(float v);
+
+void oracle_tables_clear(void);
+int oracle_add_texture(int w, int h, const void* texels, int bytesPerTexel, int vkFormat);
+int oracle_add_mesh(const float* pos4, const float* nrm4, const float* uv4, int length);
+int oracle_add_entity(int meshId, const float* matrix16,
+                      int albedoTex, int romeTex, int normalTex,
+                      uint32_t flags, const float* meanFreePath4, float ior, float bumpiness);
+void oracle_set_sky(int size, const float* faces);
+void oracle_set_brdf_lut(int w, int h, const float* texels2);
+void oracle_bake_brdf_lut(int w, int h, int samples, float* texelsOut2);
+
+/* restatement of CmdCornellBox (src/rendering/render_system.c:1109-1306) on the
+ * reference's own math headers; fills the tables above. */
+void oracle_cornell_box(int spheres);
+
+int oracle_entity_count(void);
+void oracle_entity_get(int i, int* meshId, float* matrix16, int* texIds3,
+                       uint32_t* flags, float* meanFreePath4, float* ior, float* bumpiness);
+int oracle_mesh_get(int meshId, const float** pos4, const float** nrm4, const float** uv4);
+int oracle_texture_get(int texId, int* w, int* h, const void** texels, int* vkFormat);
+
+typedef struct OracleSceneInfo
+{
+    int32_t vertCount, matCount, emissiveCount;
+    int32_t gridSize[3];
+    float gridLo[4], gridHi[4];
+    float cellsPerMeter;
+    float rcpMajorant;
+    const float* positions;     /* float4[vertCount] */
+    const float* normals;       /* float4[vertCount] */
+    const float* uvs;           /* float2[vertCount] */
+    const int32_t* matIds;      /* [vertCount] */
+    const int32_t* vertToEmit;  /* [vertCount] */
+    const int32_t* emitToVert;  /* [emissiveCount] */
+} OracleSceneInfo;
+
+int oracle_sys_init(void);
+void* oracle_scene_new(void);
+void oracle_scene_del(void* scene);
+void oracle_scene_info(const void* scene, OracleSceneInfo* info);
+/* copies cell `cell`'s distribution; returns its length (0 = no distribution) */
+int oracle_scene_dist(const void* scene, int cell, float* pdf, float* cdf, uint32_t* live);
+/* overwrite a cell's pdf (length must match or be 0) and re-bake its cdf */
+void oracle_scene_set_dist(void* scene, int cell, int length, const float* pdf);
+void oracle_scene_set_live(void* scene, int cell, const uint32_t* live);
+
+typedef struct OracleCamera { float position[4]; float rotation[4]; float zNear, zFar, fovy; } OracleCamera;
+typedef struct OracleDof
+{
+    float aperture, focalLength; int32_t bladeCount; float bladeRot;
+    float focalPlaneCurvature, autoFocusSpeed; int32_t autoFocus;
+} OracleDof;
+
+void oracle_dof_default(OracleDof* dof);
+void oracle_camera_lookat(OracleCamera* cam, const float* eye3, const float* at3, float fovy);
+
+/* one call of the reference's Pt_Trace (1 spp) on host float3 images */
+void oracle_trace(void* scene, int w, int h, float* color3, float* albedo3, float* normal3,
+                  float sampleWeight, const OracleCamera* cam, OracleDof* dof, uint32_t pass);
+/* Pt_Intersect over n rays: ro4[i].xyz, rd4[i].xyz, rd4[i].w = tFar; out = PtRayHit[n] (48 B each) */
+void oracle_intersect_n(const void* scene, const float* ro4, const float* rd4, float tNear,
+                        int64_t n, void* hitsOut);
+/* Pt_TraceRay over n rays, item i seeded as stream RAYS; out = PtResult[n] (9 floats each) */
+void oracle_trace_rays(void* scene, const float* ro4, const float* rd4, int64_t n,
+                       uint32_t pass, float* resultsOut9);
+/* Pt_RayGen */
+void oracle_raygen(void* scene, const float* origin4, int count, uint32_t pass,
+                   float* colors4, float* directions4);
+
+/* fetch counters of the canonical BVH, summed over worker threads since reset */
+void oracle_counters_reset(void);
+void oracle_counters_get(uint64_t* nodes, uint64_t* tris, uint64_t* rays);
+
+/* brute-force fp64 ground truth on the scene's triangles; flags[i]: 0 miss, 1 hit, 2 hit with near-tie */
+void oracle_brute_n(const void* scene, const float* ro4, const float* rd4, float tNear,
+                    int64_t n, float* tuv3, int32_t* prim, int32_t* flags);
+
+/* CalcStdDev (src/rendering/render_system.c:1374-1394) */
+float oracle_stddev(const float* color3, int w, int h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
