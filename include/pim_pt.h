@@ -1,0 +1,271 @@
+/* pim_pt.h — C ABI of libpimpt.so, the B200 (sm_100a) replacement for pim's CPU
+ * path-tracing hot path.
+ *
+ * The reference has no FFI layer: its boundary for this path is the plain C
+ * header src/rendering/path_tracer.h:67-103 plus LmPack_Bake
+ * (src/rendering/lightmap.h:69), linked statically into the engine. This
+ * header exports the same names with the same struct layouts, so an engine
+ * build can link libpimpt.so in place of path_tracer.c,
+ * and adds the batch / device-pointer forms a GPU backend needs.
+ *
+ * Every entry point is blocking (the stream is synchronised before return)
+ * unless it takes a cudaStream_t-like `stream` argument. Nothing aborts: on
+ * failure functions return NULL / a negative status and Pt_LastError() holds
+ * a message. There is no CPU fallback; without a CUDA device PtSys_Init fails.
+ */
+#ifndef PIM_PT_H
+#define PIM_PT_H
+
+#include <stdint.h>
+#include <stdbool.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- value types (layouts of src/math/types.h:52-73) ---------------------- */
+#if defined(__CUDACC__) || defined(PIM_PT_NO_VECTOR_TYPES)
+/* CUDA already defines float2/3/4 with the same layouts */
+#else
+typedef struct pim_float2_s { float x, y; } pim_float2;
+typedef struct pim_float3_s { float x, y, z; } pim_float3;
+typedef struct pim_float4_s { float x, y, z, w; } __attribute__((aligned(16))) pim_float4;
+typedef struct pim_int2_s { int32_t x, y; } pim_int2;
+#define PIM_PT_OWN_VECTOR_TYPES 1
+#endif
+#ifndef PIM_PT_OWN_VECTOR_TYPES
+typedef float2 pim_float2;
+typedef float3 pim_float3;
+typedef float4 pim_float4;
+typedef int2 pim_int2;
+#endif
+
+/* src/rendering/material.h:8-20 */
+enum
+{
+    PtMatFlag_Emissive = 1 << 0,
+    PtMatFlag_Sky = 1 << 1,
+    PtMatFlag_Refractive = 1 << 5,
+};
+
+/* src/rendering/path_tracer.h:15-22 */
+typedef enum { PtHit_Nothing = 0, PtHit_Backface, PtHit_Triangle, PtHit_COUNT } PtHitType;
+
+/* src/rendering/path_tracer.h:24-31 (48 bytes) */
+typedef struct PtRayHit_s
+{
+    pim_float4 wuvt;     /* barycentrics (w,u,v) and hit distance t */
+    pim_float4 normal;   /* unit geometric normal, flipped to face the ray */
+    int32_t type;        /* PtHitType */
+    int32_t iVert;       /* 3 * triangle index, -1 on miss */
+    uint32_t flags;      /* material flags of the hit triangle */
+} PtRayHit;
+
+/* src/rendering/path_tracer.h:33-42 (28 bytes) */
+typedef struct PtDofInfo_s
+{
+    float aperture;
+    float focalLength;
+    int32_t bladeCount;
+    float bladeRot;
+    float focalPlaneCurvature;
+    float autoFocusSpeed;
+    bool autoFocus;
+} PtDofInfo;
+
+/* src/rendering/path_tracer.h:44-52. The four images are host memory (pinned by
+ * PtTrace_New) that the engine's denoiser and blit read after Pt_Trace. */
+typedef struct PtTrace_s
+{
+    pim_float3* color;
+    pim_float3* albedo;
+    pim_float3* normal;
+    pim_float3* denoised;
+    pim_int2 imageSize;
+    float sampleWeight;
+} PtTrace;
+
+/* src/rendering/path_tracer.h:54-59 (36 bytes) */
+typedef struct PtResult_s { pim_float3 color, albedo, normal; } PtResult;
+
+/* src/rendering/path_tracer.h:61-65 */
+typedef struct PtResults_s { pim_float4* colors; pim_float4* directions; } PtResults;
+
+/* src/rendering/camera.h:8-15 */
+typedef struct Camera_s
+{
+    pim_float4 position;
+    pim_float4 rotation;   /* quaternion xyzw */
+    float zNear, zFar, fovy;
+} Camera;
+
+typedef struct PtScene_s PtScene;
+
+/* ---- scene input ----------------------------------------------------------
+ * The reference's PtScene_New(void) reads engine globals (Entities_Get,
+ * Mesh_Get, Texture_Get, Cubemaps_Get "sky", g_BrdfLut, cv_pt_dist_meters;
+ * src/rendering/path_tracer.c:692-782, 1011-1021, 905). Here the same data is
+ * handed over as one flat description; the in-engine adapter that fills it is
+ * shown in INTEGRATION.md. */
+typedef enum { PtTex_RGBA8 = 0, PtTex_RG16 = 1 } PtTexFormat;
+
+typedef struct PtTextureDesc_s
+{
+    int32_t width, height;
+    int32_t format;         /* PtTexFormat: albedo/rome = RGBA8, normal = RG16 (short2) */
+    const void* texels;     /* host memory, row-major */
+} PtTextureDesc;
+
+typedef struct PtMaterialDesc_s   /* src/rendering/material.h:22-31 */
+{
+    int32_t albedo, rome, normal; /* indices into PtSceneDesc.textures, -1 = none */
+    uint32_t flags;
+    float meanFreePath[4];
+    float ior;
+    float bumpiness;
+} PtMaterialDesc;
+
+typedef struct PtEntityDesc_s     /* one drawable: src/rendering/drawable.h:14-27 + mesh.h:25-33 */
+{
+    const pim_float4* positions;  /* [length] object space, unindexed triangles */
+    const pim_float4* normals;    /* [length] */
+    const pim_float4* uvs;        /* [length] xy used */
+    int32_t length;
+    float matrix[16];             /* local-to-world, column major (float4x4 c0..c3) */
+    PtMaterialDesc material;
+} PtEntityDesc;
+
+typedef struct PtConfig_s
+{
+    float ptDistMeters;     /* cv_pt_dist_meters, default 1.5 (src/common/cvars.c:208) */
+    uint32_t seed;          /* replaces the wall-clock seeding of src/common/random.c:45-65 */
+    int32_t pathPoolSize;   /* resident path slots of the wavefront pool; 0 = default */
+    int32_t reserved;
+} PtConfig;
+
+typedef struct PtSceneDesc_s
+{
+    const PtEntityDesc* entities;
+    int32_t entityCount;
+    const PtTextureDesc* textures;
+    int32_t textureCount;
+    const float* skyFaces;  /* 6 faces (XP,XM,YP,YM,ZP,ZM) of skySize^2 float3, or NULL */
+    int32_t skySize;
+    const float* brdfLut;   /* lutWidth*lutHeight float2 (g_BrdfLut), or NULL = bake on device */
+    int32_t lutWidth, lutHeight;
+    PtConfig config;
+} PtSceneDesc;
+
+/* ---- the reference's entry points (src/rendering/path_tracer.h:67-103) ---- */
+void PtSys_Init(void);
+void PtSys_Update(void);
+void PtSys_Shutdown(void);
+
+/* PtScene_New(void) builds from the description registered with
+ * PtSys_SetSceneDesc (the adapter's stand-in for the engine globals). */
+void PtSys_SetSceneDesc(const PtSceneDesc* desc);
+PtScene* PtScene_New(void);
+PtScene* PtScene_NewFromDesc(const PtSceneDesc* desc);
+void PtScene_Update(PtScene* scene);
+void PtScene_Del(PtScene* scene);
+void PtScene_Gui(PtScene* scene);   /* no-op */
+
+void PtTrace_New(PtTrace* trace, pim_int2 imageSize);
+void PtTrace_Del(PtTrace* trace);
+
+void DofInfo_New(PtDofInfo* dof);
+void DofInfo_Gui(PtDofInfo* dof);   /* no-op */
+
+PtRayHit Pt_Intersect(const PtScene* scene, pim_float4 ro, pim_float4 rd, float tNear, float tFar);
+PtResult Pt_TraceRay(PtScene* scene, pim_float4 ro, pim_float4 rd);
+void Pt_Trace(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera* camera);
+PtResults Pt_RayGen(PtScene* scene, pim_float4 origin, int32_t count);
+
+/* ---- batch forms (host buffers; copies are inside the call) ---------------- */
+/* ro[i].xyz origin, rd[i].xyz direction, rd[i].w = tFar. Replaces n calls of
+ * Pt_Intersect (path_tracer.c:1466-1474 -> rtcIntersect1 :484). */
+int32_t Pt_IntersectN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd,
+                      float tNear, PtRayHit* hitsOut, int64_t n);
+/* any-hit: occluded[i] = 1 when something lies in [tNear, rd[i].w]. Replaces
+ * RtcOccluded16 (path_tracer.c:524-553). */
+int32_t Pt_OccludedN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd,
+                     float tNear, uint8_t* occludedOut, int64_t n);
+/* n calls of Pt_TraceRay; path i is seeded from (i, pass, seed). */
+int32_t Pt_TraceRayN(PtScene* scene, const pim_float4* ro, const pim_float4* rd,
+                     uint32_t pass, PtResult* resultsOut, int64_t n);
+/* sppCount calls of Pt_Trace folded into one: samples sppBegin..sppBegin+sppCount-1
+ * of every pixel; images hold the running mean over sppBegin+sppCount samples.
+ * The light-grid relearn (PtScene_Update) runs once per call. trace->sampleWeight
+ * <= 0 leaves raw per-call sums in the images (multi-GPU partial results). */
+int32_t Pt_TraceSpp(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera* camera,
+                    int32_t sppBegin, int32_t sppCount);
+
+/* ---- device-resident forms (pointers are CUDA device memory) --------------- */
+int32_t Pt_IntersectN_Device(const PtScene* scene, const void* dRo, const void* dRd,
+                             float tNear, void* dHitsOut, int64_t n, void* stream);
+int32_t Pt_OccludedN_Device(const PtScene* scene, const void* dRo, const void* dRd,
+                            float tNear, void* dOccludedOut, int64_t n, void* stream);
+/* Adds sppCount samples per pixel into the three float3 sum images (w*h*3 floats each). */
+int32_t Pt_TraceSpp_Device(PtScene* scene, const Camera* camera, PtDofInfo* dof,
+                           int32_t width, int32_t height, int32_t sppBegin, int32_t sppCount,
+                           void* dSumColor, void* dSumAlbedo, void* dSumNormal, void* stream);
+
+/* ---- lightmap bake (src/rendering/lightmap.h:69, lightmap.c:1117-1223) ------
+ * The reference bakes the global LmPack; here the pack's texel arrays are passed
+ * explicitly. Layout per lightmap page as Lightmap_New (lightmap.c:81-123):
+ * probes[5][texels] float4, position[texels] float3, normal[texels] float3,
+ * sampleCounts[texels] float. All host pointers; probes and sampleCounts are
+ * read and written. */
+typedef struct PtLightmapDesc_s
+{
+    pim_float4* probes[5];
+    const pim_float3* position;
+    const pim_float3* normal;
+    float* sampleCounts;
+    int32_t size;           /* page is size x size texels */
+} PtLightmapDesc;
+
+int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCount,
+                        float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass);
+
+/* ---- introspection ----------------------------------------------------------- */
+typedef struct PtSceneStats_s
+{
+    int32_t vertCount, matCount, emissiveCount;
+    int32_t gridSize[3];
+    float gridLo[4], gridHi[4];
+    float cellsPerMeter;
+    int32_t bvhNodeCount, bvhTriCount;
+    float buildMs;
+} PtSceneStats;
+
+int32_t PtScene_GetStats(const PtScene* scene, PtSceneStats* stats);
+/* copies of the flattened scene (path_tracer.c:130-146); any pointer may be NULL */
+int32_t PtScene_Download(const PtScene* scene, pim_float4* positions, pim_float4* normals,
+                         pim_float2* uvs, int32_t* matIds, int32_t* vertToEmit, int32_t* emitToVert);
+/* light-grid cell: returns the cell's distribution length (0 = none) */
+int32_t PtScene_GetDist(const PtScene* scene, int32_t cell, float* pdf, float* cdf, uint32_t* live);
+int32_t PtScene_SetDist(PtScene* scene, int32_t cell, int32_t length, const float* pdf);
+/* BRDF LUT actually in use (lutWidth*lutHeight float2) */
+int32_t PtScene_GetBrdfLut(const PtScene* scene, float* texels, int32_t* width, int32_t* height);
+
+typedef struct PtCounters_s
+{
+    uint64_t paths;          /* camera paths / probe paths completed */
+    uint64_t rays;           /* closest-hit BVH queries */
+    uint64_t occlusionRays;  /* any-hit BVH queries */
+    uint64_t kernelLaunches;
+    uint64_t iterations;     /* wavefront iterations */
+} PtCounters;
+void Pt_GetCounters(PtCounters* out);
+void Pt_ResetCounters(void);
+/* milliseconds the last batch call spent in kernels, measured with CUDA events on
+ * the library's stream (0 when events were not recorded) */
+float Pt_LastKernelMs(void);
+
+const char* Pt_LastError(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIM_PT_H */

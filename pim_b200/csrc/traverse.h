@@ -1,0 +1,264 @@
+// traverse.h — one-ray-per-thread traversal of the 8-wide compressed BVH:
+// closest hit (rtcIntersect1), any hit (rtcOccluded16) and nearest triangle
+// within a radius (rtcPointQuery + RtcPointQueryFn, path_tracer.c:555-616).
+#pragma once
+
+#include "bvh.h"
+
+namespace pt {
+
+// Traversal stack: the first kSharedDepth entries live in caller-provided memory
+// addressed [depth * stride] (shared memory, stride = block size, so a warp's
+// accesses hit 32 different banks whatever the per-thread depths are); deeper
+// entries spill to a small per-thread array.
+template <int kSharedDepth>
+struct TravStack
+{
+    unsigned long long* base;
+    int stride;
+    int sp;
+    unsigned long long spill[40];
+
+    PT_D void init(unsigned long long* b, int s) { base = b; stride = s; sp = 0; }
+    PT_D void push(uint32_t node, uint32_t key)
+    {
+        unsigned long long e = ((unsigned long long)key << 32) | node;
+        if (sp < kSharedDepth) base[sp * stride] = e;
+        else if (sp - kSharedDepth < 40) spill[sp - kSharedDepth] = e;
+        ++sp;
+    }
+    PT_D unsigned long long pop()
+    {
+        --sp;
+        if (sp < kSharedDepth) return base[sp * stride];
+        return (sp - kSharedDepth < 40) ? spill[sp - kSharedDepth] : 0ull;
+    }
+};
+
+PT_D float safeRcp(float d)
+{
+    // keep the slab arithmetic finite for axis-parallel rays
+    const float tiny = 1e-20f;
+    if (f1_abs(d) < tiny) d = (f2u(d) >> 31) ? -tiny : tiny;
+    return 1.0f / d;
+}
+
+struct TravCounters { uint32_t nodes, tris; };
+
+PT_D uint32_t max8(const uint32_t k[8])
+{
+    uint32_t a = k[0] > k[1] ? k[0] : k[1];
+    uint32_t b = k[2] > k[3] ? k[2] : k[3];
+    uint32_t c = k[4] > k[5] ? k[4] : k[5];
+    uint32_t d = k[6] > k[7] ? k[6] : k[7];
+    a = a > b ? a : b;
+    c = c > d ? c : d;
+    return a > c ? a : c;
+}
+
+template <bool kAnyHit, bool kCount, class Stack>
+PT_D bool traverse(const Bvh& bvh, V3 ro, V3 rd, float tNear, float tFar, Hit& hit, Stack& st,
+                   TravCounters* cnt)
+{
+    hit.prim = -1;
+    hit.t = tFar;
+    hit.u = hit.v = 0.0f;
+    hit.ng = v3(0, 0, 0);
+    if (bvh.nodeCount <= 0) return false;
+
+    const V3 idir = v3(safeRcp(rd.x), safeRcp(rd.y), safeRcp(rd.z));
+    const bool negx = rd.x < 0.0f, negy = rd.y < 0.0f, negz = rd.z < 0.0f;
+    float tBest = tFar;
+    bool found = false;
+    uint32_t bestPrim = 0xffffffffu;
+
+    st.sp = 0;
+    uint32_t cur = 0;
+    bool haveCur = true;
+    for (;;)
+    {
+        if (!haveCur)
+        {
+            if (st.sp == 0) break;
+            unsigned long long e = st.pop();
+            uint32_t key = (uint32_t)(e >> 32);
+            if (u2f((key - 8u) & ~7u) > tBest) continue;
+            cur = (uint32_t)e;
+        }
+        haveCur = false;
+        if (kCount) cnt->nodes++;
+
+        const WideNode* np = bvh.nodes + cur;
+        const U4 n0 = ldg128(&np->ox);
+        const U4 n1 = ldg128(&np->childBase);
+        const U4 n2 = ldg128(&np->qlox[0]);
+        const U4 n3 = ldg128(&np->qloz[0]);
+        const U4 n4 = ldg128(&np->qhiy[0]);
+
+        const uint32_t imask = n0.w >> 24;
+        const float sx = u2f((n0.w & 0xffu) << 23) * idir.x;
+        const float sy = u2f(((n0.w >> 8) & 0xffu) << 23) * idir.y;
+        const float sz = u2f(((n0.w >> 16) & 0xffu) << 23) * idir.z;
+        const float bx = (u2f(n0.x) - ro.x) * idir.x;
+        const float by = (u2f(n0.y) - ro.y) * idir.y;
+        const float bz = (u2f(n0.z) - ro.z) * idir.z;
+
+        // near / far plane bytes per axis, picked by the ray's direction sign
+        uint32_t nxw[2], fxw[2], nyw[2], fyw[2], nzw[2], fzw[2];
+        nxw[0] = negx ? n3.z : n2.x; nxw[1] = negx ? n3.w : n2.y;
+        fxw[0] = negx ? n2.x : n3.z; fxw[1] = negx ? n2.y : n3.w;
+        nyw[0] = negy ? n4.x : n2.z; nyw[1] = negy ? n4.y : n2.w;
+        fyw[0] = negy ? n2.z : n4.x; fyw[1] = negy ? n2.w : n4.y;
+        nzw[0] = negz ? n4.z : n3.x; nzw[1] = negz ? n4.w : n3.y;
+        fzw[0] = negz ? n3.x : n4.z; fzw[1] = negz ? n3.y : n4.w;
+        const uint32_t metaw[2] = { n1.z, n1.w };
+
+        uint32_t keys[8];
+        uint32_t hitMask = 0;
+#if defined(__CUDA_ARCH__)
+        #pragma unroll
+#endif
+        for (int i = 0; i < 8; ++i)
+        {
+            const int w = i >> 2, sh = 8 * (i & 3);
+            float tnx = (float)((nxw[w] >> sh) & 0xffu) * sx + bx;
+            float tfx = (float)((fxw[w] >> sh) & 0xffu) * sx + bx;
+            float tny = (float)((nyw[w] >> sh) & 0xffu) * sy + by;
+            float tfy = (float)((fyw[w] >> sh) & 0xffu) * sy + by;
+            float tnz = (float)((nzw[w] >> sh) & 0xffu) * sz + bz;
+            float tfz = (float)((fzw[w] >> sh) & 0xffu) * sz + bz;
+            float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tNear));
+            float tmax = fminf(fminf(tfx, tfy), fminf(tfz, tBest));
+            // a few ulps of slack: the planes come out of an fma on rounded inputs
+            bool h = (((metaw[w] >> sh) & 0xffu) != 0u) && (tmin <= tmax * 1.0000004f);
+            keys[i] = h ? (((f2u(tmin) & ~7u) | (uint32_t)i) + 8u) : 0u;
+            hitMask |= h ? (1u << i) : 0u;
+        }
+
+        // leaf children: test their triangles now
+        uint32_t leafMask = hitMask & ~imask;
+        while (leafMask)
+        {
+            const int i = ffs32(leafMask);
+            leafMask &= leafMask - 1;
+            const uint32_t m = (metaw[i >> 2] >> (8 * (i & 3))) & 0xffu;
+            const uint32_t count = m >> 5, first = n1.y + (m & 31u);
+            for (uint32_t j = 0; j < count; ++j)
+            {
+                if (kCount) cnt->tris++;
+                float t, u, v; uint32_t prim; V3 ng;
+                if (triTest(bvh.tris + first + j, ro, rd, tNear, tBest, t, u, v, prim, ng))
+                {
+                    if (kAnyHit) return true;
+                    // equal-t hits resolve to the lowest primitive id (as the oracle does)
+                    if (!found || t < tBest || prim < bestPrim)
+                    {
+                        found = true;
+                        tBest = t; bestPrim = prim;
+                        hit.t = t; hit.u = u; hit.v = v; hit.prim = (int32_t)prim; hit.ng = ng;
+                    }
+                }
+            }
+        }
+
+        // internal children: push far-to-near, keep the nearest as the next node
+        uint32_t intMask = hitMask & imask;
+        if (intMask)
+        {
+#if defined(__CUDA_ARCH__)
+            #pragma unroll
+#endif
+            for (int i = 0; i < 8; ++i) keys[i] = ((intMask >> i) & 1u) ? keys[i] : 0u;
+            int n = popc32(intMask);
+            while (n > 1)
+            {
+                const uint32_t best = max8(keys);
+                const uint32_t idx = (best - 8u) & 7u;
+                st.push(n1.x + (uint32_t)popc32(imask & ((1u << idx) - 1u)), best);
+#if defined(__CUDA_ARCH__)
+                #pragma unroll
+#endif
+                for (int i = 0; i < 8; ++i) keys[i] = (keys[i] == best) ? 0u : keys[i];
+                --n;
+            }
+            const uint32_t best = max8(keys);
+            if (u2f((best - 8u) & ~7u) <= tBest)
+            {
+                const uint32_t idx = (best - 8u) & 7u;
+                cur = n1.x + (uint32_t)popc32(imask & ((1u << idx) - 1u));
+                haveCur = true;
+            }
+        }
+    }
+    return found;
+}
+
+// Nearest triangle to p among those closer than `radius` (unsigned distance as
+// sdTriangle3D returns it). Returns kRcpEpsilon when there is none, like
+// RtcPointQuery's initial usr.distance (path_tracer.c:603).
+template <class Stack>
+PT_D float pointQuery(const Bvh& bvh, V3 p, float radius, Stack& st)
+{
+    float best = kRcpEpsilon;
+    if (bvh.nodeCount <= 0) return best;
+    st.sp = 0;
+    st.push(0, 0);
+    while (st.sp > 0)
+    {
+        const uint32_t cur = (uint32_t)st.pop();
+        const WideNode* np = bvh.nodes + cur;
+        const U4 n0 = ldg128(&np->ox);
+        const U4 n1 = ldg128(&np->childBase);
+        const U4 n2 = ldg128(&np->qlox[0]);
+        const U4 n3 = ldg128(&np->qloz[0]);
+        const U4 n4 = ldg128(&np->qhiy[0]);
+        const uint32_t imask = n0.w >> 24;
+        const float sx = u2f((n0.w & 0xffu) << 23);
+        const float sy = u2f(((n0.w >> 8) & 0xffu) << 23);
+        const float sz = u2f(((n0.w >> 16) & 0xffu) << 23);
+        const uint32_t lox[2] = { n2.x, n2.y }, loy[2] = { n2.z, n2.w }, loz[2] = { n3.x, n3.y };
+        const uint32_t hix[2] = { n3.z, n3.w }, hiy[2] = { n4.x, n4.y }, hiz[2] = { n4.z, n4.w };
+        const uint32_t metaw[2] = { n1.z, n1.w };
+        for (int i = 0; i < 8; ++i)
+        {
+            const int w = i >> 2, sh = 8 * (i & 3);
+            const uint32_t m = (metaw[w] >> sh) & 0xffu;
+            if (m == 0u) continue;
+            float lx = u2f(n0.x) + (float)((lox[w] >> sh) & 0xffu) * sx;
+            float ly = u2f(n0.y) + (float)((loy[w] >> sh) & 0xffu) * sy;
+            float lz = u2f(n0.z) + (float)((loz[w] >> sh) & 0xffu) * sz;
+            float hx = u2f(n0.x) + (float)((hix[w] >> sh) & 0xffu) * sx;
+            float hy = u2f(n0.y) + (float)((hiy[w] >> sh) & 0xffu) * sy;
+            float hz = u2f(n0.z) + (float)((hiz[w] >> sh) & 0xffu) * sz;
+            float dx = fmaxf(fmaxf(lx - p.x, p.x - hx), 0.0f);
+            float dy = fmaxf(fmaxf(ly - p.y, p.y - hy), 0.0f);
+            float dz = fmaxf(fmaxf(lz - p.z, p.z - hz), 0.0f);
+            if (dx * dx + dy * dy + dz * dz > radius * radius) continue;
+            if ((imask >> i) & 1u)
+            {
+                st.push(n1.x + (uint32_t)popc32(imask & ((1u << i) - 1u)), 0);
+            }
+            else
+            {
+                const uint32_t count = m >> 5, first = n1.y + (m & 31u);
+                for (uint32_t j = 0; j < count; ++j)
+                {
+                    const PackedTri* tp = bvh.tris + first + j;
+                    U4 a = ldg128(&tp->v0x), b = ldg128(&tp->e1x), c = ldg128(&tp->e2x);
+                    V3 A = v3(u2f(a.x), u2f(a.y), u2f(a.z));
+                    V3 B = A + v3(u2f(b.x), u2f(b.y), u2f(b.z));
+                    V3 C = A + v3(u2f(c.x), u2f(c.y), u2f(c.z));
+                    float d = sdTriangle3D(A, B, C, p);
+                    if (d < radius && d < best)
+                    {
+                        best = d;
+                        radius = f1_min(radius, d);
+                    }
+                }
+            }
+        }
+    }
+    return best;
+}
+
+} // namespace pt
