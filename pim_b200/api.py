@@ -1,0 +1,372 @@
+"""ctypes binding of libpimpt.so — the names and argument meaning of include/pim_pt.h,
+which mirrors /root/reference/src/rendering/path_tracer.h:67-103.
+
+Everything computes on the GPU through the C ABI; there is no Python or CPU
+implementation behind these wrappers. Loading fails loudly when the library has
+not been built (python -m pim_b200.build, or __graft_entry__.build()).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import scenes
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libpimpt.so")
+
+f32p = C.POINTER(C.c_float)
+
+
+class Float4(C.Structure):
+    _fields_ = [("x", C.c_float), ("y", C.c_float), ("z", C.c_float), ("w", C.c_float)]
+
+
+class Int2(C.Structure):
+    _fields_ = [("x", C.c_int32), ("y", C.c_int32)]
+
+
+class PtRayHit(C.Structure):
+    _fields_ = [("wuvt", Float4), ("normal", Float4), ("type", C.c_int32), ("iVert", C.c_int32),
+                ("flags", C.c_uint32), ("_pad", C.c_uint32)]
+
+
+class PtDofInfo(C.Structure):
+    _fields_ = [("aperture", C.c_float), ("focalLength", C.c_float), ("bladeCount", C.c_int32),
+                ("bladeRot", C.c_float), ("focalPlaneCurvature", C.c_float), ("autoFocusSpeed", C.c_float),
+                ("autoFocus", C.c_bool)]
+
+
+class PtTrace(C.Structure):
+    _fields_ = [("color", f32p), ("albedo", f32p), ("normal", f32p), ("denoised", f32p),
+                ("imageSize", Int2), ("sampleWeight", C.c_float)]
+
+
+class PtResult(C.Structure):
+    _fields_ = [("color", C.c_float * 3), ("albedo", C.c_float * 3), ("normal", C.c_float * 3)]
+
+
+class PtResults(C.Structure):
+    _fields_ = [("colors", C.POINTER(Float4)), ("directions", C.POINTER(Float4))]
+
+
+class Camera(C.Structure):
+    _fields_ = [("position", Float4), ("rotation", Float4), ("zNear", C.c_float), ("zFar", C.c_float),
+                ("fovy", C.c_float), ("_pad", C.c_float)]
+
+
+class PtTextureDesc(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("format", C.c_int32), ("texels", C.c_void_p)]
+
+
+class PtMaterialDesc(C.Structure):
+    _fields_ = [("albedo", C.c_int32), ("rome", C.c_int32), ("normal", C.c_int32), ("flags", C.c_uint32),
+                ("meanFreePath", C.c_float * 4), ("ior", C.c_float), ("bumpiness", C.c_float)]
+
+
+class PtEntityDesc(C.Structure):
+    _fields_ = [("positions", C.c_void_p), ("normals", C.c_void_p), ("uvs", C.c_void_p), ("length", C.c_int32),
+                ("matrix", C.c_float * 16), ("material", PtMaterialDesc)]
+
+
+class PtConfig(C.Structure):
+    _fields_ = [("ptDistMeters", C.c_float), ("seed", C.c_uint32), ("pathPoolSize", C.c_int32), ("reserved", C.c_int32)]
+
+
+class PtSceneDesc(C.Structure):
+    _fields_ = [("entities", C.POINTER(PtEntityDesc)), ("entityCount", C.c_int32),
+                ("textures", C.POINTER(PtTextureDesc)), ("textureCount", C.c_int32),
+                ("skyFaces", C.c_void_p), ("skySize", C.c_int32),
+                ("brdfLut", C.c_void_p), ("lutWidth", C.c_int32), ("lutHeight", C.c_int32),
+                ("config", PtConfig)]
+
+
+class PtLightmapDesc(C.Structure):
+    _fields_ = [("probes", C.c_void_p * 5), ("position", C.c_void_p), ("normal", C.c_void_p),
+                ("sampleCounts", C.c_void_p), ("size", C.c_int32)]
+
+
+class PtSceneStats(C.Structure):
+    _fields_ = [("vertCount", C.c_int32), ("matCount", C.c_int32), ("emissiveCount", C.c_int32),
+                ("gridSize", C.c_int32 * 3), ("gridLo", C.c_float * 4), ("gridHi", C.c_float * 4),
+                ("cellsPerMeter", C.c_float), ("bvhNodeCount", C.c_int32), ("bvhTriCount", C.c_int32),
+                ("buildMs", C.c_float)]
+
+
+class PtCounters(C.Structure):
+    _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("occlusionRays", C.c_uint64),
+                ("kernelLaunches", C.c_uint64), ("iterations", C.c_uint64)]
+
+
+HIT_DTYPE = np.dtype([("wuvt", np.float32, 4), ("normal", np.float32, 4), ("type", np.int32),
+                      ("iVert", np.int32), ("flags", np.uint32), ("pad", np.uint32)])
+
+EXPORTS = [
+    "PtSys_Init", "PtSys_Update", "PtSys_Shutdown", "PtSys_SetSceneDesc", "PtScene_New", "PtScene_NewFromDesc",
+    "PtScene_Update", "PtScene_Del", "PtScene_Gui", "PtTrace_New", "PtTrace_Del", "DofInfo_New", "DofInfo_Gui",
+    "Pt_Intersect", "Pt_TraceRay", "Pt_Trace", "Pt_RayGen", "Pt_IntersectN", "Pt_OccludedN", "Pt_TraceRayN",
+    "Pt_TraceSpp", "Pt_IntersectN_Device", "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc",
+    "PtScene_GetStats", "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut",
+    "Pt_GetCounters", "Pt_ResetCounters", "Pt_LastKernelMs", "Pt_LastError",
+]
+
+_lib = None
+
+
+def load():
+    """dlopen libpimpt.so and declare prototypes. Raises if the library is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("pim_b200/libpimpt.so is not built: run `python -m pim_b200.build` "
+                          "(there is no CPU fallback for this library)")
+    L = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    L.Pt_LastError.restype = C.c_char_p
+    L.PtScene_New.restype = vp
+    L.PtScene_NewFromDesc.restype = vp
+    L.PtScene_NewFromDesc.argtypes = [C.POINTER(PtSceneDesc)]
+    L.PtSys_SetSceneDesc.argtypes = [C.POINTER(PtSceneDesc)]
+    L.PtScene_Update.argtypes = [vp]
+    L.PtScene_Del.argtypes = [vp]
+    L.PtTrace_New.argtypes = [C.POINTER(PtTrace), Int2]
+    L.PtTrace_Del.argtypes = [C.POINTER(PtTrace)]
+    L.DofInfo_New.argtypes = [C.POINTER(PtDofInfo)]
+    L.Pt_Intersect.restype = PtRayHit
+    L.Pt_Intersect.argtypes = [vp, Float4, Float4, C.c_float, C.c_float]
+    L.Pt_TraceRay.restype = PtResult
+    L.Pt_TraceRay.argtypes = [vp, Float4, Float4]
+    L.Pt_Trace.argtypes = [C.POINTER(PtTrace), C.POINTER(PtDofInfo), vp, C.POINTER(Camera)]
+    L.Pt_RayGen.restype = PtResults
+    L.Pt_RayGen.argtypes = [vp, Float4, C.c_int32]
+    L.Pt_IntersectN.argtypes = [vp, vp, vp, C.c_float, vp, C.c_int64]
+    L.Pt_OccludedN.argtypes = [vp, vp, vp, C.c_float, vp, C.c_int64]
+    L.Pt_TraceRayN.argtypes = [vp, vp, vp, C.c_uint32, vp, C.c_int64]
+    L.Pt_TraceSpp.argtypes = [C.POINTER(PtTrace), C.POINTER(PtDofInfo), vp, C.POINTER(Camera), C.c_int32, C.c_int32]
+    L.Pt_IntersectN_Device.argtypes = [vp, vp, vp, C.c_float, vp, C.c_int64, vp]
+    L.Pt_OccludedN_Device.argtypes = [vp, vp, vp, C.c_float, vp, C.c_int64, vp]
+    L.Pt_TraceSpp_Device.argtypes = [vp, C.POINTER(Camera), C.POINTER(PtDofInfo), C.c_int32, C.c_int32, C.c_int32,
+                                     C.c_int32, vp, vp, vp, vp]
+    L.LmPack_BakeDesc.argtypes = [vp, C.POINTER(PtLightmapDesc), C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_uint32]
+    L.PtScene_GetStats.argtypes = [vp, C.POINTER(PtSceneStats)]
+    L.PtScene_Download.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    L.PtScene_GetDist.argtypes = [vp, C.c_int32, vp, vp, vp]
+    L.PtScene_SetDist.argtypes = [vp, C.c_int32, C.c_int32, vp]
+    L.PtScene_GetBrdfLut.argtypes = [vp, vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.Pt_GetCounters.argtypes = [C.POINTER(PtCounters)]
+    L.Pt_LastKernelMs.restype = C.c_float
+    for name in ("Pt_IntersectN", "Pt_OccludedN", "Pt_TraceRayN", "Pt_TraceSpp", "Pt_IntersectN_Device",
+                 "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc", "PtScene_GetStats",
+                 "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut"):
+        getattr(L, name).restype = C.c_int32
+    _lib = L
+    return L
+
+
+def last_error():
+    return (load().Pt_LastError() or b"").decode()
+
+
+class PtError(RuntimeError):
+    pass
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise PtError("%s failed: %s" % (what, last_error()))
+
+
+def _f4(v):
+    v = list(v) + [0.0] * (4 - len(v))
+    return Float4(float(v[0]), float(v[1]), float(v[2]), float(v[3]))
+
+
+def make_camera(eye, at, fovy=90.0):
+    pos, rot, fov = scenes.camera_lookat(eye, at, fovy)
+    cam = Camera()
+    cam.position = _f4(pos)
+    cam.rotation = _f4(rot)
+    cam.zNear, cam.zFar, cam.fovy = 0.1, 500.0, fov
+    return cam
+
+
+def default_dof(auto_focus=True):
+    d = PtDofInfo()
+    load().DofInfo_New(C.byref(d))
+    d.autoFocus = auto_focus
+    return d
+
+
+def counters():
+    c = PtCounters()
+    load().Pt_GetCounters(C.byref(c))
+    return {k: getattr(c, k) for k, _ in PtCounters._fields_}
+
+
+class Scene:
+    """PtScene built from a scenes.SceneDesc (PtScene_NewFromDesc)."""
+
+    def __init__(self, desc):
+        L = load()
+        L.PtSys_Init()
+        self._keep = []
+        ents = (PtEntityDesc * max(len(desc.entities), 1))()
+        for i, e in enumerate(desc.entities):
+            pos = np.ascontiguousarray(e.positions, np.float32)
+            nrm = np.ascontiguousarray(e.normals, np.float32)
+            uvs = np.ascontiguousarray(e.uvs, np.float32)
+            # entities that share one mesh object share one upload (keyed by the source array)
+            key = id(e.positions)
+            cached = next((k for k in self._keep if isinstance(k, tuple) and k[0] == key), None)
+            if cached is None:
+                cached = (key, pos, nrm, uvs)
+                self._keep.append(cached)
+            _, pos, nrm, uvs = cached
+            ents[i].positions = pos.ctypes.data
+            ents[i].normals = nrm.ctypes.data
+            ents[i].uvs = uvs.ctypes.data
+            ents[i].length = len(pos)
+            ents[i].matrix[:] = [float(x) for x in np.asarray(e.matrix, np.float32).reshape(-1)]
+            m = ents[i].material
+            m.albedo, m.rome, m.normal, m.flags = e.albedo, e.rome, e.normal, e.flags
+            m.meanFreePath[:] = [float(x) for x in e.mean_free_path]
+            m.ior, m.bumpiness = e.ior, e.bumpiness
+        texs = (PtTextureDesc * max(len(desc.textures), 1))()
+        for i, t in enumerate(desc.textures):
+            arr = np.ascontiguousarray(t.texels, np.uint32)
+            self._keep.append(arr)
+            texs[i].width, texs[i].height, texs[i].format, texs[i].texels = t.width, t.height, t.format, arr.ctypes.data
+        d = PtSceneDesc()
+        d.entities = ents
+        d.entityCount = len(desc.entities)
+        d.textures = texs
+        d.textureCount = len(desc.textures)
+        if desc.sky is not None:
+            sky = np.ascontiguousarray(desc.sky, np.float32)
+            self._keep.append(sky)
+            d.skyFaces, d.skySize = sky.ctypes.data, sky.shape[1]
+        if desc.brdf_lut is not None:
+            lut = np.ascontiguousarray(desc.brdf_lut, np.float32)
+            self._keep.append(lut)
+            d.brdfLut, d.lutWidth, d.lutHeight = lut.ctypes.data, lut.shape[1], lut.shape[0]
+        d.config.ptDistMeters = desc.pt_dist_meters
+        d.config.seed = desc.seed
+        d.config.pathPoolSize = desc.path_pool_size
+        self.h = L.PtScene_NewFromDesc(C.byref(d))
+        if not self.h:
+            raise PtError("PtScene_NewFromDesc failed: " + last_error())
+        self.stats = PtSceneStats()
+        _check(L.PtScene_GetStats(self.h, C.byref(self.stats)), "PtScene_GetStats")
+
+    def close(self):
+        if getattr(self, "h", None):
+            load().PtScene_Del(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- introspection -------------------------------------------------------
+    def download(self):
+        n, E = self.stats.vertCount, self.stats.emissiveCount
+        out = {"positions": np.zeros((n, 4), np.float32), "normals": np.zeros((n, 4), np.float32),
+               "uvs": np.zeros((n, 2), np.float32), "matIds": np.zeros(n, np.int32),
+               "vertToEmit": np.zeros(n, np.int32), "emitToVert": np.zeros(E, np.int32)}
+        _check(load().PtScene_Download(self.h, *[out[k].ctypes.data for k in
+                                                 ("positions", "normals", "uvs", "matIds", "vertToEmit", "emitToVert")]),
+               "PtScene_Download")
+        return out
+
+    @property
+    def grid_size(self):
+        return tuple(self.stats.gridSize)
+
+    def dist(self, cell):
+        E = self.stats.emissiveCount
+        pdf = np.zeros(E, np.float32); cdf = np.zeros(E + 1, np.float32); live = np.zeros(E, np.uint32)
+        n = load().PtScene_GetDist(self.h, cell, pdf.ctypes.data, cdf.ctypes.data, live.ctypes.data)
+        if n < 0:
+            raise PtError("PtScene_GetDist failed: " + last_error())
+        return n, pdf, cdf, live
+
+    def set_dist(self, cell, pdf):
+        pdf = np.ascontiguousarray(pdf, np.float32)
+        _check(load().PtScene_SetDist(self.h, cell, len(pdf), pdf.ctypes.data), "PtScene_SetDist")
+
+    def brdf_lut(self):
+        w, h = C.c_int32(), C.c_int32()
+        L = load()
+        _check(L.PtScene_GetBrdfLut(self.h, None, C.byref(w), C.byref(h)), "PtScene_GetBrdfLut")
+        out = np.zeros((h.value, w.value, 2), np.float32)
+        _check(L.PtScene_GetBrdfLut(self.h, out.ctypes.data, C.byref(w), C.byref(h)), "PtScene_GetBrdfLut")
+        return out
+
+    # ---- ray batches -----------------------------------------------------------
+    def intersect(self, ro, rd, t_near=0.0):
+        ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)
+        out = np.zeros(len(ro), HIT_DTYPE)
+        _check(load().Pt_IntersectN(self.h, ro.ctypes.data, rd.ctypes.data, t_near, out.ctypes.data, len(ro)), "Pt_IntersectN")
+        return out
+
+    def occluded(self, ro, rd, t_near=0.0):
+        ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)
+        out = np.zeros(len(ro), np.uint8)
+        _check(load().Pt_OccludedN(self.h, ro.ctypes.data, rd.ctypes.data, t_near, out.ctypes.data, len(ro)), "Pt_OccludedN")
+        return out
+
+    def trace_rays(self, ro, rd, pass_index=0):
+        ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)
+        out = np.zeros((len(ro), 9), np.float32)
+        _check(load().Pt_TraceRayN(self.h, ro.ctypes.data, rd.ctypes.data, pass_index, out.ctypes.data, len(ro)), "Pt_TraceRayN")
+        return out
+
+    def raygen(self, origin, count):
+        r = load().Pt_RayGen(self.h, _f4(origin), count)
+        if not r.colors:
+            raise PtError("Pt_RayGen failed: " + last_error())
+        colors = np.ctypeslib.as_array(C.cast(r.colors, f32p), (count, 4)).copy()
+        dirs = np.ctypeslib.as_array(C.cast(r.directions, f32p), (count, 4)).copy()
+        return colors, dirs
+
+    def bake_lightmap(self, probes, position, normal, sample_counts, texels_per_meter, time_slice=1.0, spp=1, pass_index=0):
+        """LmPack_BakeDesc on one page. probes: float32 [5, size*size, 4] (updated in place)."""
+        size = int(round(np.sqrt(len(sample_counts))))
+        d = PtLightmapDesc()
+        for k in range(5):
+            d.probes[k] = probes[k].ctypes.data
+        d.position, d.normal, d.sampleCounts, d.size = position.ctypes.data, normal.ctypes.data, sample_counts.ctypes.data, size
+        _check(load().LmPack_BakeDesc(self.h, C.byref(d), 1, texels_per_meter, time_slice, spp, pass_index), "LmPack_BakeDesc")
+
+
+class Trace:
+    """PtTrace: three pinned host float3 images the library writes (PtTrace_New / PtTrace_Del)."""
+
+    def __init__(self, width, height):
+        self.t = PtTrace()
+        load().PtTrace_New(C.byref(self.t), Int2(width, height))
+        if not self.t.color:
+            raise PtError("PtTrace_New failed: " + last_error())
+        self.width, self.height = width, height
+
+    def image(self, name="color"):
+        return np.ctypeslib.as_array(getattr(self.t, name), (self.height, self.width, 3))
+
+    def close(self):
+        if self.t.color:
+            load().PtTrace_Del(C.byref(self.t))
+
+    def trace(self, scene, cam, dof, sample_weight):
+        """One reference-style frame: Pt_Trace (1 spp, lerp by sample_weight)."""
+        self.t.sampleWeight = sample_weight
+        load().Pt_Trace(C.byref(self.t), C.byref(dof), scene.h, C.byref(cam))
+        err = last_error()
+        if err:
+            raise PtError("Pt_Trace failed: " + err)
+
+    def trace_spp(self, scene, cam, dof, spp_begin, spp_count, sums=False):
+        self.t.sampleWeight = -1.0 if sums else 1.0
+        _check(load().Pt_TraceSpp(C.byref(self.t), C.byref(dof), scene.h, C.byref(cam), spp_begin, spp_count), "Pt_TraceSpp")

@@ -1,0 +1,871 @@
+// api.cu — the C ABI of libpimpt.so (include/pim_pt.h): the reference's entry
+// points of src/rendering/path_tracer.h:67-103 and LmPack_Bake, implemented on
+// the CUDA kernels of this directory. No CPU implementation exists behind any
+// of them: without a CUDA device every call fails with Pt_LastError set.
+#include <cuda_runtime.h>
+#define PIM_PT_NO_VECTOR_TYPES 1
+#include "../../include/pim_pt.h"
+#include "pt_device.h"
+
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+
+namespace pt {
+
+static thread_local char t_error[512];
+LibCounters g_counters = { 0, 0, 0, 0, 0 };
+static float g_lastKernelMs = 0.0f;
+
+void setError(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_error, sizeof(t_error), fmt, ap);
+    va_end(ap);
+}
+
+bool cudaOk(cudaError_t e, const char* what)
+{
+    if (e == cudaSuccess) return true;
+    setError("CUDA error %s (%d) at %s", cudaGetErrorString(e), (int)e, what);
+    return false;
+}
+
+} // namespace pt
+
+using namespace pt;
+
+struct DeviceImages
+{
+    float* image[3] = { nullptr, nullptr, nullptr };   // running means, w*h*3 floats each
+    float* sum[3] = { nullptr, nullptr, nullptr };     // per-call sums
+    int64_t texels = 0;
+};
+
+struct PtScene_s
+{
+    cudaStream_t stream = nullptr;
+    DScene view;
+    BvhBuffers bvh;
+    std::vector<void*> allocs;
+    PathPool pool;
+    PtConfig config;
+    float* dLut = nullptr;
+    int32_t gridCells = 0;
+    uint32_t nextPass = 0;
+    float buildMs = 0.0f;
+    // Pt_RayGen results: library-owned, valid until the second next call (the reference
+    // hands out per-frame linear-allocator memory, path_tracer.c:2630-2631)
+    pim_float4* rayGenColors[2] = { nullptr, nullptr };
+    pim_float4* rayGenDirs[2] = { nullptr, nullptr };
+    int32_t rayGenCap[2] = { 0, 0 };
+    int rayGenFlip = 0;
+};
+
+static bool g_initialised = false;
+static PtSceneDesc g_sceneDesc;
+static bool g_haveSceneDesc = false;
+static std::map<PtTrace*, DeviceImages> g_traces;
+static std::mutex g_mutex;
+
+template <class T>
+static bool sceneAlloc(PtScene* s, T*& p, size_t count)
+{
+    p = nullptr;
+    if (count == 0) count = 1;
+    if (!PT_CUDA(cudaMalloc((void**)&p, sizeof(T) * count))) return false;
+    s->allocs.push_back(p);
+    return true;
+}
+
+static bool ensureInit()
+{
+    if (g_initialised) return true;
+    int n = 0;
+    if (!PT_CUDA(cudaGetDeviceCount(&n))) return false;
+    if (n <= 0) { setError("no CUDA device: libpimpt has no CPU path"); return false; }
+    g_initialised = true;
+    return true;
+}
+
+// ---- host math for the camera and entity matrices (same formulas as the reference) ----
+
+static V3 quatMulDir(const float q[4], V3 dir)       // quat_funcs.h:86-97
+{
+    V3 qv = v3(q[0], q[1], q[2]);
+    V3 uv = cross(qv, dir);
+    V3 uuv = cross(qv, uv);
+    V3 y = uv * q[3];
+    y = y + uuv;
+    y = y * 2.0f;
+    return y + dir;
+}
+
+static void inverseTranspose3x3(const float* M, float* out)   // f3x3_IM, float3x3_funcs.h:54-110
+{
+    // m = transpose(upper 3x3 of M); [column][row]
+    float m00 = M[0], m01 = M[4], m02 = M[8];
+    float m10 = M[1], m11 = M[5], m12 = M[9];
+    float m20 = M[2], m21 = M[6], m22 = M[10];
+    float m_00_11_10_01 = m00 * m11 - m10 * m01;
+    float m_00_12_10_02 = m00 * m12 - m10 * m02;
+    float m_00_21_20_01 = m00 * m21 - m20 * m01;
+    float m_00_22_20_02 = m00 * m22 - m20 * m02;
+    float m_01_12_11_02 = m01 * m12 - m11 * m02;
+    float m_01_22_21_02 = m01 * m22 - m21 * m02;
+    float m_10_21_20_11 = m10 * m21 - m20 * m11;
+    float m_10_22_20_12 = m10 * m22 - m20 * m12;
+    float m_11_22_21_12 = m11 * m22 - m21 * m12;
+    float d0 = m00 * m_11_22_21_12;
+    float d1 = -m10 * m_01_22_21_02;
+    float d2 = m20 * m_01_12_11_02;
+    float rcpDet = 1.0f / (d0 + d1 + d2);
+    out[0] = rcpDet * m_11_22_21_12;   // 00
+    out[3] = -rcpDet * m_10_22_20_12;  // 10
+    out[6] = rcpDet * m_10_21_20_11;   // 20
+    out[1] = -rcpDet * m_01_22_21_02;  // 01
+    out[4] = rcpDet * m_00_22_20_02;   // 11
+    out[7] = -rcpDet * m_00_21_20_01;  // 21
+    out[2] = rcpDet * m_01_12_11_02;   // 02
+    out[5] = -rcpDet * m_00_12_10_02;  // 12
+    out[8] = rcpDet * m_00_11_10_01;   // 22
+}
+
+static float f1_ceil_ref(float x)     // scalar.h:149-157
+{
+    float i = (float)(int32_t)x;
+    return i + ((x > i) ? 1.0f : 0.0f);
+}
+
+static CamParams makeCam(const Camera* camera, const PtDofInfo* dof, int w, int h)
+{
+    CamParams C;
+    const float q[4] = { camera->rotation.x, camera->rotation.y, camera->rotation.z, camera->rotation.w };
+    C.eye = v3(camera->position.x, camera->position.y, camera->position.z);
+    C.right = quatMulDir(q, v3(1.0f, 0.0f, 0.0f));
+    C.up = quatMulDir(q, v3(0.0f, 1.0f, 0.0f));
+    C.fwd = quatMulDir(q, v3(0.0f, 0.0f, -1.0f));
+    const float fovy = camera->fovy * (kTau / 360.0f);
+    const float tanHalfFov = tanf(fovy * 0.5f);
+    C.slope = v2(((float)w / (float)h) * tanHalfFov, tanHalfFov);
+    C.width = w; C.height = h;
+    C.aperture = dof->aperture; C.focalLength = dof->focalLength; C.bladeCount = dof->bladeCount;
+    C.bladeRot = dof->bladeRot; C.focalPlaneCurvature = dof->focalPlaneCurvature;
+    return C;
+}
+
+// ---- scene construction -------------------------------------------------------
+
+static void sceneFree(PtScene* s)
+{
+    if (!s) return;
+    for (void* p : s->allocs) cudaFree(p);
+    freeBvh(s->bvh);
+    poolFree(s->pool);
+    for (int i = 0; i < 2; ++i)
+    {
+        if (s->rayGenColors[i]) cudaFreeHost(s->rayGenColors[i]);
+        if (s->rayGenDirs[i]) cudaFreeHost(s->rayGenDirs[i]);
+    }
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+static PtScene* sceneBuild(const PtSceneDesc* desc)
+{
+    if (!ensureInit()) return nullptr;
+    if (!desc) { setError("PtScene_NewFromDesc: null description"); return nullptr; }
+    auto t0 = std::chrono::steady_clock::now();
+    PtScene* s = new PtScene_s();
+    memset(&s->view, 0, sizeof(s->view));
+    s->config = desc->config;
+    if (s->config.ptDistMeters <= 0.0f) s->config.ptDistMeters = 1.5f;
+    bool ok = PT_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    cudaStream_t st = s->stream;
+    DScene& V = s->view;
+    V.media = MediaDesc_Default();
+
+    // textures
+    std::vector<DTexture> texTable((size_t)std::max(desc->textureCount, 0));
+    for (int i = 0; ok && i < desc->textureCount; ++i)
+    {
+        const PtTextureDesc& t = desc->textures[i];
+        uint32_t* d = nullptr;
+        size_t n = (size_t)t.width * (size_t)t.height;
+        ok = sceneAlloc(s, d, n);
+        ok = ok && PT_CUDA(cudaMemcpyAsync(d, t.texels, n * 4, cudaMemcpyHostToDevice, st));
+        texTable[i].texels = d; texTable[i].w = t.width; texTable[i].h = t.height;
+    }
+    DTexture* dTex = nullptr;
+    ok = ok && sceneAlloc(s, dTex, texTable.size());
+    if (ok && !texTable.empty())
+        ok = PT_CUDA(cudaMemcpyAsync(dTex, texTable.data(), sizeof(DTexture) * texTable.size(), cudaMemcpyHostToDevice, st));
+    V.textures = dTex;
+
+    // entities: concatenate distinct source meshes, one upload each
+    int32_t vertCount = 0, srcCount = 0;
+    std::map<const void*, int32_t> srcOffsets;
+    std::vector<EntityUpload> ents((size_t)std::max(desc->entityCount, 0));
+    std::vector<DMaterial> mats((size_t)std::max(desc->entityCount, 0));
+    for (int i = 0; i < desc->entityCount; ++i)
+    {
+        const PtEntityDesc& e = desc->entities[i];
+        EntityUpload& u = ents[i];
+        memcpy(u.M, e.matrix, sizeof(u.M));
+        inverseTranspose3x3(e.matrix, u.IM);
+        u.vertOffset = vertCount; u.length = e.length; u.pad = 0;
+        auto it = srcOffsets.find(e.positions);
+        if (it == srcOffsets.end())
+        {
+            srcOffsets[e.positions] = srcCount;
+            u.srcOffset = srcCount;
+            srcCount += e.length;
+        }
+        else u.srcOffset = it->second;
+        vertCount += e.length;
+        DMaterial m; memset(&m, 0, sizeof(m));
+        m.albedo = e.material.albedo; m.rome = e.material.rome; m.normal = e.material.normal;
+        m.flags = e.material.flags; memcpy(m.mfp, e.material.meanFreePath, sizeof(m.mfp));
+        m.ior = e.material.ior; m.bumpiness = e.material.bumpiness;
+        mats[i] = m;
+    }
+    F4 *dSrcPos = nullptr, *dSrcNrm = nullptr, *dSrcUv = nullptr;
+    ok = ok && PT_CUDA(cudaMalloc((void**)&dSrcPos, sizeof(F4) * (size_t)std::max(srcCount, 1)));
+    ok = ok && PT_CUDA(cudaMalloc((void**)&dSrcNrm, sizeof(F4) * (size_t)std::max(srcCount, 1)));
+    ok = ok && PT_CUDA(cudaMalloc((void**)&dSrcUv, sizeof(F4) * (size_t)std::max(srcCount, 1)));
+    {
+        std::map<const void*, bool> done;
+        for (int i = 0; ok && i < desc->entityCount; ++i)
+        {
+            const PtEntityDesc& e = desc->entities[i];
+            if (done[e.positions]) continue;
+            done[e.positions] = true;
+            const size_t bytes = sizeof(F4) * (size_t)e.length;
+            ok = ok && PT_CUDA(cudaMemcpyAsync(dSrcPos + ents[i].srcOffset, e.positions, bytes, cudaMemcpyHostToDevice, st));
+            ok = ok && PT_CUDA(cudaMemcpyAsync(dSrcNrm + ents[i].srcOffset, e.normals, bytes, cudaMemcpyHostToDevice, st));
+            ok = ok && PT_CUDA(cudaMemcpyAsync(dSrcUv + ents[i].srcOffset, e.uvs, bytes, cudaMemcpyHostToDevice, st));
+        }
+    }
+    EntityUpload* dEnts = nullptr;
+    DMaterial* dMats = nullptr;
+    F4 *dPos = nullptr, *dNrm = nullptr;
+    V2* dUv = nullptr;
+    int32_t *dMatIds = nullptr, *dVertToEmit = nullptr, *dEmitToVert = nullptr;
+    ok = ok && PT_CUDA(cudaMalloc((void**)&dEnts, sizeof(EntityUpload) * std::max<size_t>(ents.size(), 1)));
+    ok = ok && sceneAlloc(s, dMats, mats.size()) && sceneAlloc(s, dPos, (size_t)vertCount) &&
+         sceneAlloc(s, dNrm, (size_t)vertCount) && sceneAlloc(s, dUv, (size_t)vertCount) &&
+         sceneAlloc(s, dMatIds, (size_t)vertCount) && sceneAlloc(s, dVertToEmit, (size_t)vertCount);
+    if (ok && !ents.empty())
+    {
+        ok = PT_CUDA(cudaMemcpyAsync(dEnts, ents.data(), sizeof(EntityUpload) * ents.size(), cudaMemcpyHostToDevice, st));
+        ok = ok && PT_CUDA(cudaMemcpyAsync(dMats, mats.data(), sizeof(DMaterial) * mats.size(), cudaMemcpyHostToDevice, st));
+    }
+    ok = ok && launchFlatten(dEnts, desc->entityCount, dSrcPos, dSrcNrm, dSrcUv, dPos, dNrm, dUv, dMatIds, vertCount, st);
+    V.positions = dPos; V.normals = dNrm; V.uvs = dUv; V.matIds = dMatIds; V.materials = dMats;
+    V.vertCount = vertCount; V.matCount = desc->entityCount;
+
+    // sky + BRDF LUT
+    if (ok && desc->skyFaces && desc->skySize > 0)
+    {
+        float* dSky = nullptr;
+        size_t n = (size_t)6 * desc->skySize * desc->skySize * 3;
+        ok = sceneAlloc(s, dSky, n) && PT_CUDA(cudaMemcpyAsync(dSky, desc->skyFaces, n * 4, cudaMemcpyHostToDevice, st));
+        V.sky = dSky; V.skySize = desc->skySize;
+    }
+    {
+        int lw = desc->brdfLut ? desc->lutWidth : 128, lh = desc->brdfLut ? desc->lutHeight : 128;
+        ok = ok && sceneAlloc(s, s->dLut, (size_t)lw * lh * 2);
+        if (ok && desc->brdfLut)
+            ok = PT_CUDA(cudaMemcpyAsync(s->dLut, desc->brdfLut, sizeof(float) * 2 * lw * lh, cudaMemcpyHostToDevice, st));
+        else if (ok)
+            ok = launchBrdfLutBake(s->dLut, lw, lh, 4096, s->config.seed, st);
+        V.lut = s->dLut; V.lutW = lw; V.lutH = lh;
+    }
+
+    // BVH (RtcNewScene)
+    const int32_t triCount = vertCount / 3;
+    ok = ok && buildBvh(dPos, triCount, s->bvh, st);
+    V.bvh.nodes = s->bvh.nodes; V.bvh.tris = s->bvh.tris;
+    V.bvh.nodeCount = s->bvh.nodeCount; V.bvh.triCount = s->bvh.triCount;
+
+    // SetupEmissives (path_tracer.c:845-883): device pdf, ordered compaction
+    int32_t emissiveCount = 0;
+    if (ok && triCount > 0)
+    {
+        float* dPdf = nullptr;
+        ok = PT_CUDA(cudaMalloc((void**)&dPdf, sizeof(float) * (size_t)triCount));
+        ok = ok && launchEmissionPdf(V, triCount, s->config.seed, dPdf, st);
+        std::vector<float> pdf((size_t)triCount);
+        ok = ok && PT_CUDA(cudaMemcpyAsync(pdf.data(), dPdf, sizeof(float) * (size_t)triCount, cudaMemcpyDeviceToHost, st));
+        ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+        cudaFree(dPdf);
+        if (ok)
+        {
+            std::vector<int32_t> vertToEmit((size_t)vertCount, -1), emitToVert;
+            for (int32_t t = 0; t < triCount; ++t)
+            {
+                if (pdf[t] > 0.01f)
+                {
+                    vertToEmit[3 * t] = vertToEmit[3 * t + 1] = vertToEmit[3 * t + 2] = emissiveCount;
+                    emitToVert.push_back(3 * t);
+                    ++emissiveCount;
+                }
+            }
+            ok = sceneAlloc(s, dEmitToVert, emitToVert.size());
+            ok = ok && PT_CUDA(cudaMemcpyAsync(dVertToEmit, vertToEmit.data(), sizeof(int32_t) * vertToEmit.size(), cudaMemcpyHostToDevice, st));
+            if (ok && !emitToVert.empty())
+                ok = PT_CUDA(cudaMemcpyAsync(dEmitToVert, emitToVert.data(), sizeof(int32_t) * emitToVert.size(), cudaMemcpyHostToDevice, st));
+            ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+        }
+    }
+    V.vertToEmit = dVertToEmit; V.emitToVert = dEmitToVert; V.emissiveCount = emissiveCount;
+
+    // SetupLightGrid (path_tracer.c:992-1009): Grid_New over box_from_pts
+    if (ok && vertCount > 0)
+    {
+        Grid g;
+        g.lo = v3(s->bvh.sceneLo[0], s->bvh.sceneLo[1], s->bvh.sceneLo[2]);
+        g.hi = v3(s->bvh.sceneHi[0], s->bvh.sceneHi[1], s->bvh.sceneHi[2]);
+        g.cellsPerMeter = 1.0f / s->config.ptDistMeters;
+        g.sx = (int)f1_ceil_ref((g.hi.x - g.lo.x) * g.cellsPerMeter);
+        g.sy = (int)f1_ceil_ref((g.hi.y - g.lo.y) * g.cellsPerMeter);
+        g.sz = (int)f1_ceil_ref((g.hi.z - g.lo.z) * g.cellsPerMeter);
+        V.grid = g;
+        const size_t cells = (size_t)std::max(Grid_Len(g), 0);
+        s->gridCells = (int32_t)cells;
+        const size_t E = (size_t)emissiveCount;
+        ok = sceneAlloc(s, V.distPdf, cells * E) && sceneAlloc(s, V.distCdf, cells * (E + 1)) &&
+             sceneAlloc(s, V.distLive, cells * E) && sceneAlloc(s, V.distLength, cells) && sceneAlloc(s, V.distSum, cells);
+        ok = ok && PT_CUDA(cudaMemsetAsync(V.distLength, 0, sizeof(int32_t) * std::max<size_t>(cells, 1), st));
+        ok = ok && PT_CUDA(cudaMemsetAsync(V.distLive, 0, sizeof(uint32_t) * std::max<size_t>(cells * E, 1), st));
+        ok = ok && launchLightGrid(V, s->config.ptDistMeters, s->config.seed, st);
+    }
+
+    // wavefront pool: sized so the path state (about 200 B per slot) stays L2 resident
+    if (ok)
+    {
+        int32_t cap = s->config.pathPoolSize > 0 ? s->config.pathPoolSize : (1 << 19);
+        cap = (cap + 255) & ~255;
+        ok = poolAlloc(s->pool, cap);
+    }
+    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    if (dSrcPos) cudaFree(dSrcPos);
+    if (dSrcNrm) cudaFree(dSrcNrm);
+    if (dSrcUv) cudaFree(dSrcUv);
+    if (dEnts) cudaFree(dEnts);
+    if (!ok) { sceneFree(s); return nullptr; }
+    s->buildMs = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return s;
+}
+
+// ---- helpers for host <-> device batches ---------------------------------------
+
+struct DevBuf
+{
+    void* p = nullptr;
+    bool alloc(size_t bytes) { return PT_CUDA(cudaMalloc(&p, bytes ? bytes : 1)); }
+    ~DevBuf() { if (p) cudaFree(p); }
+};
+
+static bool traceSppDevice(PtScene* scene, const Camera* camera, PtDofInfo* dof, int w, int h, int sppBegin, int sppCount,
+                           float* dColor, float* dAlbedo, float* dNormal, cudaStream_t st)
+{
+    if (!launchDistUpdate(scene->view, st)) return false;       // PtScene_Update -> UpdateDists
+    WorkDesc W; memset(&W, 0, sizeof(W));
+    W.kind = Work_Camera;
+    W.cam = makeCam(camera, dof, w, h);
+    W.count = (int64_t)w * h * sppCount;
+    W.passBase = (uint32_t)sppBegin;
+    W.seed = scene->config.seed;
+    W.salt = Salt_Trace;
+    W.sumColor = dColor; W.sumAlbedo = dAlbedo; W.sumNormal = dNormal;
+    W.accumulate = 1;
+    float ms = 0.0f;
+    bool ok = runWavefront(scene->view, scene->pool, W, st, &ms);
+    g_lastKernelMs = ms;
+    return ok;
+}
+
+// DofUpdate (path_tracer.c:2485-2503); the frame time is fixed at 1/60 s so results
+// do not depend on wall-clock speed
+static bool dofUpdate(PtScene* scene, PtDofInfo* dof, const Camera* camera)
+{
+    if (!dof->autoFocus) return true;
+    const float q[4] = { camera->rotation.x, camera->rotation.y, camera->rotation.z, camera->rotation.w };
+    V3 fwd = quatMulDir(q, v3(0.0f, 0.0f, -1.0f));
+    F4 ro = f4(camera->position.x, camera->position.y, camera->position.z, 0.0f);
+    F4 rd = f4(fwd, kRcpEpsilon);
+    PtRayHit hit;
+    if (Pt_IntersectN(scene, (const pim_float4*)&ro, (const pim_float4*)&rd, 0.0f, &hit, 1) != 0) return false;
+    if (hit.type != PtHit_Nothing)
+    {
+        const float dt = 1.0f / 60.0f;
+        float t = 1.0f - expf(-dt * dof->autoFocusSpeed);
+        dof->focalLength = f1_lerp(dof->focalLength, hit.wuvt.w, t);
+    }
+    return true;
+}
+
+static DeviceImages* traceImages(PtTrace* trace)
+{
+    std::lock_guard<std::mutex> lock(g_mutex);
+    auto it = g_traces.find(trace);
+    const int64_t texels = (int64_t)trace->imageSize.x * trace->imageSize.y;
+    if (it != g_traces.end() && it->second.texels == texels) return &it->second;
+    DeviceImages im;
+    im.texels = texels;
+    for (int k = 0; k < 3; ++k)
+    {
+        if (!PT_CUDA(cudaMalloc((void**)&im.image[k], sizeof(float) * 3 * texels))) return nullptr;
+        if (!PT_CUDA(cudaMalloc((void**)&im.sum[k], sizeof(float) * 3 * texels))) return nullptr;
+        cudaMemset(im.image[k], 0, sizeof(float) * 3 * texels);
+    }
+    g_traces[trace] = im;
+    return &g_traces[trace];
+}
+
+static void releaseImages(PtTrace* trace)
+{
+    std::lock_guard<std::mutex> lock(g_mutex);
+    auto it = g_traces.find(trace);
+    if (it == g_traces.end()) return;
+    for (int k = 0; k < 3; ++k) { cudaFree(it->second.image[k]); cudaFree(it->second.sum[k]); }
+    g_traces.erase(it);
+}
+
+// ================================================================== C ABI =====
+
+extern "C" {
+
+const char* Pt_LastError(void) { return t_error; }
+
+void PtSys_Init(void) { t_error[0] = 0; ensureInit(); }
+void PtSys_Update(void) {}
+void PtSys_Shutdown(void)
+{
+    std::vector<PtTrace*> keys;
+    { std::lock_guard<std::mutex> lock(g_mutex); for (auto& kv : g_traces) keys.push_back(kv.first); }
+    for (PtTrace* t : keys) releaseImages(t);
+    g_initialised = false;
+}
+
+void PtSys_SetSceneDesc(const PtSceneDesc* desc)
+{
+    g_haveSceneDesc = desc != nullptr;
+    if (desc) g_sceneDesc = *desc;
+}
+
+PtScene* PtScene_New(void)
+{
+    if (!g_haveSceneDesc) { setError("PtScene_New: no scene description registered (PtSys_SetSceneDesc)"); return nullptr; }
+    return sceneBuild(&g_sceneDesc);
+}
+PtScene* PtScene_NewFromDesc(const PtSceneDesc* desc) { return sceneBuild(desc); }
+
+void PtScene_Update(PtScene* scene)
+{
+    if (!scene) return;
+    launchDistUpdate(scene->view, scene->stream);
+    PT_CUDA(cudaStreamSynchronize(scene->stream));
+}
+void PtScene_Del(PtScene* scene) { sceneFree(scene); }
+void PtScene_Gui(PtScene* scene) { (void)scene; }
+
+void PtTrace_New(PtTrace* trace, pim_int2 imageSize)      // path_tracer.c:1117-1130
+{
+    memset(trace, 0, sizeof(*trace));
+    const size_t texels = (size_t)imageSize.x * (size_t)imageSize.y;
+    trace->imageSize = imageSize;
+    trace->sampleWeight = 1.0f;
+    if (!ensureInit() || texels == 0) return;
+    const size_t bytes = sizeof(float) * 3 * texels;
+    bool ok = PT_CUDA(cudaMallocHost((void**)&trace->color, bytes)) && PT_CUDA(cudaMallocHost((void**)&trace->albedo, bytes)) &&
+              PT_CUDA(cudaMallocHost((void**)&trace->normal, bytes)) && PT_CUDA(cudaMallocHost((void**)&trace->denoised, bytes));
+    if (!ok) { PtTrace_Del(trace); return; }
+    memset(trace->color, 0, bytes); memset(trace->albedo, 0, bytes);
+    memset(trace->normal, 0, bytes); memset(trace->denoised, 0, bytes);
+}
+
+void PtTrace_Del(PtTrace* trace)
+{
+    if (!trace) return;
+    releaseImages(trace);
+    if (trace->color) cudaFreeHost(trace->color);
+    if (trace->albedo) cudaFreeHost(trace->albedo);
+    if (trace->normal) cudaFreeHost(trace->normal);
+    if (trace->denoised) cudaFreeHost(trace->denoised);
+    memset(trace, 0, sizeof(*trace));
+}
+
+void DofInfo_New(PtDofInfo* dof)      // path_tracer.c:1141-1153
+{
+    if (!dof) return;
+    dof->aperture = 5.0f * kMilli;
+    dof->focalLength = 6.0f;
+    dof->bladeCount = 5;
+    dof->bladeRot = kPi / 10.0f;
+    dof->focalPlaneCurvature = 0.05f;
+    dof->autoFocus = true;
+    dof->autoFocusSpeed = 3.0f;
+}
+void DofInfo_Gui(PtDofInfo* dof) { (void)dof; }
+
+int32_t Pt_IntersectN_Device(const PtScene* scene, const void* dRo, const void* dRd, float tNear, void* dHitsOut,
+                             int64_t n, void* stream)
+{
+    if (!scene) { setError("Pt_IntersectN_Device: null scene"); return -1; }
+    cudaStream_t st = stream ? (cudaStream_t)stream : scene->stream;
+    return launchIntersect(scene->view, (const F4*)dRo, (const F4*)dRd, tNear, (RayHitOut*)dHitsOut, n, st) ? 0 : -1;
+}
+
+int32_t Pt_OccludedN_Device(const PtScene* scene, const void* dRo, const void* dRd, float tNear, void* dOccludedOut,
+                            int64_t n, void* stream)
+{
+    if (!scene) { setError("Pt_OccludedN_Device: null scene"); return -1; }
+    cudaStream_t st = stream ? (cudaStream_t)stream : scene->stream;
+    return launchOccluded(scene->view, (const F4*)dRo, (const F4*)dRd, tNear, (uint8_t*)dOccludedOut, n, st) ? 0 : -1;
+}
+
+int32_t Pt_IntersectN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd, float tNear, PtRayHit* hitsOut,
+                      int64_t n)
+{
+    if (!scene) { setError("Pt_IntersectN: null scene"); return -1; }
+    if (n <= 0) return 0;
+    const int64_t chunk = 1 << 24;
+    DevBuf dRo, dRd, dOut;
+    const int64_t m = std::min(n, chunk);
+    if (!dRo.alloc(sizeof(F4) * m) || !dRd.alloc(sizeof(F4) * m) || !dOut.alloc(sizeof(RayHitOut) * m)) return -1;
+    cudaStream_t st = scene->stream;
+    for (int64_t base = 0; base < n; base += chunk)
+    {
+        const int64_t c = std::min(chunk, n - base);
+        bool ok = PT_CUDA(cudaMemcpyAsync(dRo.p, ro + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+                  PT_CUDA(cudaMemcpyAsync(dRd.p, rd + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+                  launchIntersect(scene->view, (const F4*)dRo.p, (const F4*)dRd.p, tNear, (RayHitOut*)dOut.p, c, st) &&
+                  PT_CUDA(cudaMemcpyAsync(hitsOut + base, dOut.p, sizeof(RayHitOut) * c, cudaMemcpyDeviceToHost, st)) &&
+                  PT_CUDA(cudaStreamSynchronize(st));
+        if (!ok) return -1;
+    }
+    return 0;
+}
+
+int32_t Pt_OccludedN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd, float tNear, uint8_t* occludedOut,
+                     int64_t n)
+{
+    if (!scene) { setError("Pt_OccludedN: null scene"); return -1; }
+    if (n <= 0) return 0;
+    const int64_t chunk = 1 << 24;
+    DevBuf dRo, dRd, dOut;
+    const int64_t m = std::min(n, chunk);
+    if (!dRo.alloc(sizeof(F4) * m) || !dRd.alloc(sizeof(F4) * m) || !dOut.alloc(m)) return -1;
+    cudaStream_t st = scene->stream;
+    for (int64_t base = 0; base < n; base += chunk)
+    {
+        const int64_t c = std::min(chunk, n - base);
+        bool ok = PT_CUDA(cudaMemcpyAsync(dRo.p, ro + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+                  PT_CUDA(cudaMemcpyAsync(dRd.p, rd + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+                  launchOccluded(scene->view, (const F4*)dRo.p, (const F4*)dRd.p, tNear, (uint8_t*)dOut.p, c, st) &&
+                  PT_CUDA(cudaMemcpyAsync(occludedOut + base, dOut.p, c, cudaMemcpyDeviceToHost, st)) &&
+                  PT_CUDA(cudaStreamSynchronize(st));
+        if (!ok) return -1;
+    }
+    return 0;
+}
+
+PtRayHit Pt_Intersect(const PtScene* scene, pim_float4 ro, pim_float4 rd, float tNear, float tFar)
+{
+    PtRayHit hit;
+    memset(&hit, 0, sizeof(hit));
+    hit.wuvt.w = -1.0f; hit.iVert = -1;
+    rd.w = tFar;
+    Pt_IntersectN(scene, &ro, &rd, tNear, &hit, 1);
+    return hit;
+}
+
+int32_t Pt_TraceRayN(PtScene* scene, const pim_float4* ro, const pim_float4* rd, uint32_t pass, PtResult* resultsOut,
+                     int64_t n)
+{
+    if (!scene) { setError("Pt_TraceRayN: null scene"); return -1; }
+    if (n <= 0) return 0;
+    DevBuf dRo, dRd, dOut;
+    if (!dRo.alloc(sizeof(F4) * n) || !dRd.alloc(sizeof(F4) * n) || !dOut.alloc(sizeof(float) * 9 * n)) return -1;
+    cudaStream_t st = scene->stream;
+    bool ok = PT_CUDA(cudaMemcpyAsync(dRo.p, ro, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
+              PT_CUDA(cudaMemcpyAsync(dRd.p, rd, sizeof(F4) * n, cudaMemcpyHostToDevice, st));
+    if (ok && n < 4096)
+    {
+        ok = launchTraceRays(scene->view, (const F4*)dRo.p, (const F4*)dRd.p, n, pass, scene->config.seed, (float*)dOut.p, st);
+    }
+    else if (ok)
+    {
+        // results are per item: colour, albedo, normal triples interleaved as PtResult
+        DevBuf c, a, nr;
+        ok = c.alloc(sizeof(float) * 3 * n) && a.alloc(sizeof(float) * 3 * n) && nr.alloc(sizeof(float) * 3 * n);
+        WorkDesc W; memset(&W, 0, sizeof(W));
+        W.kind = Work_Rays; W.ro = (const F4*)dRo.p; W.rd = (const F4*)dRd.p; W.count = n;
+        W.passBase = pass; W.seed = scene->config.seed; W.salt = Salt_Rays;
+        W.sumColor = (float*)c.p; W.sumAlbedo = (float*)a.p; W.sumNormal = (float*)nr.p; W.accumulate = 0;
+        float ms = 0.0f;
+        ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
+        g_lastKernelMs = ms;
+        // interleave on the host side of the copy: three strided 2D copies into PtResult
+        ok = ok && PT_CUDA(cudaMemcpy2DAsync((float*)dOut.p + 0, 36, c.p, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
+        ok = ok && PT_CUDA(cudaMemcpy2DAsync((float*)dOut.p + 3, 36, a.p, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
+        ok = ok && PT_CUDA(cudaMemcpy2DAsync((float*)dOut.p + 6, 36, nr.p, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
+        ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    }
+    ok = ok && PT_CUDA(cudaMemcpyAsync(resultsOut, dOut.p, sizeof(float) * 9 * n, cudaMemcpyDeviceToHost, st));
+    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    return ok ? 0 : -1;
+}
+
+PtResult Pt_TraceRay(PtScene* scene, pim_float4 ro, pim_float4 rd)
+{
+    PtResult r;
+    memset(&r, 0, sizeof(r));
+    if (scene) Pt_TraceRayN(scene, &ro, &rd, scene->nextPass++, &r, 1);
+    return r;
+}
+
+int32_t Pt_TraceSpp_Device(PtScene* scene, const Camera* camera, PtDofInfo* dof, int32_t width, int32_t height,
+                           int32_t sppBegin, int32_t sppCount, void* dSumColor, void* dSumAlbedo, void* dSumNormal,
+                           void* stream)
+{
+    if (!scene || !camera || !dof) { setError("Pt_TraceSpp_Device: null argument"); return -1; }
+    cudaStream_t st = stream ? (cudaStream_t)stream : scene->stream;
+    return traceSppDevice(scene, camera, dof, width, height, sppBegin, sppCount, (float*)dSumColor, (float*)dSumAlbedo,
+                          (float*)dSumNormal, st) ? 0 : -1;
+}
+
+int32_t Pt_TraceSpp(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera* camera, int32_t sppBegin, int32_t sppCount)
+{
+    if (!trace || !dof || !scene || !camera || !trace->color) { setError("Pt_TraceSpp: null argument"); return -1; }
+    if (sppCount <= 0) return 0;
+    DeviceImages* im = traceImages(trace);
+    if (!im) return -1;
+    cudaStream_t st = scene->stream;
+    const int w = trace->imageSize.x, h = trace->imageSize.y;
+    const int64_t n3 = im->texels * 3;
+    bool ok = true;
+    for (int k = 0; k < 3; ++k) ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[k], 0, sizeof(float) * n3, st));
+    ok = ok && traceSppDevice(scene, camera, dof, w, h, sppBegin, sppCount, im->sum[0], im->sum[1], im->sum[2], st);
+    float* host[3] = { (float*)trace->color, (float*)trace->albedo, (float*)trace->normal };
+    for (int k = 0; ok && k < 3; ++k)
+    {
+        if (trace->sampleWeight > 0.0f)
+        {
+            ok = launchResolve(im->image[k], im->sum[k], n3, (float)sppBegin, (float)sppCount, st);
+            ok = ok && PT_CUDA(cudaMemcpyAsync(host[k], im->image[k], sizeof(float) * n3, cudaMemcpyDeviceToHost, st));
+        }
+        else
+        {
+            ok = PT_CUDA(cudaMemcpyAsync(host[k], im->sum[k], sizeof(float) * n3, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    return ok ? 0 : -1;
+}
+
+void Pt_Trace(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera* camera)      // path_tracer.c:2557-2585
+{
+    t_error[0] = 0;
+    if (!trace || !dof || !scene || !camera || !trace->color) { setError("Pt_Trace: null argument"); return; }
+    DeviceImages* im = traceImages(trace);
+    if (!im) return;
+    cudaStream_t st = scene->stream;
+    const int w = trace->imageSize.x, h = trace->imageSize.y;
+    const int64_t n3 = im->texels * 3;
+    if (!dofUpdate(scene, dof, camera)) return;
+    bool ok = true;
+    for (int k = 0; k < 3; ++k) ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[k], 0, sizeof(float) * n3, st));
+    ok = ok && traceSppDevice(scene, camera, dof, w, h, (int32_t)scene->nextPass, 1, im->sum[0], im->sum[1], im->sum[2], st);
+    scene->nextPass++;
+    float* host[3] = { (float*)trace->color, (float*)trace->albedo, (float*)trace->normal };
+    for (int k = 0; ok && k < 3; ++k)
+    {
+        ok = launchLerp(im->image[k], im->sum[k], n3, trace->sampleWeight, st);
+        ok = ok && PT_CUDA(cudaMemcpyAsync(host[k], im->image[k], sizeof(float) * n3, cudaMemcpyDeviceToHost, st));
+    }
+    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+}
+
+PtResults Pt_RayGen(PtScene* scene, pim_float4 origin, int32_t count)      // path_tracer.c:2615-2644
+{
+    PtResults res = { nullptr, nullptr };
+    if (!scene || count <= 0) return res;
+    const int slot = scene->rayGenFlip;
+    scene->rayGenFlip ^= 1;
+    if (scene->rayGenCap[slot] < count)
+    {
+        if (scene->rayGenColors[slot]) cudaFreeHost(scene->rayGenColors[slot]);
+        if (scene->rayGenDirs[slot]) cudaFreeHost(scene->rayGenDirs[slot]);
+        scene->rayGenColors[slot] = nullptr; scene->rayGenDirs[slot] = nullptr; scene->rayGenCap[slot] = 0;
+        if (!PT_CUDA(cudaMallocHost((void**)&scene->rayGenColors[slot], sizeof(F4) * (size_t)count))) return res;
+        if (!PT_CUDA(cudaMallocHost((void**)&scene->rayGenDirs[slot], sizeof(F4) * (size_t)count))) return res;
+        scene->rayGenCap[slot] = count;
+    }
+    cudaStream_t st = scene->stream;
+    DevBuf c, d;
+    if (!c.alloc(sizeof(float) * 3 * (size_t)count) || !d.alloc(sizeof(F4) * (size_t)count)) return res;
+    bool ok = launchDistUpdate(scene->view, st);
+    WorkDesc W; memset(&W, 0, sizeof(W));
+    W.kind = Work_Sphere; W.origin = v3(origin.x, origin.y, origin.z); W.count = count;
+    W.passBase = scene->nextPass++; W.seed = scene->config.seed; W.salt = Salt_RayGen;
+    W.sumColor = (float*)c.p; W.directions = (F4*)d.p; W.accumulate = 0;
+    float ms = 0.0f;
+    ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
+    g_lastKernelMs = ms;
+    // colours come back as float3; widen to the reference's float4 (w = 0)
+    ok = ok && PT_CUDA(cudaMemcpyAsync(scene->rayGenDirs[slot], d.p, sizeof(F4) * (size_t)count, cudaMemcpyDeviceToHost, st));
+    std::vector<float> tmp((size_t)count * 3);
+    ok = ok && PT_CUDA(cudaMemcpyAsync(tmp.data(), c.p, sizeof(float) * 3 * (size_t)count, cudaMemcpyDeviceToHost, st));
+    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    if (!ok) return res;
+    for (int32_t i = 0; i < count; ++i)
+    {
+        scene->rayGenColors[slot][i].x = tmp[3 * (size_t)i]; scene->rayGenColors[slot][i].y = tmp[3 * (size_t)i + 1];
+        scene->rayGenColors[slot][i].z = tmp[3 * (size_t)i + 2]; scene->rayGenColors[slot][i].w = 0.0f;
+    }
+    res.colors = scene->rayGenColors[slot];
+    res.directions = scene->rayGenDirs[slot];
+    return res;
+}
+
+int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCount, float texelsPerMeter, float timeSlice,
+                        int32_t spp, uint32_t pass)
+{
+    if (!scene || (!lightmaps && lmCount > 0)) { setError("LmPack_BakeDesc: null argument"); return -1; }
+    cudaStream_t st = scene->stream;
+    bool ok = launchDistUpdate(scene->view, st);       // LmPack_Bake -> PtScene_Update (lightmap.c:1209)
+    int32_t texelBase = 0;
+    for (int32_t i = 0; ok && i < lmCount; ++i)
+    {
+        PtLightmapDesc& lm = lightmaps[i];
+        const size_t n = (size_t)lm.size * (size_t)lm.size;
+        DevBuf probes[5], pos, nrm, cnt;
+        LightmapView view;
+        for (int k = 0; ok && k < 5; ++k)
+        {
+            ok = probes[k].alloc(sizeof(F4) * n) &&
+                 PT_CUDA(cudaMemcpyAsync(probes[k].p, lm.probes[k], sizeof(F4) * n, cudaMemcpyHostToDevice, st));
+            view.probes[k] = (F4*)probes[k].p;
+        }
+        ok = ok && pos.alloc(12 * n) && nrm.alloc(12 * n) && cnt.alloc(4 * n);
+        ok = ok && PT_CUDA(cudaMemcpyAsync(pos.p, lm.position, 12 * n, cudaMemcpyHostToDevice, st));
+        ok = ok && PT_CUDA(cudaMemcpyAsync(nrm.p, lm.normal, 12 * n, cudaMemcpyHostToDevice, st));
+        ok = ok && PT_CUDA(cudaMemcpyAsync(cnt.p, lm.sampleCounts, 4 * n, cudaMemcpyHostToDevice, st));
+        view.position = (const float*)pos.p; view.normal = (const float*)nrm.p; view.sampleCounts = (float*)cnt.p;
+        view.texelCount = (int32_t)n; view.texelBase = texelBase;
+        ok = ok && launchLightmapBake(scene->view, view, 1.0f / texelsPerMeter, timeSlice, spp, pass, scene->config.seed, st);
+        for (int k = 0; ok && k < 5; ++k)
+            ok = PT_CUDA(cudaMemcpyAsync(lm.probes[k], probes[k].p, sizeof(F4) * n, cudaMemcpyDeviceToHost, st));
+        ok = ok && PT_CUDA(cudaMemcpyAsync(lm.sampleCounts, cnt.p, 4 * n, cudaMemcpyDeviceToHost, st));
+        ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+        texelBase += (int32_t)n;
+    }
+    return ok ? 0 : -1;
+}
+
+int32_t PtScene_GetStats(const PtScene* scene, PtSceneStats* stats)
+{
+    if (!scene || !stats) return -1;
+    memset(stats, 0, sizeof(*stats));
+    const DScene& V = scene->view;
+    stats->vertCount = V.vertCount; stats->matCount = V.matCount; stats->emissiveCount = V.emissiveCount;
+    stats->gridSize[0] = V.grid.sx; stats->gridSize[1] = V.grid.sy; stats->gridSize[2] = V.grid.sz;
+    stats->gridLo[0] = V.grid.lo.x; stats->gridLo[1] = V.grid.lo.y; stats->gridLo[2] = V.grid.lo.z;
+    stats->gridHi[0] = V.grid.hi.x; stats->gridHi[1] = V.grid.hi.y; stats->gridHi[2] = V.grid.hi.z;
+    stats->cellsPerMeter = V.grid.cellsPerMeter;
+    stats->bvhNodeCount = V.bvh.nodeCount; stats->bvhTriCount = V.bvh.triCount;
+    stats->buildMs = scene->buildMs;
+    return 0;
+}
+
+int32_t PtScene_Download(const PtScene* scene, pim_float4* positions, pim_float4* normals, pim_float2* uvs, int32_t* matIds,
+                         int32_t* vertToEmit, int32_t* emitToVert)
+{
+    if (!scene) return -1;
+    const DScene& V = scene->view;
+    const size_t n = (size_t)V.vertCount;
+    bool ok = true;
+    if (positions && n) ok = ok && PT_CUDA(cudaMemcpy(positions, V.positions, sizeof(F4) * n, cudaMemcpyDeviceToHost));
+    if (normals && n) ok = ok && PT_CUDA(cudaMemcpy(normals, V.normals, sizeof(F4) * n, cudaMemcpyDeviceToHost));
+    if (uvs && n) ok = ok && PT_CUDA(cudaMemcpy(uvs, V.uvs, sizeof(V2) * n, cudaMemcpyDeviceToHost));
+    if (matIds && n) ok = ok && PT_CUDA(cudaMemcpy(matIds, V.matIds, 4 * n, cudaMemcpyDeviceToHost));
+    if (vertToEmit && n) ok = ok && PT_CUDA(cudaMemcpy(vertToEmit, V.vertToEmit, 4 * n, cudaMemcpyDeviceToHost));
+    if (emitToVert && V.emissiveCount) ok = ok && PT_CUDA(cudaMemcpy(emitToVert, V.emitToVert, 4 * (size_t)V.emissiveCount, cudaMemcpyDeviceToHost));
+    return ok ? 0 : -1;
+}
+
+int32_t PtScene_GetDist(const PtScene* scene, int32_t cell, float* pdf, float* cdf, uint32_t* live)
+{
+    if (!scene || cell < 0 || cell >= scene->gridCells) return -1;
+    const DScene& V = scene->view;
+    int32_t len = 0;
+    if (!PT_CUDA(cudaMemcpy(&len, V.distLength + cell, 4, cudaMemcpyDeviceToHost))) return -1;
+    const size_t E = (size_t)V.emissiveCount;
+    if (len > 0)
+    {
+        if (pdf && !PT_CUDA(cudaMemcpy(pdf, V.distPdf + cell * E, 4 * E, cudaMemcpyDeviceToHost))) return -1;
+        if (cdf && !PT_CUDA(cudaMemcpy(cdf, V.distCdf + cell * (E + 1), 4 * (E + 1), cudaMemcpyDeviceToHost))) return -1;
+        if (live && !PT_CUDA(cudaMemcpy(live, V.distLive + cell * E, 4 * E, cudaMemcpyDeviceToHost))) return -1;
+    }
+    return len;
+}
+
+int32_t PtScene_SetDist(PtScene* scene, int32_t cell, int32_t length, const float* pdf)
+{
+    if (!scene || cell < 0 || cell >= scene->gridCells) return -1;
+    const DScene& V = scene->view;
+    const int32_t E = V.emissiveCount;
+    if (length != 0 && length != E) { setError("PtScene_SetDist: length must be 0 or the emissive count"); return -1; }
+    bool ok = PT_CUDA(cudaMemcpy(V.distLength + cell, &length, 4, cudaMemcpyHostToDevice));
+    if (ok && length > 0)
+    {
+        // Dist1D_Bake on the host (dist1d.c:33-73), then upload
+        std::vector<float> p(pdf, pdf + E), c((size_t)E + 1);
+        const float rcpLen = 1.0f / E;
+        c[0] = 0.0f;
+        for (int i = 1; i <= E; ++i) c[i] = c[i - 1] + p[i - 1] * rcpLen;
+        float integral = c[E];
+        if (integral == 0.0f) { for (int i = 1; i <= E; ++i) c[i] = i * rcpLen; }
+        else
+        {
+            float r = 1.0f / integral;
+            for (int i = 1; i <= E; ++i) c[i] *= r;
+            for (int i = 0; i < E; ++i) p[i] *= r;
+        }
+        std::vector<uint32_t> zero((size_t)E, 0u);
+        uint32_t zsum = 0;
+        ok = PT_CUDA(cudaMemcpy(V.distPdf + (size_t)cell * E, p.data(), 4 * (size_t)E, cudaMemcpyHostToDevice)) &&
+             PT_CUDA(cudaMemcpy(V.distCdf + (size_t)cell * (E + 1), c.data(), 4 * ((size_t)E + 1), cudaMemcpyHostToDevice)) &&
+             PT_CUDA(cudaMemcpy(V.distLive + (size_t)cell * E, zero.data(), 4 * (size_t)E, cudaMemcpyHostToDevice)) &&
+             PT_CUDA(cudaMemcpy(V.distSum + cell, &zsum, 4, cudaMemcpyHostToDevice));
+    }
+    return ok ? 0 : -1;
+}
+
+int32_t PtScene_GetBrdfLut(const PtScene* scene, float* texels, int32_t* width, int32_t* height)
+{
+    if (!scene) return -1;
+    if (width) *width = scene->view.lutW;
+    if (height) *height = scene->view.lutH;
+    if (texels && !PT_CUDA(cudaMemcpy(texels, scene->dLut, sizeof(float) * 2 * (size_t)scene->view.lutW * scene->view.lutH, cudaMemcpyDeviceToHost))) return -1;
+    return 0;
+}
+
+void Pt_GetCounters(PtCounters* out)
+{
+    if (!out) return;
+    out->paths = g_counters.paths; out->rays = g_counters.rays; out->occlusionRays = g_counters.occlusionRays;
+    out->kernelLaunches = g_counters.kernelLaunches; out->iterations = g_counters.iterations;
+}
+void Pt_ResetCounters(void) { g_counters = LibCounters{ 0, 0, 0, 0, 0 }; }
+float Pt_LastKernelMs(void) { return g_lastKernelMs; }
+
+} // extern "C"

@@ -1,0 +1,419 @@
+// bvh_build.cu — GPU build of the 8-wide compressed BVH (replaces Embree's
+// rtcCommitScene at RTC_BUILD_QUALITY_HIGH, src/rendering/path_tracer.c:618-690).
+//
+//   K1a triBounds   per-triangle box + centroid bounds (block reduce, ordered-int atomics)
+//   K1b morton      63-bit Morton key of the centroid, value = triangle index
+//   K1c radix sort  LSD, 8 x 8-bit digits: histogram / scan / stable scatter with
+//                   warp match-any ranking
+//   K2a radixTree   Karras' binary radix tree over the sorted keys
+//   K2b refit       bottom-up boxes, one atomic visit counter per internal node
+//   K2c collapse    breadth-first greedy collapse to 8-wide nodes, child boxes
+//                   quantised to 8 bits; triangles copied into leaf order
+#include "pt_device.h"
+
+#include <algorithm>
+#include <cstdio>
+
+namespace pt {
+
+namespace {
+
+constexpr int kSortThreads = 256;
+constexpr int kSortItems = 8;
+constexpr int kSortTile = kSortThreads * kSortItems;   // keys per block
+
+__device__ __forceinline__ int floatToOrdered(float f)
+{
+    int i = __float_as_int(f);
+    return (i >= 0) ? i : (i ^ 0x7fffffff);
+}
+__device__ __forceinline__ float orderedToFloat(int i)
+{
+    return __int_as_float((i >= 0) ? i : (i ^ 0x7fffffff));
+}
+
+// bounds[0..2] = centroid min, [3..5] = centroid max, [6..8] = vertex min, [9..11] = vertex max (ordered ints)
+__global__ void k_initBounds(int* bounds)
+{
+    int i = threadIdx.x;
+    if (i < 12) bounds[i] = ((i / 3) & 1) ? floatToOrdered(-3.0e38f) : floatToOrdered(3.0e38f);
+}
+
+__global__ void __launch_bounds__(256) k_triBounds(const F4* __restrict__ pos, int n, F4* __restrict__ leafLo,
+                                                   F4* __restrict__ leafHi, int* bounds)
+{
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+    float clo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, chi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+    if (t < n)
+    {
+        U4 a = ldg128(pos + 3 * (size_t)t), b = ldg128(pos + 3 * (size_t)t + 1), c = ldg128(pos + 3 * (size_t)t + 2);
+        float ax[3] = { u2f(a.x), u2f(a.y), u2f(a.z) };
+        float bx[3] = { u2f(b.x), u2f(b.y), u2f(b.z) };
+        float cx[3] = { u2f(c.x), u2f(c.y), u2f(c.z) };
+        for (int k = 0; k < 3; ++k)
+        {
+            lo[k] = f1_min(ax[k], f1_min(bx[k], cx[k]));
+            hi[k] = f1_max(ax[k], f1_max(bx[k], cx[k]));
+            clo[k] = chi[k] = (lo[k] + hi[k]) * 0.5f;
+        }
+        leafLo[t] = f4(lo[0], lo[1], lo[2], 0.0f);
+        leafHi[t] = f4(hi[0], hi[1], hi[2], 0.0f);
+    }
+    for (int k = 0; k < 3; ++k)
+    {
+        for (int o = 16; o > 0; o >>= 1)
+        {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+            clo[k] = fminf(clo[k], __shfl_xor_sync(0xffffffffu, clo[k], o));
+            chi[k] = fmaxf(chi[k], __shfl_xor_sync(0xffffffffu, chi[k], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0)
+    {
+        for (int k = 0; k < 3; ++k)
+        {
+            atomicMin(&bounds[k], floatToOrdered(clo[k]));
+            atomicMax(&bounds[3 + k], floatToOrdered(chi[k]));
+            atomicMin(&bounds[6 + k], floatToOrdered(lo[k]));
+            atomicMax(&bounds[9 + k], floatToOrdered(hi[k]));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_morton(const F4* __restrict__ leafLo, const F4* __restrict__ leafHi, int n,
+                                                const int* __restrict__ bounds, uint64_t* __restrict__ keys,
+                                                uint32_t* __restrict__ vals)
+{
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    V3 lo = v3(orderedToFloat(bounds[0]), orderedToFloat(bounds[1]), orderedToFloat(bounds[2]));
+    V3 hi = v3(orderedToFloat(bounds[3]), orderedToFloat(bounds[4]), orderedToFloat(bounds[5]));
+    V3 ext = hi - lo;
+    V3 invExt = v3(ext.x > 0.0f ? 1.0f / ext.x : 0.0f, ext.y > 0.0f ? 1.0f / ext.y : 0.0f,
+                   ext.z > 0.0f ? 1.0f / ext.z : 0.0f);
+    F4 a = leafLo[t], b = leafHi[t];
+    V3 c = v3((a.x + b.x) * 0.5f, (a.y + b.y) * 0.5f, (a.z + b.z) * 0.5f);
+    keys[t] = morton63(c, lo, invExt);
+    vals[t] = (uint32_t)t;
+}
+
+// ---- radix sort -------------------------------------------------------------
+
+// hist[digit * numBlocks + block]
+__global__ void __launch_bounds__(kSortThreads) k_sortHist(const uint64_t* __restrict__ keys, int n, int shift,
+                                                           uint32_t* __restrict__ hist, int numBlocks)
+{
+    __shared__ uint32_t sh[256];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    int base = blockIdx.x * kSortTile;
+    for (int r = 0; r < kSortItems; ++r)
+    {
+        int i = base + r * kSortThreads + threadIdx.x;
+        if (i < n) atomicAdd(&sh[(uint32_t)(keys[i] >> shift) & 0xffu], 1u);
+    }
+    __syncthreads();
+    hist[(size_t)threadIdx.x * numBlocks + blockIdx.x] = sh[threadIdx.x];
+}
+
+// exclusive scan of `count` entries by one block of 1024 threads
+__global__ void __launch_bounds__(1024) k_sortScan(uint32_t* __restrict__ hist, int count)
+{
+    __shared__ uint32_t partial[1024];
+    int per = (count + 1023) / 1024;
+    int b = threadIdx.x * per, e = min(b + per, count);
+    uint32_t sum = 0;
+    for (int i = b; i < e; ++i) sum += hist[i];
+    partial[threadIdx.x] = sum;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1)
+    {
+        uint32_t v = (threadIdx.x >= o) ? partial[threadIdx.x - o] : 0;
+        __syncthreads();
+        partial[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = partial[threadIdx.x] - sum;
+    for (int i = b; i < e; ++i)
+    {
+        uint32_t v = hist[i];
+        hist[i] = run;
+        run += v;
+    }
+}
+
+// stable scatter: every warp ranks its 256 consecutive keys with match-any
+__global__ void __launch_bounds__(kSortThreads) k_sortScatter(const uint64_t* __restrict__ keysIn,
+                                                              const uint32_t* __restrict__ valsIn, int n, int shift,
+                                                              const uint32_t* __restrict__ hist, int numBlocks,
+                                                              uint64_t* __restrict__ keysOut,
+                                                              uint32_t* __restrict__ valsOut)
+{
+    constexpr int kWarps = kSortThreads / 32;
+    __shared__ uint32_t warpCnt[kWarps][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < kWarps * 256; i += kSortThreads) (&warpCnt[0][0])[i] = 0;
+    __syncthreads();
+
+    const int warpBase = blockIdx.x * kSortTile + warp * (kSortItems * 32);
+    uint64_t key[kSortItems];
+    uint32_t val[kSortItems];
+    uint32_t rank[kSortItems];
+    const uint32_t ltMask = (1u << lane) - 1u;
+    for (int r = 0; r < kSortItems; ++r)
+    {
+        int i = warpBase + r * 32 + lane;
+        bool valid = i < n;
+        key[r] = valid ? keysIn[i] : ~0ull;
+        val[r] = valid ? valsIn[i] : 0u;
+        uint32_t digit = valid ? ((uint32_t)(key[r] >> shift) & 0xffu) : (0x100u + (uint32_t)lane);
+        uint32_t peers = __match_any_sync(0xffffffffu, digit);
+        int leader = __ffs((int)peers) - 1;
+        uint32_t old = 0;
+        if (valid && lane == leader)
+        {
+            old = warpCnt[warp][digit];
+            warpCnt[warp][digit] = old + (uint32_t)__popc(peers);
+        }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        rank[r] = old + (uint32_t)__popc(peers & ltMask);
+        __syncwarp();
+    }
+    __syncthreads();
+    // per digit: exclusive prefix over warps, plus this block's global base
+    {
+        uint32_t d = threadIdx.x;
+        uint32_t run = hist[(size_t)d * numBlocks + blockIdx.x];
+        for (int w = 0; w < kWarps; ++w)
+        {
+            uint32_t c = warpCnt[w][d];
+            warpCnt[w][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+    for (int r = 0; r < kSortItems; ++r)
+    {
+        int i = warpBase + r * 32 + lane;
+        if (i < n)
+        {
+            uint32_t digit = (uint32_t)(key[r] >> shift) & 0xffu;
+            uint32_t dst = warpCnt[warp][digit] + rank[r];
+            keysOut[dst] = key[r];
+            valsOut[dst] = val[r];
+        }
+    }
+}
+
+// ---- hierarchy --------------------------------------------------------------
+
+__global__ void __launch_bounds__(256) k_radixTree(const uint64_t* __restrict__ keys, int n, F4* lo, F4* hi,
+                                                   int* first, int* last, int* parent)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int f, l, s;
+    lbvhRange(keys, n, i, f, l, s);
+    int left = (s == f) ? (n - 1 + s) : s;
+    int right = (s + 1 == l) ? (n - 1 + s + 1) : (s + 1);
+    first[i] = f; last[i] = l;
+    lo[i].w = u2f((uint32_t)left);
+    hi[i].w = u2f((uint32_t)right);
+    parent[left] = i;
+    parent[right] = i;
+}
+
+__global__ void __launch_bounds__(256) k_leafInit(const uint32_t* __restrict__ vals, const F4* __restrict__ leafLo,
+                                                  const F4* __restrict__ leafHi, int n, F4* lo, F4* hi, int* first,
+                                                  int* last)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    uint32_t t = vals[k];
+    int id = n - 1 + k;
+    F4 a = leafLo[t], b = leafHi[t];
+    lo[id] = f4(a.x, a.y, a.z, 0.0f);
+    hi[id] = f4(b.x, b.y, b.z, 0.0f);
+    first[id] = k; last[id] = k;
+}
+
+__global__ void __launch_bounds__(256) k_refit(int n, F4* lo, F4* hi, const int* __restrict__ parent, int* visits)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int node = parent[n - 1 + k];
+    while (node >= 0)
+    {
+        __threadfence();
+        if (atomicAdd(&visits[node], 1) == 0) return;   // first arrival waits for the sibling subtree
+        // second arrival: both children are final
+        volatile F4* vlo = lo; volatile F4* vhi = hi;
+        int l = (int)f2u(vlo[node].w), r = (int)f2u(vhi[node].w);
+        float lx = fminf(vlo[l].x, vlo[r].x), ly = fminf(vlo[l].y, vlo[r].y), lz = fminf(vlo[l].z, vlo[r].z);
+        float hx = fmaxf(vhi[l].x, vhi[r].x), hy = fmaxf(vhi[l].y, vhi[r].y), hz = fmaxf(vhi[l].z, vhi[r].z);
+        vlo[node].x = lx; vlo[node].y = ly; vlo[node].z = lz;
+        vhi[node].x = hx; vhi[node].y = hy; vhi[node].z = hz;
+        node = parent[node];
+    }
+}
+
+struct CollapseWork { int32_t bin; uint32_t wide; };
+
+// counters: [0] wide nodes allocated, [1] triangles allocated, [2] next-level queue length
+__global__ void __launch_bounds__(128) k_collapse(BinTree T, const CollapseWork* __restrict__ qIn, int nIn,
+                                                  CollapseWork* __restrict__ qOut, uint32_t* counters,
+                                                  const uint32_t* __restrict__ vals, const F4* __restrict__ pos,
+                                                  WideNode* nodes, PackedTri* tris)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nIn) return;
+    CollapseWork w = qIn[i];
+    int kids[8];
+    int nk = collapseChildren(T, w.bin, kids);
+    uint32_t nInt = 0, nTri = 0;
+    for (int k = 0; k < nk; ++k)
+    {
+        if (binIsLeafCluster(T, kids[k])) nTri += (uint32_t)(T.last[kids[k]] - T.first[kids[k]] + 1);
+        else nInt++;
+    }
+    uint32_t childBase = nInt ? atomicAdd(&counters[0], nInt) : 0u;
+    uint32_t triBase = nTri ? atomicAdd(&counters[1], nTri) : 0u;
+    uint32_t qBase = nInt ? atomicAdd(&counters[2], nInt) : 0u;
+    WideNode node;
+    encodeWideNode(node, T, kids, nk, childBase, triBase);
+    nodes[w.wide] = node;
+    uint32_t ci = 0, ti = 0;
+    for (int k = 0; k < nk; ++k)
+    {
+        int kid = kids[k];
+        if (binIsLeafCluster(T, kid))
+        {
+            for (int s = T.first[kid]; s <= T.last[kid]; ++s)
+            {
+                uint32_t t = vals[s];
+                U4 a = ldg128(pos + 3 * (size_t)t), b = ldg128(pos + 3 * (size_t)t + 1), c = ldg128(pos + 3 * (size_t)t + 2);
+                PackedTri pt;
+                pt.v0x = u2f(a.x); pt.v0y = u2f(a.y); pt.v0z = u2f(a.z); pt.prim = t;
+                pt.e1x = u2f(b.x) - u2f(a.x); pt.e1y = u2f(b.y) - u2f(a.y); pt.e1z = u2f(b.z) - u2f(a.z); pt.pad0 = 0;
+                pt.e2x = u2f(c.x) - u2f(a.x); pt.e2y = u2f(c.y) - u2f(a.y); pt.e2z = u2f(c.z) - u2f(a.z); pt.pad1 = 0;
+                tris[triBase + ti++] = pt;
+            }
+        }
+        else
+        {
+            CollapseWork c; c.bin = kid; c.wide = childBase + ci;
+            qOut[qBase + ci] = c;
+            ++ci;
+        }
+    }
+}
+
+template <class T>
+bool devAlloc(T*& p, size_t count)
+{
+    p = nullptr;
+    if (count == 0) count = 1;
+    return PT_CUDA(cudaMalloc((void**)&p, sizeof(T) * count));
+}
+
+} // namespace
+
+void freeBvh(BvhBuffers& b)
+{
+    if (b.nodes) cudaFree(b.nodes);
+    if (b.tris) cudaFree(b.tris);
+    b = BvhBuffers();
+}
+
+bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t stream)
+{
+    out = BvhBuffers();
+    if (n <= 0) return true;
+
+    const int total = 2 * n - 1;
+    F4 *leafLo = nullptr, *leafHi = nullptr, *lo = nullptr, *hi = nullptr;
+    int *bounds = nullptr, *first = nullptr, *last = nullptr, *parent = nullptr, *visits = nullptr;
+    uint64_t *keysA = nullptr, *keysB = nullptr;
+    uint32_t *valsA = nullptr, *valsB = nullptr, *hist = nullptr, *counters = nullptr;
+    CollapseWork *q0 = nullptr, *q1 = nullptr;
+    const int sortBlocks = (n + kSortTile - 1) / kSortTile;
+    bool ok = devAlloc(leafLo, n) && devAlloc(leafHi, n) && devAlloc(lo, total) && devAlloc(hi, total) &&
+              devAlloc(bounds, 12) && devAlloc(first, total) && devAlloc(last, total) && devAlloc(parent, total) &&
+              devAlloc(visits, n) && devAlloc(keysA, n) && devAlloc(keysB, n) && devAlloc(valsA, n) &&
+              devAlloc(valsB, n) && devAlloc(hist, (size_t)256 * sortBlocks) && devAlloc(counters, 4) &&
+              devAlloc(q0, n) && devAlloc(q1, n) && devAlloc(out.nodes, n) && devAlloc(out.tris, n);
+    const int blocks = (n + 255) / 256;
+    if (ok)
+    {
+        k_initBounds<<<1, 32, 0, stream>>>(bounds);
+        k_triBounds<<<blocks, 256, 0, stream>>>(dPositions, n, leafLo, leafHi, bounds);
+        k_morton<<<blocks, 256, 0, stream>>>(leafLo, leafHi, n, bounds, keysA, valsA);
+        g_counters.kernelLaunches += 3;
+        uint64_t* kin = keysA; uint64_t* kout = keysB;
+        uint32_t* vin = valsA; uint32_t* vout = valsB;
+        for (int pass = 0; pass < 8; ++pass)
+        {
+            const int shift = pass * 8;
+            k_sortHist<<<sortBlocks, kSortThreads, 0, stream>>>(kin, n, shift, hist, sortBlocks);
+            k_sortScan<<<1, 1024, 0, stream>>>(hist, 256 * sortBlocks);
+            k_sortScatter<<<sortBlocks, kSortThreads, 0, stream>>>(kin, vin, n, shift, hist, sortBlocks, kout, vout);
+            g_counters.kernelLaunches += 3;
+            std::swap(kin, kout);
+            std::swap(vin, vout);
+        }
+        // 8 passes: result is back in keysA / valsA
+        ok = ok && PT_CUDA(cudaMemsetAsync(parent, 0xff, sizeof(int) * total, stream));
+        ok = ok && PT_CUDA(cudaMemsetAsync(visits, 0, sizeof(int) * n, stream));
+        if (n > 1) k_radixTree<<<(n - 1 + 255) / 256, 256, 0, stream>>>(kin, n, lo, hi, first, last, parent);
+        k_leafInit<<<blocks, 256, 0, stream>>>(vin, leafLo, leafHi, n, lo, hi, first, last);
+        if (n > 1) k_refit<<<blocks, 256, 0, stream>>>(n, lo, hi, parent, visits);
+        g_counters.kernelLaunches += 3;
+
+        // breadth-first collapse; the root wide node is index 0
+        CollapseWork root; root.bin = (n == 1) ? 0 : 0; root.wide = 0;
+        uint32_t initCounters[4] = { 1u, 0u, 0u, 0u };
+        ok = ok && PT_CUDA(cudaMemcpyAsync(q0, &root, sizeof(root), cudaMemcpyHostToDevice, stream));
+        ok = ok && PT_CUDA(cudaMemcpyAsync(counters, initCounters, sizeof(initCounters), cudaMemcpyHostToDevice, stream));
+        BinTree T; T.lo = lo; T.hi = hi; T.first = first; T.last = last; T.n = n;
+        int levelCount = 1;
+        CollapseWork* qin = q0; CollapseWork* qout = q1;
+        while (ok && levelCount > 0)
+        {
+            k_collapse<<<(levelCount + 127) / 128, 128, 0, stream>>>(T, qin, levelCount, qout, counters, vin,
+                                                                     dPositions, out.nodes, out.tris);
+            g_counters.kernelLaunches += 1;
+            uint32_t h[4];
+            ok = ok && PT_CUDA(cudaMemcpyAsync(h, counters, sizeof(h), cudaMemcpyDeviceToHost, stream));
+            ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
+            levelCount = (int)h[2];
+            out.nodeCount = (int32_t)h[0];
+            out.triCount = (int32_t)h[1];
+            ok = ok && PT_CUDA(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), stream));
+            std::swap(qin, qout);
+        }
+        int hb[12];
+        ok = ok && PT_CUDA(cudaMemcpyAsync(hb, bounds, sizeof(hb), cudaMemcpyDeviceToHost, stream));
+        ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
+        if (ok)
+        {
+            for (int k = 0; k < 3; ++k)
+            {
+                int a = hb[6 + k], b = hb[9 + k];
+                union { int i; float f; } ua, ub;
+                ua.i = (a >= 0) ? a : (a ^ 0x7fffffff);
+                ub.i = (b >= 0) ? b : (b ^ 0x7fffffff);
+                out.sceneLo[k] = ua.f; out.sceneHi[k] = ub.f;
+            }
+        }
+    }
+    cudaFree(leafLo); cudaFree(leafHi); cudaFree(lo); cudaFree(hi); cudaFree(bounds);
+    cudaFree(first); cudaFree(last); cudaFree(parent); cudaFree(visits);
+    cudaFree(keysA); cudaFree(keysB); cudaFree(valsA); cudaFree(valsB); cudaFree(hist); cudaFree(counters);
+    cudaFree(q0); cudaFree(q1);
+    if (!ok) freeBvh(out);
+    return ok;
+}
+
+} // namespace pt

@@ -1,0 +1,151 @@
+// pt_device.h — host-side objects of libpimpt.so and the launch functions each
+// .cu file exports to the C-ABI layer (api.cu).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "integrator.h"
+
+namespace pt {
+
+void setError(const char* fmt, ...);
+bool cudaOk(cudaError_t e, const char* what);
+#define PT_CUDA(call) ::pt::cudaOk((call), #call)
+
+struct LibCounters
+{
+    unsigned long long paths, rays, occlusionRays, kernelLaunches, iterations;
+};
+extern LibCounters g_counters;
+
+constexpr int kSmCount = 148;           // B200: 2 dies x 74 SMs
+
+// ------------------------------------------------------------------ BVH build
+struct BvhBuffers
+{
+    WideNode* nodes = nullptr;
+    PackedTri* tris = nullptr;
+    int32_t nodeCount = 0;
+    int32_t triCount = 0;
+    float sceneLo[3] = { 0, 0, 0 }, sceneHi[3] = { 0, 0, 0 };   // bounds of all vertices
+};
+// positions: device float4[3*triCount]. Allocates nodes/tris with cudaMalloc.
+bool buildBvh(const F4* dPositions, int32_t triCount, BvhBuffers& out, cudaStream_t stream);
+void freeBvh(BvhBuffers& b);
+
+// ---------------------------------------------------------------- ray batches
+struct RayHitOut      // PtRayHit, 48 bytes
+{
+    float w, u, v, t;
+    float nx, ny, nz, nw;
+    int32_t type, iVert;
+    uint32_t flags, pad;
+};
+bool launchIntersect(const DScene& S, const F4* dRo, const F4* dRd, float tNear, RayHitOut* dOut, int64_t n,
+                     cudaStream_t stream);
+bool launchOccluded(const DScene& S, const F4* dRo, const F4* dRd, float tNear, uint8_t* dOut, int64_t n,
+                    cudaStream_t stream);
+// counting variant for the bytes-per-ray roofline: returns total node / triangle fetches
+bool launchIntersectCount(const DScene& S, const F4* dRo, const F4* dRd, float tNear, int64_t n,
+                          unsigned long long* nodesOut, unsigned long long* trisOut, cudaStream_t stream);
+
+// ---------------------------------------------------------------- scene build
+struct EntityUpload
+{
+    float M[16];        // local to world (column major)
+    float IM[9];        // inverse transpose of the upper 3x3 (column major)
+    int32_t vertOffset;
+    int32_t length;
+    int32_t srcOffset;  // into the concatenated source mesh arrays
+    int32_t pad;
+};
+bool launchFlatten(const EntityUpload* dEntities, int32_t entityCount, const F4* dSrcPos, const F4* dSrcNrm,
+                   const F4* dSrcUv, F4* dPos, F4* dNrm, V2* dUv, int32_t* dMatIds, int32_t vertCount,
+                   cudaStream_t stream);
+bool launchEmissionPdf(const DScene& S, int32_t triCount, uint32_t seed, float* dPdfOut, cudaStream_t stream);
+bool launchLightGrid(const DScene& S, float ptDistMeters, uint32_t seed, cudaStream_t stream);
+bool launchDistUpdate(const DScene& S, cudaStream_t stream);
+bool launchBrdfLutBake(float* dLut, int32_t w, int32_t h, int32_t samples, uint32_t seed, cudaStream_t stream);
+
+// ------------------------------------------------------------------ wavefront
+struct PathPool
+{
+    int32_t capacity = 0;
+    // path state, one entry per slot
+    U4* rng = nullptr;
+    F4* ro = nullptr;       // xyz origin, w = weight
+    F4* rd = nullptr;       // xyz direction, w = bits: bounce | prevFlags<<16
+    F4* atten = nullptr;    // xyz attenuation, w = bits: work item index
+    F4* lum = nullptr;      // xyz luminance
+    F4* albedo = nullptr;   // xyz albedo accumulator
+    F4* normal = nullptr;   // xyz normal accumulator
+    U4* hit1 = nullptr;     // t, u, v (float bits), iVert | type<<30
+    F4* ro2 = nullptr;      // secondary ray origin, w = tFar
+    F4* rd2 = nullptr;      // secondary ray direction, w = bits: kind | iVertLight<<2
+    F4* pend = nullptr;     // Pending.a0..a3
+    U4* hit2 = nullptr;
+    // queues of slot indices + counters
+    int32_t* queueA = nullptr;   // paths to extend
+    int32_t* queueB = nullptr;   // paths between stage A and stage B
+    int32_t* queueNext = nullptr;
+    int32_t* freeList = nullptr;
+    int32_t* freeNext = nullptr;
+    int32_t* counters = nullptr; // device: see WfCounter
+    int32_t* hostCounters = nullptr; // pinned mirror ring
+    void* all = nullptr;
+};
+enum WfCounter : int
+{
+    Wf_NumA = 0, Wf_NumB, Wf_NumNext, Wf_NumFree, Wf_NumFreeNext, Wf_WorkCursor, Wf_WorkTotal,
+    Wf_Rays, Wf_Paths, Wf_COUNT = 16
+};
+bool poolAlloc(PathPool& pool, int32_t capacity);
+void poolFree(PathPool& pool);
+
+enum WorkKind : int { Work_Camera = 0, Work_Rays = 1, Work_Sphere = 2 };
+
+struct WorkDesc
+{
+    int32_t kind;
+    CamParams cam;          // Work_Camera: work item = sample * (w*h) + pixel
+    const F4* ro;           // Work_Rays: explicit rays, one path per item
+    const F4* rd;
+    V3 origin;              // Work_Sphere: Pt_RayGen, uniform sphere directions from origin
+    int64_t count;          // total work items
+    uint32_t passBase;      // RNG pass of sample 0
+    uint32_t seed;
+    uint32_t salt;
+    // outputs
+    float* sumColor;        // Work_Camera: += per pixel (3 floats); else per item (3 floats)
+    float* sumAlbedo;
+    float* sumNormal;
+    F4* directions;         // Work_Sphere: generated directions per item
+    int32_t accumulate;     // 1: atomicAdd into sums (camera), 0: store per item
+};
+// Runs all work items to completion through the wavefront; blocking on `stream`.
+bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStream_t stream, float* kernelMsOut);
+
+// one thread per path, whole path in the thread (small batches, bake)
+bool launchTraceRays(const DScene& S, const F4* dRo, const F4* dRd, int64_t n, uint32_t pass, uint32_t seed,
+                     float* dOut9, cudaStream_t stream);
+
+struct LightmapView
+{
+    F4* probes[5];
+    const float* position;   // float3
+    const float* normal;     // float3
+    float* sampleCounts;
+    int32_t texelCount;
+    int32_t texelBase;       // global work index of texel 0 (for seeding)
+};
+bool launchLightmapBake(const DScene& S, const LightmapView& lm, float metersPerTexel, float timeSlice, int32_t spp,
+                        uint32_t pass, uint32_t seed, cudaStream_t stream);
+
+// image helpers
+bool launchResolve(float* dImage, const float* dSum, int64_t n, float prevCount, float addCount, cudaStream_t stream);
+bool launchLerp(float* dImage, const float* dSample, int64_t n, float weight, cudaStream_t stream);
+
+} // namespace pt

@@ -1,0 +1,416 @@
+// scene.cu — scene-build kernels and ray-batch kernels.
+//
+//   K3  closestHit      Pt_Intersect over a ray batch (path_tracer.c:1466-1474)
+//   K4  anyHit          RtcOccluded16 over a ray batch (path_tracer.c:524-553)
+//   K0  flatten         FlattenDrawables (path_tracer.c:692-782)
+//   K9  emissionPdf     CalcEmissionPdfFn / EmissionPdf (path_tracer.c:784-843)
+//   K10 lightGrid       SetupLightGridFn (path_tracer.c:891-990): point query,
+//                       16 probe rays, cells x emissives x 16 occlusion rays,
+//                       then Dist1D_Bake (dist1d.c:33-73)
+//   K11 distUpdate      Dist1D_Update (dist1d.c:128-163) per cell
+//       brdfLutBake     BakeBrdfFn (src/math/lighting.c:31-86)
+#include "pt_device.h"
+#include "kernels_common.cuh"
+
+namespace pt {
+
+// ---------------------------------------------------------------- ray batches
+
+__global__ void __launch_bounds__(kTravThreads) k_closestHit(DScene S, const F4* __restrict__ ro,
+                                                              const F4* __restrict__ rd, float tNear,
+                                                              RayHitOut* __restrict__ out, int64_t n)
+{
+    PT_DECLARE_STACK(st);
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    U4 o = ldg128(ro + i), d = ldg128(rd + i);
+    V3 dir = v3(u2f(d.x), u2f(d.y), u2f(d.z));
+    RayHit h = intersectLocal(S, v3(u2f(o.x), u2f(o.y), u2f(o.z)), dir, tNear, u2f(d.w), st);
+    // PtRayHit is 48 bytes: three 128-bit stores
+    U4* dst = reinterpret_cast<U4*>(out + i);
+    U4 a; a.x = f2u(h.w); a.y = f2u(h.u); a.z = f2u(h.v); a.w = f2u(h.t);
+    U4 b; b.x = f2u(h.normal.x); b.y = f2u(h.normal.y); b.z = f2u(h.normal.z); b.w = 0;
+    U4 c; c.x = (uint32_t)h.type; c.y = (uint32_t)h.iVert; c.z = h.flags; c.w = 0;
+    dst[0] = a; dst[1] = b; dst[2] = c;
+}
+
+__global__ void __launch_bounds__(kTravThreads) k_anyHit(DScene S, const F4* __restrict__ ro,
+                                                          const F4* __restrict__ rd, float tNear,
+                                                          uint8_t* __restrict__ out, int64_t n)
+{
+    PT_DECLARE_STACK(st);
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    U4 o = ldg128(ro + i), d = ldg128(rd + i);
+    Hit hit;
+    bool occ = traverse<true, false>(S.bvh, v3(u2f(o.x), u2f(o.y), u2f(o.z)), v3(u2f(d.x), u2f(d.y), u2f(d.z)),
+                                     tNear, u2f(d.w), hit, st, (TravCounters*)nullptr);
+    out[i] = occ ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(kTravThreads) k_closestHitCount(DScene S, const F4* __restrict__ ro,
+                                                                   const F4* __restrict__ rd, float tNear, int64_t n,
+                                                                   unsigned long long* totals)
+{
+    PT_DECLARE_STACK(st);
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    TravCounters c; c.nodes = 0; c.tris = 0;
+    if (i < n)
+    {
+        U4 o = ldg128(ro + i), d = ldg128(rd + i);
+        Hit hit;
+        traverse<false, true>(S.bvh, v3(u2f(o.x), u2f(o.y), u2f(o.z)), v3(u2f(d.x), u2f(d.y), u2f(d.z)), tNear,
+                              u2f(d.w), hit, st, &c);
+    }
+    uint32_t nodes = c.nodes, tris = c.tris;
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        nodes += __shfl_xor_sync(0xffffffffu, nodes, o);
+        tris += __shfl_xor_sync(0xffffffffu, tris, o);
+    }
+    if ((threadIdx.x & 31) == 0)
+    {
+        atomicAdd(&totals[0], (unsigned long long)nodes);
+        atomicAdd(&totals[1], (unsigned long long)tris);
+    }
+}
+
+static inline unsigned gridFor(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+bool launchIntersect(const DScene& S, const F4* dRo, const F4* dRd, float tNear, RayHitOut* dOut, int64_t n,
+                     cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    k_closestHit<<<gridFor(n, kTravThreads), kTravThreads, 0, stream>>>(S, dRo, dRd, tNear, dOut, n);
+    g_counters.kernelLaunches++;
+    g_counters.rays += (unsigned long long)n;
+    return PT_CUDA(cudaGetLastError());
+}
+
+bool launchOccluded(const DScene& S, const F4* dRo, const F4* dRd, float tNear, uint8_t* dOut, int64_t n,
+                    cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    k_anyHit<<<gridFor(n, kTravThreads), kTravThreads, 0, stream>>>(S, dRo, dRd, tNear, dOut, n);
+    g_counters.kernelLaunches++;
+    g_counters.occlusionRays += (unsigned long long)n;
+    return PT_CUDA(cudaGetLastError());
+}
+
+bool launchIntersectCount(const DScene& S, const F4* dRo, const F4* dRd, float tNear, int64_t n,
+                          unsigned long long* nodesOut, unsigned long long* trisOut, cudaStream_t stream)
+{
+    unsigned long long* dTotals = nullptr;
+    if (!PT_CUDA(cudaMalloc((void**)&dTotals, 16))) return false;
+    bool ok = PT_CUDA(cudaMemsetAsync(dTotals, 0, 16, stream));
+    if (ok && n > 0)
+    {
+        k_closestHitCount<<<gridFor(n, kTravThreads), kTravThreads, 0, stream>>>(S, dRo, dRd, tNear, n, dTotals);
+        g_counters.kernelLaunches++;
+    }
+    unsigned long long h[2] = { 0, 0 };
+    ok = ok && PT_CUDA(cudaMemcpyAsync(h, dTotals, 16, cudaMemcpyDeviceToHost, stream));
+    ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
+    cudaFree(dTotals);
+    *nodesOut = h[0]; *trisOut = h[1];
+    return ok;
+}
+
+// -------------------------------------------------------------------- flatten
+
+__global__ void __launch_bounds__(256) k_flatten(const EntityUpload* __restrict__ ents, int entityCount,
+                                                 const F4* __restrict__ srcPos, const F4* __restrict__ srcNrm,
+                                                 const F4* __restrict__ srcUv, F4* __restrict__ pos,
+                                                 F4* __restrict__ nrm, V2* __restrict__ uv,
+                                                 int32_t* __restrict__ matIds, int vertCount)
+{
+    int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= vertCount) return;
+    // entity whose [vertOffset, vertOffset+length) holds v
+    int lo = 0, hi = entityCount - 1;
+    while (lo < hi)
+    {
+        int mid = (lo + hi + 1) >> 1;
+        if (ents[mid].vertOffset <= v) lo = mid; else hi = mid - 1;
+    }
+    const EntityUpload& e = ents[lo];
+    int j = v - e.vertOffset;
+    U4 p = ldg128(srcPos + e.srcOffset + j), nn = ldg128(srcNrm + e.srcOffset + j), t = ldg128(srcUv + e.srcOffset + j);
+    const float* M = e.M;
+    // f4x4_mul_pt: (c0*x + c1*y) + (c2*z + c3)
+    float px = u2f(p.x), py = u2f(p.y), pz = u2f(p.z);
+    F4 wp;
+    wp.x = (M[0] * px + M[4] * py) + (M[8] * pz + M[12]);
+    wp.y = (M[1] * px + M[5] * py) + (M[9] * pz + M[13]);
+    wp.z = (M[2] * px + M[6] * py) + (M[10] * pz + M[14]);
+    wp.w = (M[3] * px + M[7] * py) + (M[11] * pz + M[15]);
+    pos[v] = wp;
+    // f3x3_mul_col: c0*x + (c1*y + c2*z), then f4_normalize3
+    const float* I = e.IM;
+    float nx = u2f(nn.x), ny = u2f(nn.y), nz = u2f(nn.z);
+    V3 wn = v3(I[0] * nx + (I[3] * ny + I[6] * nz), I[1] * nx + (I[4] * ny + I[7] * nz),
+               I[2] * nx + (I[5] * ny + I[8] * nz));
+    wn = normalize(wn);
+    nrm[v] = f4(wn, 0.0f);
+    // uvs are copied per whole triangle (path_tracer.c:755-766)
+    int tri = j / 3;
+    V2 tuv = v2(0.0f, 0.0f);
+    if (tri * 3 + 3 <= e.length) tuv = v2(u2f(t.x), u2f(t.y));
+    uv[v] = tuv;
+    matIds[v] = lo;
+}
+
+bool launchFlatten(const EntityUpload* dEntities, int32_t entityCount, const F4* dSrcPos, const F4* dSrcNrm,
+                   const F4* dSrcUv, F4* dPos, F4* dNrm, V2* dUv, int32_t* dMatIds, int32_t vertCount,
+                   cudaStream_t stream)
+{
+    if (vertCount <= 0) return true;
+    k_flatten<<<gridFor(vertCount, 256), 256, 0, stream>>>(dEntities, entityCount, dSrcPos, dSrcNrm, dSrcUv, dPos,
+                                                           dNrm, dUv, dMatIds, vertCount);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+// --------------------------------------------------------------- emission pdf
+
+__global__ void __launch_bounds__(128) k_emissionPdf(DScene S, int triCount, uint32_t seed, float* __restrict__ pdfs)
+{
+    int tri = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tri >= triCount) return;
+    const int iVert = tri * 3;
+    const DMaterial& mat = S.materials[S.matIds[iVert]];
+    if (mat.flags & MatFlag_Sky) { pdfs[tri] = 1.0f; return; }
+    if (mat.rome < 0) { pdfs[tri] = 0.0f; return; }
+    const DTexture tex = S.textures[mat.rome];
+    const V2 UA = S.uvs[iVert], UB = S.uvs[iVert + 1], UC = S.uvs[iVert + 2];
+    Rng rng = seed_prng((uint32_t)tri, 0u, seed, Salt_Emission);
+    const int attempts = 1000;
+    int hits = 0;
+    for (int i = 0; i < attempts; ++i)
+    {
+        V3 wuv = SampleBaryCoord(rng_f2(rng));
+        V2 uv = v2((UA.x * wuv.x + UB.x * wuv.y) + UC.x * wuv.z, (UA.y * wuv.x + UB.y * wuv.y) + UC.y * wuv.z);
+        int cx = PointWrap1D(tex.w, uv.x), cy = PointWrap1D(tex.h, uv.y);
+        uint32_t sample = tex.texels[tex.w * cy + cx] >> 24;
+        hits += sample ? 1 : 0;
+    }
+    pdfs[tri] = (float)hits / (float)attempts;
+}
+
+bool launchEmissionPdf(const DScene& S, int32_t triCount, uint32_t seed, float* dPdfOut, cudaStream_t stream)
+{
+    if (triCount <= 0) return true;
+    k_emissionPdf<<<gridFor(triCount, 128), 128, 0, stream>>>(S, triCount, seed, dPdfOut);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+// ----------------------------------------------------------------- light grid
+
+__device__ void distBake(const DScene& S, int cell)      // Dist1D_Bake, dist1d.c:33-73
+{
+    const int pdfLen = S.emissiveCount;
+    const int cdfLen = pdfLen + 1;
+    float* pdf = S.distPdf + (size_t)cell * pdfLen;
+    float* cdf = S.distCdf + (size_t)cell * cdfLen;
+    const float rcpLen = 1.0f / pdfLen;
+    cdf[0] = 0.0f;
+    for (int i = 1; i < cdfLen; ++i) cdf[i] = cdf[i - 1] + pdf[i - 1] * rcpLen;
+    float integral = cdf[cdfLen - 1];
+    if (integral == 0.0f)
+    {
+        for (int i = 1; i < cdfLen; ++i) cdf[i] = i * rcpLen;
+    }
+    else
+    {
+        float rcpIntegral = 1.0f / integral;
+        for (int i = 1; i < cdfLen; ++i) cdf[i] = cdf[i] * rcpIntegral;
+        for (int i = 0; i < pdfLen; ++i) pdf[i] = pdf[i] * rcpIntegral;
+    }
+}
+
+__global__ void __launch_bounds__(kTravThreads) k_lightGrid(DScene S, float metersPerCell, uint32_t seed)
+{
+    PT_DECLARE_STACK(st);
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= Grid_Len(S.grid)) return;
+    const float radius = metersPerCell * 0.666f;
+    const V3 position = Grid_Position(S.grid, cell);
+    S.distLength[cell] = 0;
+    S.distSum[cell] = 0;
+    {
+        float dist = pointQuery(S.bvh, position, radius + 0.01f * kMilli, st);
+        if (dist > radius)
+        {
+            // far from any surface: keep the cell only if most probe rays see front faces
+            float hitcount = 0.0f;
+            for (int j = 0; j < 16; ++j)
+            {
+                V3 dir = SampleUnitSphere(Hammersley2D((uint32_t)j, 16u));
+                RayHit hit = intersectLocal(S, position, dir, 0.0f, kRcpEpsilon, st);
+                if (hit.type == Hit_Triangle) hitcount += 1.0f;
+            }
+            if (hitcount / 16.0f < 0.5f) return;
+        }
+    }
+    const int E = S.emissiveCount;
+    if (E <= 0) return;
+    Rng rng = seed_prng((uint32_t)cell, 0u, seed, Salt_LightGrid);
+    float* pdf = S.distPdf + (size_t)cell * E;
+    uint32_t* live = S.distLive + (size_t)cell * E;
+    for (int iEmit = 0; iEmit < E; ++iEmit)
+    {
+        const int iVert = S.emitToVert[iEmit];
+        const V3 A = ld3(S.positions, iVert), B = ld3(S.positions, iVert + 1), C = ld3(S.positions, iVert + 2);
+        int hits = 0;
+        for (int k = 0; k < 16; ++k)
+        {
+            F4 r4 = rng_f4(rng);
+            V3 t = v3(-1.5f + r4.x * 3.0f, -1.5f + r4.y * 3.0f, -1.5f + r4.z * 3.0f) * radius;
+            V3 ro = position + t;
+            V3 wuv = SampleBaryCoord(rng_f2(rng));
+            V3 at = blend(A, B, C, wuv.x, wuv.y, wuv.z);
+            V3 rd = at - ro;
+            float dist = length(rd);
+            rd = rd / dist;
+            float tFar = dist - 0.01f * kMilli;
+            bool visible = false;
+            if (tFar > 0.0f)
+            {
+                Hit hit;
+                visible = !traverse<true, false>(S.bvh, ro, rd, 0.0f, tFar, hit, st, (TravCounters*)nullptr);
+            }
+            hits += visible ? 1 : 0;
+        }
+        pdf[iEmit] = (float)hits / 16.0f;
+        live[iEmit] = 0;
+    }
+    distBake(S, cell);
+    S.distLength[cell] = E;
+}
+
+bool launchLightGrid(const DScene& S, float ptDistMeters, uint32_t seed, cudaStream_t stream)
+{
+    int cells = Grid_Len(S.grid);
+    if (cells <= 0) return true;
+    k_lightGrid<<<gridFor(cells, kTravThreads), kTravThreads, 0, stream>>>(S, ptDistMeters, seed);
+    g_counters.kernelLaunches++;
+    g_counters.occlusionRays += (unsigned long long)cells * (unsigned long long)S.emissiveCount * 16ull;
+    return PT_CUDA(cudaGetLastError());
+}
+
+__global__ void __launch_bounds__(128) k_distUpdate(DScene S)     // Dist1D_Update, dist1d.c:128-163
+{
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= Grid_Len(S.grid)) return;
+    const int pdfLen = S.distLength[cell];
+    if (pdfLen <= 0) return;
+    float* pdf = S.distPdf + (size_t)cell * pdfLen;
+    uint32_t* live = S.distLive + (size_t)cell * pdfLen;
+    uint32_t sum = 0;
+    for (int i = 0; i < pdfLen; ++i) sum += live[i];
+    if (sum < 30) return;
+    const float scale = 1.0f / sum;
+    const uint32_t prevSum = S.distSum[cell];
+    S.distSum[cell] = sum;
+    float alpha = 0.5f;
+    if (prevSum > 0)
+    {
+        double ratio = (double)sum / (double)prevSum;
+        alpha = f1_sat((float)ratio) * 0.9f;
+        alpha = alpha * alpha;
+    }
+    for (int i = 0; i < pdfLen; ++i)
+    {
+        uint32_t ct = live[i];
+        pdf[i] = f1_lerp(pdf[i], ct * scale, alpha);
+        live[i] = ct >> 1;
+    }
+    distBake(S, cell);
+}
+
+bool launchDistUpdate(const DScene& S, cudaStream_t stream)
+{
+    int cells = Grid_Len(S.grid);
+    if (cells <= 0 || S.emissiveCount <= 0) return true;
+    k_distUpdate<<<gridFor(cells, 128), 128, 0, stream>>>(S);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------- BRDF LUT
+
+__global__ void __launch_bounds__(128) k_brdfLut(float* __restrict__ texels, int w, int h, int numSamples, uint32_t seed)
+{
+    const int iTexel = blockIdx.x * blockDim.x + threadIdx.x;
+    if (iTexel >= w * h) return;
+    const int cx = iTexel % w, cy = iTexel / w;
+    const float dx = 1.0f / numSamples;
+    const float rcpWidth = 1.0f / w, rcpHeight = 1.0f / h;
+    Rng rng = seed_prng((uint32_t)iTexel, 0u, seed, Salt_Lut);
+    float rx = 0.0f, ry = 0.0f;
+    for (int iSample = 0; iSample < numSamples; ++iSample)
+    {
+        V2 aa = SampleGaussPixelFilter(rng_f2(rng), 0.5f);
+        const float NoV = f1_clamp((cx + aa.x) * rcpWidth, kEpsilon, 1.0f - kEpsilon);
+        const float alpha = f1_clamp((cy + aa.y) * rcpHeight, kMinAlpha, 1.0f);
+        const V3 V = SphericalToCartesian(NoV, rng_f32(rng) * kTau);
+        V3 H = SampleGGXMicrofacet(rng_f2(rng), alpha);
+        V3 L = reflect(-V, H);
+        float NoL = L.z, NoH = H.z, HoV = dot(H, V);
+        float pdf = GGXPdf(NoH, HoV, alpha);
+        if ((NoL > kEpsilon) && (pdf > kEpsilon))
+        {
+            float D = D_GTR(NoH, alpha) / pdf;
+            float G = V_SmithCorrelated(NoL, NoV, alpha);
+            float Fc = F_Dielectric(HoV, 1.000293f, 1.52f);
+            float DG_NoL_dx = D * G * NoL * dx;
+            rx += DG_NoL_dx * Fc;
+            ry += DG_NoL_dx;
+        }
+    }
+    texels[2 * iTexel] = rx;
+    texels[2 * iTexel + 1] = ry;
+}
+
+bool launchBrdfLutBake(float* dLut, int32_t w, int32_t h, int32_t samples, uint32_t seed, cudaStream_t stream)
+{
+    k_brdfLut<<<gridFor((int64_t)w * h, 128), 128, 0, stream>>>(dLut, w, h, samples, seed);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+// -------------------------------------------------------------------- images
+
+__global__ void __launch_bounds__(256) k_resolve(float* __restrict__ image, const float* __restrict__ sum, int64_t n,
+                                                 float prevCount, float addCount)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    image[i] = (image[i] * prevCount + sum[i]) / (prevCount + addCount);
+}
+__global__ void __launch_bounds__(256) k_lerp(float* __restrict__ image, const float* __restrict__ sample, int64_t n,
+                                              float weight)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float a = image[i];
+    image[i] = a + (sample[i] - a) * weight;      // f3_lerpvs, path_tracer.c:2550-2552
+}
+
+bool launchResolve(float* dImage, const float* dSum, int64_t n, float prevCount, float addCount, cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    k_resolve<<<gridFor(n, 256), 256, 0, stream>>>(dImage, dSum, n, prevCount, addCount);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+bool launchLerp(float* dImage, const float* dSample, int64_t n, float weight, cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    k_lerp<<<gridFor(n, 256), 256, 0, stream>>>(dImage, dSample, n, weight);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+} // namespace pt

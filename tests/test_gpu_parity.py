@@ -1,0 +1,188 @@
+"""GPU parity tests: every call goes through the C ABI of libpimpt.so and is compared
+with the oracle (the reference's own path_tracer.c over the CPU BVH restatement) on the
+same seeded inputs, or with the committed golden fixtures the oracle produced."""
+import os
+
+import numpy as np
+import pytest
+
+import parity
+from pim_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+
+T_REL = 1e-5        # hit distance tolerance from BASELINE.json north_star
+AGREE = 0.9999      # hit/miss + primitive id agreement from north_star
+
+
+@pytest.fixture(scope="module")
+def api():
+    from pim_b200 import api as a
+    a.load()
+    return a
+
+
+@pytest.fixture(scope="module")
+def lut():
+    return parity.reference_lut()
+
+
+@pytest.fixture(scope="module")
+def boxes(api, lut):
+    desc = scenes.cornell_box("boxes", brdf_lut=lut, seed=1)
+    s = api.Scene(desc)
+    yield desc, s
+    s.close()
+
+
+@pytest.fixture(scope="module")
+def spheres(api, lut):
+    desc = scenes.cornell_box("spheres", brdf_lut=lut, seed=1)
+    s = api.Scene(desc)
+    yield desc, s
+    s.close()
+
+
+def _check_hits(got, want, exempt=None):
+    agree = parity.hit_agreement(got, want, exempt)
+    assert agree >= AGREE, "hit/primID agreement %.6f" % agree
+    both = (got["type"] != 0) & (want["type"] != 0) & (got["iVert"] == want["iVert"])
+    t0, t1 = got["wuvt"][both, 3], want["wuvt"][both, 3]
+    rel = np.abs(t0 - t1) / np.maximum(np.abs(t1), 1e-20)
+    assert rel.max() <= T_REL, "hit t relative error %.3g" % rel.max()
+    assert np.abs(got["wuvt"][both, :3] - want["wuvt"][both, :3]).max() < 1e-4
+    assert np.abs(got["normal"][both, :3] - want["normal"][both, :3]).max() < 1e-5
+    assert (got["flags"][both] == want["flags"][both]).all()
+
+
+# ------------------------------------------------------------------ scene build
+
+def test_flatten_matches_golden(boxes):
+    """FlattenDrawables + SetupEmissives on the device vs the reference's flattened arrays."""
+    _, s = boxes
+    g = np.load(os.path.join(parity.GOLDEN, "cornell_boxes_hits.npz"))
+    d = s.download()
+    assert d["positions"].shape == g["positions"].shape
+    assert np.abs(d["positions"][:, :3] - g["positions"][:, :3]).max() < 2e-6
+    assert np.abs(d["normals"][:, :3] - g["normals"][:, :3]).max() < 2e-6
+    assert np.abs(d["uvs"] - g["uvs"]).max() < 1e-7
+    assert (d["matIds"] == g["matIds"]).all()
+    assert (d["vertToEmit"] == g["vertToEmit"]).all()
+    assert (d["emitToVert"] == g["emitToVert"]).all()
+    assert tuple(g["grid"]) == s.grid_size
+
+
+def test_light_grid_matches_golden(boxes):
+    """SetupLightGridFn: same RNG stream as the oracle, so the k/16 visibility pdfs match."""
+    _, s = boxes
+    g = np.load(os.path.join(parity.GOLDEN, "cornell_boxes_64x36.npz"))
+    cells = int(np.prod(s.grid_size))
+    lens = np.zeros(cells, np.int32)
+    pdf = np.zeros_like(g["pdf"])
+    for c in range(cells):
+        n, p, cdf, _ = s.dist(c)
+        lens[c] = n
+        if n:
+            pdf[c] = p
+            assert abs(cdf[-1] - 1.0) < 1e-5 and (np.diff(cdf) >= 0).all()
+    assert (lens == g["lens"]).all()
+    # a visibility ray grazing an edge may flip one of 16 trials
+    close = np.abs(pdf - g["pdf"]) <= 1e-5
+    assert close.mean() >= 0.995, close.mean()
+
+
+def test_brdf_lut_device_bake(api):
+    """brdfLutBake (BakeBrdfFn arithmetic on the device) vs the reference-baked table."""
+    desc = scenes.cornell_box("boxes", brdf_lut=None, seed=1)
+    s = api.Scene(desc)
+    got, want = s.brdf_lut(), parity.reference_lut()
+    s.close()
+    assert got.shape == want.shape
+    assert np.abs(got - want).mean() < 2e-3
+    assert np.abs(got - want).max() < 5e-2
+
+
+# ----------------------------------------------------------------- intersection
+
+def test_intersect_matches_golden(boxes):
+    _, s = boxes
+    g = np.load(os.path.join(parity.GOLDEN, "cornell_boxes_hits.npz"))
+    _check_hits(s.intersect(g["ro"], g["rd"]), g["hits"])
+
+
+def test_intersect_matches_oracle_and_brute_force(spheres, oracle):
+    desc, s = spheres
+    oracle.load_scene_desc(desc)
+    ref = oracle.Scene()
+    ro, rd = parity.box_rays(200000, seed=7)
+    got = s.intersect(ro, rd)
+    want = ref.intersect(ro, rd)
+    sub = slice(0, 20000)
+    tuv, prim, flags = ref.brute(ro[sub], rd[sub])
+    ref.close()
+    ties = np.zeros(len(ro), bool)
+    ties[sub] = flags == 2
+    _check_hits(got, want, ties)
+    # against the fp64 all-triangles ground truth
+    hit = flags != 0
+    assert ((got["type"][sub] != 0) == hit).mean() >= AGREE
+    ok = hit & (got["iVert"][sub] == prim * 3)
+    assert (ok | (flags == 2) | ~hit).mean() >= AGREE
+    rel = np.abs(got["wuvt"][sub][ok, 3] - tuv[ok, 0]) / np.maximum(tuv[ok, 0], 1e-20)
+    assert rel.max() <= T_REL
+
+
+def test_intersect_edge_cases(boxes, api):
+    _, s = boxes
+    assert len(s.intersect(np.zeros((0, 4), np.float32), np.zeros((0, 4), np.float32))) == 0
+    # tFar shorter than the first surface -> miss; axis-parallel rays stay finite
+    ro = np.array([[0, 0, 0, 0], [0, 0, 0, 0], [0, 0, 0, 0]], np.float32)
+    rd = np.array([[1, 0, 0, 0.5], [1, 0, 0, 100.0], [0, -1, 0, 100.0]], np.float32)
+    h = s.intersect(ro, rd)
+    assert h["type"][0] == 0 and h["iVert"][0] == -1
+    assert h["type"][1] != 0 and abs(h["wuvt"][1, 3] - 4.95) < 1e-4
+    assert h["type"][2] != 0 and np.isfinite(h["wuvt"][2]).all()
+    one = api.load().Pt_Intersect(s.h, api._f4([0, 0, 0]), api._f4([1, 0, 0]), 0.0, 100.0)
+    assert one.iVert == h["iVert"][1] and abs(one.wuvt.w - h["wuvt"][1, 3]) < 1e-6
+
+
+def test_occluded_matches_closest_hit(spheres):
+    """any-hit (RtcOccluded16 semantics) is consistent with closest hit on the same segments"""
+    _, s = spheres
+    ro, rd = parity.box_rays(100000, seed=11)
+    rng = np.random.default_rng(5)
+    rd[:, 3] = rng.uniform(0.5, 8.0, len(rd))
+    occ = s.occluded(ro, rd)
+    hit = s.intersect(ro, rd)["type"] != 0
+    assert (occ.astype(bool) == hit).mean() >= AGREE
+
+
+def test_random_soup_1m_vs_brute_force(api, oracle):
+    """1M random triangles: GPU-built LBVH vs fp64 brute force on a ray subsample."""
+    desc = scenes.random_soup(1_000_000, seed=11)
+    s = api.Scene(desc)
+    ro, rd = scenes.random_rays(200000, seed=13)
+    got = s.intersect(ro, rd)
+    n = 800
+    verts = desc.entities[0].positions
+    import ctypes as C
+    lib = C.CDLL(oracle.ORACLE_SO)
+    lib.brute_intersect_f64.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p]
+
+    class CpuHit(C.Structure):
+        _fields_ = [("t", C.c_float), ("u", C.c_float), ("v", C.c_float), ("prim", C.c_int32), ("ng", C.c_float * 3)]
+    bad = 0
+    worst = 0.0
+    for i in range(n):
+        h = CpuHit()
+        r = lib.brute_intersect_f64(verts.ctypes.data, 4, len(verts) // 3, ro[i].ctypes.data, rd[i].ctypes.data,
+                                    0.0, float(rd[i, 3]), C.byref(h))
+        if r == 2:
+            continue
+        if (r != 0) != (got["type"][i] != 0) or (r and got["iVert"][i] != h.prim * 3):
+            bad += 1
+        elif r:
+            worst = max(worst, abs(got["wuvt"][i, 3] - h.t) / h.t)
+    s.close()
+    assert bad == 0, bad
+    assert worst <= T_REL
