@@ -263,6 +263,21 @@ void Pt_ResetCounters(void);
  * the library's stream (0 when events were not recorded) */
 float Pt_LastKernelMs(void);
 
+/* Per-kernel timing of the wavefront, measured with CUDA events on the launching
+ * stream while enabled (index: 0 regen, 1 extend, 2 shadeA, 3 connect, 4 shadeB). */
+typedef struct PtKernelStats_s
+{
+    double ms[5];
+    uint64_t launches[5];
+    uint64_t extendRays;     /* rays traced by the extend kernel */
+    uint64_t connectRays;    /* NEE / MIS rays traced by the connect kernel */
+} PtKernelStats;
+void Pt_SetKernelTiming(int32_t enable);   /* also clears the accumulated stats */
+void Pt_GetKernelStats(PtKernelStats* out);
+/* closest-hit batch that only counts wide-node and triangle fetches (bytes-per-ray bookkeeping) */
+int32_t Pt_IntersectCountN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd, float tNear,
+                           int64_t n, uint64_t* nodeFetches, uint64_t* triFetches);
+
 const char* Pt_LastError(void);
 
 #ifdef __cplusplus

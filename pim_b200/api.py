@@ -98,6 +98,13 @@ class PtCounters(C.Structure):
                 ("kernelLaunches", C.c_uint64), ("iterations", C.c_uint64)]
 
 
+class PtKernelStats(C.Structure):
+    _fields_ = [("ms", C.c_double * 5), ("launches", C.c_uint64 * 5), ("extendRays", C.c_uint64),
+                ("connectRays", C.c_uint64)]
+
+
+KERNEL_NAMES = ["regen", "extend", "shadeA", "connect", "shadeB"]
+
 HIT_DTYPE = np.dtype([("wuvt", np.float32, 4), ("normal", np.float32, 4), ("type", np.int32),
                       ("iVert", np.int32), ("flags", np.uint32), ("pad", np.uint32)])
 
@@ -108,6 +115,7 @@ EXPORTS = [
     "Pt_TraceSpp", "Pt_IntersectN_Device", "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc",
     "PtScene_GetStats", "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut",
     "Pt_GetCounters", "Pt_ResetCounters", "Pt_LastKernelMs", "Pt_LastError",
+    "Pt_SetKernelTiming", "Pt_GetKernelStats", "Pt_IntersectCountN",
 ]
 
 _lib = None
@@ -156,6 +164,10 @@ def load():
     L.PtScene_GetBrdfLut.argtypes = [vp, vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.Pt_GetCounters.argtypes = [C.POINTER(PtCounters)]
     L.Pt_LastKernelMs.restype = C.c_float
+    L.Pt_SetKernelTiming.argtypes = [C.c_int32]
+    L.Pt_GetKernelStats.argtypes = [C.POINTER(PtKernelStats)]
+    L.Pt_IntersectCountN.argtypes = [vp, vp, vp, C.c_float, C.c_int64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.Pt_IntersectCountN.restype = C.c_int32
     for name in ("Pt_IntersectN", "Pt_OccludedN", "Pt_TraceRayN", "Pt_TraceSpp", "Pt_IntersectN_Device",
                  "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc", "PtScene_GetStats",
                  "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut"):
@@ -202,6 +214,14 @@ def counters():
     c = PtCounters()
     load().Pt_GetCounters(C.byref(c))
     return {k: getattr(c, k) for k, _ in PtCounters._fields_}
+
+
+def kernel_stats():
+    k = PtKernelStats()
+    load().Pt_GetKernelStats(C.byref(k))
+    out = {n: {"ms": k.ms[i], "launches": k.launches[i]} for i, n in enumerate(KERNEL_NAMES)}
+    out["extendRays"], out["connectRays"] = k.extendRays, k.connectRays
+    return out
 
 
 class Scene:
@@ -317,6 +337,14 @@ class Scene:
         out = np.zeros(len(ro), np.uint8)
         _check(load().Pt_OccludedN(self.h, ro.ctypes.data, rd.ctypes.data, t_near, out.ctypes.data, len(ro)), "Pt_OccludedN")
         return out
+
+    def fetch_counts(self, ro, rd, t_near=0.0):
+        """(wide-node fetches, triangle fetches) summed over a closest-hit batch"""
+        ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)
+        a, b = C.c_uint64(), C.c_uint64()
+        _check(load().Pt_IntersectCountN(self.h, ro.ctypes.data, rd.ctypes.data, t_near, len(ro), C.byref(a), C.byref(b)),
+               "Pt_IntersectCountN")
+        return a.value, b.value
 
     def trace_rays(self, ro, rd, pass_index=0):
         ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)

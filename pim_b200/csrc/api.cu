@@ -866,6 +866,33 @@ void Pt_GetCounters(PtCounters* out)
     out->kernelLaunches = g_counters.kernelLaunches; out->iterations = g_counters.iterations;
 }
 void Pt_ResetCounters(void) { g_counters = LibCounters{ 0, 0, 0, 0, 0 }; }
+
+void Pt_SetKernelTiming(int32_t enable)
+{
+    g_kernelTiming = enable != 0;
+    memset(&g_kernelStats, 0, sizeof(g_kernelStats));
+}
+void Pt_GetKernelStats(PtKernelStats* out)
+{
+    if (!out) return;
+    for (int k = 0; k < 5; ++k) { out->ms[k] = g_kernelStats.ms[k]; out->launches[k] = g_kernelStats.launches[k]; }
+    out->extendRays = g_kernelStats.extendRays;
+    out->connectRays = g_kernelStats.connectRays;
+}
+int32_t Pt_IntersectCountN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd, float tNear, int64_t n,
+                           uint64_t* nodeFetches, uint64_t* triFetches)
+{
+    if (!scene || n <= 0) { setError("Pt_IntersectCountN: bad argument"); return -1; }
+    DevBuf dRo, dRd;
+    if (!dRo.alloc(sizeof(F4) * n) || !dRd.alloc(sizeof(F4) * n)) return -1;
+    cudaStream_t st = scene->stream;
+    unsigned long long a = 0, b = 0;
+    bool ok = PT_CUDA(cudaMemcpyAsync(dRo.p, ro, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
+              PT_CUDA(cudaMemcpyAsync(dRd.p, rd, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
+              launchIntersectCount(scene->view, (const F4*)dRo.p, (const F4*)dRd.p, tNear, n, &a, &b, st);
+    *nodeFetches = a; *triFetches = b;
+    return ok ? 0 : -1;
+}
 float Pt_LastKernelMs(void) { return g_lastKernelMs; }
 
 } // extern "C"

@@ -285,8 +285,27 @@ PT_D int popc32(uint32_t x) { return __builtin_popcount(x); }
 PT_D int ffs32(uint32_t x) { return __builtin_ffs((int)x) - 1; }
 #endif
 
-// two-sided Moller-Trumbore on a packed triangle; same arithmetic as
-// oracle/cpu_bvh.c tri_test so both sides agree on edge cases
+// Unfused arithmetic for the triangle test: the oracle's CPU code rounds every
+// multiply and add separately, so the kernel does too (no fma contraction) and both
+// sides take the same side of every edge / tFar comparison.
+#if defined(__CUDA_ARCH__)
+PT_D float mulr(float a, float b) { return __fmul_rn(a, b); }
+PT_D float addr(float a, float b) { return __fadd_rn(a, b); }
+PT_D float subr(float a, float b) { return __fsub_rn(a, b); }
+#else
+PT_D float mulr(float a, float b) { return a * b; }
+PT_D float addr(float a, float b) { return a + b; }
+PT_D float subr(float a, float b) { return a - b; }
+#endif
+PT_D float dotr(V3 a, V3 b) { return addr(addr(mulr(a.x, b.x), mulr(a.y, b.y)), mulr(a.z, b.z)); }
+PT_D V3 crossr(V3 a, V3 b)
+{
+    return v3(subr(mulr(a.y, b.z), mulr(a.z, b.y)), subr(mulr(a.z, b.x), mulr(a.x, b.z)),
+              subr(mulr(a.x, b.y), mulr(a.y, b.x)));
+}
+
+// two-sided Moller-Trumbore on a packed triangle; same arithmetic, in the same order,
+// as oracle/cpu_bvh.c tri_test
 PT_D bool triTest(const PackedTri* tp, V3 ro, V3 rd, float tNear, float tFar,
                   float& t, float& u, float& v, uint32_t& prim, V3& ng)
 {
@@ -294,20 +313,20 @@ PT_D bool triTest(const PackedTri* tp, V3 ro, V3 rd, float tNear, float tFar,
     V3 v0 = v3(u2f(a.x), u2f(a.y), u2f(a.z));
     V3 e1 = v3(u2f(b.x), u2f(b.y), u2f(b.z));
     V3 e2 = v3(u2f(c.x), u2f(c.y), u2f(c.z));
-    V3 p = cross(rd, e2);
-    float det = dot(e1, p);
+    V3 p = crossr(rd, e2);
+    float det = dotr(e1, p);
     if (det == 0.0f) return false;
     float inv = 1.0f / det;
-    V3 tv = ro - v0;
-    u = dot(tv, p) * inv;
+    V3 tv = v3(subr(ro.x, v0.x), subr(ro.y, v0.y), subr(ro.z, v0.z));
+    u = mulr(dotr(tv, p), inv);
     if (!(u >= 0.0f && u <= 1.0f)) return false;
-    V3 q = cross(tv, e1);
-    v = dot(rd, q) * inv;
-    if (!(v >= 0.0f && u + v <= 1.0f)) return false;
-    t = dot(e2, q) * inv;
+    V3 q = crossr(tv, e1);
+    v = mulr(dotr(rd, q), inv);
+    if (!(v >= 0.0f && addr(u, v) <= 1.0f)) return false;
+    t = mulr(dotr(e2, q), inv);
     if (!(t >= tNear && t <= tFar)) return false;
     prim = a.w;
-    ng = cross(e1, e2);
+    ng = crossr(e1, e2);
     return true;
 }
 

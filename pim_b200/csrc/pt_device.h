@@ -21,6 +21,16 @@ struct LibCounters
 };
 extern LibCounters g_counters;
 
+// per-kernel CUDA-event timing of the wavefront (bench.py's roofline numbers)
+struct KernelStats
+{
+    double ms[5];                    // regen, extend, shadeA, connect, shadeB
+    unsigned long long launches[5];
+    unsigned long long extendRays, connectRays;
+};
+extern bool g_kernelTiming;
+extern KernelStats g_kernelStats;
+
 constexpr int kSmCount = 148;           // B200: 2 dies x 74 SMs
 
 // ------------------------------------------------------------------ BVH build

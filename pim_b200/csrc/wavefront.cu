@@ -21,6 +21,9 @@
 
 namespace pt {
 
+bool g_kernelTiming = false;
+KernelStats g_kernelStats = {};
+
 namespace {
 
 struct PoolView
@@ -248,7 +251,11 @@ __global__ void __launch_bounds__(kTravThreads) k_wfShadeA(DScene S, PoolView P,
     warpAppend(toNext, slot, queueNext, &P.counters[Wf_NumNext]);
     warpAppend(dead, slot, P.freeList, &P.counters[Wf_NumFree]);
     const unsigned rmask = __ballot_sync(0xffffffffu, ray2);
-    if ((threadIdx.x & 31) == 0 && rmask) atomicAdd(&P.counters[Wf_Rays], __popc(rmask));
+    if ((threadIdx.x & 31) == 0 && rmask)
+    {
+        atomicAdd(&P.counters[Wf_Rays], __popc(rmask));
+        atomicAdd(&P.counters[Wf_Paths], __popc(rmask));
+    }
 }
 
 // K4'
@@ -321,6 +328,7 @@ __global__ void k_wfEndIteration(PoolView P, int32_t* status)
     status[0] = n;
     status[1] = (left > 0x7fffffffull) ? 0x7fffffff : (int32_t)left;
     status[2] = P.counters[Wf_Rays];
+    status[3] = P.counters[Wf_Paths];      // connect (NEE / MIS) rays so far
 }
 
 PoolView makeView(const PathPool& pool)
@@ -389,28 +397,52 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     // An upper bound on live paths per iteration is the pool capacity; grids are sized
     // for it and threads past the device-side counts exit at once.
     unsigned long long iterations = 0;
-    int32_t lastRays = 0;
+    int32_t lastRays = 0, lastConnect = 0;
+    const bool timing = g_kernelTiming;
+    cudaEvent_t ev[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
+    if (timing) for (int k = 0; ok && k < 6; ++k) ok = PT_CUDA(cudaEventCreate(&ev[k]));
     while (ok)
     {
         int32_t* queueA = q[parity];
         int32_t* queueNext = q[parity ^ 1];
+        if (timing) cudaEventRecord(ev[0], stream);
         k_wfRegen<<<gridCap, 128, 0, stream>>>(S, P, work, queueA);
         k_wfAfterRegen<<<1, 1, 0, stream>>>(P);
+        if (timing) cudaEventRecord(ev[1], stream);
         k_wfExtend<<<gridCap, kTravThreads, 0, stream>>>(S, P, queueA);
+        if (timing) cudaEventRecord(ev[2], stream);
         k_wfShadeA<<<gridCap, kTravThreads, 0, stream>>>(S, P, work, queueA, pool.queueB, queueNext);
+        if (timing) cudaEventRecord(ev[3], stream);
         k_wfConnect<<<gridCap, kTravThreads, 0, stream>>>(S, P, pool.queueB);
+        if (timing) cudaEventRecord(ev[4], stream);
         k_wfShadeB<<<gridCap, kTravThreads, 0, stream>>>(S, P, work, pool.queueB, queueNext);
+        if (timing) cudaEventRecord(ev[5], stream);
         k_wfEndIteration<<<1, 1, 0, stream>>>(P, dStatus);
         g_counters.kernelLaunches += 7;
         ++iterations;
-        ok = ok && PT_CUDA(cudaMemcpyAsync(pool.hostCounters, dStatus, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+        ok = ok && PT_CUDA(cudaMemcpyAsync(pool.hostCounters, dStatus, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
         ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
         if (!ok) break;
+        if (timing)
+        {
+            for (int k = 0; k < 5; ++k)
+            {
+                float ms = 0.0f;
+                cudaEventElapsedTime(&ms, ev[k], ev[k + 1]);
+                g_kernelStats.ms[k] += ms;
+                g_kernelStats.launches[k] += 1;
+            }
+            g_kernelStats.extendRays += (unsigned long long)(uint32_t)(pool.hostCounters[2] - lastRays) -
+                                        (unsigned long long)(uint32_t)(pool.hostCounters[3] - lastConnect);
+            g_kernelStats.connectRays += (unsigned long long)(uint32_t)(pool.hostCounters[3] - lastConnect);
+        }
         lastRays = pool.hostCounters[2];
+        lastConnect = pool.hostCounters[3];
         if (pool.hostCounters[0] == 0 && pool.hostCounters[1] == 0) break;
         parity ^= 1;
         if (iterations > 100000ull) { setError("runWavefront: iteration limit"); ok = false; }
     }
+    for (int k = 0; k < 6; ++k) if (ev[k]) cudaEventDestroy(ev[k]);
     ok = ok && PT_CUDA(cudaEventRecord(e1, stream));
     ok = ok && PT_CUDA(cudaEventSynchronize(e1));
     if (ok && kernelMsOut) cudaEventElapsedTime(kernelMsOut, e0, e1);
