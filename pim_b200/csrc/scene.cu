@@ -137,20 +137,22 @@ __global__ void __launch_bounds__(256) k_flatten(const EntityUpload* __restrict_
     int j = v - e.vertOffset;
     U4 p = ldg128(srcPos + e.srcOffset + j), nn = ldg128(srcNrm + e.srcOffset + j), t = ldg128(srcUv + e.srcOffset + j);
     const float* M = e.M;
-    // f4x4_mul_pt: (c0*x + c1*y) + (c2*z + c3)
+    // f4x4_mul_pt: (c0*x + c1*y) + (c2*z + c3), every product and sum rounded on its own
+    // (the reference's CPU code has no fused multiply-add), so vertices come out bit-equal
     float px = u2f(p.x), py = u2f(p.y), pz = u2f(p.z);
     F4 wp;
-    wp.x = (M[0] * px + M[4] * py) + (M[8] * pz + M[12]);
-    wp.y = (M[1] * px + M[5] * py) + (M[9] * pz + M[13]);
-    wp.z = (M[2] * px + M[6] * py) + (M[10] * pz + M[14]);
-    wp.w = (M[3] * px + M[7] * py) + (M[11] * pz + M[15]);
+    wp.x = addr(addr(mulr(M[0], px), mulr(M[4], py)), addr(mulr(M[8], pz), M[12]));
+    wp.y = addr(addr(mulr(M[1], px), mulr(M[5], py)), addr(mulr(M[9], pz), M[13]));
+    wp.z = addr(addr(mulr(M[2], px), mulr(M[6], py)), addr(mulr(M[10], pz), M[14]));
+    wp.w = addr(addr(mulr(M[3], px), mulr(M[7], py)), addr(mulr(M[11], pz), M[15]));
     pos[v] = wp;
     // f3x3_mul_col: c0*x + (c1*y + c2*z), then f4_normalize3
     const float* I = e.IM;
     float nx = u2f(nn.x), ny = u2f(nn.y), nz = u2f(nn.z);
-    V3 wn = v3(I[0] * nx + (I[3] * ny + I[6] * nz), I[1] * nx + (I[4] * ny + I[7] * nz),
-               I[2] * nx + (I[5] * ny + I[8] * nz));
-    wn = normalize(wn);
+    V3 wn = v3(addr(mulr(I[0], nx), addr(mulr(I[3], ny), mulr(I[6], nz))),
+               addr(mulr(I[1], nx), addr(mulr(I[4], ny), mulr(I[7], nz))),
+               addr(mulr(I[2], nx), addr(mulr(I[5], ny), mulr(I[8], nz))));
+    wn = wn / sqrtf(dotr(wn, wn));
     nrm[v] = f4(wn, 0.0f);
     // uvs are copied per whole triangle (path_tracer.c:755-766)
     int tri = j / 3;
@@ -265,13 +267,18 @@ __global__ void __launch_bounds__(kTravThreads) k_lightGrid(DScene S, float mete
         int hits = 0;
         for (int k = 0; k < 16; ++k)
         {
+            // ray setup without fused multiply-adds: same roundings as the reference's CPU code,
+            // so the any-hit decisions (and with them the k/16 pdfs) come out the same
             F4 r4 = rng_f4(rng);
-            V3 t = v3(-1.5f + r4.x * 3.0f, -1.5f + r4.y * 3.0f, -1.5f + r4.z * 3.0f) * radius;
-            V3 ro = position + t;
+            V3 t = v3(mulr(addr(-1.5f, mulr(r4.x, 3.0f)), radius), mulr(addr(-1.5f, mulr(r4.y, 3.0f)), radius),
+                      mulr(addr(-1.5f, mulr(r4.z, 3.0f)), radius));
+            V3 ro = v3(addr(position.x, t.x), addr(position.y, t.y), addr(position.z, t.z));
             V3 wuv = SampleBaryCoord(rng_f2(rng));
-            V3 at = blend(A, B, C, wuv.x, wuv.y, wuv.z);
-            V3 rd = at - ro;
-            float dist = length(rd);
+            V3 at = v3(addr(addr(mulr(A.x, wuv.x), mulr(B.x, wuv.y)), mulr(C.x, wuv.z)),
+                       addr(addr(mulr(A.y, wuv.x), mulr(B.y, wuv.y)), mulr(C.y, wuv.z)),
+                       addr(addr(mulr(A.z, wuv.x), mulr(B.z, wuv.y)), mulr(C.z, wuv.z)));
+            V3 rd = v3(subr(at.x, ro.x), subr(at.y, ro.y), subr(at.z, ro.z));
+            float dist = sqrtf(dotr(rd, rd));
             rd = rd / dist;
             float tFar = dist - 0.01f * kMilli;
             bool visible = false;

@@ -26,6 +26,14 @@ def lut():
     return parity.reference_lut()
 
 
+def _copy_grid(scene, pdf, lens):
+    """Give the device scene the oracle's light-grid pdfs, so that per-path comparisons test the
+    integrator alone (the device-built grid is checked on its own in test_gpu_parity.py)."""
+    for c in range(len(lens)):
+        if lens[c]:
+            scene.set_dist(c, pdf[c])
+
+
 def _cams(api, oracle=None):
     cam, dof = api.make_camera([-4, 0, 4], [0, -1, 0]), api.default_dof(auto_focus=False)
     if oracle is None:
@@ -39,6 +47,7 @@ def test_frame_matches_golden_per_path(api, lut):
     """Two reference-style frames (1 spp each, relearn between) vs the committed oracle frames."""
     g = np.load(os.path.join(parity.GOLDEN, "cornell_boxes_64x36.npz"))
     s = api.Scene(scenes.cornell_box("boxes", brdf_lut=lut, seed=1))
+    _copy_grid(s, g["pdf"], g["lens"])
     cam, dof = _cams(api)
     tr = api.Trace(64, 36)
     for p in range(2):
@@ -57,6 +66,9 @@ def test_frames_match_oracle_per_path(api, lut, oracle, variant):
     oracle.load_scene_desc(desc)
     ref = oracle.Scene()
     cam, dof, ocam, odof = _cams(api, oracle)
+    cells = int(np.prod(s.grid_size))
+    dists = [ref.dist(c) for c in range(cells)]
+    _copy_grid(s, [d[1] for d in dists], [d[0] for d in dists])
     W, H = 96, 54
     tr = api.Trace(W, H)
     for p in range(3):
@@ -66,8 +78,6 @@ def test_frames_match_oracle_per_path(api, lut, oracle, variant):
         frac = parity.path_agreement(tr.image("color"), col)
         assert frac >= (PATH_AGREE if variant == "boxes" else 0.98), (p, frac)
     # the adaptive light grid learned the same counters (integer atomics, order free)
-    E = s.stats.emissiveCount
-    cells = int(np.prod(s.grid_size))
     diff = tot = 0
     for c in range(0, cells, 7):
         n0, _, _, live0 = s.dist(c)
@@ -143,6 +153,9 @@ def test_trace_rays_match_oracle(api, lut, oracle):
     s = api.Scene(desc)
     oracle.load_scene_desc(desc)
     ref = oracle.Scene()
+    cells = int(np.prod(s.grid_size))
+    dists = [ref.dist(c) for c in range(cells)]
+    _copy_grid(s, [d[1] for d in dists], [d[0] for d in dists])
     for n in (1000, 20000):
         ro, rd = parity.box_rays(n, seed=21, extent=4.0)
         want = ref.trace_rays(ro, rd, 5)
@@ -157,6 +170,9 @@ def test_raygen_matches_oracle(api, lut, oracle):
     s = api.Scene(desc)
     oracle.load_scene_desc(desc)
     ref = oracle.Scene()
+    cells = int(np.prod(s.grid_size))
+    dists = [ref.dist(c) for c in range(cells)]
+    _copy_grid(s, [d[1] for d in dists], [d[0] for d in dists])
     want_c, want_d = ref.raygen([0, 0, 0, 0], 5000, 0)
     got_c, got_d = s.raygen([0, 0, 0, 0], 5000)
     assert np.abs(got_d - want_d).max() < 1e-5
