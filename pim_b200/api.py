@@ -13,7 +13,7 @@ import numpy as np
 from . import scenes
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpimpt.so")
+LIB_PATH = os.environ.get("PIMPT_LIB", os.path.join(HERE, "libpimpt.so"))   # PIMPT_LIB: tuning builds
 
 f32p = C.POINTER(C.c_float)
 

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpimpt.so")
-SOURCES = ["api.cu", "bvh_build.cu", "scene.cu", "wavefront.cu"]
+SOURCES = ["api.cu", "bvh_build.cu", "scene.cu", "wavefront.cu", "pathkernels.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
     "--ftz=true",                      # the reference runs with FTZ/DAZ (src/threading/task.c:73-74)
@@ -21,11 +21,14 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_library(force=False, verbose=False):
+def build_library(force=False, verbose=False, defines=(), lib=None, tag=""):
+    """Compile csrc/*.cu and link libpimpt.so. `defines`/`lib`/`tag` build tuning variants
+    (experiments only; the shipped library is the default build)."""
     nvcc = os.environ.get("NVCC", "nvcc")
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(os.path.dirname(HERE), "include", "pim_pt.h"))
-    objdir = os.path.join(HERE, "build")
+    objdir = os.path.join(HERE, "build" + tag)
+    out_lib = lib or LIB
     os.makedirs(objdir, exist_ok=True)
     objs = []
     procs = []
@@ -36,7 +39,7 @@ def build_library(force=False, verbose=False):
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
         objs.append(obj)
         if force or _stale(obj, [path] + headers):
-            cmd = [nvcc] + NVCC_FLAGS + ["-c", path, "-o", obj]
+            cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-c", path, "-o", obj]
             log = open(obj + ".log", "w")
             procs.append((src, subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT), log, obj))
     failed = False
@@ -50,10 +53,10 @@ def build_library(force=False, verbose=False):
             sys.stdout.write(open(obj + ".log").read())
     if failed:
         raise RuntimeError("nvcc failed")
-    if force or procs or _stale(LIB, objs):
-        cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-lcudart"]
+    if force or procs or _stale(out_lib, objs):
+        cmd = [nvcc, "-shared", "-o", out_lib] + objs + ["-lcudart"]
         subprocess.check_call(cmd)
-    return LIB
+    return out_lib
 
 
 if __name__ == "__main__":

@@ -172,6 +172,14 @@ PT_D RayHit intersectLocal(const DScene& S, V3 ro, V3 rd, float tNear, float tFa
     return finishHit(S, rd, h);
 }
 
+// Same query for the places the shading stages need one in the middle of a bounce (glass
+// thickness, light sample from inside the medium): rare, so not inlined into the stage.
+template <class Stack>
+PT_D_RARE RayHit intersectLocalRare(const DScene& S, V3 ro, V3 rd, float tNear, float tFar, Stack& st)
+{
+    return intersectLocal(S, ro, rd, tNear, tFar, st);
+}
+
 // ------------------------------------------------------------ attributes
 
 PT_D V3 ld3(const F4* p, int i)
@@ -398,7 +406,7 @@ PT_D Scatter Scatter_Refractive(Rng& rng, const DScene& S, const SurfHit& surf, 
     r.pos = P; r.dir = L; r.pdf = pdf; r.evalW = 0.0f;
     if (refr && entering)
     {
-        RayHit hit = intersectLocal(S, P, L, 0.0f, kRcpEpsilon, st);
+        RayHit hit = intersectLocalRare(S, P, L, 0.0f, kRcpEpsilon, st);
         float thickness = f1_max(hit.t, kEpsilon);
         if (hit.type == Hit_Nothing) thickness = kRcpEpsilon;
         V3 tr = AlbedoToTransmittance(surf.albedo, surf.roughness, thickness);
@@ -565,7 +573,7 @@ PT_D V3 CalcTransmittance(Rng& rng, const DScene& S, V3 ro, V3 rd, float rayLen)
 // SampleLight (:1785-1827) with its closest-hit query done in place; used by the
 // volumetric branch, where the wavefront does not split the bounce.
 template <class Stack>
-PT_D bool EvaluateLight(Rng& rng, const DScene& S, V3 P, V3& lightOut, V3& dirOut, Stack& st)   // :1921-1942
+PT_D_RARE bool EvaluateLight(Rng& rng, const DScene& S, V3 P, V3& lightOut, V3& dirOut, Stack& st)   // :1921-1942
 {
     int iVert; float selectPdf;
     if (!LightSelect(rng, S, P, iVert, selectPdf)) return false;
@@ -579,7 +587,7 @@ PT_D bool EvaluateLight(Rng& rng, const DScene& S, V3 P, V3& lightOut, V3& dirOu
     rd = rd / distance;
     float pdf = 0.0f;
     V3 lum = v3s(0.0f);
-    RayHit hit = intersectLocal(S, P, rd, 0.0f, distance + 0.01f * kMilli, st);
+    RayHit hit = intersectLocalRare(S, P, rd, 0.0f, distance + 0.01f * kMilli, st);
     if (hit.type != Hit_Nothing && hit.iVert == iVert)
     {
         float cosTheta = f1_abs(dot(rd, hit.normal));

@@ -17,4 +17,13 @@ using GpuStack = TravStack<kTravSharedDepth>;
     ::pt::GpuStack st;                                                              \
     st.init(pt_stackMem + threadIdx.x, ::pt::kTravThreads)
 
+// Shading kernels only traverse on their cold paths (glass thickness, in-medium light sample):
+// their stack is a plain per-thread array, which leaves shared memory and registers to the
+// shading arithmetic.
+struct ColdStack : TravStack<24>
+{
+    unsigned long long mem[24];
+    __device__ __forceinline__ ColdStack() { init(mem, 1); }
+};
+
 } // namespace pt

@@ -14,9 +14,11 @@
 #if defined(__CUDACC__)
 #define PT_HD __host__ __device__ __forceinline__
 #define PT_D __device__ __forceinline__
+#define PT_D_RARE __device__ __noinline__      // cold paths: keep them out of the callers' register budget
 #else
 #define PT_HD inline
 #define PT_D inline
+#define PT_D_RARE inline
 #endif
 
 namespace pt {

@@ -97,14 +97,9 @@ struct PathPool
     F4* rd2 = nullptr;      // secondary ray direction, w = bits: kind | iVertLight<<2
     F4* pend = nullptr;     // Pending.a0..a3
     U4* hit2 = nullptr;
-    // queues of slot indices + counters
-    int32_t* queueA = nullptr;   // paths to extend
-    int32_t* queueB = nullptr;   // paths between stage A and stage B
-    int32_t* queueNext = nullptr;
-    int32_t* freeList = nullptr;
-    int32_t* freeNext = nullptr;
+    int32_t* stage = nullptr;    // per slot: dead / needs extend / needs connect / shade only
     int32_t* counters = nullptr; // device: see WfCounter
-    int32_t* hostCounters = nullptr; // pinned mirror ring
+    int32_t* hostCounters = nullptr; // pinned mirror of the per-iteration status
     void* all = nullptr;
 };
 enum WfCounter : int
