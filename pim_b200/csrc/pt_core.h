@@ -14,7 +14,7 @@
 #if defined(__CUDACC__)
 #define PT_HD __host__ __device__ __forceinline__
 #define PT_D __device__ __forceinline__
-#define PT_D_RARE __device__ __noinline__      // cold paths: keep them out of the callers' register budget
+#define PT_D_RARE __device__ __forceinline__   // cold paths; a __noinline__ call here measured 8% slower (profiles/README.md)
 #else
 #define PT_HD inline
 #define PT_D inline

@@ -84,15 +84,16 @@ bool launchBrdfLutBake(float* dLut, int32_t w, int32_t h, int32_t samples, uint3
 struct PathPool
 {
     int32_t capacity = 0;
-    // path state, one entry per slot
-    U4* rng = nullptr;
-    F4* ro = nullptr;       // xyz origin, w = weight
-    F4* rd = nullptr;       // xyz direction, w = bits: bounce | prevFlags<<16
-    F4* atten = nullptr;    // xyz attenuation, w = bits: work item index
-    F4* lum = nullptr;      // xyz luminance
-    F4* albedo = nullptr;   // xyz albedo accumulator
-    F4* normal = nullptr;   // xyz normal accumulator
-    U4* hit1 = nullptr;     // t, u, v (float bits), iVert | type<<30
+    // persistent path state, double buffered (survivors are moved when they are compacted)
+    U4* rng[2] = { nullptr, nullptr };
+    F4* ro[2] = { nullptr, nullptr };       // xyz origin, w = weight
+    F4* rd[2] = { nullptr, nullptr };       // xyz direction, w = bits: bounce | prevFlags<<16
+    F4* atten[2] = { nullptr, nullptr };    // xyz attenuation, w = bits: output index
+    F4* lum[2] = { nullptr, nullptr };      // xyz luminance
+    F4* albedo[2] = { nullptr, nullptr };   // xyz albedo accumulator
+    F4* normal[2] = { nullptr, nullptr };   // xyz normal accumulator
+    // per-iteration temporaries
+    U4* hit1 = nullptr;     // t, u, v (float bits), primitive index
     F4* ro2 = nullptr;      // secondary ray origin, w = tFar
     F4* rd2 = nullptr;      // secondary ray direction, w = bits: kind | iVertLight<<2
     F4* pend = nullptr;     // Pending.a0..a3

@@ -12,10 +12,15 @@
 //   K8  (in regen/shade) work claims and live counts are warp-aggregated with
 //                 ballot/popc: one atomic per warp
 //
-// Thread i of every kernel owns slot i. Regenerating in place (instead of compacting
-// survivors into index queues) keeps all twelve state arrays fully coalesced: a warp reads
-// 512 contiguous bytes per array. An earlier queue-indexed version of these kernels paid
-// for a 32-byte sector per 16-byte field once slot order had decayed (profiles/README.md).
+// Compaction moves state, not indices: the seven persistent state arrays are double
+// buffered, stage B writes each surviving path to the next free position of the other
+// buffer (one atomic per warp, so a warp's survivors land contiguously) and regen appends
+// the new paths behind them. Every kernel therefore runs over a dense range [0, N) with
+// full warps, fully coalesced 16-byte fields (512 contiguous bytes per warp and array) and
+// the freshly generated, coherent camera rays side by side. Index queues over fixed slots
+// (an earlier version) paid a 32-byte sector per 16-byte field once slot order had decayed;
+// regenerating in place instead scattered the camera rays among old paths and slowed the
+// traversal kernels (profiles/README.md has the three measurements).
 #include "pt_device.h"
 #include "kernels_common.cuh"
 
@@ -38,10 +43,12 @@ constexpr int kShadeBlocksPerSm = PT_SHADE_BLOCKS;
 
 enum : int32_t { Slot_Dead = 0, Slot_Extend = 1, Slot_Connect = 2, Slot_ShadeOnly = 3 };
 
+struct PathArrays { U4* rng; F4* ro; F4* rd; F4* atten; F4* lum; F4* albedo; F4* normal; };
+
 struct PoolView
 {
-    U4* rng; F4* ro; F4* rd; F4* atten; F4* lum; F4* albedo; F4* normal;
-    U4* hit1; F4* ro2; F4* rd2; F4* pend; U4* hit2;
+    PathArrays cur, next;         // persistent path state, ping-pong
+    U4* hit1; F4* ro2; F4* rd2; F4* pend; U4* hit2;   // per-iteration temporaries
     int32_t* stage;
     int32_t* counters;
     unsigned long long* cursor;   // [0] next work item (may run past the total), [1] total
@@ -57,7 +64,19 @@ __device__ __forceinline__ void warpCount(bool pred, int32_t* counter)
     if (mask && (threadIdx.x & 31) == (__ffs((int)mask) - 1)) atomicAdd(counter, __popc(mask));
 }
 
-__device__ __forceinline__ void loadPath(const PoolView& P, int slot, Path& p, uint32_t& outIndex)
+// warp-aggregated allocation of consecutive positions: one atomic per warp (K8)
+__device__ __forceinline__ int warpAlloc(bool pred, int32_t* counter)
+{
+    const unsigned mask = __ballot_sync(0xffffffffu, pred);
+    if (mask == 0u) return 0;
+    const int lane = threadIdx.x & 31, leader = __ffs((int)mask) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + __popc(mask & ((1u << lane) - 1u));
+}
+
+__device__ __forceinline__ void loadPath(const PathArrays& P, int slot, Path& p, uint32_t& outIndex)
 {
     U4 r = P.rng[slot];
     p.rng.x = r.x; p.rng.y = r.y; p.rng.z = r.z; p.rng.w = r.w;
@@ -73,7 +92,7 @@ __device__ __forceinline__ void loadPath(const PoolView& P, int slot, Path& p, u
     p.normal = v3(f);
 }
 
-__device__ __forceinline__ void storePath(const PoolView& P, int slot, const Path& p, uint32_t outIndex)
+__device__ __forceinline__ void storePath(const PathArrays& P, int slot, const Path& p, uint32_t outIndex)
 {
     U4 r; r.x = p.rng.x; r.y = p.rng.y; r.z = p.rng.z; r.w = p.rng.w;
     P.rng[slot] = r;
@@ -128,7 +147,6 @@ __device__ __forceinline__ void emitResult(const WorkDesc& W, const Path& p, uin
 __global__ void k_wfInit(PoolView P, unsigned long long total)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < P.capacity) P.stage[i] = Slot_Dead;
     if (i == 0)
     {
         for (int k = 0; k < Wf_COUNT; ++k) P.counters[k] = 0;
@@ -137,26 +155,18 @@ __global__ void k_wfInit(PoolView P, unsigned long long total)
     }
 }
 
-// K5: dead slots claim the next work items of the call (one atomic per warp)
+// K5: new paths go behind the survivors, in work-item order (coherent camera rays)
 __global__ void __launch_bounds__(128) k_wfRegen(DScene S, PoolView P, WorkDesc W)
 {
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool dead = slot < P.capacity && P.stage[slot] == Slot_Dead;
-    const unsigned long long total = P.cursor[1];
-    const unsigned mask = __ballot_sync(0xffffffffu, dead);
-    if (mask == 0u) return;
-    const int lane = threadIdx.x & 31, leader = __ffs((int)mask) - 1;
-    unsigned long long base = 0;
-    if (lane == leader)
-    {
-        // skip the atomic once the call's work is known to be used up
-        base = (*(volatile unsigned long long*)&P.cursor[0] >= total) ? total
-             : atomicAdd(&P.cursor[0], (unsigned long long)__popc(mask));
-    }
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (!dead) return;
-    const unsigned long long item = base + (unsigned long long)__popc(mask & ((1u << lane) - 1u));
-    if (item >= total) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = P.counters[Wf_NumA];
+    const unsigned long long cursor = P.cursor[0], total = P.cursor[1];
+    const unsigned long long left = total - cursor;
+    const int room = P.capacity - n;
+    const int nNew = (left < (unsigned long long)room) ? (int)left : room;
+    if (i >= nNew) return;
+    const int slot = n + i;
+    const unsigned long long item = cursor + (unsigned long long)i;
 
     Path p;
     uint32_t outIndex;
@@ -188,8 +198,18 @@ __global__ void __launch_bounds__(128) k_wfRegen(DScene S, PoolView P, WorkDesc 
     }
     pathInit(p, rng, ro, rd);
     pathRoulette(p);    // bounce 0: probability 1, consumes one word like the reference
-    storePath(P, slot, p, outIndex);
-    P.stage[slot] = Slot_Extend;
+    storePath(P.cur, slot, p, outIndex);
+}
+
+__global__ void k_wfAfterRegen(PoolView P)
+{
+    const int n = P.counters[Wf_NumA];
+    const unsigned long long left = P.cursor[1] - P.cursor[0];
+    const int room = P.capacity - n;
+    const int nNew = (left < (unsigned long long)room) ? (int)left : room;
+    P.counters[Wf_NumA] = n + nNew;
+    P.cursor[0] += (unsigned long long)nNew;
+    P.counters[Wf_NumNext] = 0;
 }
 
 // K3'
@@ -197,8 +217,8 @@ __global__ void __launch_bounds__(kTravThreads) k_wfExtend(DScene S, PoolView P)
 {
     PT_DECLARE_STACK(st);
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= P.capacity || P.stage[slot] != Slot_Extend) return;
-    F4 o = P.ro[slot], d = P.rd[slot];
+    if (slot >= P.counters[Wf_NumA]) return;
+    F4 o = P.cur.ro[slot], d = P.cur.rd[slot];
     Hit hit;
     traverse<false, false>(S.bvh, v3(o), v3(d), 0.0f, kRcpEpsilon, hit, st, (TravCounters*)nullptr);
     U4 h; h.x = f2u(hit.t); h.y = f2u(hit.u); h.z = f2u(hit.v); h.w = (uint32_t)hit.prim;
@@ -208,21 +228,25 @@ __global__ void __launch_bounds__(kTravThreads) k_wfExtend(DScene S, PoolView P)
 // K6a
 __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeA(DScene S, PoolView P, WorkDesc W)
 {
+#if defined(PT_SHADE_SHARED_STACK)
+    PT_DECLARE_STACK(st);
+#else
     ColdStack st;
+#endif
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool active = slot < P.capacity && P.stage[slot] == Slot_Extend;
-    bool ray2 = false;
+    const bool active = slot < P.counters[Wf_NumA];
+    bool ray2 = false, moved = false;
+    Path p; uint32_t outIndex = 0;
     if (active)
     {
-        Path p; uint32_t outIndex;
-        loadPath(P, slot, p, outIndex);
+        loadPath(P.cur, slot, p, outIndex);
         RayHit hit = unpackHit(S, p.rd, P.hit1[slot]);
         Pending pend;
         int r = pathStageA(S, p, hit, pend, st);
         if (r == Stage_Next)
         {
             // scattered inside the medium: next bounce starts without a surface interaction
-            if (pathAdvance(p)) storePath(P, slot, p, outIndex);
+            if (pathAdvance(p)) moved = true;
             else r = Stage_Done;
         }
         if (r == Stage_Done)
@@ -235,14 +259,19 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeA(D
             ray2 = (r == Stage_Ray2);
             // stage A only changes rng, atten, lum
             U4 rr; rr.x = p.rng.x; rr.y = p.rng.y; rr.z = p.rng.z; rr.w = p.rng.w;
-            P.rng[slot] = rr;
-            P.atten[slot] = f4(p.atten, u2f(outIndex));
-            P.lum[slot] = f4(p.lum, 0.0f);
+            P.cur.rng[slot] = rr;
+            P.cur.atten[slot] = f4(p.atten, u2f(outIndex));
+            P.cur.lum[slot] = f4(p.lum, 0.0f);
             P.ro2[slot] = f4(pend.ro2, pend.tFar2);
             P.rd2[slot] = f4(pend.rd2, u2f((uint32_t)pend.kind | ((uint32_t)(pend.iVertLight + 1) << 2)));
             P.pend[slot] = f4(pend.a0, pend.a1, pend.a2, pend.a3);
             P.stage[slot] = ray2 ? Slot_Connect : Slot_ShadeOnly;
         }
+        if (moved) P.stage[slot] = Slot_Dead;
+    }
+    {
+        const int dst = warpAlloc(moved, &P.counters[Wf_NumNext]);
+        if (moved) storePath(P.next, dst, p, outIndex);
     }
     warpCount(active, &P.counters[Wf_Rays]);       // rays the extend kernel traced this iteration
     warpCount(ray2, &P.counters[Wf_Paths]);        // rays the connect kernel will trace
@@ -253,7 +282,7 @@ __global__ void __launch_bounds__(kTravThreads) k_wfConnect(DScene S, PoolView P
 {
     PT_DECLARE_STACK(st);
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= P.capacity || P.stage[slot] != Slot_Connect) return;
+    if (slot >= P.counters[Wf_NumA] || P.stage[slot] != Slot_Connect) return;
     F4 o = P.ro2[slot], d = P.rd2[slot];
     Hit hit;
     traverse<false, false>(S.bvh, v3(o), v3(d), 0.0f, o.w, hit, st, (TravCounters*)nullptr);
@@ -264,14 +293,18 @@ __global__ void __launch_bounds__(kTravThreads) k_wfConnect(DScene S, PoolView P
 // K6b
 __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeB(DScene S, PoolView P, WorkDesc W)
 {
+#if defined(PT_SHADE_SHARED_STACK)
+    PT_DECLARE_STACK(st);
+#else
     ColdStack st;
+#endif
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    const int stage = (slot < P.capacity) ? P.stage[slot] : Slot_Dead;
-    bool alive = stage == Slot_Extend;      // medium-scattered paths passed stage A already
+    const int stage = (slot < P.counters[Wf_NumA]) ? P.stage[slot] : Slot_Dead;
+    bool alive = false;
+    Path p; uint32_t outIndex = 0;
     if (stage == Slot_Connect || stage == Slot_ShadeOnly)
     {
-        Path p; uint32_t outIndex;
-        loadPath(P, slot, p, outIndex);
+        loadPath(P.cur, slot, p, outIndex);
         RayHit hit = unpackHit(S, p.rd, P.hit1[slot]);
         Pending pend;
         F4 o2 = P.ro2[slot], d2 = P.rd2[slot], pa = P.pend[slot];
@@ -285,19 +318,12 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeB(D
         hit2.normal = v3s(0.0f); hit2.w = hit2.u = hit2.v = 0.0f;
         if (stage == Slot_Connect) hit2 = unpackHit(S, pend.rd2, P.hit2[slot]);
         int r = pathStageB(S, p, hit, pend, hit2, st);
-        if (r == Stage_Next && pathAdvance(p))
-        {
-            alive = true;
-            storePath(P, slot, p, outIndex);
-            P.stage[slot] = Slot_Extend;
-        }
-        else
-        {
-            emitResult(W, p, outIndex);
-            P.stage[slot] = Slot_Dead;
-        }
+        if (r == Stage_Next && pathAdvance(p)) alive = true;
+        else emitResult(W, p, outIndex);
     }
-    warpCount(alive, &P.counters[Wf_NumNext]);
+    // survivors move to the other buffer, packed (K8)
+    const int dst = warpAlloc(alive, &P.counters[Wf_NumNext]);
+    if (alive) storePath(P.next, dst, p, outIndex);
 }
 
 // end of an iteration: publish progress for the host loop
@@ -306,6 +332,7 @@ __global__ void k_wfEndIteration(PoolView P, int32_t* status)
     const unsigned long long cur = P.cursor[0], total = P.cursor[1];
     const unsigned long long left = cur < total ? total - cur : 0ull;
     status[0] = P.counters[Wf_NumNext];
+    P.counters[Wf_NumA] = P.counters[Wf_NumNext];
     status[1] = (left > 0x7fffffffull) ? 0x7fffffff : (int32_t)left;
     status[2] = P.counters[Wf_Rays];
     status[3] = P.counters[Wf_Paths];
@@ -317,9 +344,13 @@ __global__ void k_wfEndIteration(PoolView P, int32_t* status)
 PoolView makeView(const PathPool& pool)
 {
     PoolView v;
-    v.rng = pool.rng; v.ro = pool.ro; v.rd = pool.rd; v.atten = pool.atten; v.lum = pool.lum;
-    v.albedo = pool.albedo; v.normal = pool.normal; v.hit1 = pool.hit1; v.ro2 = pool.ro2; v.rd2 = pool.rd2;
-    v.pend = pool.pend; v.hit2 = pool.hit2;
+    for (int b = 0; b < 2; ++b)
+    {
+        PathArrays& a = b ? v.next : v.cur;
+        a.rng = pool.rng[b]; a.ro = pool.ro[b]; a.rd = pool.rd[b]; a.atten = pool.atten[b]; a.lum = pool.lum[b];
+        a.albedo = pool.albedo[b]; a.normal = pool.normal[b];
+    }
+    v.hit1 = pool.hit1; v.ro2 = pool.ro2; v.rd2 = pool.rd2; v.pend = pool.pend; v.hit2 = pool.hit2;
     v.stage = pool.stage;
     v.counters = pool.counters;
     v.cursor = reinterpret_cast<unsigned long long*>(pool.counters + Wf_COUNT);
@@ -335,7 +366,7 @@ bool poolAlloc(PathPool& pool, int32_t capacity)
     if (capacity < 1024) capacity = 1024;
     capacity = (capacity + 255) & ~255;
     const size_t cap = (size_t)capacity;
-    const size_t stateBytes = cap * 16 * 12;
+    const size_t stateBytes = cap * 16 * 19;
     const size_t stageBytes = cap * sizeof(int32_t);
     const size_t counterBytes = 256;
     char* base = nullptr;
@@ -344,9 +375,13 @@ bool poolAlloc(PathPool& pool, int32_t capacity)
     pool.capacity = capacity;
     char* p = base;
     auto take = [&](size_t bytes) { char* r = p; p += bytes; return r; };
-    pool.rng = (U4*)take(cap * 16); pool.ro = (F4*)take(cap * 16); pool.rd = (F4*)take(cap * 16);
-    pool.atten = (F4*)take(cap * 16); pool.lum = (F4*)take(cap * 16); pool.albedo = (F4*)take(cap * 16);
-    pool.normal = (F4*)take(cap * 16); pool.hit1 = (U4*)take(cap * 16); pool.ro2 = (F4*)take(cap * 16);
+    for (int b = 0; b < 2; ++b)
+    {
+        pool.rng[b] = (U4*)take(cap * 16); pool.ro[b] = (F4*)take(cap * 16); pool.rd[b] = (F4*)take(cap * 16);
+        pool.atten[b] = (F4*)take(cap * 16); pool.lum[b] = (F4*)take(cap * 16); pool.albedo[b] = (F4*)take(cap * 16);
+        pool.normal[b] = (F4*)take(cap * 16);
+    }
+    pool.hit1 = (U4*)take(cap * 16); pool.ro2 = (F4*)take(cap * 16);
     pool.rd2 = (F4*)take(cap * 16); pool.pend = (F4*)take(cap * 16); pool.hit2 = (U4*)take(cap * 16);
     pool.stage = (int32_t*)take(stageBytes);
     pool.counters = (int32_t*)take(counterBytes);
@@ -385,6 +420,7 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     {
         if (timing) cudaEventRecord(ev[0], stream);
         k_wfRegen<<<grid, 128, 0, stream>>>(S, P, work);
+        k_wfAfterRegen<<<1, 1, 0, stream>>>(P);
         if (timing) cudaEventRecord(ev[1], stream);
         k_wfExtend<<<grid, kTravThreads, 0, stream>>>(S, P);
         if (timing) cudaEventRecord(ev[2], stream);
@@ -395,8 +431,9 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
         k_wfShadeB<<<grid, kShadeThreads, 0, stream>>>(S, P, work);
         if (timing) cudaEventRecord(ev[5], stream);
         k_wfEndIteration<<<1, 1, 0, stream>>>(P, dStatus);
-        g_counters.kernelLaunches += 6;
+        g_counters.kernelLaunches += 7;
         ++iterations;
+        std::swap(P.cur, P.next);
         ok = ok && PT_CUDA(cudaMemcpyAsync(pool.hostCounters, dStatus, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
         ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
         if (!ok) break;
