@@ -210,6 +210,32 @@ int32_t Pt_TraceSpp_Device(PtScene* scene, const Camera* camera, PtDofInfo* dof,
                            int32_t width, int32_t height, int32_t sppBegin, int32_t sppCount,
                            void* dSumColor, void* dSumAlbedo, void* dSumNormal, void* stream);
 
+/* Pt_TraceRayN for callers that must not allocate. No counterpart in the reference.
+ *
+ * Some hosts cannot call cudaMalloc where they trace: a render or simulation loop that
+ * bans allocation after start-up to keep frame latency flat, a thread holding a lock that
+ * an allocating CUDA call could stall behind, an embedding that accounts for all device
+ * memory at load time. This entry point performs no cudaMalloc / cudaFree / cudaMallocHost
+ * and creates no events: the wavefront's scratch (path state, ray and hit temporaries,
+ * counters) is a fixed array inside the library image, about 10 MB, that every GPU
+ * loading libpimpt.so holds until the process exits.
+ *
+ *  - dRo, dRd: device float4[n] (xyz used); outputs are device float3[n] arrays written
+ *    per path; dAlbedo3 and dNormal3 may be NULL. Results equal Pt_TraceRayN's for the
+ *    same scene, rays and pass.
+ *  - n may not exceed PT_NOALLOC_MAX_PATHS; larger batches fail with -1 and a message in
+ *    Pt_LastError() — split them, or use Pt_TraceRayN.
+ *  - The first call on each device looks up the array's device address (with that device
+ *    current, as it is for the scene's owner). Make that first call outside any CUDA
+ *    stream capture.
+ *  - All calls on a device share the one array. It is not cleared between calls (the call
+ *    resets the counters it depends on), so two calls that overlap on the GPU — different
+ *    streams, different host threads — corrupt each other. Serialise them.
+ *  - Blocking: returns after the stream has drained. */
+#define PT_NOALLOC_MAX_PATHS 32768
+int32_t Pt_TraceRayN_NoAlloc(PtScene* scene, const void* dRo, const void* dRd, uint32_t pass,
+                             void* dColor3, void* dAlbedo3, void* dNormal3, int64_t n, void* stream);
+
 /* ---- lightmap bake (src/rendering/lightmap.h:69, lightmap.c:1117-1223) ------
  * The reference bakes the global LmPack; here the pack's texel arrays are passed
  * explicitly. Layout per lightmap page as Lightmap_New (lightmap.c:81-123):

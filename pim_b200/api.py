@@ -115,8 +115,10 @@ EXPORTS = [
     "Pt_TraceSpp", "Pt_IntersectN_Device", "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc",
     "PtScene_GetStats", "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut",
     "Pt_GetCounters", "Pt_ResetCounters", "Pt_LastKernelMs", "Pt_LastError",
-    "Pt_SetKernelTiming", "Pt_GetKernelStats", "Pt_IntersectCountN",
+    "Pt_SetKernelTiming", "Pt_GetKernelStats", "Pt_IntersectCountN", "Pt_TraceRayN_NoAlloc",
 ]
+
+NOALLOC_MAX_PATHS = 32768
 
 _lib = None
 
@@ -164,6 +166,8 @@ def load():
     L.PtScene_GetBrdfLut.argtypes = [vp, vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.Pt_GetCounters.argtypes = [C.POINTER(PtCounters)]
     L.Pt_LastKernelMs.restype = C.c_float
+    L.Pt_TraceRayN_NoAlloc.argtypes = [vp, vp, vp, C.c_uint32, vp, vp, vp, C.c_int64, vp]
+    L.Pt_TraceRayN_NoAlloc.restype = C.c_int32
     L.Pt_SetKernelTiming.argtypes = [C.c_int32]
     L.Pt_GetKernelStats.argtypes = [C.POINTER(PtKernelStats)]
     L.Pt_IntersectCountN.argtypes = [vp, vp, vp, C.c_float, C.c_int64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]

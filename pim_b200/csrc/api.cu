@@ -624,6 +624,21 @@ int32_t Pt_TraceRayN(PtScene* scene, const pim_float4* ro, const pim_float4* rd,
     return ok ? 0 : -1;
 }
 
+int32_t Pt_TraceRayN_NoAlloc(PtScene* scene, const void* dRo, const void* dRd, uint32_t pass, void* dColor3,
+                             void* dAlbedo3, void* dNormal3, int64_t n, void* stream)
+{
+    if (!scene || (n > 0 && (!dRo || !dRd || !dColor3))) { setError("Pt_TraceRayN_NoAlloc: null argument"); return -1; }
+    if (n > PT_NOALLOC_MAX_PATHS)
+    {
+        setError("Pt_TraceRayN_NoAlloc: n = %lld is beyond PT_NOALLOC_MAX_PATHS = %d; split the batch or use Pt_TraceRayN",
+                 (long long)n, PT_NOALLOC_MAX_PATHS);
+        return -1;
+    }
+    cudaStream_t st = stream ? (cudaStream_t)stream : scene->stream;
+    return runWavefrontNoAlloc(scene->view, (const F4*)dRo, (const F4*)dRd, n, pass, scene->config.seed, (float*)dColor3,
+                               (float*)dAlbedo3, (float*)dNormal3, st) ? 0 : -1;
+}
+
 PtResult Pt_TraceRay(PtScene* scene, pim_float4 ro, pim_float4 rd)
 {
     PtResult r;

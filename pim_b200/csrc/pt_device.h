@@ -134,6 +134,12 @@ struct WorkDesc
 // Runs all work items to completion through the wavefront; blocking on `stream`.
 bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStream_t stream, float* kernelMsOut);
 
+// Same wavefront over explicit rays with its scratch in a static device array (no allocation);
+// device pointers in and out, at most noAllocMaxPaths() paths per call.
+bool runWavefrontNoAlloc(const DScene& S, const F4* dRo, const F4* dRd, int64_t n, uint32_t pass, uint32_t seed,
+                         float* dColor3, float* dAlbedo3, float* dNormal3, cudaStream_t stream);
+int32_t noAllocMaxPaths();
+
 // one thread per path, whole path in the thread (small batches, bake)
 bool launchTraceRays(const DScene& S, const F4* dRo, const F4* dRd, int64_t n, uint32_t pass, uint32_t seed,
                      float* dOut9, cudaStream_t stream);

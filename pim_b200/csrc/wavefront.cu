@@ -25,6 +25,7 @@
 #include "kernels_common.cuh"
 
 #include <algorithm>
+#include <cstring>
 
 namespace pt {
 
@@ -463,6 +464,108 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     g_counters.iterations += iterations;
     g_counters.paths += (unsigned long long)work.count;
     g_counters.rays += extendRays + connectRays;
+    return ok;
+}
+
+// ------------------------------------------------------------------------------------
+// Pt_TraceRayN without allocations.
+//
+// Who needs it: code that may not call cudaMalloc at the point where it traces — a frame
+// loop that forbids allocation after start-up so its latency stays flat, a host thread that
+// holds a lock other allocating CUDA calls would contend on, or an embedding that budgets
+// device memory once when the library is loaded. For those callers the wavefront's scratch
+// (double-buffered path state, per-iteration ray/hit temporaries, stage flags, counters) lives
+// in the file-scope array below instead of a cudaMalloc'ed pool. Every GPU that loads the
+// library carries the array until the process exits, hence the modest fixed size.
+constexpr int kNoAllocMaxPaths = 32768;                                   // paths (= scratch slots) per call
+constexpr size_t kNoAllocSlotBytes = 19 * 16 + sizeof(int32_t);           // 14 state + 5 temporary fields + stage
+constexpr size_t kNoAllocBytes = (size_t)kNoAllocMaxPaths * kNoAllocSlotBytes + 256;   // + counter block
+
+static __device__ __align__(256) unsigned char g_noAllocScratch[kNoAllocBytes];
+
+// In host code `g_noAllocScratch` is only a handle for the runtime, not a device address;
+// the address a kernel can use comes from cudaGetSymbolAddress, once per device.
+static unsigned char* g_noAllocPtr[64] = {};
+
+int32_t noAllocMaxPaths() { return kNoAllocMaxPaths; }
+
+bool runWavefrontNoAlloc(const DScene& S, const F4* dRo, const F4* dRd, int64_t n, uint32_t pass, uint32_t seed,
+                         float* dColor3, float* dAlbedo3, float* dNormal3, cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    if (n > kNoAllocMaxPaths)
+    {
+        setError("Pt_TraceRayN_NoAlloc: %lld paths exceed the static scratch (at most %d per call)", (long long)n,
+                 kNoAllocMaxPaths);
+        return false;
+    }
+    int dev = 0;
+    if (!PT_CUDA(cudaGetDevice(&dev))) return false;
+    if (dev < 0 || dev >= 64) { setError("Pt_TraceRayN_NoAlloc: device index %d out of range", dev); return false; }
+    if (!g_noAllocPtr[dev])
+    {
+        // first call on this device (it is the current one): resolve the array's device address
+        void* p = nullptr;
+        if (!PT_CUDA(cudaGetSymbolAddress(&p, g_noAllocScratch))) return false;
+        g_noAllocPtr[dev] = (unsigned char*)p;
+    }
+    // carve the same layout poolAlloc uses out of the static array
+    const size_t cap = (size_t)kNoAllocMaxPaths;
+    unsigned char* p = g_noAllocPtr[dev];
+    auto take = [&](size_t bytes) { unsigned char* r = p; p += bytes; return r; };
+    PoolView P;
+    for (int b = 0; b < 2; ++b)
+    {
+        PathArrays& a = b ? P.next : P.cur;
+        a.rng = (U4*)take(cap * 16); a.ro = (F4*)take(cap * 16); a.rd = (F4*)take(cap * 16);
+        a.atten = (F4*)take(cap * 16); a.lum = (F4*)take(cap * 16); a.albedo = (F4*)take(cap * 16);
+        a.normal = (F4*)take(cap * 16);
+    }
+    P.hit1 = (U4*)take(cap * 16); P.ro2 = (F4*)take(cap * 16); P.rd2 = (F4*)take(cap * 16);
+    P.pend = (F4*)take(cap * 16); P.hit2 = (U4*)take(cap * 16);
+    P.stage = (int32_t*)take(cap * sizeof(int32_t));
+    P.counters = (int32_t*)take(256);
+    P.cursor = reinterpret_cast<unsigned long long*>(P.counters + Wf_COUNT);
+    P.capacity = (int32_t)((n + 127) & ~127ll);
+    int32_t* dStatus = P.counters + Wf_COUNT + 8;
+
+    WorkDesc W;
+    memset(&W, 0, sizeof(W));
+    W.kind = Work_Rays; W.ro = dRo; W.rd = dRd; W.count = n;
+    W.passBase = pass; W.seed = seed; W.salt = Salt_Rays;
+    W.sumColor = dColor3; W.sumAlbedo = dAlbedo3; W.sumNormal = dNormal3; W.accumulate = 0;
+
+    // The array keeps whatever the previous call left: k_wfInit zeroes the counter block and
+    // the work cursor; state, temporaries and stage flags are written before they are read.
+    const int cap1 = P.capacity;
+    const unsigned grid = (unsigned)((cap1 + kTravThreads - 1) / kTravThreads);
+    k_wfInit<<<1, 32, 0, stream>>>(P, (unsigned long long)n);
+    g_counters.kernelLaunches++;
+    bool ok = PT_CUDA(cudaGetLastError());
+    unsigned long long iterations = 0, rays = 0;
+    while (ok)
+    {
+        k_wfRegen<<<grid, 128, 0, stream>>>(S, P, W);
+        k_wfAfterRegen<<<1, 1, 0, stream>>>(P);
+        k_wfExtend<<<grid, kTravThreads, 0, stream>>>(S, P);
+        k_wfShadeA<<<grid, kShadeThreads, 0, stream>>>(S, P, W);
+        k_wfConnect<<<grid, kTravThreads, 0, stream>>>(S, P);
+        k_wfShadeB<<<grid, kShadeThreads, 0, stream>>>(S, P, W);
+        k_wfEndIteration<<<1, 1, 0, stream>>>(P, dStatus);
+        g_counters.kernelLaunches += 7;
+        ++iterations;
+        int32_t status[4] = { 0, 0, 0, 0 };
+        ok = ok && PT_CUDA(cudaMemcpyAsync(status, dStatus, sizeof(status), cudaMemcpyDeviceToHost, stream));
+        ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
+        if (!ok) break;
+        rays += (unsigned long long)(uint32_t)status[2] + (unsigned long long)(uint32_t)status[3];
+        if (status[0] == 0 && status[1] == 0) break;
+        std::swap(P.cur, P.next);
+        if (iterations > 1000000ull) { setError("Pt_TraceRayN_NoAlloc: iteration limit"); ok = false; }
+    }
+    g_counters.iterations += iterations;
+    g_counters.paths += (unsigned long long)n;
+    g_counters.rays += rays;
     return ok;
 }
 
