@@ -188,7 +188,7 @@ def run_ours(args, rank, world, local_rank):
     import ctypes as C
     import torch
     import torch.distributed as dist
-    from pim_b200 import api, scenes
+    from pim_b200 import api, scenes, multigpu
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -210,14 +210,12 @@ def run_ours(args, rank, world, local_rank):
 
     def step(i):
         # every rank renders its own sample indices of the whole frame
-        begin = (i * world + rank) * spp
+        begin, _ = multigpu.sample_range(i, rank, world, spp)
         rc = L.Pt_TraceSpp_Device(scene.h, C.byref(cam), C.byref(dof), WIDTH, HEIGHT, begin, spp,
                                   sums[0].data_ptr(), sums[1].data_ptr(), sums[2].data_ptr(), stream.cuda_stream)
         if rc != 0:
             raise RuntimeError("Pt_TraceSpp_Device: " + api.last_error())
-        if world > 1:
-            for t in sums:
-                dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
+        multigpu.reduce_sums(sums, dst=0)
 
     def barrier():
         if world > 1:
@@ -244,10 +242,7 @@ def run_ours(args, rank, world, local_rank):
     counters = api.counters()
     kstats = api.kernel_stats()
     L.Pt_SetKernelTiming(0)
-    if world > 1:
-        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
+    total_ms = multigpu.max_over_ranks(total_ms, dev)
     samples_per_step = WIDTH * HEIGHT * spp * world
     value = samples_per_step * args.steps / (total_ms * 1e-3) / 1e6
 
@@ -263,10 +258,7 @@ def run_ours(args, rank, world, local_rank):
         trace.trace_spp(scene, cam, dof, (2 + i) * spp, spp)
     barrier()
     e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
+    e2e_s = multigpu.max_over_ranks(e2e_s, dev)
     e2e_value = WIDTH * HEIGHT * spp * world * e2e_steps / e2e_s / 1e6
     mean_lum = float(trace.image("color").mean())
     trace.close()

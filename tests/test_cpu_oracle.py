@@ -1,0 +1,101 @@
+"""CPU suite: the oracle against its own golden fixtures and ground truth (no GPU)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+import parity
+from pim_b200 import scenes
+
+
+def _desc():
+    return scenes.cornell_box("boxes", brdf_lut=parity.reference_lut(), seed=1)
+
+
+def test_reference_reproduces_golden_hits_and_frames(oracle):
+    """oracle/_ref rebuilt here gives the committed fixtures bit for bit (deterministic seeding)."""
+    oracle.load_scene_desc(_desc())
+    s = oracle.Scene()
+    g = np.load(os.path.join(parity.GOLDEN, "cornell_boxes_hits.npz"))
+    hits = s.intersect(g["ro"], g["rd"])
+    assert (hits["iVert"] == g["hits"]["iVert"]).all() and (hits["type"] == g["hits"]["type"]).all()
+    assert np.array_equal(hits["wuvt"], g["hits"]["wuvt"])
+    assert np.array_equal(s.array("positions"), g["positions"])
+    f = np.load(os.path.join(parity.GOLDEN, "cornell_boxes_64x36.npz"))
+    cam, dof = oracle.camera_lookat([-4, 0, 4], [0, -1, 0]), oracle.default_dof()
+    dof.autoFocus = 0
+    for p in range(2):
+        col = np.zeros((36, 64, 3), np.float32); alb = col.copy(); nor = col.copy()
+        s.trace(col, alb, nor, 1.0, cam, dof, p)
+        assert parity.path_agreement(col, f["color%d" % p], rel=1e-6) == 1.0
+    s.close()
+
+
+def test_thread_count_does_not_change_results(oracle):
+    oracle.load_scene_desc(_desc())
+    cam, dof = oracle.camera_lookat([-4, 0, 4], [0, -1, 0]), oracle.default_dof()
+    dof.autoFocus = 0
+    imgs = []
+    for threads in (1, 4):
+        oracle.set_threads(threads)
+        s = oracle.Scene()
+        col = np.zeros((18, 32, 3), np.float32); alb = col.copy(); nor = col.copy()
+        s.trace(col, alb, nor, 1.0, cam, dof, 0)
+        imgs.append(col)
+        s.close()
+    oracle.set_threads(min(os.cpu_count() or 1, 64))
+    assert np.array_equal(imgs[0], imgs[1])
+
+
+def test_cpu_bvh_against_fp64_brute_force(oracle):
+    """The Embree restatement (cpu_bvh.c) is pinned by the all-triangles fp64 loop."""
+    oracle.load_scene_desc(scenes.cornell_box("spheres", brdf_lut=parity.reference_lut(), seed=1))
+    s = oracle.Scene()
+    ro, rd = parity.box_rays(20000, seed=17)
+    hits = s.intersect(ro, rd)
+    tuv, prim, flags = s.brute(ro, rd)
+    s.close()
+    ok = flags == 2
+    ok |= (flags == 0) & (hits["type"] == 0)
+    good = (flags == 1) & (hits["iVert"] == prim * 3)
+    err = np.abs(hits["wuvt"][good, 3] - tuv[good, 0]) / np.maximum(tuv[good, 0], 0.05)
+    assert (ok | good).mean() >= 0.9999
+    assert err.max() <= 4e-5
+
+
+def test_cornell_box_python_matches_reference_math(oracle):
+    """scenes.cornell_box (numpy float32) vs the C restatement on the reference's own headers."""
+    L = oracle.lib()
+    for variant, flag in (("boxes", 0), ("spheres", 1)):
+        d = scenes.cornell_box(variant, brdf_lut=parity.reference_lut())
+        L.oracle_cornell_box(flag)
+        assert L.oracle_entity_count() == len(d.entities)
+        for i, e in enumerate(d.entities):
+            mid = C.c_int32(); M = np.zeros(16, np.float32); t3 = np.zeros(3, np.int32)
+            fl = C.c_uint32(); mfp = np.zeros(4, np.float32); ior = C.c_float(); b = C.c_float()
+            L.oracle_entity_get(i, C.byref(mid), oracle._ptr(M), oracle._ptr(t3, oracle.i32p), C.byref(fl),
+                                oracle._ptr(mfp), C.byref(ior), C.byref(b))
+            assert np.abs(M - e.matrix).max() < 1e-6 and fl.value == e.flags and abs(ior.value - e.ior) < 1e-7
+            for k, ti in enumerate((e.albedo, e.rome)):
+                w = C.c_int32(); h = C.c_int32(); p = C.c_void_p(); f = C.c_int32()
+                assert L.oracle_texture_get(int(t3[k]), C.byref(w), C.byref(h), C.byref(p), C.byref(f))
+                tex = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint32)), (1,))
+                assert tex[0] == d.textures[ti].texels[0]
+            pp, pn, pu = oracle.f32p(), oracle.f32p(), oracle.f32p()
+            n = L.oracle_mesh_get(mid.value, C.byref(pp), C.byref(pn), C.byref(pu))
+            assert n == len(e.positions)
+            assert np.abs(np.ctypeslib.as_array(pp, (n, 4))[:, :3] - e.positions[:, :3]).max() < 2e-6
+
+
+def test_stddev_metric(oracle):
+    """CalcStdDev restatement (render_system.c:1374-1394): unbiased, over avglum."""
+    rng = np.random.default_rng(0)
+    img = rng.uniform(0, 2, (9, 16, 3)).astype(np.float32)
+    lum = img.mean(axis=2).astype(np.float64)
+    assert abs(oracle.stddev(img) - lum.std(ddof=1)) < 1e-5
+
+
+def test_pcg32_known_answer():
+    """O'Neill's pcg32 demo vector (seed 42, stream 54): first outputs of pcg32-demo."""
+    r = scenes.Pcg32(42, 54)
+    assert [r.next_u32() for _ in range(3)] == [0xa15c02b7, 0x7b47f409, 0xba1d3330]
