@@ -3,7 +3,7 @@
 
 A step is one progressive pass of the hot path: `--spp-per-step` samples of every
 pixel of the 1080p frame (BASELINE.json configs[1]; the full config is 1024 spp =
-64 default steps of 16 spp). `value` times Pt_TraceSpp_Device with the scene and the
+16 steps of the default 64 spp). `value` times Pt_TraceSpp_Device with the scene and the
 accumulation images resident in HBM; `e2e` times Pt_TraceSpp, the reference-facing
 call with host PtTrace buffers (device->host copies of the three images inside).
 With N > 1 every rank renders its own sample indices of the full frame (scene
@@ -34,10 +34,10 @@ TRAVERSAL_COUNTS = os.path.join(ROOT, "baseline", "traversal_counts.json")
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--spp-per-step", type=int, default=64)
     ap.add_argument("--pool", type=int, default=0, help="path pool slots (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -286,7 +286,7 @@ def run_ours(args, rank, world, local_rank):
                        "sharding": "sample index per rank, scene replicated, NCCL reduce of the sums per step",
                        "l2": "256 MB buffer written between timed steps (L2 flush)",
                        "path_pool_slots": args.pool or (1 << 19)},
-            "mrays_per_s": total_rays / (total_ms * 1e-3) / 1e6,
+            "mrays_per_s": value * total_rays / max(counters["paths"], 1),      # all ranks, from rank 0's rays per sample
             "rays_per_sample": total_rays / max(counters["paths"], 1),
             "gpu_launches": int(counters["kernelLaunches"]),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": C.sizeof(api.Camera) + C.sizeof(api.PtDofInfo),

@@ -438,6 +438,8 @@ PT_HD F4 f4_bilerp(F4 a, F4 b, F4 c, F4 d, float fx, float fy)
 PT_HD F4 UvBilinearWrap_c32(const uint32_t* texels, int w, int h, V2 uv)
 {
     Bilinear bi = BilinearWrap(w, h, uv);
+    // all four taps on one texel (1x1 textures, clamped borders): a + (a-a)*t is a, exactly
+    if (bi.a == bi.d) return GammaDecode_rgba8(texels[bi.a]);
     return f4_bilerp(GammaDecode_rgba8(texels[bi.a]), GammaDecode_rgba8(texels[bi.b]),
                      GammaDecode_rgba8(texels[bi.c]), GammaDecode_rgba8(texels[bi.d]), bi.fx, bi.fy);
 }

@@ -413,49 +413,73 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     k_wfInit<<<(cap + 255) / 256, 256, 0, stream>>>(P, (unsigned long long)work.count);
     g_counters.kernelLaunches++;
     ok = ok && PT_CUDA(cudaEventRecord(e0, stream));
-    unsigned long long iterations = 0, extendRays = 0, connectRays = 0;
+    // The host runs kLag iterations ahead of the device: iteration i's status (live paths, work
+    // left) is copied to a pinned ring and read kLag iterations later, so the stream never
+    // drains between iterations. The few iterations launched after the last path ended find
+    // empty ranges and cost a few microseconds each.
+    constexpr int kRing = 8, kLag = 3;
+    unsigned long long iterations = 0, consumed = 0, extendRays = 0, connectRays = 0;
     const bool timing = g_kernelTiming;
-    cudaEvent_t ev[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
-    if (timing) for (int k = 0; ok && k < 6; ++k) ok = PT_CUDA(cudaEventCreate(&ev[k]));
-    while (ok)
+    cudaEvent_t done[kRing] = {};
+    cudaEvent_t ev[kRing][6] = {};
+    for (int r = 0; ok && r < kRing; ++r)
     {
-        if (timing) cudaEventRecord(ev[0], stream);
-        k_wfRegen<<<grid, 128, 0, stream>>>(S, P, work);
-        k_wfAfterRegen<<<1, 1, 0, stream>>>(P);
-        if (timing) cudaEventRecord(ev[1], stream);
-        k_wfExtend<<<grid, kTravThreads, 0, stream>>>(S, P);
-        if (timing) cudaEventRecord(ev[2], stream);
-        k_wfShadeA<<<grid, kShadeThreads, 0, stream>>>(S, P, work);
-        if (timing) cudaEventRecord(ev[3], stream);
-        k_wfConnect<<<grid, kTravThreads, 0, stream>>>(S, P);
-        if (timing) cudaEventRecord(ev[4], stream);
-        k_wfShadeB<<<grid, kShadeThreads, 0, stream>>>(S, P, work);
-        if (timing) cudaEventRecord(ev[5], stream);
-        k_wfEndIteration<<<1, 1, 0, stream>>>(P, dStatus);
-        g_counters.kernelLaunches += 7;
-        ++iterations;
-        std::swap(P.cur, P.next);
-        ok = ok && PT_CUDA(cudaMemcpyAsync(pool.hostCounters, dStatus, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
-        ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
-        if (!ok) break;
-        extendRays += (unsigned long long)(uint32_t)pool.hostCounters[2];
-        connectRays += (unsigned long long)(uint32_t)pool.hostCounters[3];
+        ok = PT_CUDA(cudaEventCreateWithFlags(&done[r], cudaEventDisableTiming));
+        if (timing) for (int k = 0; ok && k < 6; ++k) ok = PT_CUDA(cudaEventCreate(&ev[r][k]));
+    }
+    bool finished = false;
+    auto consume = [&](unsigned long long it) -> bool
+    {
+        const int r = (int)(it % kRing);
+        if (!PT_CUDA(cudaEventSynchronize(done[r]))) return false;
+        const int32_t* st = pool.hostCounters + 4 * r;
+        extendRays += (unsigned long long)(uint32_t)st[2];
+        connectRays += (unsigned long long)(uint32_t)st[3];
         if (timing)
         {
             for (int k = 0; k < 5; ++k)
             {
                 float ms = 0.0f;
-                cudaEventElapsedTime(&ms, ev[k], ev[k + 1]);
+                cudaEventElapsedTime(&ms, ev[r][k], ev[r][k + 1]);
                 g_kernelStats.ms[k] += ms;
-                g_kernelStats.launches[k] += 1;
+                if (st[2] != 0 || st[3] != 0) g_kernelStats.launches[k] += 1;
             }
-            g_kernelStats.extendRays += (unsigned long long)(uint32_t)pool.hostCounters[2];
-            g_kernelStats.connectRays += (unsigned long long)(uint32_t)pool.hostCounters[3];
+            g_kernelStats.extendRays += (unsigned long long)(uint32_t)st[2];
+            g_kernelStats.connectRays += (unsigned long long)(uint32_t)st[3];
         }
-        if (pool.hostCounters[0] == 0 && pool.hostCounters[1] == 0) break;
+        if (st[0] == 0 && st[1] == 0) finished = true;
+        return true;
+    };
+    while (ok && !finished)
+    {
+        const int r = (int)(iterations % kRing);
+        if (timing) cudaEventRecord(ev[r][0], stream);
+        k_wfRegen<<<grid, 128, 0, stream>>>(S, P, work);
+        k_wfAfterRegen<<<1, 1, 0, stream>>>(P);
+        if (timing) cudaEventRecord(ev[r][1], stream);
+        k_wfExtend<<<grid, kTravThreads, 0, stream>>>(S, P);
+        if (timing) cudaEventRecord(ev[r][2], stream);
+        k_wfShadeA<<<grid, kShadeThreads, 0, stream>>>(S, P, work);
+        if (timing) cudaEventRecord(ev[r][3], stream);
+        k_wfConnect<<<grid, kTravThreads, 0, stream>>>(S, P);
+        if (timing) cudaEventRecord(ev[r][4], stream);
+        k_wfShadeB<<<grid, kShadeThreads, 0, stream>>>(S, P, work);
+        if (timing) cudaEventRecord(ev[r][5], stream);
+        k_wfEndIteration<<<1, 1, 0, stream>>>(P, dStatus);
+        g_counters.kernelLaunches += 7;
+        ok = ok && PT_CUDA(cudaMemcpyAsync(pool.hostCounters + 4 * r, dStatus, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+        ok = ok && PT_CUDA(cudaEventRecord(done[r], stream));
+        ++iterations;
+        std::swap(P.cur, P.next);
+        if (ok && iterations - consumed > (unsigned long long)kLag) ok = consume(consumed++);
         if (iterations > 1000000ull) { setError("runWavefront: iteration limit"); ok = false; }
     }
-    for (int k = 0; k < 6; ++k) if (ev[k]) cudaEventDestroy(ev[k]);
+    while (ok && consumed < iterations) ok = consume(consumed++);
+    for (int r = 0; r < kRing; ++r)
+    {
+        if (done[r]) cudaEventDestroy(done[r]);
+        for (int k = 0; k < 6; ++k) if (ev[r][k]) cudaEventDestroy(ev[r][k]);
+    }
     ok = ok && PT_CUDA(cudaEventRecord(e1, stream));
     ok = ok && PT_CUDA(cudaEventSynchronize(e1));
     if (ok && kernelMsOut) cudaEventElapsedTime(kernelMsOut, e0, e1);
