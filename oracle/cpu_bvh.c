@@ -513,3 +513,48 @@ int brute_intersect_f64(const float* verts, int stride, int64_t ntris,
     if (second < DBL_MAX && (second - bestT) <= 1e-6 * fmax(1.0, fabs(bestT))) return 2;
     return 1;
 }
+
+/* Multi-threaded closest-hit batch for timing the CPU baseline and for the canonical
+ * fetch counts: ro4/rd4 are float4 per ray, rd4.w = tFar. */
+#include <pthread.h>
+
+typedef struct BatchArg
+{
+    const CpuBvh* bvh; const float* ro4; const float* rd4; float tnear; int64_t begin, end;
+    int32_t* prim; uint64_t nodes, tris;
+} BatchArg;
+
+static void* batch_main(void* p)
+{
+    BatchArg* a = (BatchArg*)p;
+    cpubvh_counters_reset();
+    for (int64_t i = a->begin; i < a->end; ++i)
+    {
+        CpuHit hit;
+        int found = cpubvh_intersect(a->bvh, a->ro4 + 4 * i, a->rd4 + 4 * i, a->tnear, a->rd4[4 * i + 3], &hit);
+        a->prim[i] = found ? hit.prim : -1;
+    }
+    uint64_t rays;
+    cpubvh_counters_get(&a->nodes, &a->tris, &rays);
+    return NULL;
+}
+
+void cpubvh_intersect_batch(const CpuBvh* bvh, const float* ro4, const float* rd4, float tnear, int64_t n,
+                            int threads, int32_t* prim, uint64_t* nodes, uint64_t* tris)
+{
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    pthread_t th[256]; BatchArg args[256];
+    for (int t = 0; t < threads; ++t)
+    {
+        args[t].bvh = bvh; args[t].ro4 = ro4; args[t].rd4 = rd4; args[t].tnear = tnear; args[t].prim = prim;
+        args[t].begin = n * t / threads; args[t].end = n * (t + 1) / threads;
+        pthread_create(&th[t], NULL, batch_main, &args[t]);
+    }
+    *nodes = *tris = 0;
+    for (int t = 0; t < threads; ++t)
+    {
+        pthread_join(th[t], NULL);
+        *nodes += args[t].nodes; *tris += args[t].tris;
+    }
+}

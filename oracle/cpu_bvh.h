@@ -69,6 +69,11 @@ int brute_intersect_f64(const float* verts, int stride, int64_t ntris,
                         const float ro[3], const float rd[3],
                         float tnear, float tfar, CpuHit* hit);
 
+/* closest hit over n rays on `threads` host threads (ro4/rd4: float4 per ray, rd4.w = tFar);
+ * prim[i] = primitive or -1; returns summed wide-node and triangle fetches */
+void cpubvh_intersect_batch(const CpuBvh* bvh, const float* ro4, const float* rd4, float tnear, int64_t n,
+                            int threads, int32_t* prim, uint64_t* nodes, uint64_t* tris);
+
 #ifdef __cplusplus
 }
 #endif

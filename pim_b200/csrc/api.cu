@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -89,6 +90,7 @@ static bool ensureInit()
     int n = 0;
     if (!PT_CUDA(cudaGetDeviceCount(&n))) return false;
     if (n <= 0) { setError("no CUDA device: libpimpt has no CPU path"); return false; }
+    if (const char* e = getenv("PIMPT_PERSISTENT")) g_persistentTraversal = atoi(e);   // tuning switch
     g_initialised = true;
     return true;
 }

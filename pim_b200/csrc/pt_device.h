@@ -29,6 +29,8 @@ struct KernelStats
     unsigned long long extendRays, connectRays;
 };
 extern bool g_kernelTiming;
+extern int g_persistentTraversal;   // 0: one thread per ray, 1: persistent warps that refill idle lanes, -1: by BVH size
+bool usePersistent(int32_t bvhNodeCount);
 extern KernelStats g_kernelStats;
 
 constexpr int kSmCount = 148;           // B200: 2 dies x 74 SMs
@@ -99,6 +101,7 @@ struct PathPool
     F4* pend = nullptr;     // Pending.a0..a3
     U4* hit2 = nullptr;
     int32_t* stage = nullptr;    // per slot: dead / needs extend / needs connect / shade only
+    int32_t* connectList = nullptr;   // slots that need a connect ray this iteration (persistent traversal)
     int32_t* counters = nullptr; // device: see WfCounter
     int32_t* hostCounters = nullptr; // pinned mirror of the per-iteration status
     void* all = nullptr;
@@ -106,7 +109,7 @@ struct PathPool
 enum WfCounter : int
 {
     Wf_NumA = 0, Wf_NumB, Wf_NumNext, Wf_NumFree, Wf_NumFreeNext, Wf_WorkCursor, Wf_WorkTotal,
-    Wf_Rays, Wf_Paths, Wf_COUNT = 16
+    Wf_Rays, Wf_Paths, Wf_ExtendCursor, Wf_ConnectCursor, Wf_NumConnect, Wf_COUNT = 16
 };
 bool poolAlloc(PathPool& pool, int32_t capacity);
 void poolFree(PathPool& pool);

@@ -12,6 +12,8 @@
 #include "pt_device.h"
 #include "kernels_common.cuh"
 
+#include <algorithm>
+
 namespace pt {
 
 // ---------------------------------------------------------------- ray batches
@@ -32,6 +34,57 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHit(DScene S, const F4*
     U4 b; b.x = f2u(h.normal.x); b.y = f2u(h.normal.y); b.z = f2u(h.normal.z); b.w = 0;
     U4 c; c.x = (uint32_t)h.type; c.y = (uint32_t)h.iVert; c.z = h.flags; c.w = 0;
     dst[0] = a; dst[1] = b; dst[2] = c;
+}
+
+// persistent form: warps refill finished lanes with the next rays of the batch (one atomic per warp)
+__global__ void __launch_bounds__(kTravThreads) k_closestHitPersistent(DScene S, const F4* __restrict__ ro,
+                                                                        const F4* __restrict__ rd, float tNear,
+                                                                        RayHitOut* __restrict__ out, int64_t n,
+                                                                        unsigned long long* cursor)
+{
+    PT_DECLARE_STACK(st);
+    const int lane = threadIdx.x & 31;
+    const uint32_t ltMask = (1u << lane) - 1u;
+    TravRay r;
+    bool busy = false, exhausted = false;
+    long long idx = -1;
+    for (;;)
+    {
+        const unsigned idle = __ballot_sync(0xffffffffu, !busy);
+        if (!exhausted && __popc(idle) >= 8)
+        {
+            const int leader = __ffs((int)idle) - 1;
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(cursor, (unsigned long long)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!busy)
+            {
+                idx = (long long)base + __popc(idle & ltMask);
+                if (idx < n)
+                {
+                    U4 o = ldg128(ro + idx), d = ldg128(rd + idx);
+                    travBegin(S.bvh, r, v3(u2f(o.x), u2f(o.y), u2f(o.z)), v3(u2f(d.x), u2f(d.y), u2f(d.z)), tNear, u2f(d.w), st);
+                    busy = true;
+                }
+            }
+            exhausted = (long long)base + __popc(idle) >= n;
+        }
+        if (__ballot_sync(0xffffffffu, busy) == 0u)
+        {
+            if (exhausted) break;
+            continue;
+        }
+        if (busy && !travStep<false, false>(S.bvh, r, st, (TravCounters*)nullptr))
+        {
+            RayHit h = finishHit(S, r.rd, r.hit);
+            U4* dst = reinterpret_cast<U4*>(out + idx);
+            U4 a; a.x = f2u(h.w); a.y = f2u(h.u); a.z = f2u(h.v); a.w = f2u(h.t);
+            U4 b; b.x = f2u(h.normal.x); b.y = f2u(h.normal.y); b.z = f2u(h.normal.z); b.w = 0;
+            U4 c; c.x = (uint32_t)h.type; c.y = (uint32_t)h.iVert; c.z = h.flags; c.w = 0;
+            dst[0] = a; dst[1] = b; dst[2] = c;
+            busy = false;
+        }
+    }
 }
 
 __global__ void __launch_bounds__(kTravThreads) k_anyHit(DScene S, const F4* __restrict__ ro,
@@ -81,6 +134,15 @@ bool launchIntersect(const DScene& S, const F4* dRo, const F4* dRd, float tNear,
                      cudaStream_t stream)
 {
     if (n <= 0) return true;
+    if (usePersistent(S.bvh.nodeCount))
+    {
+        static unsigned long long* dCursor = nullptr;
+        if (!dCursor && !PT_CUDA(cudaMalloc((void**)&dCursor, 8))) return false;
+        cudaMemsetAsync(dCursor, 0, 8, stream);
+        const unsigned grid = (unsigned)std::min<int64_t>(gridFor(n, kTravThreads), kSmCount * 12);
+        k_closestHitPersistent<<<grid, kTravThreads, 0, stream>>>(S, dRo, dRd, tNear, dOut, n, dCursor);
+    }
+    else
     k_closestHit<<<gridFor(n, kTravThreads), kTravThreads, 0, stream>>>(S, dRo, dRd, tNear, dOut, n);
     g_counters.kernelLaunches++;
     g_counters.rays += (unsigned long long)n;

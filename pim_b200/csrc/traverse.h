@@ -60,141 +60,166 @@ PT_D uint32_t max8(const uint32_t k[8])
     return a > c ? a : c;
 }
 
+// Traversal state of one ray. travBegin sets it up, every travStep call visits one wide node
+// (its child boxes and the triangles of its leaf children) and returns false once the ray is
+// finished, so a kernel can either loop it to completion (traverse) or interleave it with
+// fetching new rays for idle lanes (the persistent kernels of wavefront.cu).
+struct TravRay
+{
+    V3 ro, rd, idir;
+    float tNear, tBest;
+    uint32_t bestPrim;
+    uint32_t cur;
+    bool haveCur, found, negx, negy, negz;
+    Hit hit;
+};
+
+template <class Stack>
+PT_D void travBegin(const Bvh& bvh, TravRay& r, V3 ro, V3 rd, float tNear, float tFar, Stack& st)
+{
+    r.hit.prim = -1;
+    r.hit.t = tFar;
+    r.hit.u = r.hit.v = 0.0f;
+    r.hit.ng = v3(0, 0, 0);
+    r.ro = ro; r.rd = rd;
+    r.idir = v3(safeRcp(rd.x), safeRcp(rd.y), safeRcp(rd.z));
+    r.negx = rd.x < 0.0f; r.negy = rd.y < 0.0f; r.negz = rd.z < 0.0f;
+    r.tNear = tNear; r.tBest = tFar;
+    r.found = false;
+    r.bestPrim = 0xffffffffu;
+    r.cur = 0;
+    r.haveCur = bvh.nodeCount > 0;
+    st.sp = 0;
+}
+
+template <bool kAnyHit, bool kCount, class Stack>
+PT_D bool travStep(const Bvh& bvh, TravRay& r, Stack& st, TravCounters* cnt)
+{
+    while (!r.haveCur)
+    {
+        if (st.sp == 0) return false;
+        unsigned long long e = st.pop();
+        uint32_t key = (uint32_t)(e >> 32);
+        if (u2f((key - 8u) & ~7u) > r.tBest) continue;
+        r.cur = (uint32_t)e;
+        r.haveCur = true;
+    }
+    r.haveCur = false;
+    if (kCount) cnt->nodes++;
+
+    const WideNode* np = bvh.nodes + r.cur;
+    const U4 n0 = ldg128(&np->ox);
+    const U4 n1 = ldg128(&np->childBase);
+    const U4 n2 = ldg128(&np->qlox[0]);
+    const U4 n3 = ldg128(&np->qloz[0]);
+    const U4 n4 = ldg128(&np->qhiy[0]);
+
+    const uint32_t imask = n0.w >> 24;
+    const float sx = u2f((n0.w & 0xffu) << 23) * r.idir.x;
+    const float sy = u2f(((n0.w >> 8) & 0xffu) << 23) * r.idir.y;
+    const float sz = u2f(((n0.w >> 16) & 0xffu) << 23) * r.idir.z;
+    const float bx = (u2f(n0.x) - r.ro.x) * r.idir.x;
+    const float by = (u2f(n0.y) - r.ro.y) * r.idir.y;
+    const float bz = (u2f(n0.z) - r.ro.z) * r.idir.z;
+
+    // near / far plane bytes per axis, picked by the ray's direction sign
+    uint32_t nxw[2], fxw[2], nyw[2], fyw[2], nzw[2], fzw[2];
+    nxw[0] = r.negx ? n3.z : n2.x; nxw[1] = r.negx ? n3.w : n2.y;
+    fxw[0] = r.negx ? n2.x : n3.z; fxw[1] = r.negx ? n2.y : n3.w;
+    nyw[0] = r.negy ? n4.x : n2.z; nyw[1] = r.negy ? n4.y : n2.w;
+    fyw[0] = r.negy ? n2.z : n4.x; fyw[1] = r.negy ? n2.w : n4.y;
+    nzw[0] = r.negz ? n4.z : n3.x; nzw[1] = r.negz ? n4.w : n3.y;
+    fzw[0] = r.negz ? n3.x : n4.z; fzw[1] = r.negz ? n3.y : n4.w;
+    const uint32_t metaw[2] = { n1.z, n1.w };
+
+    uint32_t keys[8];
+    uint32_t hitMask = 0;
+#if defined(__CUDA_ARCH__)
+    #pragma unroll
+#endif
+    for (int i = 0; i < 8; ++i)
+    {
+        const int w = i >> 2;
+        float tnx = byteToFloat(nxw[w], i & 3) * sx + bx;
+        float tfx = byteToFloat(fxw[w], i & 3) * sx + bx;
+        float tny = byteToFloat(nyw[w], i & 3) * sy + by;
+        float tfy = byteToFloat(fyw[w], i & 3) * sy + by;
+        float tnz = byteToFloat(nzw[w], i & 3) * sz + bz;
+        float tfz = byteToFloat(fzw[w], i & 3) * sz + bz;
+        float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tNear));
+        float tmax = fminf(fminf(tfx, tfy), fminf(tfz, r.tBest));
+        // a few ulps of slack: the planes come out of an fma on rounded inputs
+        bool h = (((metaw[w] >> (8 * (i & 3))) & 0xffu) != 0u) && (tmin <= tmax * 1.0000004f);
+        keys[i] = h ? (((f2u(tmin) & ~7u) | (uint32_t)i) + 8u) : 0u;
+        hitMask |= h ? (1u << i) : 0u;
+    }
+
+    // leaf children: test their triangles now
+    uint32_t leafMask = hitMask & ~imask;
+    while (leafMask)
+    {
+        const int i = ffs32(leafMask);
+        leafMask &= leafMask - 1;
+        const uint32_t m = (metaw[i >> 2] >> (8 * (i & 3))) & 0xffu;
+        const uint32_t count = m >> 5, first = n1.y + (m & 31u);
+        for (uint32_t j = 0; j < count; ++j)
+        {
+            if (kCount) cnt->tris++;
+            float t, u, v; uint32_t prim; V3 ng;
+            if (triTest(bvh.tris + first + j, r.ro, r.rd, r.tNear, r.tBest, t, u, v, prim, ng))
+            {
+                if (kAnyHit) { r.found = true; return false; }
+                // equal-t hits resolve to the lowest primitive id (as the oracle does)
+                if (!r.found || t < r.tBest || prim < r.bestPrim)
+                {
+                    r.found = true;
+                    r.tBest = t; r.bestPrim = prim;
+                    r.hit.t = t; r.hit.u = u; r.hit.v = v; r.hit.prim = (int32_t)prim; r.hit.ng = ng;
+                }
+            }
+        }
+    }
+
+    // internal children: push far-to-near, keep the nearest as the next node
+    uint32_t intMask = hitMask & imask;
+    if (intMask)
+    {
+#if defined(__CUDA_ARCH__)
+        #pragma unroll
+#endif
+        for (int i = 0; i < 8; ++i) keys[i] = ((intMask >> i) & 1u) ? keys[i] : 0u;
+        int n = popc32(intMask);
+        while (n > 1)
+        {
+            const uint32_t best = max8(keys);
+            const uint32_t idx = (best - 8u) & 7u;
+            st.push(n1.x + (uint32_t)popc32(imask & ((1u << idx) - 1u)), best);
+#if defined(__CUDA_ARCH__)
+            #pragma unroll
+#endif
+            for (int i = 0; i < 8; ++i) keys[i] = (keys[i] == best) ? 0u : keys[i];
+            --n;
+        }
+        const uint32_t best = max8(keys);
+        if (u2f((best - 8u) & ~7u) <= r.tBest)
+        {
+            const uint32_t idx = (best - 8u) & 7u;
+            r.cur = n1.x + (uint32_t)popc32(imask & ((1u << idx) - 1u));
+            r.haveCur = true;
+        }
+    }
+    return r.haveCur || st.sp != 0;
+}
+
 template <bool kAnyHit, bool kCount, class Stack>
 PT_D bool traverse(const Bvh& bvh, V3 ro, V3 rd, float tNear, float tFar, Hit& hit, Stack& st,
                    TravCounters* cnt)
 {
-    hit.prim = -1;
-    hit.t = tFar;
-    hit.u = hit.v = 0.0f;
-    hit.ng = v3(0, 0, 0);
-    if (bvh.nodeCount <= 0) return false;
-
-    const V3 idir = v3(safeRcp(rd.x), safeRcp(rd.y), safeRcp(rd.z));
-    const bool negx = rd.x < 0.0f, negy = rd.y < 0.0f, negz = rd.z < 0.0f;
-    float tBest = tFar;
-    bool found = false;
-    uint32_t bestPrim = 0xffffffffu;
-
-    st.sp = 0;
-    uint32_t cur = 0;
-    bool haveCur = true;
-    for (;;)
-    {
-        if (!haveCur)
-        {
-            if (st.sp == 0) break;
-            unsigned long long e = st.pop();
-            uint32_t key = (uint32_t)(e >> 32);
-            if (u2f((key - 8u) & ~7u) > tBest) continue;
-            cur = (uint32_t)e;
-        }
-        haveCur = false;
-        if (kCount) cnt->nodes++;
-
-        const WideNode* np = bvh.nodes + cur;
-        const U4 n0 = ldg128(&np->ox);
-        const U4 n1 = ldg128(&np->childBase);
-        const U4 n2 = ldg128(&np->qlox[0]);
-        const U4 n3 = ldg128(&np->qloz[0]);
-        const U4 n4 = ldg128(&np->qhiy[0]);
-
-        const uint32_t imask = n0.w >> 24;
-        const float sx = u2f((n0.w & 0xffu) << 23) * idir.x;
-        const float sy = u2f(((n0.w >> 8) & 0xffu) << 23) * idir.y;
-        const float sz = u2f(((n0.w >> 16) & 0xffu) << 23) * idir.z;
-        const float bx = (u2f(n0.x) - ro.x) * idir.x;
-        const float by = (u2f(n0.y) - ro.y) * idir.y;
-        const float bz = (u2f(n0.z) - ro.z) * idir.z;
-
-        // near / far plane bytes per axis, picked by the ray's direction sign
-        uint32_t nxw[2], fxw[2], nyw[2], fyw[2], nzw[2], fzw[2];
-        nxw[0] = negx ? n3.z : n2.x; nxw[1] = negx ? n3.w : n2.y;
-        fxw[0] = negx ? n2.x : n3.z; fxw[1] = negx ? n2.y : n3.w;
-        nyw[0] = negy ? n4.x : n2.z; nyw[1] = negy ? n4.y : n2.w;
-        fyw[0] = negy ? n2.z : n4.x; fyw[1] = negy ? n2.w : n4.y;
-        nzw[0] = negz ? n4.z : n3.x; nzw[1] = negz ? n4.w : n3.y;
-        fzw[0] = negz ? n3.x : n4.z; fzw[1] = negz ? n3.y : n4.w;
-        const uint32_t metaw[2] = { n1.z, n1.w };
-
-        uint32_t keys[8];
-        uint32_t hitMask = 0;
-#if defined(__CUDA_ARCH__)
-        #pragma unroll
-#endif
-        for (int i = 0; i < 8; ++i)
-        {
-            const int w = i >> 2;
-            float tnx = byteToFloat(nxw[w], i & 3) * sx + bx;
-            float tfx = byteToFloat(fxw[w], i & 3) * sx + bx;
-            float tny = byteToFloat(nyw[w], i & 3) * sy + by;
-            float tfy = byteToFloat(fyw[w], i & 3) * sy + by;
-            float tnz = byteToFloat(nzw[w], i & 3) * sz + bz;
-            float tfz = byteToFloat(fzw[w], i & 3) * sz + bz;
-            float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tNear));
-            float tmax = fminf(fminf(tfx, tfy), fminf(tfz, tBest));
-            // a few ulps of slack: the planes come out of an fma on rounded inputs
-            bool h = (((metaw[w] >> (8 * (i & 3))) & 0xffu) != 0u) && (tmin <= tmax * 1.0000004f);
-            keys[i] = h ? (((f2u(tmin) & ~7u) | (uint32_t)i) + 8u) : 0u;
-            hitMask |= h ? (1u << i) : 0u;
-        }
-
-        // leaf children: test their triangles now
-        uint32_t leafMask = hitMask & ~imask;
-        while (leafMask)
-        {
-            const int i = ffs32(leafMask);
-            leafMask &= leafMask - 1;
-            const uint32_t m = (metaw[i >> 2] >> (8 * (i & 3))) & 0xffu;
-            const uint32_t count = m >> 5, first = n1.y + (m & 31u);
-            for (uint32_t j = 0; j < count; ++j)
-            {
-                if (kCount) cnt->tris++;
-                float t, u, v; uint32_t prim; V3 ng;
-                if (triTest(bvh.tris + first + j, ro, rd, tNear, tBest, t, u, v, prim, ng))
-                {
-                    if (kAnyHit) return true;
-                    // equal-t hits resolve to the lowest primitive id (as the oracle does)
-                    if (!found || t < tBest || prim < bestPrim)
-                    {
-                        found = true;
-                        tBest = t; bestPrim = prim;
-                        hit.t = t; hit.u = u; hit.v = v; hit.prim = (int32_t)prim; hit.ng = ng;
-                    }
-                }
-            }
-        }
-
-        // internal children: push far-to-near, keep the nearest as the next node
-        uint32_t intMask = hitMask & imask;
-        if (intMask)
-        {
-#if defined(__CUDA_ARCH__)
-            #pragma unroll
-#endif
-            for (int i = 0; i < 8; ++i) keys[i] = ((intMask >> i) & 1u) ? keys[i] : 0u;
-            int n = popc32(intMask);
-            while (n > 1)
-            {
-                const uint32_t best = max8(keys);
-                const uint32_t idx = (best - 8u) & 7u;
-                st.push(n1.x + (uint32_t)popc32(imask & ((1u << idx) - 1u)), best);
-#if defined(__CUDA_ARCH__)
-                #pragma unroll
-#endif
-                for (int i = 0; i < 8; ++i) keys[i] = (keys[i] == best) ? 0u : keys[i];
-                --n;
-            }
-            const uint32_t best = max8(keys);
-            if (u2f((best - 8u) & ~7u) <= tBest)
-            {
-                const uint32_t idx = (best - 8u) & 7u;
-                cur = n1.x + (uint32_t)popc32(imask & ((1u << idx) - 1u));
-                haveCur = true;
-            }
-        }
-    }
-    return found;
+    TravRay r;
+    travBegin(bvh, r, ro, rd, tNear, tFar, st);
+    while (travStep<kAnyHit, kCount>(bvh, r, st, cnt)) {}
+    hit = r.hit;
+    return r.found;
 }
 
 // Nearest triangle to p among those closer than `radius` (unsigned distance as
