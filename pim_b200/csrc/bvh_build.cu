@@ -22,6 +22,13 @@ constexpr int kSortThreads = 256;
 constexpr int kSortItems = 8;
 constexpr int kSortTile = kSortThreads * kSortItems;   // keys per block
 
+// up to this many triangles the tree is built top-down with binned SAH; above it with the
+// Morton-code radix tree (LBVH), whose build is one pass per level of the sort, not of the tree
+#ifndef PT_SAH_MAX_TRIS
+#define PT_SAH_MAX_TRIS (4 << 20)
+#endif
+constexpr int kSahMaxTris = PT_SAH_MAX_TRIS;
+
 __device__ __forceinline__ int floatToOrdered(float f)
 {
     int i = __float_as_int(f);
@@ -259,6 +266,221 @@ __global__ void __launch_bounds__(256) k_refit(int n, F4* lo, F4* hi, const int*
     }
 }
 
+// ---- binned SAH (top-down, one warp per node, one launch per tree level) --------------------
+// Node 0 is the root; a node with more than kLeafMaxTris primitives is split along the best of
+// 3 x 15 candidate planes (16 centroid bins per axis, cost = area(L)*n(L) + area(R)*n(R)); its
+// primitives are partitioned in place in order[] and its two children get consecutive ids.
+// Children boxes come from the bin boxes, so no extra pass is needed.
+
+constexpr int kSahBins = 16;
+constexpr int kSahWarps = 8;
+
+struct SahBins
+{
+    int lo[3][kSahBins][3];
+    int hi[3][kSahBins][3];
+    int cnt[3][kSahBins];
+};
+
+__device__ __forceinline__ float warpMinF(float v)
+{
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warpMaxF(float v)
+{
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// counters: [0] nodes allocated, [1] next-level queue length
+__global__ void __launch_bounds__(kSahWarps * 32) k_sahSplit(BinTree T, const F4* __restrict__ leafLo,
+                                                              const F4* __restrict__ leafHi, int* order, int* tmp,
+                                                              const int* __restrict__ qIn, int nIn, int* qOut,
+                                                              uint32_t* counters)
+{
+    __shared__ SahBins sbins[kSahWarps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int w = blockIdx.x * kSahWarps + warp;
+    if (w >= nIn) return;
+    SahBins& B = sbins[warp];
+    const int node = qIn[w];
+    const int f = T.first[node], l = T.last[node], cnt = l - f + 1;
+
+    // centroid bounds of the range
+    float cmin[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, cmax[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+    for (int i = f + lane; i <= l; i += 32)
+    {
+        const int t = order[i];
+        const F4 a = leafLo[t], b = leafHi[t];
+        const float c[3] = { (a.x + b.x) * 0.5f, (a.y + b.y) * 0.5f, (a.z + b.z) * 0.5f };
+        for (int k = 0; k < 3; ++k) { cmin[k] = fminf(cmin[k], c[k]); cmax[k] = fmaxf(cmax[k], c[k]); }
+    }
+    float scale[3];
+    for (int k = 0; k < 3; ++k)
+    {
+        cmin[k] = warpMinF(cmin[k]); cmax[k] = warpMaxF(cmax[k]);
+        const float ext = cmax[k] - cmin[k];
+        scale[k] = ext > 0.0f ? (float)kSahBins / ext : 0.0f;
+    }
+    // bins
+    for (int i = lane; i < 3 * kSahBins; i += 32)
+    {
+        const int a = i / kSahBins, b = i % kSahBins;
+        for (int k = 0; k < 3; ++k) { B.lo[a][b][k] = floatToOrdered(3.0e38f); B.hi[a][b][k] = floatToOrdered(-3.0e38f); }
+        B.cnt[a][b] = 0;
+    }
+    __syncwarp();
+    for (int i = f + lane; i <= l; i += 32)
+    {
+        const int t = order[i];
+        const F4 a = leafLo[t], b = leafHi[t];
+        const float c[3] = { (a.x + b.x) * 0.5f, (a.y + b.y) * 0.5f, (a.z + b.z) * 0.5f };
+        const int lo3[3] = { floatToOrdered(a.x), floatToOrdered(a.y), floatToOrdered(a.z) };
+        const int hi3[3] = { floatToOrdered(b.x), floatToOrdered(b.y), floatToOrdered(b.z) };
+        for (int ax = 0; ax < 3; ++ax)
+        {
+            if (scale[ax] == 0.0f) continue;
+            int bin = (int)((c[ax] - cmin[ax]) * scale[ax]);
+            bin = bin < 0 ? 0 : (bin > kSahBins - 1 ? kSahBins - 1 : bin);
+            for (int k = 0; k < 3; ++k) { atomicMin(&B.lo[ax][bin][k], lo3[k]); atomicMax(&B.hi[ax][bin][k], hi3[k]); }
+            atomicAdd(&B.cnt[ax][bin], 1);
+        }
+    }
+    __syncwarp();
+    // 45 candidate planes, two per lane
+    float bestCost = 3.0e38f;
+    int bestCand = -1;
+    for (int cand = lane; cand < 3 * (kSahBins - 1); cand += 32)
+    {
+        const int ax = cand / (kSahBins - 1), sp = cand % (kSahBins - 1);
+        if (scale[ax] == 0.0f) continue;
+        float llo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, lhi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+        float rlo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, rhi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+        int nl = 0, nr = 0;
+        for (int b = 0; b < kSahBins; ++b)
+        {
+            const int c = B.cnt[ax][b];
+            if (c == 0) continue;
+            if (b <= sp)
+            {
+                nl += c;
+                for (int k = 0; k < 3; ++k) { llo[k] = fminf(llo[k], orderedToFloat(B.lo[ax][b][k])); lhi[k] = fmaxf(lhi[k], orderedToFloat(B.hi[ax][b][k])); }
+            }
+            else
+            {
+                nr += c;
+                for (int k = 0; k < 3; ++k) { rlo[k] = fminf(rlo[k], orderedToFloat(B.lo[ax][b][k])); rhi[k] = fmaxf(rhi[k], orderedToFloat(B.hi[ax][b][k])); }
+            }
+        }
+        if (nl == 0 || nr == 0) continue;
+        const float al = boxArea(f4(llo[0], llo[1], llo[2], 0), f4(lhi[0], lhi[1], lhi[2], 0));
+        const float ar = boxArea(f4(rlo[0], rlo[1], rlo[2], 0), f4(rhi[0], rhi[1], rhi[2], 0));
+        const float cost = al * (float)nl + ar * (float)nr;
+        if (cost < bestCost) { bestCost = cost; bestCand = cand; }
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const float oc = __shfl_xor_sync(0xffffffffu, bestCost, o);
+        const int ocand = __shfl_xor_sync(0xffffffffu, bestCand, o);
+        if (oc < bestCost || (oc == bestCost && ocand >= 0 && (bestCand < 0 || ocand < bestCand))) { bestCost = oc; bestCand = ocand; }
+    }
+    int nLeft;
+    float clo[2][3], chi[2][3];
+    if (bestCand >= 0)
+    {
+        const int ax = bestCand / (kSahBins - 1), sp = bestCand % (kSahBins - 1);
+        for (int side = 0; side < 2; ++side)
+            for (int k = 0; k < 3; ++k) { clo[side][k] = 3.0e38f; chi[side][k] = -3.0e38f; }
+        nLeft = 0;
+        for (int b = 0; b < kSahBins; ++b)
+        {
+            if (B.cnt[ax][b] == 0) continue;
+            const int side = b <= sp ? 0 : 1;
+            if (side == 0) nLeft += B.cnt[ax][b];
+            for (int k = 0; k < 3; ++k)
+            {
+                clo[side][k] = fminf(clo[side][k], orderedToFloat(B.lo[ax][b][k]));
+                chi[side][k] = fmaxf(chi[side][k], orderedToFloat(B.hi[ax][b][k]));
+            }
+        }
+        // stable partition of order[f..l] by bin <= sp, through tmp
+        int offL = 0, offR = 0;
+        for (int base = f; base <= l; base += 32)
+        {
+            const int i = base + lane;
+            const bool valid = i <= l;
+            int t = 0; bool left = false;
+            if (valid)
+            {
+                t = order[i];
+                const F4 a = leafLo[t], b = leafHi[t];
+                const float c = ax == 0 ? (a.x + b.x) * 0.5f : (ax == 1 ? (a.y + b.y) * 0.5f : (a.z + b.z) * 0.5f);
+                int bin = (int)((c - cmin[ax]) * scale[ax]);
+                bin = bin < 0 ? 0 : (bin > kSahBins - 1 ? kSahBins - 1 : bin);
+                left = bin <= sp;
+            }
+            const unsigned ml = __ballot_sync(0xffffffffu, valid && left);
+            const unsigned mr = __ballot_sync(0xffffffffu, valid && !left);
+            const unsigned lt = (1u << lane) - 1u;
+            if (valid) tmp[left ? (f + offL + __popc(ml & lt)) : (f + nLeft + offR + __popc(mr & lt))] = t;
+            offL += __popc(ml); offR += __popc(mr);
+        }
+        __syncwarp();
+        for (int i = f + lane; i <= l; i += 32) order[i] = tmp[i];
+        __syncwarp();
+    }
+    else
+    {
+        // all centroids in one bin on every axis: split the range in the middle
+        nLeft = cnt / 2;
+        for (int side = 0; side < 2; ++side)
+        {
+            float lo3[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi3[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+            const int b0 = side == 0 ? f : f + nLeft, b1 = side == 0 ? f + nLeft - 1 : l;
+            for (int i = b0 + lane; i <= b1; i += 32)
+            {
+                const int t = order[i];
+                const F4 a = leafLo[t], b = leafHi[t];
+                lo3[0] = fminf(lo3[0], a.x); lo3[1] = fminf(lo3[1], a.y); lo3[2] = fminf(lo3[2], a.z);
+                hi3[0] = fmaxf(hi3[0], b.x); hi3[1] = fmaxf(hi3[1], b.y); hi3[2] = fmaxf(hi3[2], b.z);
+            }
+            for (int k = 0; k < 3; ++k) { clo[side][k] = warpMinF(lo3[k]); chi[side][k] = warpMaxF(hi3[k]); }
+        }
+    }
+    if (lane == 0)
+    {
+        const uint32_t base = atomicAdd(&counters[0], 2u);
+        const int kids[2] = { (int)base, (int)base + 1 };
+        T.lo[node].w = u2f((uint32_t)kids[0]);
+        T.hi[node].w = u2f((uint32_t)kids[1]);
+        const int kf[2] = { f, f + nLeft }, kl[2] = { f + nLeft - 1, l };
+        for (int side = 0; side < 2; ++side)
+        {
+            const int k = kids[side];
+            T.lo[k] = f4(clo[side][0], clo[side][1], clo[side][2], 0.0f);
+            T.hi[k] = f4(chi[side][0], chi[side][1], chi[side][2], 0.0f);
+            T.first[k] = kf[side]; T.last[k] = kl[side];
+            if (kl[side] - kf[side] + 1 > kLeafMaxTris) qOut[atomicAdd(&counters[1], 1u)] = k;
+        }
+    }
+}
+
+__global__ void k_sahInit(BinTree T, int n, const int* __restrict__ bounds, int* order, int* qOut, uint32_t* counters)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) order[i] = i;
+    if (i == 0)
+    {
+        T.lo[0] = f4(orderedToFloat(bounds[6]), orderedToFloat(bounds[7]), orderedToFloat(bounds[8]), 0.0f);
+        T.hi[0] = f4(orderedToFloat(bounds[9]), orderedToFloat(bounds[10]), orderedToFloat(bounds[11]), 0.0f);
+        T.first[0] = 0; T.last[0] = n - 1;
+        counters[0] = 1u;
+        counters[1] = 0u;
+        if (n > kLeafMaxTris) { qOut[0] = 0; counters[1] = 1u; }
+    }
+}
+
 struct CollapseWork { int32_t bin; uint32_t wide; };
 
 // counters: [0] wide nodes allocated, [1] triangles allocated, [2] next-level queue length
@@ -351,6 +573,34 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
         k_triBounds<<<blocks, 256, 0, stream>>>(dPositions, n, leafLo, leafHi, bounds);
         k_morton<<<blocks, 256, 0, stream>>>(leafLo, leafHi, n, bounds, keysA, valsA);
         g_counters.kernelLaunches += 3;
+        const uint32_t* sortedVals = nullptr;
+        if (n <= kSahMaxTris)
+        {
+            // binned SAH: order[] doubles as the sorted-primitive array the collapse reads
+            int* order = reinterpret_cast<int*>(valsA);
+            int* tmp = reinterpret_cast<int*>(valsB);
+            int* sq[2] = { reinterpret_cast<int*>(q0), reinterpret_cast<int*>(q1) };
+            BinTree T; T.lo = lo; T.hi = hi; T.first = first; T.last = last; T.n = n;
+            k_sahInit<<<blocks, 256, 0, stream>>>(T, n, bounds, order, sq[0], counters);
+            g_counters.kernelLaunches += 1;
+            int cur = 0;
+            for (;;)
+            {
+                uint32_t h[2];
+                ok = ok && PT_CUDA(cudaMemcpyAsync(h, counters, sizeof(h), cudaMemcpyDeviceToHost, stream));
+                ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
+                if (!ok || h[1] == 0) break;
+                ok = ok && PT_CUDA(cudaMemsetAsync(counters + 1, 0, sizeof(uint32_t), stream));
+                const int nIn = (int)h[1];
+                k_sahSplit<<<(nIn + kSahWarps - 1) / kSahWarps, kSahWarps * 32, 0, stream>>>(T, leafLo, leafHi, order, tmp,
+                                                                                             sq[cur], nIn, sq[cur ^ 1], counters);
+                g_counters.kernelLaunches += 1;
+                cur ^= 1;
+            }
+            sortedVals = valsA;
+        }
+        else
+        {
         uint64_t* kin = keysA; uint64_t* kout = keysB;
         uint32_t* vin = valsA; uint32_t* vout = valsB;
         for (int pass = 0; pass < 8; ++pass)
@@ -370,6 +620,8 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
         k_leafInit<<<blocks, 256, 0, stream>>>(vin, leafLo, leafHi, n, lo, hi, first, last);
         if (n > 1) k_refit<<<blocks, 256, 0, stream>>>(n, lo, hi, parent, visits);
         g_counters.kernelLaunches += 3;
+        sortedVals = vin;
+        }
 
         // breadth-first collapse; the root wide node is index 0
         CollapseWork root; root.bin = (n == 1) ? 0 : 0; root.wide = 0;
@@ -381,7 +633,7 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
         CollapseWork* qin = q0; CollapseWork* qout = q1;
         while (ok && levelCount > 0)
         {
-            k_collapse<<<(levelCount + 127) / 128, 128, 0, stream>>>(T, qin, levelCount, qout, counters, vin,
+            k_collapse<<<(levelCount + 127) / 128, 128, 0, stream>>>(T, qin, levelCount, qout, counters, sortedVals,
                                                                      dPositions, out.nodes, out.tris);
             g_counters.kernelLaunches += 1;
             uint32_t h[4];
