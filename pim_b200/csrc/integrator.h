@@ -180,6 +180,7 @@ PT_D_RARE RayHit intersectLocalRare(const DScene& S, V3 ro, V3 rd, float tNear, 
     return intersectLocal(S, ro, rd, tNear, tFar, st);
 }
 
+
 // ------------------------------------------------------------ attributes
 
 PT_D V3 ld3(const F4* p, int i)

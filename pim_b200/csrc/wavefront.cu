@@ -301,19 +301,17 @@ __global__ void __launch_bounds__(kTravThreads) k_wfTracePersistent(DScene S, Po
 // K6a
 __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeA(DScene S, PoolView P, WorkDesc W)
 {
-#if defined(PT_SHADE_SHARED_STACK)
-    PT_DECLARE_STACK(st);
-#else
-    ColdStack st;
-#endif
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    LazyStack st;
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;     // always below the pool capacity
+    // issue the state loads before the live count is known: they do not depend on it
+    Path p; uint32_t outIndex = 0;
+    loadPath(P.cur, slot, p, outIndex);
+    const U4 h1 = P.hit1[slot];
     const bool active = slot < P.counters[Wf_NumA];
     bool ray2 = false, moved = false;
-    Path p; uint32_t outIndex = 0;
     if (active)
     {
-        loadPath(P.cur, slot, p, outIndex);
-        RayHit hit = unpackHit(S, p.rd, P.hit1[slot]);
+        RayHit hit = unpackHit(S, p.rd, h1);
         Pending pend;
         int r = pathStageA(S, p, hit, pend, st);
         if (r == Stage_Next)
@@ -343,15 +341,18 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeA(D
         if (moved) P.stage[slot] = Slot_Dead;
     }
     {
-        const int dst = warpAlloc(moved, &P.counters[Wf_NumNext]);
+        const int dst = warpAlloc(moved, &P.counters[Wf_NumNext]);      // rare: no atomic unless a lane scattered
         if (moved) storePath(P.next, dst, p, outIndex);
     }
+    int nRay2 = 0;
+    const int idx = blockAlloc<kShadeThreads / 32>(ray2, &P.counters[Wf_NumConnect], nRay2);
+    if (ray2) P.connectList[idx] = slot;
+    const int nActive = __syncthreads_count(active);
+    if (threadIdx.x == 0)
     {
-        const int idx = warpAlloc(ray2, &P.counters[Wf_NumConnect]);
-        if (ray2) P.connectList[idx] = slot;
+        if (nActive) atomicAdd(&P.counters[Wf_Rays], nActive);      // rays the extend kernel traced
+        if (nRay2) atomicAdd(&P.counters[Wf_Paths], nRay2);         // rays the connect kernel will trace
     }
-    warpCount(active, &P.counters[Wf_Rays]);       // rays the extend kernel traced this iteration
-    warpCount(ray2, &P.counters[Wf_Paths]);        // rays the connect kernel will trace
 }
 
 // K4'
@@ -370,21 +371,19 @@ __global__ void __launch_bounds__(kTravThreads) k_wfConnect(DScene S, PoolView P
 // K6b
 __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeB(DScene S, PoolView P, WorkDesc W)
 {
-#if defined(PT_SHADE_SHARED_STACK)
-    PT_DECLARE_STACK(st);
-#else
-    ColdStack st;
-#endif
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    LazyStack st;
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;     // always below the pool capacity
+    // loads that do not depend on the live count go first
+    Path p; uint32_t outIndex = 0;
+    loadPath(P.cur, slot, p, outIndex);
+    const U4 h1 = P.hit1[slot], h2 = P.hit2[slot];
+    const F4 o2 = P.ro2[slot], d2 = P.rd2[slot], pa = P.pend[slot];
     const int stage = (slot < P.counters[Wf_NumA]) ? P.stage[slot] : Slot_Dead;
     bool alive = false;
-    Path p; uint32_t outIndex = 0;
     if (stage == Slot_Connect || stage == Slot_ShadeOnly)
     {
-        loadPath(P.cur, slot, p, outIndex);
-        RayHit hit = unpackHit(S, p.rd, P.hit1[slot]);
+        RayHit hit = unpackHit(S, p.rd, h1);
         Pending pend;
-        F4 o2 = P.ro2[slot], d2 = P.rd2[slot], pa = P.pend[slot];
         const uint32_t bits = f2u(d2.w);
         pend.kind = (int32_t)(bits & 3u);
         pend.iVertLight = (int32_t)(bits >> 2) - 1;
@@ -393,13 +392,14 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeB(D
         RayHit hit2;
         hit2.type = Hit_Nothing; hit2.iVert = -1; hit2.t = -1.0f; hit2.flags = 0;
         hit2.normal = v3s(0.0f); hit2.w = hit2.u = hit2.v = 0.0f;
-        if (stage == Slot_Connect) hit2 = unpackHit(S, pend.rd2, P.hit2[slot]);
+        if (stage == Slot_Connect) hit2 = unpackHit(S, pend.rd2, h2);
         int r = pathStageB(S, p, hit, pend, hit2, st);
         if (r == Stage_Next && pathAdvance(p)) alive = true;
         else emitResult(W, p, outIndex);
     }
-    // survivors move to the other buffer, packed (K8)
-    const int dst = warpAlloc(alive, &P.counters[Wf_NumNext]);
+    // survivors move to the other buffer, packed (K8): one atomic per CTA
+    int nAlive = 0;
+    const int dst = blockAlloc<kShadeThreads / 32>(alive, &P.counters[Wf_NumNext], nAlive);
     if (alive) storePath(P.next, dst, p, outIndex);
 }
 
