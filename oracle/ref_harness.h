@@ -27,6 +27,7 @@ enum
     ORACLE_STREAM_BAKE = 4,    /* call 0: UpdateDistsFn, call 1: BakeFn */
     ORACLE_STREAM_LUT = 5,     /* call 0: BakeBrdfFn */
     ORACLE_STREAM_RAYS = 6,    /* call 0: harness Pt_TraceRay batch */
+    ORACLE_STREAM_LMPACK = 7,  /* LmPack_Pack's parallel loops */
 };
 
 void oracle_set_threads(int n);
@@ -111,6 +112,13 @@ void oracle_counters_get(uint64_t* nodes, uint64_t* tris, uint64_t* rays);
 /* brute-force fp64 ground truth on the scene's triangles; flags[i]: 0 miss, 1 hit, 2 hit with near-tie */
 void oracle_brute_n(const void* scene, const float* ro4, const float* rd4, float tNear,
                     int64_t n, float* tuv3, int32_t* prim, int32_t* flags);
+
+/* lightmaps: LmPack_Pack (reference code, CPU pre-step) fills the global pack from the entity
+ * tables; pages follow Lightmap_New's layout; LmPack_Bake is the path under test */
+int oracle_lm_pack(int atlasSize, float texelsPerUnit, float distThresh, float degThresh);
+int oracle_lm_size(void);
+void oracle_lm_page(int i, float** probes5, float** position3, float** normal3, float** sampleCounts);
+void oracle_lm_bake(void* scene, float timeSlice, int spp, uint32_t pass);
 
 /* CalcStdDev (src/rendering/render_system.c:1374-1394) */
 float oracle_stddev(const float* color3, int w, int h);

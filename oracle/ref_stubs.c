@@ -440,3 +440,41 @@ void oracle_bake_brdf_lut(int w, int h, int samples, float* texelsOut2)
 }
 
 i32 StrLen(const char* x) { return x ? (i32)strlen(x) : 0; }
+
+/* ---------------------------------------------- stubs only lightmap.c links against */
+#include "threading/mutex.h"
+#include "common/cmd.h"
+#include "assets/crate.h"
+void Mutex_New(Mutex* mut) { pthread_mutex_init((pthread_mutex_t*)mut, NULL); }
+void Mutex_Del(Mutex* mut) { pthread_mutex_destroy((pthread_mutex_t*)mut); }
+void Mutex_Lock(Mutex* mut) { pthread_mutex_lock((pthread_mutex_t*)mut); }
+void Mutex_Unlock(Mutex* mut) { pthread_mutex_unlock((pthread_mutex_t*)mut); }
+_Static_assert(sizeof(Mutex) >= sizeof(pthread_mutex_t), "reference Mutex can hold a pthread mutex");
+void cmd_reg(const char* name, const char* argDocs, const char* helpText, cmd_fn_t fn) { (void)name; (void)argDocs; (void)helpText; (void)fn; }
+bool Mesh_Upload(MeshId id) { (void)id; return true; }
+int stbi_write_png(char const* filename, int w, int h, int comp, const void* data, int stride) { (void)filename; (void)w; (void)h; (void)comp; (void)data; (void)stride; return 0; }
+bool Crate_Get(Crate *const crate, Guid id, void* dst, i32 size) { (void)crate; (void)id; (void)dst; (void)size; return false; }
+bool Crate_Set(Crate *const crate, Guid id, const void* src, i32 size) { (void)crate; (void)id; (void)src; (void)size; return false; }
+vkrTextureId vkrTexTable_Alloc(VkImageViewType type, VkFormat format, VkSamplerAddressMode clamp, i32 width, i32 height, i32 depth, i32 layers, bool mips)
+{
+    (void)type; (void)format; (void)clamp; (void)width; (void)height; (void)depth; (void)layers; (void)mips;
+    vkrTextureId id = { 0 };
+    return id;
+}
+bool vkrTexTable_Free(vkrTextureId id) { (void)id; return true; }
+bool vkrTexTable_Upload(vkrTextureId id, i32 layer, void const *const data, i32 bytes) { (void)id; (void)layer; (void)data; (void)bytes; return true; }
+
+/* Mem_Push / Mem_Pop: the reference's alloca substitute (LIFO per thread) */
+static __thread void* t_pushStack[64];
+static __thread int t_pushTop;
+void* Mem_Push(i32 bytes)
+{
+    void* p = aligned_alloc(64, ((size_t)(bytes > 0 ? bytes : 1) + 63) & ~(size_t)63);
+    if (t_pushTop < 64) t_pushStack[t_pushTop++] = p;
+    return p;
+}
+void Mem_Pop(i32 bytes)
+{
+    (void)bytes;
+    if (t_pushTop > 0) free(t_pushStack[--t_pushTop]);
+}

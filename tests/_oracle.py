@@ -230,3 +230,29 @@ def stddev(color):
     h, w, _ = color.shape
     c = np.ascontiguousarray(color, np.float32)
     return float(lib().oracle_stddev(_ptr(c), w, h))
+
+
+# ---- lightmaps ---------------------------------------------------------------------------
+
+def lm_pack(atlas_size, texels_per_unit, dist_thresh=0.1, deg_thresh=15.0):
+    """The reference's LmPack_Pack on the loaded entity tables; returns the page count."""
+    L = lib()
+    L.oracle_lm_pack.argtypes = [C.c_int, C.c_float, C.c_float, C.c_float]
+    return L.oracle_lm_pack(atlas_size, texels_per_unit, dist_thresh, deg_thresh)
+
+
+def lm_page(i):
+    """numpy views (no copy) of page i: probes [5][S*S,4], position [S*S,3], normal [S*S,3], counts [S*S]"""
+    L = lib()
+    L.oracle_lm_page.argtypes = [C.c_int, C.POINTER(f32p * 5), C.POINTER(f32p), C.POINTER(f32p), C.POINTER(f32p)]
+    probes = (f32p * 5)(); pos = f32p(); nrm = f32p(); cnt = f32p()
+    L.oracle_lm_page(i, C.byref(probes), C.byref(pos), C.byref(nrm), C.byref(cnt))
+    n = L.oracle_lm_size() ** 2
+    return ([np.ctypeslib.as_array(probes[k], (n, 4)) for k in range(5)], np.ctypeslib.as_array(pos, (n, 3)),
+            np.ctypeslib.as_array(nrm, (n, 3)), np.ctypeslib.as_array(cnt, (n,)))
+
+
+def lm_bake(scene, time_slice, spp, pass_index):
+    L = lib()
+    L.oracle_lm_bake.argtypes = [C.c_void_p, C.c_float, C.c_int, C.c_uint32]
+    L.oracle_lm_bake(scene.h, time_slice, spp, pass_index)
