@@ -1,0 +1,154 @@
+#!/usr/bin/env python
+"""Secondary BASELINE.json configs, measured the same way as bench.py measures configs[1]:
+
+  python tools/configs.py c3 [--spp 256] [--cpu-spp 1]   ~1M-triangle interior, 1080p (configs[2])
+  python tools/configs.py c4 [--spp 64] [--cpu]          cornell lightmap bake, 16 texels/m (configs[3])
+
+GPU numbers are CUDA-event / wall times around the C-ABI calls; the CPU numbers are the
+reference's own code (oracle/_ref) on the host cores.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def c3(args):
+    import torch
+    from pim_b200 import api, scenes
+    L = api.load()
+    t0 = time.perf_counter()
+    desc = scenes.interior(args.tris, seed=7, emissive_fraction=args.emissive)
+    gen_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    scene = api.Scene(desc)
+    build_s = time.perf_counter() - t0
+    st = scene.stats
+    out = {"config": "c3 interior", "tris": desc.tri_count, "emissive_tris": st.emissiveCount,
+           "grid": list(st.gridSize), "bvh_nodes": st.bvhNodeCount, "scene_gen_s": gen_s, "scene_build_s": build_s}
+    W, H = 1920, 1080
+    eye, at = [3.0, 1.5, 3.0], [30.0, 1.2, 27.0]
+    cam, dof = api.make_camera(eye, at, 90.0), api.default_dof(auto_focus=False)
+    dev = torch.device("cuda", 0)
+    sums = [torch.zeros(W * H * 3, dtype=torch.float32, device=dev) for _ in range(3)]
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.synchronize()
+    torch.cuda.set_stream(stream)
+    step = 16
+    L.Pt_TraceSpp_Device(scene.h, C.byref(cam), C.byref(dof), W, H, 0, 4, sums[0].data_ptr(), sums[1].data_ptr(),
+                         sums[2].data_ptr(), stream.cuda_stream)
+    L.Pt_ResetCounters(); L.Pt_SetKernelTiming(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    done = 4
+    while done < 4 + args.spp:
+        rc = L.Pt_TraceSpp_Device(scene.h, C.byref(cam), C.byref(dof), W, H, done, step, sums[0].data_ptr(),
+                                  sums[1].data_ptr(), sums[2].data_ptr(), stream.cuda_stream)
+        assert rc == 0, api.last_error()
+        done += step
+    e1.record(stream); e1.synchronize()
+    ms = e0.elapsed_time(e1)
+    k = api.kernel_stats(); c = api.counters()
+    rays = k["extendRays"] + k["connectRays"]
+    out.update({"spp": args.spp, "msamples_s": W * H * args.spp / ms / 1e3, "mrays_s": rays / ms / 1e3,
+                "rays_per_sample": rays / max(c["paths"], 1),
+                "kernel_us": {n: round(k[n]["ms"] / max(k[n]["launches"], 1) * 1e3, 1) for n in api.KERNEL_NAMES},
+                "mean_luminance": float((sums[0] / (args.spp + 4)).mean().item())})
+    if args.cpu_spp > 0:
+        import _oracle as O
+        if O.available():
+            O.set_seed(1)
+            desc.brdf_lut = scene.brdf_lut()
+            t0 = time.perf_counter()
+            O.load_scene_desc(desc)
+            ref = O.Scene()
+            out["cpu_scene_build_s"] = time.perf_counter() - t0
+            ocam, odof = O.camera_lookat(eye, at, 90.0), O.default_dof()
+            odof.autoFocus = 0
+            w, h = W // 4, H // 4
+            col = np.zeros((h, w, 3), np.float32); alb = col.copy(); nor = col.copy()
+            ref.trace(col, alb, nor, 1.0, ocam, odof, 0)
+            t0 = time.perf_counter()
+            for p in range(args.cpu_spp):
+                ref.trace(col, alb, nor, 1.0 / (p + 2), ocam, odof, p + 1)
+            dt = time.perf_counter() - t0
+            out.update({"cpu_msamples_s": w * h * args.cpu_spp / dt / 1e6, "cpu_threads": O.lib().oracle_get_threads(),
+                        "cpu_sample": "%d spp at %dx%d" % (args.cpu_spp, w, h), "cpu_mean_luminance": float(col.mean())})
+            ref.close()
+    print(json.dumps(out))
+    scene.close()
+
+
+def c4(args):
+    import _oracle as O
+    from pim_b200 import api, scenes
+    import parity
+    desc = scenes.cornell_box("boxes", brdf_lut=parity.reference_lut(), seed=1)
+    O.set_seed(1)
+    O.load_scene_desc(desc)
+    t0 = time.perf_counter()
+    pages = O.lm_pack(1024, 16.0)
+    pack_s = time.perf_counter() - t0
+    out = {"config": "c4 cornell lightmap 16 texels/m", "pages": pages, "lm_pack_cpu_s": pack_s, "spp": args.spp}
+    probes, pos, nrm, cnt = O.lm_page(0)
+    covered = int((cnt > 0).sum())
+    out["covered_texels"] = covered
+    scene = api.Scene(desc)
+    g_probes = [np.ascontiguousarray(p.copy()) for p in probes]
+    g_pos, g_nrm, g_cnt = pos.copy(), nrm.copy(), cnt.copy()
+    ref = O.Scene()
+    for c in range(int(np.prod(scene.grid_size))):      # same light-grid pdfs on both sides
+        n, pdf, _, _ = ref.dist(c)
+        if n:
+            scene.set_dist(c, pdf)
+    warm = api.Scene(desc)     # warm-up on another scene object: a bake also feeds the light-grid learning
+    warm.bake_lightmap([p.copy() for p in g_probes], g_pos, g_nrm, g_cnt.copy(), 16.0, 1.0, 1, 99)
+    warm.close()
+    t0 = time.perf_counter()
+    scene.bake_lightmap(g_probes, g_pos, g_nrm, g_cnt, 16.0, 1.0, args.spp, 0)
+    dt = time.perf_counter() - t0
+    out["gpu_texel_msamples_s"] = covered * args.spp / dt / 1e6
+    out["gpu_bake_s"] = dt
+    if args.cpu:
+        t0 = time.perf_counter()
+        O.lm_bake(ref, 1.0, args.spp, 0)
+        dt = time.perf_counter() - t0
+        out["cpu_texel_msamples_s"] = covered * args.spp / dt / 1e6
+        out["cpu_bake_s"] = dt
+        out["cpu_threads"] = O.lib().oracle_get_threads()
+        k = 0
+        a, b = g_probes[k][cnt > 0], probes[k][cnt > 0]
+        out["probe0_rel_rmse"] = float(np.sqrt(np.mean((a - b) ** 2)) / np.sqrt(np.mean(b ** 2)))
+        out["probe0_texels_within_1e-3"] = float((np.abs(a - b).max(axis=1) <= 1e-3 * (np.abs(b).max(axis=1) + 1e-2)).mean())
+    ref.close()
+    print(json.dumps(out))
+    scene.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("config", choices=["c3", "c4"])
+    ap.add_argument("--spp", type=int, default=0)
+    ap.add_argument("--tris", type=int, default=1_000_000)
+    ap.add_argument("--emissive", type=float, default=0.001)
+    ap.add_argument("--cpu-spp", type=int, default=0)
+    ap.add_argument("--cpu", action="store_true")
+    args = ap.parse_args()
+    if args.config == "c3":
+        args.spp = args.spp or 256
+        c3(args)
+    else:
+        args.spp = args.spp or 64
+        c4(args)
+
+
+if __name__ == "__main__":
+    main()
