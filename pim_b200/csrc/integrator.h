@@ -424,26 +424,43 @@ template <class Stack>
 PT_D Scatter Scatter_Principled(Rng& rng, const DScene& S, const SurfHit& surf, V3 I, Stack& st)   // :1670-1707
 {
     if (surf.flags & MatFlag_Refractive) return Scatter_Refractive(rng, S, surf, I, st);
+    // Same arithmetic as the reference's two branches, arranged so that the two expensive lobe
+    // evaluations run once for the whole warp: only the direction sampling diverges.
     Scatter sc;
-    float amtSpec = f1_lerp(0.5f, 1.0f, surf.metallic);
-    float amtDiffuse = 1.0f - amtSpec;
-    if (rng_f32(rng) < amtSpec)
+    sc.luminance = v3s(0.0f);
+    sc.pos = surf.P;
+    const float amtSpec = f1_lerp(0.5f, 1.0f, surf.metallic);
+    const float amtDiffuse = 1.0f - amtSpec;
+    const bool spec = rng_f32(rng) < amtSpec;
+    if (spec)
     {
-        sc = Scatter_Specular(rng, S, surf, I);
+        V3 m = SampleGGXMicrofacet(rng_f2(rng), BrdfAlpha(surf.roughness));      // Scatter_Specular :1550-1565
+        m = TanToWorld(surf.N, m);
+        m = FixShadingNormal(surf.M, m);
+        sc.dir = reflect(I, m);
+    }
+    else
+    {
+        sc.dir = TanToWorld(surf.N, SampleCosineHemisphere(rng_f2(rng)));        // Scatter_Diffuse :1499-1514
+    }
+    const F4 evS = Eval_Specular(S, surf, I, sc.dir);
+    F4 evD = f4(0, 0, 0, 0);
+    if (!spec || amtDiffuse > kEpsilon) evD = Eval_Diffuse(surf, I, sc.dir);
+    if (spec)
+    {
+        sc.attenuation = v3(evS); sc.pdf = evS.w;
         if (amtDiffuse > kEpsilon)
         {
-            F4 ev = Eval_Diffuse(surf, I, sc.dir);
-            sc.attenuation = lerp(sc.attenuation, v3(ev), amtDiffuse);
-            sc.pdf = f1_lerp(sc.pdf, ev.w, amtDiffuse);
+            sc.attenuation = lerp(sc.attenuation, v3(evD), amtDiffuse);
+            sc.pdf = f1_lerp(sc.pdf, evD.w, amtDiffuse);
         }
     }
     else
     {
-        sc = Scatter_Diffuse(rng, surf, I);
-        F4 ev = Eval_Specular(S, surf, I, sc.dir);
-        sc.attenuation = lerp(sc.attenuation, v3(ev), amtSpec);
-        sc.pdf = f1_lerp(sc.pdf, ev.w, amtSpec);
+        sc.attenuation = lerp(v3(evD), v3(evS), amtSpec);
+        sc.pdf = f1_lerp(evD.w, evS.w, amtSpec);
     }
+    sc.evalW = sc.pdf;
     return sc;
 }
 

@@ -359,8 +359,10 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeA(D
 __global__ void __launch_bounds__(kTravThreads) k_wfConnect(DScene S, PoolView P)
 {
     PT_DECLARE_STACK(st);
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= P.counters[Wf_NumA] || P.stage[slot] != Slot_Connect) return;
+    // dense over the slots that asked for a ray (shadeA's list is ascending within each CTA's chunk)
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.counters[Wf_NumConnect]) return;
+    const int slot = P.connectList[i];
     F4 o = P.ro2[slot], d = P.rd2[slot];
     Hit hit;
     traverse<false, false>(S.bvh, v3(o), v3(d), 0.0f, o.w, hit, st, (TravCounters*)nullptr);
