@@ -532,6 +532,33 @@ __global__ void __launch_bounds__(128) k_collapse(BinTree T, const CollapseWork*
     }
 }
 
+} // namespace
+
+int radixSortBlocks(int n) { return (n + kSortTile - 1) / kSortTile; }
+
+// LSD radix sort of (64-bit key, 32-bit value) pairs, `passes` digits of 8 bits from bit 0.
+// Ping-pongs between the A and B arrays; returns true when the result is in the A arrays.
+bool radixSortPairs(uint64_t* keysA, uint64_t* keysB, uint32_t* valsA, uint32_t* valsB, int n, int passes,
+                    uint32_t* hist, cudaStream_t stream)
+{
+    const int sortBlocks = radixSortBlocks(n);
+    uint64_t* kin = keysA; uint64_t* kout = keysB;
+    uint32_t* vin = valsA; uint32_t* vout = valsB;
+    for (int pass = 0; pass < passes; ++pass)
+    {
+        const int shift = pass * 8;
+        k_sortHist<<<sortBlocks, kSortThreads, 0, stream>>>(kin, n, shift, hist, sortBlocks);
+        k_sortScan<<<1, 1024, 0, stream>>>(hist, 256 * sortBlocks);
+        k_sortScatter<<<sortBlocks, kSortThreads, 0, stream>>>(kin, vin, n, shift, hist, sortBlocks, kout, vout);
+        g_counters.kernelLaunches += 3;
+        std::swap(kin, kout);
+        std::swap(vin, vout);
+    }
+    return kin == keysA;
+}
+
+namespace {
+
 template <class T>
 bool devAlloc(T*& p, size_t count)
 {
@@ -601,19 +628,9 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
         }
         else
         {
-        uint64_t* kin = keysA; uint64_t* kout = keysB;
-        uint32_t* vin = valsA; uint32_t* vout = valsB;
-        for (int pass = 0; pass < 8; ++pass)
-        {
-            const int shift = pass * 8;
-            k_sortHist<<<sortBlocks, kSortThreads, 0, stream>>>(kin, n, shift, hist, sortBlocks);
-            k_sortScan<<<1, 1024, 0, stream>>>(hist, 256 * sortBlocks);
-            k_sortScatter<<<sortBlocks, kSortThreads, 0, stream>>>(kin, vin, n, shift, hist, sortBlocks, kout, vout);
-            g_counters.kernelLaunches += 3;
-            std::swap(kin, kout);
-            std::swap(vin, vout);
-        }
-        // 8 passes: result is back in keysA / valsA
+        radixSortPairs(keysA, keysB, valsA, valsB, n, 8, hist, stream);
+        uint64_t* kin = keysA;      // 8 passes: result is back in keysA / valsA
+        uint32_t* vin = valsA;
         ok = ok && PT_CUDA(cudaMemsetAsync(parent, 0xff, sizeof(int) * total, stream));
         ok = ok && PT_CUDA(cudaMemsetAsync(visits, 0, sizeof(int) * n, stream));
         if (n > 1) k_radixTree<<<(n - 1 + 255) / 256, 256, 0, stream>>>(kin, n, lo, hi, first, last, parent);

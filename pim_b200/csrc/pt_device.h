@@ -48,6 +48,11 @@ struct BvhBuffers
 bool buildBvh(const F4* dPositions, int32_t triCount, BvhBuffers& out, cudaStream_t stream);
 void freeBvh(BvhBuffers& b);
 
+// LSD radix sort of (64-bit key, 32-bit value) pairs (bvh_build.cu); hist holds 256 * radixSortBlocks(n) words
+int radixSortBlocks(int n);
+bool radixSortPairs(uint64_t* keysA, uint64_t* keysB, uint32_t* valsA, uint32_t* valsB, int n, int passes,
+                    uint32_t* hist, cudaStream_t stream);
+
 // ---------------------------------------------------------------- ray batches
 struct RayHitOut      // PtRayHit, 48 bytes
 {
