@@ -263,6 +263,7 @@ typedef struct PtSceneStats_s
     float cellsPerMeter;
     int32_t bvhNodeCount, bvhTriCount;
     float buildMs;
+    float phaseMs[6];       /* upload+flatten, BVH, emissive pdf, light grid, BRDF LUT, pool */
 } PtSceneStats;
 
 int32_t PtScene_GetStats(const PtScene* scene, PtSceneStats* stats);

@@ -60,6 +60,7 @@ struct PtScene_s
     int32_t gridCells = 0;
     uint32_t nextPass = 0;
     float buildMs = 0.0f;
+    float phaseMs[6] = { 0, 0, 0, 0, 0, 0 };
     // Pt_RayGen results: library-owned, valid until the second next call (the reference
     // hands out per-frame linear-allocator memory, path_tracer.c:2630-2631)
     pim_float4* rayGenColors[2] = { nullptr, nullptr };
@@ -183,7 +184,15 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
     if (!ensureInit()) return nullptr;
     if (!desc) { setError("PtScene_NewFromDesc: null description"); return nullptr; }
     auto t0 = std::chrono::steady_clock::now();
+    auto tPhase = t0;
     PtScene* s = new PtScene_s();
+    auto phase = [&](int k)
+    {
+        cudaStreamSynchronize(s->stream);
+        auto now = std::chrono::steady_clock::now();
+        s->phaseMs[k] += std::chrono::duration<float, std::milli>(now - tPhase).count();
+        tPhase = now;
+    };
     memset(&s->view, 0, sizeof(s->view));
     s->config = desc->config;
     if (s->config.ptDistMeters <= 0.0f) s->config.ptDistMeters = 1.5f;
@@ -271,6 +280,7 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
     V.positions = dPos; V.normals = dNrm; V.uvs = dUv; V.matIds = dMatIds; V.materials = dMats;
     V.vertCount = vertCount; V.matCount = desc->entityCount;
 
+    phase(0);
     // sky + BRDF LUT
     if (ok && desc->skyFaces && desc->skySize > 0)
     {
@@ -289,12 +299,14 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
         V.lut = s->dLut; V.lutW = lw; V.lutH = lh;
     }
 
+    phase(4);
     // BVH (RtcNewScene)
     const int32_t triCount = vertCount / 3;
     ok = ok && buildBvh(dPos, triCount, s->bvh, st);
     V.bvh.nodes = s->bvh.nodes; V.bvh.tris = s->bvh.tris;
     V.bvh.nodeCount = s->bvh.nodeCount; V.bvh.triCount = s->bvh.triCount;
 
+    phase(1);
     // SetupEmissives (path_tracer.c:845-883): device pdf, ordered compaction
     int32_t emissiveCount = 0;
     if (ok && triCount > 0)
@@ -327,6 +339,7 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
     }
     V.vertToEmit = dVertToEmit; V.emitToVert = dEmitToVert; V.emissiveCount = emissiveCount;
 
+    phase(2);
     // SetupLightGrid (path_tracer.c:992-1009): Grid_New over box_from_pts
     if (ok && vertCount > 0)
     {
@@ -348,6 +361,7 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
         ok = ok && launchLightGrid(V, s->config.ptDistMeters, s->config.seed, st);
     }
 
+    phase(3);
     // wavefront pool: 4 M slots x 316 B = 1.3 GB. Measured on cornell 1080p (Msamples/s): 128 K 599,
     // 512 K 1030, 1 M 1213, 2 M 1344, 4 M 1401, 8 M 1389 - the state streams through HBM fully
     // coalesced either way, and fewer, larger iterations amortise launches and the drain at the
@@ -359,6 +373,7 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
         ok = poolAlloc(s->pool, cap);
     }
     ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    phase(5);
     if (dSrcPos) cudaFree(dSrcPos);
     if (dSrcNrm) cudaFree(dSrcNrm);
     if (dSrcUv) cudaFree(dSrcUv);
@@ -803,6 +818,7 @@ int32_t PtScene_GetStats(const PtScene* scene, PtSceneStats* stats)
     stats->cellsPerMeter = V.grid.cellsPerMeter;
     stats->bvhNodeCount = V.bvh.nodeCount; stats->bvhTriCount = V.bvh.triCount;
     stats->buildMs = scene->buildMs;
+    for (int k = 0; k < 6; ++k) stats->phaseMs[k] = scene->phaseMs[k];
     return 0;
 }
 

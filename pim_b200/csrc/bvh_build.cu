@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 
 namespace pt {
 
@@ -28,6 +29,14 @@ constexpr int kSortTile = kSortThreads * kSortItems;   // keys per block
 #define PT_SAH_MAX_TRIS (4 << 20)
 #endif
 constexpr int kSahMaxTris = PT_SAH_MAX_TRIS;
+
+// PIMPT_SAH_MAX_TRIS overrides the threshold at run time (the tests use it to reach the LBVH path
+// with a scene that is quick to check)
+int sahMaxTris()
+{
+    const char* e = getenv("PIMPT_SAH_MAX_TRIS");
+    return e ? atoi(e) : kSahMaxTris;
+}
 
 __device__ __forceinline__ int floatToOrdered(float f)
 {
@@ -601,7 +610,7 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
         k_morton<<<blocks, 256, 0, stream>>>(leafLo, leafHi, n, bounds, keysA, valsA);
         g_counters.kernelLaunches += 3;
         const uint32_t* sortedVals = nullptr;
-        if (n <= kSahMaxTris)
+        if (n <= sahMaxTris())
         {
             // binned SAH: order[] doubles as the sorted-primitive array the collapse reads
             int* order = reinterpret_cast<int*>(valsA);

@@ -193,3 +193,52 @@ def test_random_soup_1m_vs_brute_force(api, oracle):
     s.close()
     assert bad == 0, bad
     assert worst <= T_REL
+
+
+def _tiny_scene(tris, lut):
+    pos = np.zeros((len(tris) * 3, 4), np.float32)
+    pos[:, :3] = np.asarray(tris, np.float32).reshape(-1, 3)
+    pos[:, 3] = 1
+    nrm = np.zeros_like(pos); nrm[:, 2] = 1
+    desc = scenes.SceneDesc(brdf_lut=lut)
+    desc.textures.append(scenes.flat_texture(np.array([0.5, 0.5, 0.5, 1], np.float32)))
+    desc.textures.append(scenes.flat_texture(np.array([0.9, 1.0, 0.0, 0.0], np.float32)))
+    desc.entities.append(scenes.Entity(pos, nrm, np.zeros_like(pos), np.eye(4, dtype=np.float32).reshape(-1), 0, 1))
+    return desc
+
+
+@pytest.mark.parametrize("count", [1, 2, 3, 4, 9])
+def test_tiny_and_degenerate_scenes(api, lut, count):
+    """1..9 triangles (root is a leaf cluster up to 3), including coincident and zero-area ones."""
+    base = [[[-1, -1, 0], [1, -1, 0], [0, 1, 0]]]
+    tris = [np.asarray(base[0], np.float32) + [0, 0, 0.5 * k] for k in range(count)]
+    if count >= 4:
+        tris[1] = tris[0].copy()                     # coincident duplicate: lowest primitive id wins
+        tris[2] = np.zeros((3, 3), np.float32)       # zero-area triangle: never hit
+    s = api.Scene(_tiny_scene(tris, lut))
+    ro = np.array([[0, 0, -5, 0], [0, 0, 5, 0], [5, 5, -5, 0]], np.float32)
+    rd = np.array([[0, 0, 1, 100], [0, 0, -1, 100], [0, 0, 1, 100]], np.float32)
+    h = s.intersect(ro, rd)
+    assert h["iVert"][0] == 0 and abs(h["wuvt"][0, 3] - 5.0) < 1e-5 and h["type"][0] == 1   # back face of CCW triangle
+    far = 3 * (count - 1)
+    if count >= 4 and far == 6:
+        far = 3
+    assert h["iVert"][1] == far and h["type"][1] == 2
+    assert h["type"][2] == 0
+    s.close()
+
+
+def test_lbvh_path_matches_sah_path(api, lut, oracle, monkeypatch):
+    """Above PT_SAH_MAX_TRIS the tree comes from the Morton radix tree; both builders must give
+    the same hits (closest hit is unique up to ties, which resolve by primitive id)."""
+    desc = scenes.random_soup(200_000, seed=5, extent=20.0)
+    ro, rd = scenes.random_rays(100_000, seed=6, extent=20.0)
+    s = api.Scene(desc)
+    a = s.intersect(ro, rd)
+    s.close()
+    monkeypatch.setenv("PIMPT_SAH_MAX_TRIS", "1000")
+    s = api.Scene(desc)
+    b = s.intersect(ro, rd)
+    s.close()
+    assert (a["iVert"] == b["iVert"]).all() and np.array_equal(a["wuvt"], b["wuvt"])
+    assert (a["type"] != 0).mean() > 0.05

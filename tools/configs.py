@@ -33,7 +33,8 @@ def c3(args):
     build_s = time.perf_counter() - t0
     st = scene.stats
     out = {"config": "c3 interior", "tris": desc.tri_count, "emissive_tris": st.emissiveCount,
-           "grid": list(st.gridSize), "bvh_nodes": st.bvhNodeCount, "scene_gen_s": gen_s, "scene_build_s": build_s}
+           "grid": list(st.gridSize), "bvh_nodes": st.bvhNodeCount, "scene_gen_s": gen_s, "scene_build_s": build_s,
+           "build_phase_ms": dict(zip(["flatten", "bvh", "emissive", "grid", "lut", "pool"], [round(x, 1) for x in st.phaseMs]))}
     W, H = 1920, 1080
     eye, at = [3.0, 1.5, 3.0], [30.0, 1.2, 27.0]
     cam, dof = api.make_camera(eye, at, 90.0), api.default_dof(auto_focus=False)
