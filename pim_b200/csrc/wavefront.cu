@@ -33,13 +33,14 @@ bool g_kernelTiming = false;
 int g_persistentTraversal = -1;   // -1: by scene size (see usePersistent)
 KernelStats g_kernelStats = {};
 
-// Refilling idle lanes pays off when rays take many steps: +22 % on the 10 M-triangle soup
-// (58 nodes per ray), -14 % on cornell boxes (3.8 nodes per ray; the refill's ballot and atomic
-// cost more than the idle lanes). The switch is the BVH size.
+// Refilling idle lanes pays off only when rays take very many steps: +22 % on the 10 M-triangle
+// soup (1.8 M nodes, 58 nodes per ray), but -14 % on cornell boxes (19 nodes, 2-4 per ray) and
+// -18 % on the 1 M-triangle interior (149 K nodes): there the refill's ballot + atomic cost more
+// than the idle lanes. The switch is the BVH size.
 bool usePersistent(int32_t bvhNodeCount)
 {
     if (g_persistentTraversal >= 0) return g_persistentTraversal != 0;
-    return bvhNodeCount >= 4096;
+    return bvhNodeCount >= (1 << 20);
 }
 
 namespace {
