@@ -140,8 +140,16 @@ typedef struct PtConfig_s
     float ptDistMeters;     /* cv_pt_dist_meters, default 1.5 (src/common/cvars.c:208) */
     uint32_t seed;          /* replaces the wall-clock seeding of src/common/random.c:45-65 */
     int32_t pathPoolSize;   /* resident path slots of the wavefront pool; 0 = default */
-    int32_t reserved;
+    int32_t bakeMode;       /* PtBakeMode for LmPack_BakeDesc */
 } PtConfig;
+
+/* How LmPack_BakeDesc orders a texel's samples. Both modes shoot BakeFn's rays (same RNG stream)
+ * and fold them into the lobes in sample order. PtBake_Wavefront traces all samples of all texels
+ * in parallel, the integrator's RNG seeded per ray. PtBake_Sequential traces a texel's samples one
+ * after the other in one thread with the integrator's RNG running on from sample to sample, which
+ * reproduces the seeded reference texel for texel (used by the parity tests) but exposes only
+ * texel-count parallelism. */
+typedef enum { PtBake_Wavefront = 0, PtBake_Sequential = 1 } PtBakeMode;
 
 typedef struct PtSceneDesc_s
 {

@@ -70,7 +70,7 @@ class PtEntityDesc(C.Structure):
 
 
 class PtConfig(C.Structure):
-    _fields_ = [("ptDistMeters", C.c_float), ("seed", C.c_uint32), ("pathPoolSize", C.c_int32), ("reserved", C.c_int32)]
+    _fields_ = [("ptDistMeters", C.c_float), ("seed", C.c_uint32), ("pathPoolSize", C.c_int32), ("bakeMode", C.c_int32)]
 
 
 class PtSceneDesc(C.Structure):
@@ -277,6 +277,7 @@ class Scene:
         d.config.ptDistMeters = desc.pt_dist_meters
         d.config.seed = desc.seed
         d.config.pathPoolSize = desc.path_pool_size
+        d.config.bakeMode = desc.bake_mode
         self.h = L.PtScene_NewFromDesc(C.byref(d))
         if not self.h:
             raise PtError("PtScene_NewFromDesc failed: " + last_error())

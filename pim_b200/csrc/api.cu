@@ -796,7 +796,11 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
         ok = ok && PT_CUDA(cudaMemcpyAsync(cnt.p, lm.sampleCounts, 4 * n, cudaMemcpyHostToDevice, st));
         view.position = (const float*)pos.p; view.normal = (const float*)nrm.p; view.sampleCounts = (float*)cnt.p;
         view.texelCount = (int32_t)n; view.texelBase = texelBase;
-        ok = ok && launchLightmapBake(scene->view, view, 1.0f / texelsPerMeter, timeSlice, spp, pass, scene->config.seed, st);
+        if (scene->config.bakeMode == PtBake_Sequential)
+            ok = ok && launchLightmapBake(scene->view, view, 1.0f / texelsPerMeter, timeSlice, spp, pass, scene->config.seed, st);
+        else
+            ok = ok && launchLightmapBakeWavefront(scene->view, scene->pool, view, 1.0f / texelsPerMeter, timeSlice, spp, pass,
+                                                   scene->config.seed, st);
         for (int k = 0; ok && k < 5; ++k)
             ok = PT_CUDA(cudaMemcpyAsync(lm.probes[k], probes[k].p, sizeof(F4) * n, cudaMemcpyDeviceToHost, st));
         ok = ok && PT_CUDA(cudaMemcpyAsync(lm.sampleCounts, cnt.p, 4 * n, cudaMemcpyDeviceToHost, st));

@@ -4,6 +4,9 @@
 #include "pt_device.h"
 #include "kernels_common.cuh"
 
+#include <algorithm>
+#include <cstring>
+
 namespace pt {
 
 namespace {
@@ -94,6 +97,143 @@ bool launchLightmapBake(const DScene& S, const LightmapView& lm, float metersPer
         S, lm, metersPerTexel, timeSlice, spp < 1 ? 1 : spp, pass, seed);
     g_counters.kernelLaunches++;
     return PT_CUDA(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------- wavefront bake
+// The same BakeFn, arranged for the GPU: (1) pick the texels that bake this pass (covered,
+// time-slice draw) and compact them, (2) one thread per picked texel writes the hemisphere
+// rays of all its samples (BakeFn's own RNG stream, so the rays are those of the sequential
+// kernel), (3) the rays of all texels and samples go through the path wavefront at once,
+// (4) one thread per texel folds its samples, in order, into the five lobes. Only the
+// integrator's RNG stream differs from k_lightmapBake: it is seeded per ray instead of running
+// on from the texel's previous sample, which is what lets the samples trace in parallel.
+
+__global__ void __launch_bounds__(256) k_bakeSelect(LightmapView lm, float timeSlice, uint32_t pass, uint32_t seed,
+                                                    int32_t* active, int32_t* counter)
+{
+    const int iTexel = blockIdx.x * blockDim.x + threadIdx.x;
+    bool pick = false;
+    if (iTexel < lm.texelCount && lm.sampleCounts[iTexel] != 0.0f)
+    {
+        Rng rng = seed_prng((uint32_t)(lm.texelBase + iTexel), pass, seed, Salt_Bake);
+        pick = !(rng_f32(rng) > timeSlice);
+    }
+    int total = 0;
+    const int idx = blockAlloc<8>(pick, counter, total);
+    if (pick) active[idx] = iTexel;
+}
+
+__global__ void __launch_bounds__(128) k_bakeRays(LightmapView lm, const int32_t* __restrict__ active, int first,
+                                                  int count, float metersPerTexel, int spp, uint32_t pass,
+                                                  uint32_t seed, F4* __restrict__ ro, F4* __restrict__ rd)
+{
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= count) return;
+    const int iTexel = active[first + a];
+    Rng rng = seed_prng((uint32_t)(lm.texelBase + iTexel), pass, seed, Salt_Bake);
+    rng_f32(rng);       // the time-slice draw
+    const V3 N = normalize(v3(lm.normal[3 * iTexel], lm.normal[3 * iTexel + 1], lm.normal[3 * iTexel + 2]));
+    const V3 P = v3(lm.position[3 * iTexel], lm.position[3 * iTexel + 1], lm.position[3 * iTexel + 2]) + N * kMilli;
+    const Tbn tbn = NormalToTBN(N);
+    for (int i = 0; i < spp; ++i)
+    {
+        V3 Lts = SampleUnitHemisphere(rng_f2(rng));
+        V3 dir = TbnToWorld(tbn, Lts);
+        float dt = (rng_f32(rng) - 0.5f) * metersPerTexel;
+        float db = (rng_f32(rng) - 0.5f) * metersPerTexel;
+        V3 org = (P + tbn.c0 * dt) + tbn.c1 * db;
+        ro[(size_t)a * spp + i] = f4(org, 0.0f);
+        rd[(size_t)a * spp + i] = f4(dir, 0.0f);
+    }
+}
+
+__global__ void __launch_bounds__(128) k_bakeFit(LightmapView lm, const int32_t* __restrict__ active, int first,
+                                                 int count, int spp, const F4* __restrict__ rd,
+                                                 const float* __restrict__ color3)
+{
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= count) return;
+    const int iTexel = active[first + a];
+    const V3 N = normalize(v3(lm.normal[3 * iTexel], lm.normal[3 * iTexel + 1], lm.normal[3 * iTexel + 2]));
+    const Tbn tbn = NormalToTBN(N);
+    const F4 kAxii[5] = {
+        f4(0.0f, 0.0f, 1.0f, 4.999773f), f4(0.577350f, 0.577350f, 0.577350f, 4.999773f),
+        f4(-0.577350f, 0.577350f, 0.577350f, 4.999773f), f4(0.577350f, -0.577350f, 0.577350f, 4.999773f),
+        f4(-0.577350f, -0.577350f, 0.577350f, 4.999773f) };
+    F4 probes[5], axii[5];
+    for (int i = 0; i < 5; ++i)
+    {
+        probes[i] = lm.probes[i][iTexel];
+        V3 ax = TbnToWorld(tbn, v3(kAxii[i]));
+        axii[i] = f4(ax, kAxii[i].w);
+    }
+    float sampleCount = lm.sampleCounts[iTexel];
+    for (int i = 0; i < spp; ++i)
+    {
+        const size_t j = (size_t)a * spp + i;
+        const V3 dir = v3(ldF4(rd + j));
+        const V3 c = v3(color3[3 * j], color3[3 * j + 1], color3[3 * j + 2]);
+        const float weight = 1.0f / sampleCount;
+        sampleCount += 1.0f;
+        SG_Accumulate(weight, dir, c, axii, probes, 5);
+    }
+    for (int i = 0; i < 5; ++i) lm.probes[i][iTexel] = probes[i];
+    lm.sampleCounts[iTexel] = sampleCount;
+}
+
+bool launchLightmapBakeWavefront(const DScene& S, PathPool& pool, const LightmapView& lm, float metersPerTexel,
+                                 float timeSlice, int32_t spp, uint32_t pass, uint32_t seed, cudaStream_t stream)
+{
+    if (lm.texelCount <= 0) return true;
+    if (spp < 1) spp = 1;
+    int32_t* dActive = nullptr;
+    int32_t* dCount = nullptr;
+    bool ok = PT_CUDA(cudaMalloc((void**)&dActive, sizeof(int32_t) * (size_t)lm.texelCount)) &&
+              PT_CUDA(cudaMalloc((void**)&dCount, sizeof(int32_t)));
+    ok = ok && PT_CUDA(cudaMemsetAsync(dCount, 0, sizeof(int32_t), stream));
+    int32_t nActive = 0;
+    if (ok)
+    {
+        k_bakeSelect<<<(lm.texelCount + 255) / 256, 256, 0, stream>>>(lm, timeSlice, pass, seed, dActive, dCount);
+        g_counters.kernelLaunches++;
+        ok = PT_CUDA(cudaMemcpyAsync(&nActive, dCount, sizeof(int32_t), cudaMemcpyDeviceToHost, stream)) &&
+             PT_CUDA(cudaStreamSynchronize(stream));
+    }
+    // texels per chunk: at most ~8 M rays (76 B each) in flight
+    const int chunkTexels = std::max(1, (8 << 20) / spp);
+    F4 *dRo = nullptr, *dRd = nullptr;
+    float* dColor = nullptr;
+    const size_t chunkRays = (size_t)std::min(chunkTexels, std::max(nActive, 1)) * (size_t)spp;
+    ok = ok && PT_CUDA(cudaMalloc((void**)&dRo, sizeof(F4) * chunkRays)) && PT_CUDA(cudaMalloc((void**)&dRd, sizeof(F4) * chunkRays)) &&
+         PT_CUDA(cudaMalloc((void**)&dColor, sizeof(float) * 3 * chunkRays));
+    for (int first = 0; ok && first < nActive; first += chunkTexels)
+    {
+        const int count = std::min(chunkTexels, nActive - first);
+        k_bakeRays<<<(count + 127) / 128, 128, 0, stream>>>(lm, dActive, first, count, metersPerTexel, spp, pass, seed, dRo, dRd);
+        g_counters.kernelLaunches++;
+        WorkDesc W;
+        memset(&W, 0, sizeof(W));
+        W.kind = Work_Rays; W.ro = dRo; W.rd = dRd; W.count = (int64_t)count * spp;
+        // per-ray integrator seeds: distinct per texel chunk and pass
+        W.passBase = pass * 0x9E3779B9u + (uint32_t)(lm.texelBase + first);
+        W.seed = seed; W.salt = Salt_Bake;
+        W.sumColor = dColor; W.accumulate = 0;
+        float ms = 0.0f;
+        ok = runWavefront(S, pool, W, stream, &ms);
+        if (ok)
+        {
+            k_bakeFit<<<(count + 127) / 128, 128, 0, stream>>>(lm, dActive, first, count, spp, dRd, dColor);
+            g_counters.kernelLaunches++;
+            ok = PT_CUDA(cudaGetLastError());
+        }
+    }
+    ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
+    if (dActive) cudaFree(dActive);
+    if (dCount) cudaFree(dCount);
+    if (dRo) cudaFree(dRo);
+    if (dRd) cudaFree(dRd);
+    if (dColor) cudaFree(dColor);
+    return ok;
 }
 
 } // namespace pt

@@ -164,6 +164,10 @@ struct LightmapView
 bool launchLightmapBake(const DScene& S, const LightmapView& lm, float metersPerTexel, float timeSlice, int32_t spp,
                         uint32_t pass, uint32_t seed, cudaStream_t stream);
 
+// the same bake through the path wavefront: all samples of all picked texels trace in parallel
+bool launchLightmapBakeWavefront(const DScene& S, PathPool& pool, const LightmapView& lm, float metersPerTexel,
+                                 float timeSlice, int32_t spp, uint32_t pass, uint32_t seed, cudaStream_t stream);
+
 // image helpers
 bool launchResolve(float* dImage, const float* dSum, int64_t n, float prevCount, float addCount, cudaStream_t stream);
 bool launchLerp(float* dImage, const float* dSample, int64_t n, float weight, cudaStream_t stream);

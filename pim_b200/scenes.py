@@ -57,6 +57,7 @@ class SceneDesc:
     pt_dist_meters: float = 1.5
     seed: int = 1
     path_pool_size: int = 0
+    bake_mode: int = 0              # 0 wavefront, 1 sequential (texel-exact vs the seeded reference)
 
     @property
     def tri_count(self):

@@ -98,10 +98,12 @@ def c4(args):
     t0 = time.perf_counter()
     pages = O.lm_pack(1024, 16.0)
     pack_s = time.perf_counter() - t0
-    out = {"config": "c4 cornell lightmap 16 texels/m", "pages": pages, "lm_pack_cpu_s": pack_s, "spp": args.spp}
+    out = {"config": "c4 cornell lightmap 16 texels/m", "pages": pages, "lm_pack_cpu_s": pack_s, "spp": args.spp,
+           "bake_mode": "sequential" if args.sequential else "wavefront"}
     probes, pos, nrm, cnt = O.lm_page(0)
     covered = int((cnt > 0).sum())
     out["covered_texels"] = covered
+    desc.bake_mode = 1 if args.sequential else 0
     scene = api.Scene(desc)
     g_probes = [np.ascontiguousarray(p.copy()) for p in probes]
     g_pos, g_nrm, g_cnt = pos.copy(), nrm.copy(), cnt.copy()
@@ -142,6 +144,7 @@ def main():
     ap.add_argument("--emissive", type=float, default=0.001)
     ap.add_argument("--cpu-spp", type=int, default=0)
     ap.add_argument("--cpu", action="store_true")
+    ap.add_argument("--sequential", action="store_true", help="c4: PtBake_Sequential")
     args = ap.parse_args()
     if args.config == "c3":
         args.spp = args.spp or 256
