@@ -125,7 +125,8 @@ __global__ void __launch_bounds__(256) k_bakeSelect(LightmapView lm, float timeS
 
 __global__ void __launch_bounds__(128) k_bakeRays(LightmapView lm, const int32_t* __restrict__ active, int first,
                                                   int count, float metersPerTexel, int spp, uint32_t pass,
-                                                  uint32_t seed, F4* __restrict__ ro, F4* __restrict__ rd)
+                                                  uint32_t seed, F4* __restrict__ ro, F4* __restrict__ rd,
+                                                  uint32_t* __restrict__ ids)
 {
     const int a = blockIdx.x * blockDim.x + threadIdx.x;
     if (a >= count) return;
@@ -144,6 +145,8 @@ __global__ void __launch_bounds__(128) k_bakeRays(LightmapView lm, const int32_t
         V3 org = (P + tbn.c0 * dt) + tbn.c1 * db;
         ro[(size_t)a * spp + i] = f4(org, 0.0f);
         rd[(size_t)a * spp + i] = f4(dir, 0.0f);
+        // the integrator's seed follows the texel and sample, not the (unordered) compaction slot
+        ids[(size_t)a * spp + i] = (uint32_t)(lm.texelBase + iTexel) * (uint32_t)spp + (uint32_t)i;
     }
 }
 
@@ -203,19 +206,20 @@ bool launchLightmapBakeWavefront(const DScene& S, PathPool& pool, const Lightmap
     const int chunkTexels = std::max(1, (8 << 20) / spp);
     F4 *dRo = nullptr, *dRd = nullptr;
     float* dColor = nullptr;
+    uint32_t* dIds = nullptr;
     const size_t chunkRays = (size_t)std::min(chunkTexels, std::max(nActive, 1)) * (size_t)spp;
     ok = ok && PT_CUDA(cudaMalloc((void**)&dRo, sizeof(F4) * chunkRays)) && PT_CUDA(cudaMalloc((void**)&dRd, sizeof(F4) * chunkRays)) &&
-         PT_CUDA(cudaMalloc((void**)&dColor, sizeof(float) * 3 * chunkRays));
+         PT_CUDA(cudaMalloc((void**)&dColor, sizeof(float) * 3 * chunkRays)) &&
+         PT_CUDA(cudaMalloc((void**)&dIds, sizeof(uint32_t) * chunkRays));
     for (int first = 0; ok && first < nActive; first += chunkTexels)
     {
         const int count = std::min(chunkTexels, nActive - first);
-        k_bakeRays<<<(count + 127) / 128, 128, 0, stream>>>(lm, dActive, first, count, metersPerTexel, spp, pass, seed, dRo, dRd);
+        k_bakeRays<<<(count + 127) / 128, 128, 0, stream>>>(lm, dActive, first, count, metersPerTexel, spp, pass, seed, dRo, dRd, dIds);
         g_counters.kernelLaunches++;
         WorkDesc W;
         memset(&W, 0, sizeof(W));
-        W.kind = Work_Rays; W.ro = dRo; W.rd = dRd; W.count = (int64_t)count * spp;
-        // per-ray integrator seeds: distinct per texel chunk and pass
-        W.passBase = pass * 0x9E3779B9u + (uint32_t)(lm.texelBase + first);
+        W.kind = Work_Rays; W.ro = dRo; W.rd = dRd; W.rngIds = dIds; W.count = (int64_t)count * spp;
+        W.passBase = pass;
         W.seed = seed; W.salt = Salt_Bake;
         W.sumColor = dColor; W.accumulate = 0;
         float ms = 0.0f;
@@ -233,6 +237,7 @@ bool launchLightmapBakeWavefront(const DScene& S, PathPool& pool, const Lightmap
     if (dRo) cudaFree(dRo);
     if (dRd) cudaFree(dRd);
     if (dColor) cudaFree(dColor);
+    if (dIds) cudaFree(dIds);
     return ok;
 }
 

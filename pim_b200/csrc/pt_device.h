@@ -127,6 +127,7 @@ struct WorkDesc
     CamParams cam;          // Work_Camera: work item = sample * (w*h) + pixel
     const F4* ro;           // Work_Rays: explicit rays, one path per item
     const F4* rd;
+    const uint32_t* rngIds; // Work_Rays: optional RNG work-item id per ray (default: the ray's index)
     V3 origin;              // Work_Sphere: Pt_RayGen, uniform sphere directions from origin
     int64_t count;          // total work items
     uint32_t passBase;      // RNG pass of sample 0

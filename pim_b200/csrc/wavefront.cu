@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(128) k_wfRegen(DScene S, PoolView P, WorkDesc 
     }
     else if (W.kind == Work_Rays)
     {
-        rng = seed_ctx((uint32_t)item, W.passBase, W.seed, W.salt);
+        rng = seed_ctx(W.rngIds ? W.rngIds[item] : (uint32_t)item, W.passBase, W.seed, W.salt);
         F4 o = ldF4(W.ro + item), d = ldF4(W.rd + item);
         ro = v3(o); rd = v3(d);
         outIndex = (uint32_t)item;
@@ -511,6 +511,11 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
         if (timing) for (int k = 0; ok && k < 6; ++k) ok = PT_CUDA(cudaEventCreate(&ev[r][k]));
     }
     bool finished = false;
+    // Upper bound on the live range of the iterations still to be launched. While work items
+    // remain the pool refills to capacity; once they are used up the live count only shrinks, so
+    // the (lagged) status gives a bound and the drain iterations launch correspondingly fewer CTAs.
+    int bound = cap;
+    bool workLeft = true;
     auto consume = [&](unsigned long long it) -> bool
     {
         const int r = (int)(it % kRing);
@@ -530,25 +535,33 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
             g_kernelStats.extendRays += (unsigned long long)(uint32_t)st[2];
             g_kernelStats.connectRays += (unsigned long long)(uint32_t)st[3];
         }
+        if (st[1] == 0)
+        {
+            workLeft = false;
+            bound = std::min(bound, std::max(st[0], 1));
+        }
         if (st[0] == 0 && st[1] == 0) finished = true;
         return true;
     };
     while (ok && !finished)
     {
         const int r = (int)(iterations % kRing);
+        const unsigned gridLive = (unsigned)((bound + kTravThreads - 1) / kTravThreads);
+        const unsigned gridRegen = workLeft ? grid : 1u;
+        const unsigned gridPersist = std::min<unsigned>(gridLive, gridP);
         if (timing) cudaEventRecord(ev[r][0], stream);
-        k_wfRegen<<<grid, 128, 0, stream>>>(S, P, work);
+        k_wfRegen<<<gridRegen, 128, 0, stream>>>(S, P, work);
         k_wfAfterRegen<<<1, 1, 0, stream>>>(P);
         if (timing) cudaEventRecord(ev[r][1], stream);
-        if (persistent) k_wfTracePersistent<false><<<gridP, kTravThreads, 0, stream>>>(S, P);
-        else k_wfExtend<<<grid, kTravThreads, 0, stream>>>(S, P);
+        if (persistent) k_wfTracePersistent<false><<<gridPersist, kTravThreads, 0, stream>>>(S, P);
+        else k_wfExtend<<<gridLive, kTravThreads, 0, stream>>>(S, P);
         if (timing) cudaEventRecord(ev[r][2], stream);
-        k_wfShadeA<<<grid, kShadeThreads, 0, stream>>>(S, P, work);
+        k_wfShadeA<<<gridLive, kShadeThreads, 0, stream>>>(S, P, work);
         if (timing) cudaEventRecord(ev[r][3], stream);
-        if (persistent) k_wfTracePersistent<true><<<gridP, kTravThreads, 0, stream>>>(S, P);
-        else k_wfConnect<<<grid, kTravThreads, 0, stream>>>(S, P);
+        if (persistent) k_wfTracePersistent<true><<<gridPersist, kTravThreads, 0, stream>>>(S, P);
+        else k_wfConnect<<<gridLive, kTravThreads, 0, stream>>>(S, P);
         if (timing) cudaEventRecord(ev[r][4], stream);
-        k_wfShadeB<<<grid, kShadeThreads, 0, stream>>>(S, P, work);
+        k_wfShadeB<<<gridLive, kShadeThreads, 0, stream>>>(S, P, work);
         if (timing) cudaEventRecord(ev[r][5], stream);
         k_wfEndIteration<<<1, 1, 0, stream>>>(P, dStatus);
         g_counters.kernelLaunches += 7;
