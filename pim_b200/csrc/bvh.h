@@ -292,10 +292,14 @@ PT_D int ffs32(uint32_t x) { return __builtin_ffs((int)x) - 1; }
 PT_D float mulr(float a, float b) { return __fmul_rn(a, b); }
 PT_D float addr(float a, float b) { return __fadd_rn(a, b); }
 PT_D float subr(float a, float b) { return __fsub_rn(a, b); }
+PT_D float divr(float a, float b) { return __fdiv_rn(a, b); }      // IEEE even under --use_fast_math
+PT_D float sqrtr(float a) { return __fsqrt_rn(a); }
 #else
 PT_D float mulr(float a, float b) { return a * b; }
 PT_D float addr(float a, float b) { return a + b; }
 PT_D float subr(float a, float b) { return a - b; }
+PT_D float divr(float a, float b) { return a / b; }
+PT_D float sqrtr(float a) { return sqrtf(a); }
 #endif
 PT_D float dotr(V3 a, V3 b) { return addr(addr(mulr(a.x, b.x), mulr(a.y, b.y)), mulr(a.z, b.z)); }
 PT_D V3 crossr(V3 a, V3 b)
@@ -316,7 +320,7 @@ PT_D bool triTest(const PackedTri* tp, V3 ro, V3 rd, float tNear, float tFar,
     V3 p = crossr(rd, e2);
     float det = dotr(e1, p);
     if (det == 0.0f) return false;
-    float inv = 1.0f / det;
+    float inv = divr(1.0f, det);
     V3 tv = v3(subr(ro.x, v0.x), subr(ro.y, v0.y), subr(ro.z, v0.z));
     u = mulr(dotr(tv, p), inv);
     if (!(u >= 0.0f && u <= 1.0f)) return false;

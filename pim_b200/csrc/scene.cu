@@ -214,7 +214,10 @@ __global__ void __launch_bounds__(256) k_flatten(const EntityUpload* __restrict_
     V3 wn = v3(addr(mulr(I[0], nx), addr(mulr(I[3], ny), mulr(I[6], nz))),
                addr(mulr(I[1], nx), addr(mulr(I[4], ny), mulr(I[7], nz))),
                addr(mulr(I[2], nx), addr(mulr(I[5], ny), mulr(I[8], nz))));
-    wn = wn / sqrtf(dotr(wn, wn));
+    {
+        const float len = sqrtr(dotr(wn, wn));      // f4_normalize3 = f4_divvs(x, length): IEEE here, the
+        wn = v3(divr(wn.x, len), divr(wn.y, len), divr(wn.z, len));   // library is built with --use_fast_math
+    }
     nrm[v] = f4(wn, 0.0f);
     // uvs are copied per whole triangle (path_tracer.c:755-766)
     int tri = j / 3;
@@ -340,8 +343,8 @@ __global__ void __launch_bounds__(kTravThreads) k_lightGrid(DScene S, float mete
                        addr(addr(mulr(A.y, wuv.x), mulr(B.y, wuv.y)), mulr(C.y, wuv.z)),
                        addr(addr(mulr(A.z, wuv.x), mulr(B.z, wuv.y)), mulr(C.z, wuv.z)));
             V3 rd = v3(subr(at.x, ro.x), subr(at.y, ro.y), subr(at.z, ro.z));
-            float dist = sqrtf(dotr(rd, rd));
-            rd = rd / dist;
+            float dist = sqrtr(dotr(rd, rd));
+            rd = v3(divr(rd.x, dist), divr(rd.y, dist), divr(rd.z, dist));
             float tFar = dist - 0.01f * kMilli;
             bool visible = false;
             if (tFar > 0.0f)
