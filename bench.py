@@ -278,6 +278,19 @@ def run_ours(args, rank, world, local_rank):
         avg_s = ext["ms"] * 1e-3 / max(ext["launches"], 1)
         achieved = rays_per_launch * b_ray / max(avg_s, 1e-12) / 1e9
         total_rays = kstats["extendRays"] + kstats["connectRays"]
+        # whole-step figure of SURVEY.md 8(d): B_sample = 72 + L*(R*B_ray + 192), L = bounces per
+        # path, R = rays per bounce, 192 = one read + one write of the path state per bounce
+        paths = max(counters["paths"], 1)
+        bounces = kstats["extendRays"] / paths
+        rays_per_bounce = total_rays / max(kstats["extendRays"], 1)
+        b_sample = 72 + bounces * (rays_per_bounce * b_ray + 192)
+        sample_gbs = value * 1e6 / world * b_sample / 1e9
+        # measured DRAM bytes per ray of k_wfExtend from the committed ncu capture (path state in, hit out)
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+        if os.path.exists(tpath):
+            with open(tpath) as f:
+                traffic = json.load(f)["k_wfExtend"]["dram_bytes_per_ray"] * rays_per_launch
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
@@ -292,11 +305,14 @@ def run_ours(args, rank, world, local_rank):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": C.sizeof(api.Camera) + C.sizeof(api.PtDofInfo),
                     "d2h_bytes_per_step": 3 * n3 * 4, "steps": e2e_steps, "mean_luminance": mean_lum},
             "roofline": {"bound": "hbm", "kernel": "k_wfExtend", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "bytes_per_ray": b_ray, "rays_per_launch": rays_per_launch,
                          "avg_launch_ms": avg_s * 1e3,
                          "note": "108-triangle BVH is L1/L2 resident: algorithmic bytes never reach HBM, "
                                  "so frac can exceed 1 (SURVEY.md 8(d))"},
+            "roofline_sample": {"bound": "hbm", "bytes_per_sample": b_sample, "bounces_per_path": bounces,
+                                "rays_per_bounce": rays_per_bounce, "achieved": sample_gbs, "peak": peak, "unit": "GB/s",
+                                "frac": sample_gbs / peak, "note": "per GPU; whole step by SURVEY.md 8(d) B_sample"},
             "kernels": kern,
             "clocks": clocks,
         }
