@@ -3,7 +3,7 @@
 
 A step is one progressive pass of the hot path: `--spp-per-step` samples of every
 pixel of the 1080p frame (BASELINE.json configs[1]; the full config is 1024 spp =
-16 steps of the default 64 spp). `value` times Pt_TraceSpp_Device with the scene and the
+the default 16 steps of 64 spp). `value` times Pt_TraceSpp_Device with the scene and the
 accumulation images resident in HBM; `e2e` times Pt_TraceSpp, the reference-facing
 call with host PtTrace buffers (device->host copies of the three images inside).
 With N > 1 every rank renders its own sample indices of the full frame (scene
@@ -34,7 +34,7 @@ TRAVERSAL_COUNTS = os.path.join(ROOT, "baseline", "traversal_counts.json")
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--steps", type=int, default=16)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--spp-per-step", type=int, default=64)
