@@ -92,12 +92,11 @@ struct PathPool
 {
     int32_t capacity = 0;
     // persistent path state, double buffered (survivors are moved when they are compacted)
-    U4* rng[2] = { nullptr, nullptr };
     F4* ro[2] = { nullptr, nullptr };       // xyz origin, w = weight
     F4* rd[2] = { nullptr, nullptr };       // xyz direction, w = bits: bounce | prevFlags<<16
-    F4* atten[2] = { nullptr, nullptr };    // xyz attenuation, w = bits: output index
-    F4* lum[2] = { nullptr, nullptr };      // xyz luminance
-    F4* albedo[2] = { nullptr, nullptr };   // xyz albedo accumulator
+    F4* atten[2] = { nullptr, nullptr };    // xyz attenuation, w = bits: rng.x
+    F4* lum[2] = { nullptr, nullptr };      // xyz luminance, w = bits: rng.y
+    F4* albedo[2] = { nullptr, nullptr };   // xyz albedo accumulator, w = bits: result index
     F4* normal[2] = { nullptr, nullptr };   // xyz normal accumulator
     // per-iteration temporaries
     U4* hit1 = nullptr;     // t, u, v (float bits), primitive index
@@ -105,7 +104,6 @@ struct PathPool
     F4* rd2 = nullptr;      // secondary ray direction, w = bits: kind | iVertLight<<2
     F4* pend = nullptr;     // Pending.a0..a3
     U4* hit2 = nullptr;
-    int32_t* stage = nullptr;    // per slot: dead / needs extend / needs connect / shade only
     int32_t* connectList = nullptr;   // slots that need a connect ray this iteration (persistent traversal)
     int32_t* counters = nullptr; // device: see WfCounter
     int32_t* hostCounters = nullptr; // pinned mirror of the per-iteration status

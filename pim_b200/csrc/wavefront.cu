@@ -53,15 +53,16 @@ constexpr int kShadeThreads = 128;
 #endif
 constexpr int kShadeBlocksPerSm = PT_SHADE_BLOCKS;
 
-enum : int32_t { Slot_Dead = 0, Slot_Extend = 1, Slot_Connect = 2, Slot_ShadeOnly = 3 };
+// what stage A leaves for stage B rides in the low two bits of rd2.w: Pend_None (shade without a
+// second ray), Pend_Light / Pend_Bsdf (the connect kernel traced one), or kPendDead
+constexpr uint32_t kPendDead = 3u;
 
-struct PathArrays { U4* rng; F4* ro; F4* rd; F4* atten; F4* lum; F4* albedo; F4* normal; };
+struct PathArrays { F4* ro; F4* rd; F4* atten; F4* lum; F4* albedo; F4* normal; };
 
 struct PoolView
 {
     PathArrays cur, next;         // persistent path state, ping-pong
     U4* hit1; F4* ro2; F4* rd2; F4* pend; U4* hit2;   // per-iteration temporaries
-    int32_t* stage;
     int32_t* connectList;
     int32_t* counters;
     unsigned long long* cursor;   // [0] next work item (may run past the total), [1] total
@@ -89,32 +90,41 @@ __device__ __forceinline__ int warpAlloc(bool pred, int32_t* counter)
     return base + __popc(mask & ((1u << lane) - 1u));
 }
 
-__device__ __forceinline__ void loadPath(const PathArrays& P, int slot, Path& p, uint32_t& outIndex)
+// Path state in HBM: six 16-byte fields per slot. Only two of the RNG's four words ever advance
+// on a path (rng_u32 / rng_f32 / rng_f2), so they ride in the spare lanes of atten and lum — the
+// fields stage A rewrites anyway — and the result index rides with the denoiser accumulators.
+//   ro     = origin.xyz, weight          rd     = direction.xyz, bounce | prevRefractive << 16
+//   atten  = attenuation.xyz, rng.x      lum    = luminance.xyz, rng.y
+//   albedo = albedo.xyz, result index    normal = normal.xyz, 0
+// Stage A needs the first four (plus the last two only when a path ends or scatters in a medium).
+__device__ __forceinline__ void loadPathHot(const PathArrays& P, int slot, Path& p)
 {
-    U4 r = P.rng[slot];
-    p.rng.x = r.x; p.rng.y = r.y; p.rng.z = r.z; p.rng.w = r.w;
-    F4 a = P.ro[slot], b = P.rd[slot], c = P.atten[slot], d = P.lum[slot], e = P.albedo[slot], f = P.normal[slot];
+    F4 a = P.ro[slot], b = P.rd[slot], c = P.atten[slot], d = P.lum[slot];
     p.ro = v3(a); p.weight = a.w;
     p.rd = v3(b);
     uint32_t bits = f2u(b.w);
     p.bounce = (int32_t)(bits & 0xffffu);
     p.prevFlags = (bits >> 16) ? MatFlag_Refractive : 0u;
-    p.atten = v3(c); outIndex = f2u(c.w);
-    p.lum = v3(d);
-    p.albedo = v3(e);
+    p.atten = v3(c); p.rng.x = f2u(c.w);
+    p.lum = v3(d); p.rng.y = f2u(d.w);
+    p.rng.z = p.rng.w = 0u;
+}
+
+__device__ __forceinline__ void loadPathCold(const PathArrays& P, int slot, Path& p, uint32_t& outIndex)
+{
+    F4 e = P.albedo[slot], f = P.normal[slot];
+    p.albedo = v3(e); outIndex = f2u(e.w);
     p.normal = v3(f);
 }
 
 __device__ __forceinline__ void storePath(const PathArrays& P, int slot, const Path& p, uint32_t outIndex)
 {
-    U4 r; r.x = p.rng.x; r.y = p.rng.y; r.z = p.rng.z; r.w = p.rng.w;
-    P.rng[slot] = r;
     P.ro[slot] = f4(p.ro, p.weight);
     uint32_t bits = (uint32_t)p.bounce | ((p.prevFlags & MatFlag_Refractive) ? 0x10000u : 0u);
     P.rd[slot] = f4(p.rd, u2f(bits));
-    P.atten[slot] = f4(p.atten, u2f(outIndex));
-    P.lum[slot] = f4(p.lum, 0.0f);
-    P.albedo[slot] = f4(p.albedo, 0.0f);
+    P.atten[slot] = f4(p.atten, u2f(p.rng.x));
+    P.lum[slot] = f4(p.lum, u2f(p.rng.y));
+    P.albedo[slot] = f4(p.albedo, u2f(outIndex));
     P.normal[slot] = f4(p.normal, 0.0f);
 }
 
@@ -305,41 +315,37 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeA(D
     LazyStack st;
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;     // always below the pool capacity
     // issue the state loads before the live count is known: they do not depend on it
-    Path p; uint32_t outIndex = 0;
-    loadPath(P.cur, slot, p, outIndex);
+    Path p;
+    loadPathHot(P.cur, slot, p);
+    p.albedo = p.normal = v3s(0.0f);
     const U4 h1 = P.hit1[slot];
     const bool active = slot < P.counters[Wf_NumA];
     bool ray2 = false, moved = false;
+    uint32_t outIndex = 0;
     if (active)
     {
         RayHit hit = unpackHit(S, p.rd, h1);
         Pending pend;
         int r = pathStageA(S, p, hit, pend, st);
-        if (r == Stage_Next)
+        if (r == Stage_Done || r == Stage_Next)
         {
-            // scattered inside the medium: next bounce starts without a surface interaction
-            if (pathAdvance(p)) moved = true;
-            else r = Stage_Done;
+            // the path ends here or scattered inside the medium: both need the rest of the state
+            loadPathCold(P.cur, slot, p, outIndex);
+            // scattered: the next bounce starts without a surface interaction
+            if (r == Stage_Next && pathAdvance(p)) moved = true;
+            else emitResult(W, p, outIndex);
+            P.rd2[slot] = f4(0.0f, 0.0f, 0.0f, u2f(kPendDead));
         }
-        if (r == Stage_Done)
-        {
-            emitResult(W, p, outIndex);
-            P.stage[slot] = Slot_Dead;
-        }
-        else if (r == Stage_Ray2 || r == Stage_NoRay2)
+        else
         {
             ray2 = (r == Stage_Ray2);
             // stage A only changes rng, atten, lum
-            U4 rr; rr.x = p.rng.x; rr.y = p.rng.y; rr.z = p.rng.z; rr.w = p.rng.w;
-            P.cur.rng[slot] = rr;
-            P.cur.atten[slot] = f4(p.atten, u2f(outIndex));
-            P.cur.lum[slot] = f4(p.lum, 0.0f);
+            P.cur.atten[slot] = f4(p.atten, u2f(p.rng.x));
+            P.cur.lum[slot] = f4(p.lum, u2f(p.rng.y));
             P.ro2[slot] = f4(pend.ro2, pend.tFar2);
             P.rd2[slot] = f4(pend.rd2, u2f((uint32_t)pend.kind | ((uint32_t)(pend.iVertLight + 1) << 2)));
             P.pend[slot] = f4(pend.a0, pend.a1, pend.a2, pend.a3);
-            P.stage[slot] = ray2 ? Slot_Connect : Slot_ShadeOnly;
         }
-        if (moved) P.stage[slot] = Slot_Dead;
     }
     {
         const int dst = warpAlloc(moved, &P.counters[Wf_NumNext]);      // rare: no atomic unless a lane scattered
@@ -378,24 +384,25 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeB(D
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;     // always below the pool capacity
     // loads that do not depend on the live count go first
     Path p; uint32_t outIndex = 0;
-    loadPath(P.cur, slot, p, outIndex);
+    loadPathHot(P.cur, slot, p);
+    loadPathCold(P.cur, slot, p, outIndex);
     const U4 h1 = P.hit1[slot], h2 = P.hit2[slot];
     const F4 o2 = P.ro2[slot], d2 = P.rd2[slot], pa = P.pend[slot];
-    const int stage = (slot < P.counters[Wf_NumA]) ? P.stage[slot] : Slot_Dead;
+    const uint32_t bits = f2u(d2.w);
+    const uint32_t kind = (slot < P.counters[Wf_NumA]) ? (bits & 3u) : kPendDead;
     bool alive = false;
-    if (stage == Slot_Connect || stage == Slot_ShadeOnly)
+    if (kind != kPendDead)
     {
         RayHit hit = unpackHit(S, p.rd, h1);
         Pending pend;
-        const uint32_t bits = f2u(d2.w);
-        pend.kind = (int32_t)(bits & 3u);
+        pend.kind = (int32_t)kind;
         pend.iVertLight = (int32_t)(bits >> 2) - 1;
         pend.ro2 = v3(o2); pend.tFar2 = o2.w; pend.rd2 = v3(d2);
         pend.a0 = pa.x; pend.a1 = pa.y; pend.a2 = pa.z; pend.a3 = pa.w;
         RayHit hit2;
         hit2.type = Hit_Nothing; hit2.iVert = -1; hit2.t = -1.0f; hit2.flags = 0;
         hit2.normal = v3s(0.0f); hit2.w = hit2.u = hit2.v = 0.0f;
-        if (stage == Slot_Connect) hit2 = unpackHit(S, pend.rd2, h2);
+        if (kind != Pend_None) hit2 = unpackHit(S, pend.rd2, h2);
         int r = pathStageB(S, p, hit, pend, hit2, st);
         if (r == Stage_Next && pathAdvance(p)) alive = true;
         else emitResult(W, p, outIndex);
@@ -427,11 +434,10 @@ PoolView makeView(const PathPool& pool)
     for (int b = 0; b < 2; ++b)
     {
         PathArrays& a = b ? v.next : v.cur;
-        a.rng = pool.rng[b]; a.ro = pool.ro[b]; a.rd = pool.rd[b]; a.atten = pool.atten[b]; a.lum = pool.lum[b];
+        a.ro = pool.ro[b]; a.rd = pool.rd[b]; a.atten = pool.atten[b]; a.lum = pool.lum[b];
         a.albedo = pool.albedo[b]; a.normal = pool.normal[b];
     }
     v.hit1 = pool.hit1; v.ro2 = pool.ro2; v.rd2 = pool.rd2; v.pend = pool.pend; v.hit2 = pool.hit2;
-    v.stage = pool.stage;
     v.connectList = pool.connectList;
     v.counters = pool.counters;
     v.cursor = reinterpret_cast<unsigned long long*>(pool.counters + Wf_COUNT);
@@ -447,24 +453,23 @@ bool poolAlloc(PathPool& pool, int32_t capacity)
     if (capacity < 1024) capacity = 1024;
     capacity = (capacity + 255) & ~255;
     const size_t cap = (size_t)capacity;
-    const size_t stateBytes = cap * 16 * 19;
-    const size_t stageBytes = cap * sizeof(int32_t) * 2;
+    const size_t stateBytes = cap * 16 * 17;      // 2 x 6 state fields + 5 temporaries
+    const size_t listBytes = cap * sizeof(int32_t);
     const size_t counterBytes = 256;
     char* base = nullptr;
-    if (!PT_CUDA(cudaMalloc((void**)&base, stateBytes + stageBytes + counterBytes))) return false;
+    if (!PT_CUDA(cudaMalloc((void**)&base, stateBytes + listBytes + counterBytes))) return false;
     pool.all = base;
     pool.capacity = capacity;
     char* p = base;
     auto take = [&](size_t bytes) { char* r = p; p += bytes; return r; };
     for (int b = 0; b < 2; ++b)
     {
-        pool.rng[b] = (U4*)take(cap * 16); pool.ro[b] = (F4*)take(cap * 16); pool.rd[b] = (F4*)take(cap * 16);
+        pool.ro[b] = (F4*)take(cap * 16); pool.rd[b] = (F4*)take(cap * 16);
         pool.atten[b] = (F4*)take(cap * 16); pool.lum[b] = (F4*)take(cap * 16); pool.albedo[b] = (F4*)take(cap * 16);
         pool.normal[b] = (F4*)take(cap * 16);
     }
     pool.hit1 = (U4*)take(cap * 16); pool.ro2 = (F4*)take(cap * 16);
     pool.rd2 = (F4*)take(cap * 16); pool.pend = (F4*)take(cap * 16); pool.hit2 = (U4*)take(cap * 16);
-    pool.stage = (int32_t*)take(cap * sizeof(int32_t));
     pool.connectList = (int32_t*)take(cap * sizeof(int32_t));
     pool.counters = (int32_t*)take(counterBytes);
     if (!PT_CUDA(cudaMallocHost((void**)&pool.hostCounters, 64 * sizeof(int32_t)))) { poolFree(pool); return false; }
@@ -596,11 +601,11 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
 // loop that forbids allocation after start-up so its latency stays flat, a host thread that
 // holds a lock other allocating CUDA calls would contend on, or an embedding that budgets
 // device memory once when the library is loaded. For those callers the wavefront's scratch
-// (double-buffered path state, per-iteration ray/hit temporaries, stage flags, counters) lives
+// (double-buffered path state, per-iteration ray/hit temporaries, connect list, counters) lives
 // in the file-scope array below instead of a cudaMalloc'ed pool. Every GPU that loads the
 // library carries the array until the process exits, hence the modest fixed size.
 constexpr int kNoAllocMaxPaths = 32768;                                   // paths (= scratch slots) per call
-constexpr size_t kNoAllocSlotBytes = 19 * 16 + 2 * sizeof(int32_t);       // 14 state + 5 temporary fields + stage + connect list
+constexpr size_t kNoAllocSlotBytes = 17 * 16 + sizeof(int32_t);       // 12 state + 5 temporary fields + connect list
 constexpr size_t kNoAllocBytes = (size_t)kNoAllocMaxPaths * kNoAllocSlotBytes + 256;   // + counter block
 
 static __device__ __align__(256) unsigned char g_noAllocScratch[kNoAllocBytes];
@@ -639,13 +644,12 @@ bool runWavefrontNoAlloc(const DScene& S, const F4* dRo, const F4* dRd, int64_t 
     for (int b = 0; b < 2; ++b)
     {
         PathArrays& a = b ? P.next : P.cur;
-        a.rng = (U4*)take(cap * 16); a.ro = (F4*)take(cap * 16); a.rd = (F4*)take(cap * 16);
+        a.ro = (F4*)take(cap * 16); a.rd = (F4*)take(cap * 16);
         a.atten = (F4*)take(cap * 16); a.lum = (F4*)take(cap * 16); a.albedo = (F4*)take(cap * 16);
         a.normal = (F4*)take(cap * 16);
     }
     P.hit1 = (U4*)take(cap * 16); P.ro2 = (F4*)take(cap * 16); P.rd2 = (F4*)take(cap * 16);
     P.pend = (F4*)take(cap * 16); P.hit2 = (U4*)take(cap * 16);
-    P.stage = (int32_t*)take(cap * sizeof(int32_t));
     P.connectList = (int32_t*)take(cap * sizeof(int32_t));
     P.counters = (int32_t*)take(256);
     P.cursor = reinterpret_cast<unsigned long long*>(P.counters + Wf_COUNT);
@@ -659,7 +663,7 @@ bool runWavefrontNoAlloc(const DScene& S, const F4* dRo, const F4* dRd, int64_t 
     W.sumColor = dColor3; W.sumAlbedo = dAlbedo3; W.sumNormal = dNormal3; W.accumulate = 0;
 
     // The array keeps whatever the previous call left: k_wfInit zeroes the counter block and
-    // the work cursor; state, temporaries and stage flags are written before they are read.
+    // the work cursor; state and temporaries are written before they are read.
     const int cap1 = P.capacity;
     const unsigned grid = (unsigned)((cap1 + kTravThreads - 1) / kTravThreads);
     k_wfInit<<<1, 32, 0, stream>>>(P, (unsigned long long)n);
