@@ -705,9 +705,10 @@ PT_D void pathFinish(const Path& p, V3& color, V3& albedo, V3& normal)   // :240
     normal = p.normal * s;
 }
 
-// Stage A: everything between the path ray's hit and EstimateDirect's ray.
+// Stage A: everything between the path ray's hit and EstimateDirect's ray. On Stage_Ray2 /
+// Stage_NoRay2 `surf` holds the surface interaction stage B continues from.
 template <class Stack>
-PT_D int pathStageA(const DScene& S, Path& p, const RayHit& hit, Pending& pend, Stack& st)
+PT_D int pathStageA(const DScene& S, Path& p, const RayHit& hit, Pending& pend, SurfHit& surf, Stack& st)
 {
     pend.kind = Pend_None;
     if (hit.type == Hit_Nothing)
@@ -735,7 +736,8 @@ PT_D int pathStageA(const DScene& S, Path& p, const RayHit& hit, Pending& pend, 
         p.atten = p.atten * sc.attenuation;
     }
 
-    SurfHit surf = GetSurface(S, p.rd, hit);
+    surf = GetSurface(S, p.rd, hit);
+    pend.ro2 = surf.P;
     if (p.bounce > 0) LightOnHit(S, p.ro, surf.emission, hit.iVert);
     if (p.bounce == 0 || (p.prevFlags & MatFlag_Refractive)) p.lum = p.lum + surf.emission * p.atten;
     if (hit.flags & MatFlag_Sky) return Stage_Done;
@@ -785,9 +787,8 @@ PT_D int pathStageA(const DScene& S, Path& p, const RayHit& hit, Pending& pend, 
 
 // Stage B: the rest of EstimateDirect, then the BSDF scatter that sets up the next bounce.
 template <class Stack>
-PT_D int pathStageB(const DScene& S, Path& p, const RayHit& hit, const Pending& pend, const RayHit& hit2, Stack& st)
+PT_D int pathStageB(const DScene& S, Path& p, const SurfHit& surf, const Pending& pend, const RayHit& hit2, Stack& st)
 {
-    SurfHit surf = GetSurface(S, p.rd, hit);
     const float pRough = f1_lerp(0.05f, 0.95f, surf.roughness);
     const float pSmooth = 1.0f - pRough;
     V3 direct = v3s(0.0f);
@@ -869,7 +870,8 @@ PT_D void traceRay(const DScene& S, Rng& rng, V3 ro, V3 rd, V3& color, V3& albed
         RayHit hit = intersectLocal(S, p.ro, p.rd, 0.0f, kRcpEpsilon, st);
         if (rayCount) (*rayCount)++;
         Pending pend;
-        int r = pathStageA(S, p, hit, pend, st);
+        SurfHit surf;
+        int r = pathStageA(S, p, hit, pend, surf, st);
         if (r == Stage_Done) break;
         if (r != Stage_Next)
         {
@@ -881,7 +883,7 @@ PT_D void traceRay(const DScene& S, Rng& rng, V3 ro, V3 rd, V3& color, V3& albed
                 hit2 = intersectLocal(S, pend.ro2, pend.rd2, 0.0f, pend.tFar2, st);
                 if (rayCount) (*rayCount)++;
             }
-            r = pathStageB(S, p, hit, pend, hit2, st);
+            r = pathStageB(S, p, surf, pend, hit2, st);
             if (r == Stage_Done) break;
         }
         alive = pathAdvance(p);

@@ -101,9 +101,12 @@ struct PathPool
     // per-iteration temporaries
     U4* hit1 = nullptr;     // t, u, v (float bits), primitive index
     F4* ro2 = nullptr;      // secondary ray origin, w = tFar
-    F4* rd2 = nullptr;      // secondary ray direction, w = bits: kind | iVertLight<<2
+    F4* rd2 = nullptr;      // secondary ray direction, w = bits: kind | surface flags
     F4* pend = nullptr;     // Pending.a0..a3
     U4* hit2 = nullptr;
+    F4* surfN = nullptr;    // stage A's surface for stage B: N + roughness
+    F4* surfA = nullptr;    // albedo + metallic
+    F4* surfM = nullptr;    // interpolated normal, written only where a normal map changed N
     int32_t* connectList = nullptr;   // slots that need a connect ray this iteration (persistent traversal)
     int32_t* counters = nullptr; // device: see WfCounter
     int32_t* hostCounters = nullptr; // pinned mirror of the per-iteration status

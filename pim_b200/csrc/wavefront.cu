@@ -53,9 +53,16 @@ constexpr int kShadeThreads = 128;
 #endif
 constexpr int kShadeBlocksPerSm = PT_SHADE_BLOCKS;
 
-// what stage A leaves for stage B rides in the low two bits of rd2.w: Pend_None (shade without a
-// second ray), Pend_Light / Pend_Bsdf (the connect kernel traced one), or kPendDead
+// What stage A leaves for stage B. rd2.w holds flag bits: the low two are Pend_None (shade
+// without a second ray), Pend_Light / Pend_Bsdf (the connect kernel traced one) or kPendDead;
+// then the surface's back-face, refractive and "shading normal differs from the interpolated
+// one" bits. The surface itself travels as surfN = (N, roughness), surfA = (albedo, metallic)
+// and, only when the normal map changed it, surfM = (M, 0); re-deriving it in stage B cost a
+// second walk through vertex, material and texture gathers. pend = (selectPdf, distSq,
+// light vertex bits, -) for a light sample, (attenuation, pdf) for a BSDF sample, (ior, ...)
+// when there is no second ray (the only case that can be refractive).
 constexpr uint32_t kPendDead = 3u;
+constexpr uint32_t kSurfBackface = 4u, kSurfRefractive = 8u, kSurfHasM = 16u;
 
 struct PathArrays { F4* ro; F4* rd; F4* atten; F4* lum; F4* albedo; F4* normal; };
 
@@ -63,6 +70,7 @@ struct PoolView
 {
     PathArrays cur, next;         // persistent path state, ping-pong
     U4* hit1; F4* ro2; F4* rd2; F4* pend; U4* hit2;   // per-iteration temporaries
+    F4* surfN; F4* surfA; F4* surfM;                  // stage A's surface interaction for stage B
     int32_t* connectList;
     int32_t* counters;
     unsigned long long* cursor;   // [0] next work item (may run past the total), [1] total
@@ -326,7 +334,8 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeA(D
     {
         RayHit hit = unpackHit(S, p.rd, h1);
         Pending pend;
-        int r = pathStageA(S, p, hit, pend, st);
+        SurfHit surf;
+        int r = pathStageA(S, p, hit, pend, surf, st);
         if (r == Stage_Done || r == Stage_Next)
         {
             // the path ends here or scattered inside the medium: both need the rest of the state
@@ -342,9 +351,17 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeA(D
             // stage A only changes rng, atten, lum
             P.cur.atten[slot] = f4(p.atten, u2f(p.rng.x));
             P.cur.lum[slot] = f4(p.lum, u2f(p.rng.y));
+            const bool hasM = (surf.M.x != surf.N.x) | (surf.M.y != surf.N.y) | (surf.M.z != surf.N.z);
+            const uint32_t bits = (uint32_t)pend.kind | (surf.type == Hit_Backface ? kSurfBackface : 0u) |
+                                  ((surf.flags & MatFlag_Refractive) ? kSurfRefractive : 0u) | (hasM ? kSurfHasM : 0u);
+            if (pend.kind == Pend_Light) pend.a2 = u2f((uint32_t)pend.iVertLight);
+            else if (pend.kind == Pend_None) pend.a0 = surf.ior;
             P.ro2[slot] = f4(pend.ro2, pend.tFar2);
-            P.rd2[slot] = f4(pend.rd2, u2f((uint32_t)pend.kind | ((uint32_t)(pend.iVertLight + 1) << 2)));
+            P.rd2[slot] = f4(pend.rd2, u2f(bits));
             P.pend[slot] = f4(pend.a0, pend.a1, pend.a2, pend.a3);
+            P.surfN[slot] = f4(surf.N, surf.roughness);
+            P.surfA[slot] = f4(surf.albedo, surf.metallic);
+            if (hasM) P.surfM[slot] = f4(surf.M, 0.0f);
         }
     }
     {
@@ -386,24 +403,34 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeB(D
     Path p; uint32_t outIndex = 0;
     loadPathHot(P.cur, slot, p);
     loadPathCold(P.cur, slot, p, outIndex);
-    const U4 h1 = P.hit1[slot], h2 = P.hit2[slot];
+    const U4 h2 = P.hit2[slot];
     const F4 o2 = P.ro2[slot], d2 = P.rd2[slot], pa = P.pend[slot];
+    const F4 sn = P.surfN[slot], sa = P.surfA[slot];
     const uint32_t bits = f2u(d2.w);
     const uint32_t kind = (slot < P.counters[Wf_NumA]) ? (bits & 3u) : kPendDead;
     bool alive = false;
     if (kind != kPendDead)
     {
-        RayHit hit = unpackHit(S, p.rd, h1);
         Pending pend;
         pend.kind = (int32_t)kind;
-        pend.iVertLight = (int32_t)(bits >> 2) - 1;
+        pend.iVertLight = (kind == Pend_Light) ? (int32_t)f2u(pa.z) : -1;
         pend.ro2 = v3(o2); pend.tFar2 = o2.w; pend.rd2 = v3(d2);
         pend.a0 = pa.x; pend.a1 = pa.y; pend.a2 = pa.z; pend.a3 = pa.w;
+        SurfHit surf;
+        surf.P = pend.ro2;
+        surf.N = v3(sn); surf.roughness = sn.w;
+        surf.albedo = v3(sa); surf.metallic = sa.w;
+        surf.M = surf.N;
+        if (bits & kSurfHasM) surf.M = v3(P.surfM[slot]);
+        surf.emission = v3s(0.0f); surf.occlusion = 0.0f;
+        surf.ior = (kind == Pend_None) ? pa.x : 1.0f;
+        surf.flags = (bits & kSurfRefractive) ? MatFlag_Refractive : 0u;
+        surf.type = (bits & kSurfBackface) ? Hit_Backface : Hit_Triangle;
         RayHit hit2;
         hit2.type = Hit_Nothing; hit2.iVert = -1; hit2.t = -1.0f; hit2.flags = 0;
         hit2.normal = v3s(0.0f); hit2.w = hit2.u = hit2.v = 0.0f;
         if (kind != Pend_None) hit2 = unpackHit(S, pend.rd2, h2);
-        int r = pathStageB(S, p, hit, pend, hit2, st);
+        int r = pathStageB(S, p, surf, pend, hit2, st);
         if (r == Stage_Next && pathAdvance(p)) alive = true;
         else emitResult(W, p, outIndex);
     }
@@ -438,6 +465,7 @@ PoolView makeView(const PathPool& pool)
         a.albedo = pool.albedo[b]; a.normal = pool.normal[b];
     }
     v.hit1 = pool.hit1; v.ro2 = pool.ro2; v.rd2 = pool.rd2; v.pend = pool.pend; v.hit2 = pool.hit2;
+    v.surfN = pool.surfN; v.surfA = pool.surfA; v.surfM = pool.surfM;
     v.connectList = pool.connectList;
     v.counters = pool.counters;
     v.cursor = reinterpret_cast<unsigned long long*>(pool.counters + Wf_COUNT);
@@ -453,7 +481,7 @@ bool poolAlloc(PathPool& pool, int32_t capacity)
     if (capacity < 1024) capacity = 1024;
     capacity = (capacity + 255) & ~255;
     const size_t cap = (size_t)capacity;
-    const size_t stateBytes = cap * 16 * 17;      // 2 x 6 state fields + 5 temporaries
+    const size_t stateBytes = cap * 16 * 20;      // 2 x 6 state fields + 8 temporaries
     const size_t listBytes = cap * sizeof(int32_t);
     const size_t counterBytes = 256;
     char* base = nullptr;
@@ -470,6 +498,7 @@ bool poolAlloc(PathPool& pool, int32_t capacity)
     }
     pool.hit1 = (U4*)take(cap * 16); pool.ro2 = (F4*)take(cap * 16);
     pool.rd2 = (F4*)take(cap * 16); pool.pend = (F4*)take(cap * 16); pool.hit2 = (U4*)take(cap * 16);
+    pool.surfN = (F4*)take(cap * 16); pool.surfA = (F4*)take(cap * 16); pool.surfM = (F4*)take(cap * 16);
     pool.connectList = (int32_t*)take(cap * sizeof(int32_t));
     pool.counters = (int32_t*)take(counterBytes);
     if (!PT_CUDA(cudaMallocHost((void**)&pool.hostCounters, 64 * sizeof(int32_t)))) { poolFree(pool); return false; }
@@ -605,7 +634,7 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
 // in the file-scope array below instead of a cudaMalloc'ed pool. Every GPU that loads the
 // library carries the array until the process exits, hence the modest fixed size.
 constexpr int kNoAllocMaxPaths = 32768;                                   // paths (= scratch slots) per call
-constexpr size_t kNoAllocSlotBytes = 17 * 16 + sizeof(int32_t);       // 12 state + 5 temporary fields + connect list
+constexpr size_t kNoAllocSlotBytes = 20 * 16 + sizeof(int32_t);       // 12 state + 8 temporary fields + connect list
 constexpr size_t kNoAllocBytes = (size_t)kNoAllocMaxPaths * kNoAllocSlotBytes + 256;   // + counter block
 
 static __device__ __align__(256) unsigned char g_noAllocScratch[kNoAllocBytes];
@@ -650,6 +679,7 @@ bool runWavefrontNoAlloc(const DScene& S, const F4* dRo, const F4* dRd, int64_t 
     }
     P.hit1 = (U4*)take(cap * 16); P.ro2 = (F4*)take(cap * 16); P.rd2 = (F4*)take(cap * 16);
     P.pend = (F4*)take(cap * 16); P.hit2 = (U4*)take(cap * 16);
+    P.surfN = (F4*)take(cap * 16); P.surfA = (F4*)take(cap * 16); P.surfM = (F4*)take(cap * 16);
     P.connectList = (int32_t*)take(cap * sizeof(int32_t));
     P.counters = (int32_t*)take(256);
     P.cursor = reinterpret_cast<unsigned long long*>(P.counters + Wf_COUNT);
