@@ -45,6 +45,7 @@ PT_D float safeRcp(float d)
 
 struct TravCounters { uint32_t nodes, tris; };
 
+
 // byte `idx` (0..3) of `word` as a float (I2F.U8; splicing the byte into a float mantissa with
 // PRMT + FADD instead measured 4 % slower on B200)
 PT_D float byteToFloat(uint32_t word, int idx) { return (float)((word >> (8 * idx)) & 0xffu); }
@@ -158,8 +159,16 @@ PT_D bool travStep(const Bvh& bvh, TravRay& r, Stack& st, TravCounters* cnt)
     uint32_t leafMask = hitMask & ~imask;
     while (leafMask)
     {
-        const int i = ffs32(leafMask);
-        leafMask &= leafMask - 1;
+        // nearest leaf first, so the farther ones can be skipped once something is hit
+        // (cornell 1080p: extend 71.4 -> 61.7 ms, connect 101.0 -> 92.8 ms per 6 steps)
+        uint32_t lk = 0xffffffffu;
+#if defined(__CUDA_ARCH__)
+        #pragma unroll
+#endif
+        for (int k = 0; k < 8; ++k) { const uint32_t kk = ((leafMask >> k) & 1u) ? keys[k] : 0xffffffffu; lk = kk < lk ? kk : lk; }
+        const int i = (int)((lk - 8u) & 7u);
+        leafMask &= ~(1u << i);
+        if (!kAnyHit && u2f((lk - 8u) & ~7u) > r.tBest) break;
         const uint32_t m = (metaw[i >> 2] >> (8 * (i & 3))) & 0xffu;
         const uint32_t count = m >> 5, first = n1.y + (m & 31u);
         for (uint32_t j = 0; j < count; ++j)

@@ -48,10 +48,12 @@ namespace {
 // shading kernels are latency bound (dependent loads through hit -> vertex -> material ->
 // texel); PT_SHADE_BLOCKS trades registers per thread for resident warps
 constexpr int kShadeThreads = 128;
-#ifndef PT_SHADE_BLOCKS
-#define PT_SHADE_BLOCKS 4
+#ifndef PT_SHADE_BLOCKS_A
+#define PT_SHADE_BLOCKS_A 8
 #endif
-constexpr int kShadeBlocksPerSm = PT_SHADE_BLOCKS;
+#ifndef PT_SHADE_BLOCKS_B
+#define PT_SHADE_BLOCKS_B 5
+#endif
 
 // What stage A leaves for stage B. rd2.w holds flag bits: the low two are Pend_None (shade
 // without a second ray), Pend_Light / Pend_Bsdf (the connect kernel traced one) or kPendDead;
@@ -318,7 +320,7 @@ __global__ void __launch_bounds__(kTravThreads) k_wfTracePersistent(DScene S, Po
 }
 
 // K6a
-__global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeA(DScene S, PoolView P, WorkDesc W)
+__global__ void __launch_bounds__(kShadeThreads, PT_SHADE_BLOCKS_A) k_wfShadeA(DScene S, PoolView P, WorkDesc W)
 {
     LazyStack st;
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;     // always below the pool capacity
@@ -395,7 +397,7 @@ __global__ void __launch_bounds__(kTravThreads) k_wfConnect(DScene S, PoolView P
 }
 
 // K6b
-__global__ void __launch_bounds__(kShadeThreads, kShadeBlocksPerSm) k_wfShadeB(DScene S, PoolView P, WorkDesc W)
+__global__ void __launch_bounds__(kShadeThreads, PT_SHADE_BLOCKS_B) k_wfShadeB(DScene S, PoolView P, WorkDesc W)
 {
     LazyStack st;
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;     // always below the pool capacity
