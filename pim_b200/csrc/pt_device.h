@@ -112,11 +112,21 @@ struct PathPool
     int32_t* hostCounters = nullptr; // pinned mirror of the per-iteration status
     void* all = nullptr;
 };
+// The counters many CTAs bump with atomics each sit in a 128-byte line of their own, away from
+// the values every thread only reads (Wf_NumA, the work cursor): same-address atomics serialise
+// in one L2 slice at about one per two clocks, and neighbours in the line queue behind them.
 enum WfCounter : int
 {
-    Wf_NumA = 0, Wf_NumB, Wf_NumNext, Wf_NumFree, Wf_NumFreeNext, Wf_WorkCursor, Wf_WorkTotal,
-    Wf_Rays, Wf_Paths, Wf_ExtendCursor, Wf_ConnectCursor, Wf_NumConnect, Wf_COUNT = 16
+    Wf_NumA = 0,                 // live paths this iteration (read by every kernel)
+    Wf_CursorLo = 8,             // 64-bit work cursor and total (ints 8..11)
+    Wf_Status = 16,              // 4 ints published per iteration
+    Wf_NumNext = 32,             // survivors written to the other buffer (one atomic per CTA of stage B)
+    Wf_NumConnect = 64,          // slots asking for a second ray (one atomic per CTA of stage A)
+    Wf_ExtendCursor = 96, Wf_ConnectCursor = 128,    // ray fetch cursors of the persistent traversal kernels
+    Wf_COUNT = 160
 };
+constexpr size_t kWfCounterBytes = 1024;
+
 bool poolAlloc(PathPool& pool, int32_t capacity);
 void poolFree(PathPool& pool);
 

@@ -47,7 +47,10 @@ namespace {
 
 // shading kernels are latency bound (dependent loads through hit -> vertex -> material ->
 // texel); PT_SHADE_BLOCKS trades registers per thread for resident warps
-constexpr int kShadeThreads = 128;
+#ifndef PT_SHADE_THREADS
+#define PT_SHADE_THREADS 128
+#endif
+constexpr int kShadeThreads = PT_SHADE_THREADS;
 #ifndef PT_SHADE_BLOCKS_A
 #define PT_SHADE_BLOCKS_A 8
 #endif
@@ -373,12 +376,6 @@ __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_BLOCKS_A) k_wfShadeA(D
     int nRay2 = 0;
     const int idx = blockAlloc<kShadeThreads / 32>(ray2, &P.counters[Wf_NumConnect], nRay2);
     if (ray2) P.connectList[idx] = slot;
-    const int nActive = __syncthreads_count(active);
-    if (threadIdx.x == 0)
-    {
-        if (nActive) atomicAdd(&P.counters[Wf_Rays], nActive);      // rays the extend kernel traced
-        if (nRay2) atomicAdd(&P.counters[Wf_Paths], nRay2);         // rays the connect kernel will trace
-    }
 }
 
 // K4'
@@ -448,13 +445,11 @@ __global__ void k_wfEndIteration(PoolView P, int32_t* status)
     const unsigned long long cur = P.cursor[0], total = P.cursor[1];
     const unsigned long long left = cur < total ? total - cur : 0ull;
     status[0] = P.counters[Wf_NumNext];
-    P.counters[Wf_NumA] = P.counters[Wf_NumNext];
     status[1] = (left > 0x7fffffffull) ? 0x7fffffff : (int32_t)left;
-    status[2] = P.counters[Wf_Rays];
-    status[3] = P.counters[Wf_Paths];
+    status[2] = P.counters[Wf_NumA];          // rays the extend kernel traced
+    status[3] = P.counters[Wf_NumConnect];    // rays the connect kernel traced
+    P.counters[Wf_NumA] = P.counters[Wf_NumNext];
     P.counters[Wf_NumNext] = 0;
-    P.counters[Wf_Rays] = 0;
-    P.counters[Wf_Paths] = 0;
 }
 
 PoolView makeView(const PathPool& pool)
@@ -470,7 +465,7 @@ PoolView makeView(const PathPool& pool)
     v.surfN = pool.surfN; v.surfA = pool.surfA; v.surfM = pool.surfM;
     v.connectList = pool.connectList;
     v.counters = pool.counters;
-    v.cursor = reinterpret_cast<unsigned long long*>(pool.counters + Wf_COUNT);
+    v.cursor = reinterpret_cast<unsigned long long*>(pool.counters + Wf_CursorLo);
     v.capacity = pool.capacity;
     return v;
 }
@@ -485,7 +480,7 @@ bool poolAlloc(PathPool& pool, int32_t capacity)
     const size_t cap = (size_t)capacity;
     const size_t stateBytes = cap * 16 * 20;      // 2 x 6 state fields + 8 temporaries
     const size_t listBytes = cap * sizeof(int32_t);
-    const size_t counterBytes = 256;
+    const size_t counterBytes = kWfCounterBytes;
     char* base = nullptr;
     if (!PT_CUDA(cudaMalloc((void**)&base, stateBytes + listBytes + counterBytes))) return false;
     pool.all = base;
@@ -526,7 +521,7 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     const unsigned grid = (unsigned)((cap + kTravThreads - 1) / kTravThreads);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     bool ok = PT_CUDA(cudaEventCreate(&e0)) && PT_CUDA(cudaEventCreate(&e1));
-    int32_t* dStatus = pool.counters + Wf_COUNT + 8;     // 4 ints inside the counter block
+    int32_t* dStatus = pool.counters + Wf_Status;     // 4 ints inside the counter block
     k_wfInit<<<(cap + 255) / 256, 256, 0, stream>>>(P, (unsigned long long)work.count);
     g_counters.kernelLaunches++;
     ok = ok && PT_CUDA(cudaEventRecord(e0, stream));
@@ -585,6 +580,7 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
         const unsigned gridLive = (unsigned)((bound + kTravThreads - 1) / kTravThreads);
         const unsigned gridRegen = workLeft ? grid : 1u;
         const unsigned gridPersist = std::min<unsigned>(gridLive, gridP);
+        const unsigned gridShade = (unsigned)((bound + kShadeThreads - 1) / kShadeThreads);
         if (timing) cudaEventRecord(ev[r][0], stream);
         k_wfRegen<<<gridRegen, 128, 0, stream>>>(S, P, work);
         k_wfAfterRegen<<<1, 1, 0, stream>>>(P);
@@ -592,12 +588,12 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
         if (persistent) k_wfTracePersistent<false><<<gridPersist, kTravThreads, 0, stream>>>(S, P);
         else k_wfExtend<<<gridLive, kTravThreads, 0, stream>>>(S, P);
         if (timing) cudaEventRecord(ev[r][2], stream);
-        k_wfShadeA<<<gridLive, kShadeThreads, 0, stream>>>(S, P, work);
+        k_wfShadeA<<<gridShade, kShadeThreads, 0, stream>>>(S, P, work);
         if (timing) cudaEventRecord(ev[r][3], stream);
         if (persistent) k_wfTracePersistent<true><<<gridPersist, kTravThreads, 0, stream>>>(S, P);
         else k_wfConnect<<<gridLive, kTravThreads, 0, stream>>>(S, P);
         if (timing) cudaEventRecord(ev[r][4], stream);
-        k_wfShadeB<<<gridLive, kShadeThreads, 0, stream>>>(S, P, work);
+        k_wfShadeB<<<gridShade, kShadeThreads, 0, stream>>>(S, P, work);
         if (timing) cudaEventRecord(ev[r][5], stream);
         k_wfEndIteration<<<1, 1, 0, stream>>>(P, dStatus);
         g_counters.kernelLaunches += 7;
@@ -637,7 +633,7 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
 // library carries the array until the process exits, hence the modest fixed size.
 constexpr int kNoAllocMaxPaths = 32768;                                   // paths (= scratch slots) per call
 constexpr size_t kNoAllocSlotBytes = 20 * 16 + sizeof(int32_t);       // 12 state + 8 temporary fields + connect list
-constexpr size_t kNoAllocBytes = (size_t)kNoAllocMaxPaths * kNoAllocSlotBytes + 256;   // + counter block
+constexpr size_t kNoAllocBytes = (size_t)kNoAllocMaxPaths * kNoAllocSlotBytes + kWfCounterBytes;   // + counter block
 
 static __device__ __align__(256) unsigned char g_noAllocScratch[kNoAllocBytes];
 
@@ -683,10 +679,10 @@ bool runWavefrontNoAlloc(const DScene& S, const F4* dRo, const F4* dRd, int64_t 
     P.pend = (F4*)take(cap * 16); P.hit2 = (U4*)take(cap * 16);
     P.surfN = (F4*)take(cap * 16); P.surfA = (F4*)take(cap * 16); P.surfM = (F4*)take(cap * 16);
     P.connectList = (int32_t*)take(cap * sizeof(int32_t));
-    P.counters = (int32_t*)take(256);
-    P.cursor = reinterpret_cast<unsigned long long*>(P.counters + Wf_COUNT);
+    P.counters = (int32_t*)take(kWfCounterBytes);
+    P.cursor = reinterpret_cast<unsigned long long*>(P.counters + Wf_CursorLo);
     P.capacity = (int32_t)((n + 127) & ~127ll);
-    int32_t* dStatus = P.counters + Wf_COUNT + 8;
+    int32_t* dStatus = P.counters + Wf_Status;
 
     WorkDesc W;
     memset(&W, 0, sizeof(W));
@@ -698,6 +694,7 @@ bool runWavefrontNoAlloc(const DScene& S, const F4* dRo, const F4* dRd, int64_t 
     // the work cursor; state and temporaries are written before they are read.
     const int cap1 = P.capacity;
     const unsigned grid = (unsigned)((cap1 + kTravThreads - 1) / kTravThreads);
+    const unsigned gridShade = (unsigned)((cap1 + kShadeThreads - 1) / kShadeThreads);
     k_wfInit<<<1, 32, 0, stream>>>(P, (unsigned long long)n);
     g_counters.kernelLaunches++;
     bool ok = PT_CUDA(cudaGetLastError());
@@ -707,9 +704,9 @@ bool runWavefrontNoAlloc(const DScene& S, const F4* dRo, const F4* dRd, int64_t 
         k_wfRegen<<<grid, 128, 0, stream>>>(S, P, W);
         k_wfAfterRegen<<<1, 1, 0, stream>>>(P);
         k_wfExtend<<<grid, kTravThreads, 0, stream>>>(S, P);
-        k_wfShadeA<<<grid, kShadeThreads, 0, stream>>>(S, P, W);
+        k_wfShadeA<<<gridShade, kShadeThreads, 0, stream>>>(S, P, W);
         k_wfConnect<<<grid, kTravThreads, 0, stream>>>(S, P);
-        k_wfShadeB<<<grid, kShadeThreads, 0, stream>>>(S, P, W);
+        k_wfShadeB<<<gridShade, kShadeThreads, 0, stream>>>(S, P, W);
         k_wfEndIteration<<<1, 1, 0, stream>>>(P, dStatus);
         g_counters.kernelLaunches += 7;
         ++iterations;
