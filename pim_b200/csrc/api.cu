@@ -362,7 +362,7 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
     }
 
     phase(3);
-    // wavefront pool: 4 M slots x 316 B = 1.3 GB. Measured on cornell 1080p (Msamples/s): 128 K 599,
+    // wavefront pool: 4 M slots x 324 B = 1.36 GB. Measured on cornell 1080p (Msamples/s): 128 K 599,
     // 512 K 1030, 1 M 1213, 2 M 1344, 4 M 1401, 8 M 1389 - the state streams through HBM fully
     // coalesced either way, and fewer, larger iterations amortise launches and the drain at the
     // end of a call. Calls with less work than slots run a correspondingly smaller range.
