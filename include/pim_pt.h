@@ -262,6 +262,57 @@ typedef struct PtLightmapDesc_s
 int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCount,
                         float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass);
 
+/* ---- callers either side of the path -------------------
+ * The reference functions that feed the path tracer (sky) or consume Pt_TraceRay /
+ * Pt_RayGen (cubemap and ambient-cube bakes) or its image (screenshot), same names and
+ * struct layouts where the reference exports them. */
+
+/* src/rendering/cubemap.h:28-34. Cubemap_New allocates the twelve arrays as page-locked
+ * host memory: color[f] = float3[size*size], convolved[f] = float4[elemCount] (mip chain). */
+typedef struct Cubemap_s
+{
+    int32_t size;
+    int32_t mipCount;
+    pim_float3* color[6];
+    pim_float4* convolved[6];
+} Cubemap;
+void Cubemap_New(Cubemap* cm, int32_t size);                                          /* cubemap.c:95-114 */
+void Cubemap_Del(Cubemap* cm);                                                        /* cubemap.c:116-127 */
+/* one jittered path per face texel from `origin`, lerped into color[] by `weight`; the pass
+ * index is the scene's running counter (the reference draws from its thread generators) */
+void Cubemap_Bake(Cubemap* cm, PtScene* scene, pim_float4 origin, float weight);     /* cubemap.c:162-187 */
+/* GGX prefilter of color[] into every mip of convolved[], blended by `weight` */
+void Cubemap_Convolve(Cubemap* cm, uint32_t sampleCount, float weight);               /* cubemap.c:262-303 */
+/* the same two with the random stream named by the caller (seed, pass); 0 on success */
+int32_t Cubemap_BakePass(Cubemap* cm, PtScene* scene, pim_float4 origin, float weight, uint32_t pass);
+int32_t Cubemap_ConvolvePass(Cubemap* cm, uint32_t sampleCount, float weight, uint32_t seed, uint32_t pass);
+
+/* src/math/types.h:513-517, src/math/ambcube.c:5-33: fits `samples` Pt_RayGen probes from
+ * `origin` into the cube; returns prevSampleCount + 1 */
+typedef struct AmbCube_s { pim_float4 Values[6]; } AmbCube_t;
+int32_t AmbCube_Bake(PtScene* scene, AmbCube_t* pCube, pim_float4 origin, int32_t samples, int32_t prevSampleCount);
+
+/* src/math/types.h:531-542 */
+typedef struct SkyMedium_s
+{
+    float rCrust;
+    float rAtmos;
+    pim_float3 muR;
+    float rhoR;
+    float muM;
+    float rhoM;
+    float gM;
+} SkyMedium;
+/* BakeSky's task (static in src/rendering/render_system.c:403-425, 473-491): Atmosphere()
+ * raymarch per texel of cm->color; 0 on success */
+int32_t Pt_BakeSky(Cubemap* cm, const SkyMedium* sky, pim_float3 sunDir, float sunLum, int32_t steps);
+
+/* CmdScreenshot's pixel loop (static in src/rendering/render_system.c:707-727): exposure,
+ * GT tonemap, sRGB inverse EOTF, 1/255 dither, RGBA8. light: host float4[count]; rgba8Out:
+ * host uint32[count] (R in the low byte); 0 on success */
+int32_t Pt_Tonemap(const pim_float4* light, int64_t count, float exposure, uint32_t seed, uint32_t pass,
+                   uint32_t* rgba8Out);
+
 /* ---- introspection ----------------------------------------------------------- */
 typedef struct PtSceneStats_s
 {

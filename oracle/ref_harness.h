@@ -28,6 +28,10 @@ enum
     ORACLE_STREAM_LUT = 5,     /* call 0: BakeBrdfFn */
     ORACLE_STREAM_RAYS = 6,    /* call 0: harness Pt_TraceRay batch */
     ORACLE_STREAM_LMPACK = 7,  /* LmPack_Pack's parallel loops */
+    ORACLE_STREAM_CUBEBAKE = 8, /* call 0: cubemap.c BakeFn */
+    ORACLE_STREAM_CONVOLVE = 9, /* call m: cubemap.c PrefilterFn of mip m */
+    ORACLE_STREAM_SKY = 10,     /* call 0: BakeSkyFn (no random numbers) */
+    ORACLE_STREAM_TONEMAP = 11, /* call 0: screenshot pixel loop (dither) */
 };
 
 void oracle_set_threads(int n);
@@ -119,6 +123,15 @@ int oracle_lm_pack(int atlasSize, float texelsPerUnit, float distThresh, float d
 int oracle_lm_size(void);
 void oracle_lm_page(int i, float** probes5, float** position3, float** normal3, float** sampleCounts);
 void oracle_lm_bake(void* scene, float timeSlice, int spp, uint32_t pass);
+
+/* SURVEY 8(f) rows (ref_cm_wrap.c). color: 6 x size*size float3; convolved: 6 x elemCount float4 */
+int oracle_cubemap_elem_count(int size);
+int oracle_cubemap_mip_count(int size);
+void oracle_cubemap_bake(void* scene, int size, float* color, const float* origin4, float weight, uint32_t pass);
+void oracle_cubemap_convolve(int size, float* color, float* convolved, uint32_t sampleCount, float weight, uint32_t pass);
+int oracle_ambcube_bake(void* scene, float* cube24, const float* origin4, int samples, int prevSampleCount, uint32_t pass);
+void oracle_bake_sky(int size, float* color, const float* sky9, const float* sunDir3, float sunLum, int steps);
+void oracle_tonemap(const float* light4, int count, float exposure, uint32_t pass, uint32_t* rgba8);
 
 /* CalcStdDev (src/rendering/render_system.c:1374-1394) */
 float oracle_stddev(const float* color3, int w, int h);

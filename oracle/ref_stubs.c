@@ -198,6 +198,12 @@ void Task_Run(void* task, TaskExecuteFn fn, i32 worksize)
     _mm_setcsr(savedCsr);
 }
 
+/* Task_Submit + TaskSys_Schedule + Task_Await (cubemap.c:271-300 queues one task per mip):
+ * run each task when it is submitted, so call number c is the c-th submitted task */
+void Task_Submit(void* task, TaskExecuteFn fn, i32 worksize) { Task_Run(task, fn, worksize); }
+void TaskSys_Schedule(void) {}
+void Task_Await(void* task) { (void)task; }
+
 /* ------------------------------------------------- cvars / console / misc */
 
 ConVar cv_pt_dist_meters;
@@ -237,6 +243,13 @@ Guid VEC_CALL Guid_FromStr(char const *const pim_noalias str)
     }
     g.a = a; g.b = b;
     return g;
+}
+
+bool VEC_CALL Guid_IsNull(Guid x) { return !(x.a | x.b); }
+i32 Guid_Find(Guid const *const pim_noalias ptr, i32 count, Guid key)
+{
+    for (i32 i = 0; i < count; ++i) { if (ptr[i].a == key.a && ptr[i].b == key.b) return i; }
+    return -1;
 }
 
 /* serializer / ImGui: unreachable from the harness, present only to link */

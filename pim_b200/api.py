@@ -103,6 +103,20 @@ class PtKernelStats(C.Structure):
                 ("connectRays", C.c_uint64)]
 
 
+class Float3(C.Structure):
+    _fields_ = [("x", C.c_float), ("y", C.c_float), ("z", C.c_float)]
+
+
+class CubemapStruct(C.Structure):       # Cubemap, src/rendering/cubemap.h:28-34
+    _fields_ = [("size", C.c_int32), ("mipCount", C.c_int32), ("color", C.POINTER(C.c_float) * 6),
+                ("convolved", C.POINTER(C.c_float) * 6)]
+
+
+class SkyMedium(C.Structure):           # src/math/types.h:531-542
+    _fields_ = [("rCrust", C.c_float), ("rAtmos", C.c_float), ("muR", Float3), ("rhoR", C.c_float),
+                ("muM", C.c_float), ("rhoM", C.c_float), ("gM", C.c_float)]
+
+
 KERNEL_NAMES = ["regen", "extend", "shadeA", "connect", "shadeB"]
 
 HIT_DTYPE = np.dtype([("wuvt", np.float32, 4), ("normal", np.float32, 4), ("type", np.int32),
@@ -116,6 +130,8 @@ EXPORTS = [
     "PtScene_GetStats", "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut",
     "Pt_GetCounters", "Pt_ResetCounters", "Pt_LastKernelMs", "Pt_LastError",
     "Pt_SetKernelTiming", "Pt_GetKernelStats", "Pt_IntersectCountN", "Pt_TraceRayN_NoAlloc",
+    "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
+    "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -172,6 +188,20 @@ def load():
     L.Pt_GetKernelStats.argtypes = [C.POINTER(PtKernelStats)]
     L.Pt_IntersectCountN.argtypes = [vp, vp, vp, C.c_float, C.c_int64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.Pt_IntersectCountN.restype = C.c_int32
+    L.Cubemap_New.argtypes = [C.POINTER(CubemapStruct), C.c_int32]
+    L.Cubemap_Del.argtypes = [C.POINTER(CubemapStruct)]
+    L.Cubemap_Bake.argtypes = [C.POINTER(CubemapStruct), vp, Float4, C.c_float]
+    L.Cubemap_Convolve.argtypes = [C.POINTER(CubemapStruct), C.c_uint32, C.c_float]
+    L.Cubemap_BakePass.argtypes = [C.POINTER(CubemapStruct), vp, Float4, C.c_float, C.c_uint32]
+    L.Cubemap_BakePass.restype = C.c_int32
+    L.Cubemap_ConvolvePass.argtypes = [C.POINTER(CubemapStruct), C.c_uint32, C.c_float, C.c_uint32, C.c_uint32]
+    L.Cubemap_ConvolvePass.restype = C.c_int32
+    L.AmbCube_Bake.argtypes = [vp, vp, Float4, C.c_int32, C.c_int32]
+    L.AmbCube_Bake.restype = C.c_int32
+    L.Pt_BakeSky.argtypes = [C.POINTER(CubemapStruct), C.POINTER(SkyMedium), Float3, C.c_float, C.c_int32]
+    L.Pt_BakeSky.restype = C.c_int32
+    L.Pt_Tonemap.argtypes = [vp, C.c_int64, C.c_float, C.c_uint32, C.c_uint32, vp]
+    L.Pt_Tonemap.restype = C.c_int32
     for name in ("Pt_IntersectN", "Pt_OccludedN", "Pt_TraceRayN", "Pt_TraceSpp", "Pt_IntersectN_Device",
                  "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc", "PtScene_GetStats",
                  "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut"):
@@ -403,3 +433,94 @@ class Trace:
     def trace_spp(self, scene, cam, dof, spp_begin, spp_count, sums=False):
         self.t.sampleWeight = -1.0 if sums else 1.0
         _check(load().Pt_TraceSpp(C.byref(self.t), C.byref(dof), scene.h, C.byref(cam), spp_begin, spp_count), "Pt_TraceSpp")
+
+
+def cubemap_elem_count(size):
+    """Texels of one face's mip chain (cubemap.c:104-105: offset of the last, 1x1, mip plus one)."""
+    n, m = 0, 0
+    while (size >> m) >= 1:
+        n += (size >> m) ** 2
+        m += 1
+    return n
+
+
+class Cubemap:
+    """Cubemap (src/rendering/cubemap.h:28-34): six colour faces and their convolved mip chains in page-locked
+    host memory owned by the library (Cubemap_New / Cubemap_Del)."""
+
+    def __init__(self, size):
+        self.c = CubemapStruct()
+        load().Cubemap_New(C.byref(self.c), size)
+        if self.c.size != size:
+            raise PtError("Cubemap_New failed: " + last_error())
+        self.size = size
+        self.elem_count = cubemap_elem_count(size)
+
+    def color(self, face):
+        return np.ctypeslib.as_array(self.c.color[face], (self.size, self.size, 3))
+
+    def colors(self):
+        return np.stack([self.color(f) for f in range(6)])
+
+    def convolved(self, face):
+        return np.ctypeslib.as_array(self.c.convolved[face], (self.elem_count, 4))
+
+    def mip(self, face, m):
+        off = sum((self.size >> i) ** 2 for i in range(m))
+        s = self.size >> m
+        return self.convolved(face)[off:off + s * s].reshape(s, s, 4)
+
+    def close(self):
+        if self.c.size:
+            load().Cubemap_Del(C.byref(self.c))
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def bake(self, scene, origin, weight, pass_index=None):
+        """Cubemap_Bake: one jittered path per face texel, lerped into the colour faces."""
+        if pass_index is None:
+            load().Cubemap_Bake(C.byref(self.c), scene.h, _f4(origin), weight)
+            err = last_error()
+            if err:
+                raise PtError("Cubemap_Bake failed: " + err)
+        else:
+            _check(load().Cubemap_BakePass(C.byref(self.c), scene.h, _f4(origin), weight, pass_index), "Cubemap_BakePass")
+
+    def convolve(self, sample_count, weight, seed=1, pass_index=0):
+        _check(load().Cubemap_ConvolvePass(C.byref(self.c), sample_count, weight, seed, pass_index), "Cubemap_ConvolvePass")
+
+    def bake_sky(self, sky, sun_dir, sun_lum, steps):
+        _check(load().Pt_BakeSky(C.byref(self.c), C.byref(sky), Float3(*[float(x) for x in sun_dir]), sun_lum, steps),
+               "Pt_BakeSky")
+
+
+def earth_sky():
+    """BakeSky's medium from the cvar defaults (src/common/cvars.c sky_*; render_system.c:473-482)."""
+    kilo = 1000.0
+    mfp = (192.0, 82.0, 34.0)
+    return SkyMedium(6360.0 * kilo, 60.0 * kilo, Float3(*[1.0 / (m * kilo) for m in mfp]), 1.0 / (8.5 * kilo),
+                     1.0 / (48.0 * kilo), 1.0 / (1.2 * kilo), 0.758)
+
+
+def ambcube_bake(scene, cube, origin, samples, prev_sample_count):
+    """AmbCube_Bake: cube is a float32 array (6, 4) updated in place; returns the new sample count."""
+    cube = np.ascontiguousarray(cube, np.float32)
+    assert cube.shape == (6, 4)
+    aligned = np.zeros(24 + 4, np.float32)          # AmbCube_t holds float4s: 16-byte aligned
+    off = (-aligned.ctypes.data % 16) // 4
+    a = aligned[off:off + 24]
+    a[:] = cube.ravel()
+    n = load().AmbCube_Bake(scene.h, a.ctypes.data, _f4(origin), samples, prev_sample_count)
+    return n, a.reshape(6, 4).copy()
+
+
+def tonemap(light, exposure=1.0, seed=1, pass_index=0):
+    """Pt_Tonemap: float4 HDR image -> RGBA8 (uint32, R in the low byte)."""
+    light = np.ascontiguousarray(light, np.float32).reshape(-1, 4)
+    out = np.zeros(light.shape[0], np.uint32)
+    _check(load().Pt_Tonemap(light.ctypes.data, light.shape[0], exposure, seed, pass_index, out.ctypes.data), "Pt_Tonemap")
+    return out

@@ -810,6 +810,202 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
     return ok ? 0 : -1;
 }
 
+// ---- cubemap / ambient-cube bakes, sky bake, screenshot tonemap ----
+
+// CUDA events around a call's kernels on their stream; stop() leaves the time in Pt_LastKernelMs()
+struct KernelTimer
+{
+    cudaEvent_t a = nullptr, b = nullptr;
+    cudaStream_t st;
+    explicit KernelTimer(cudaStream_t s) : st(s)
+    {
+        if (cudaEventCreate(&a) == cudaSuccess && cudaEventCreate(&b) == cudaSuccess) cudaEventRecord(a, st);
+    }
+    void stop()
+    {
+        if (!a || !b) return;
+        cudaEventRecord(b, st);
+        float ms = 0.0f;
+        if (cudaEventSynchronize(b) == cudaSuccess && cudaEventElapsedTime(&ms, a, b) == cudaSuccess) g_lastKernelMs = ms;
+    }
+    ~KernelTimer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+};
+
+void Cubemap_New(Cubemap* cm, int32_t size)       // cubemap.c:95-114
+{
+    if (!cm) return;
+    memset(cm, 0, sizeof(*cm));
+    if (size <= 0 || !ensureInit()) return;
+    const size_t len = (size_t)size * size, elemCount = (size_t)cubemapElemCount(size);
+    float* color = nullptr; float* conv = nullptr;
+    if (!PT_CUDA(cudaMallocHost((void**)&color, sizeof(float) * 3 * len * 6))) return;
+    if (!PT_CUDA(cudaMallocHost((void**)&conv, sizeof(float) * 4 * elemCount * 6))) { cudaFreeHost(color); return; }
+    memset(color, 0, sizeof(float) * 3 * len * 6);
+    memset(conv, 0, sizeof(float) * 4 * elemCount * 6);
+    cm->size = size;
+    cm->mipCount = cubemapMipCount(size);
+    for (int f = 0; f < 6; ++f)
+    {
+        cm->color[f] = reinterpret_cast<pim_float3*>(color + 3 * len * f);
+        cm->convolved[f] = reinterpret_cast<pim_float4*>(conv + 4 * elemCount * f);
+    }
+}
+
+void Cubemap_Del(Cubemap* cm)                     // cubemap.c:116-127
+{
+    if (!cm) return;
+    // the six faces of each kind are slices of one page-locked block
+    if (cm->color[0]) cudaFreeHost(cm->color[0]);
+    if (cm->convolved[0]) cudaFreeHost(cm->convolved[0]);
+    memset(cm, 0, sizeof(*cm));
+}
+
+// faces may be separate host arrays (a caller-built Cubemap): copy face by face
+static bool cubeUpload(const Cubemap* cm, float* dColor, float* dConv, cudaStream_t st)
+{
+    const size_t len = (size_t)cm->size * cm->size, elemCount = (size_t)cubemapElemCount(cm->size);
+    bool ok = true;
+    for (int f = 0; ok && f < 6; ++f)
+    {
+        if (dColor) ok = PT_CUDA(cudaMemcpyAsync(dColor + 3 * len * f, cm->color[f], 12 * len, cudaMemcpyHostToDevice, st));
+        if (ok && dConv) ok = PT_CUDA(cudaMemcpyAsync(dConv + 4 * elemCount * f, cm->convolved[f], 16 * elemCount, cudaMemcpyHostToDevice, st));
+    }
+    return ok;
+}
+static bool cubeDownload(Cubemap* cm, const float* dColor, const float* dConv, cudaStream_t st)
+{
+    const size_t len = (size_t)cm->size * cm->size, elemCount = (size_t)cubemapElemCount(cm->size);
+    bool ok = true;
+    for (int f = 0; ok && f < 6; ++f)
+    {
+        if (dColor) ok = PT_CUDA(cudaMemcpyAsync(cm->color[f], dColor + 3 * len * f, 12 * len, cudaMemcpyDeviceToHost, st));
+        if (ok && dConv) ok = PT_CUDA(cudaMemcpyAsync(cm->convolved[f], dConv + 4 * elemCount * f, 16 * elemCount, cudaMemcpyDeviceToHost, st));
+    }
+    return ok && PT_CUDA(cudaStreamSynchronize(st));
+}
+static bool cubeValid(const Cubemap* cm, const char* who, bool needConvolved)
+{
+    if (!cm || cm->size <= 0) { setError("%s: null or empty cubemap", who); return false; }
+    for (int f = 0; f < 6; ++f)
+    {
+        if (!cm->color[f] || (needConvolved && !cm->convolved[f])) { setError("%s: cubemap face %d has no storage", who, f); return false; }
+    }
+    return true;
+}
+
+int32_t Cubemap_BakePass(Cubemap* cm, PtScene* scene, pim_float4 origin, float weight, uint32_t pass)
+{
+    if (!scene) { setError("Cubemap_Bake: null scene"); return -1; }
+    if (!cubeValid(cm, "Cubemap_Bake", false)) return -1;
+    const int64_t n = 6ll * cm->size * cm->size;
+    cudaStream_t st = scene->stream;
+    DevBuf dColor, dRo, dRd, dRes;
+    if (!dColor.alloc(12 * n) || !dRo.alloc(16 * n) || !dRd.alloc(16 * n) || !dRes.alloc(12 * n)) return -1;
+    bool ok = cubeUpload(cm, (float*)dColor.p, nullptr, st);
+    KernelTimer timer(st);
+    ok = ok && launchCubeRays(cm->size, v3(origin.x, origin.y, origin.z), pass, scene->config.seed, (F4*)dRo.p, (F4*)dRd.p, st);
+    WorkDesc W; memset(&W, 0, sizeof(W));
+    W.kind = Work_Rays; W.ro = (const F4*)dRo.p; W.rd = (const F4*)dRd.p; W.count = n;
+    W.passBase = pass; W.seed = scene->config.seed; W.salt = Salt_CubeBake;
+    W.sumColor = (float*)dRes.p; W.accumulate = 0;
+    float ms = 0.0f;
+    ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
+    ok = ok && launchLerp((float*)dColor.p, (const float*)dRes.p, 3 * n, weight, st);      // f3_lerpvs, cubemap.c:158
+    timer.stop();
+    ok = ok && cubeDownload(cm, (const float*)dColor.p, nullptr, st);
+    return ok ? 0 : -1;
+}
+
+void Cubemap_Bake(Cubemap* cm, PtScene* scene, pim_float4 origin, float weight)
+{
+    if (scene) Cubemap_BakePass(cm, scene, origin, weight, scene->nextPass++);
+}
+
+static uint32_t g_convolvePass = 0;
+
+int32_t Cubemap_ConvolvePass(Cubemap* cm, uint32_t sampleCount, float weight, uint32_t seed, uint32_t pass)
+{
+    if (!ensureInit()) return -1;
+    if (!cubeValid(cm, "Cubemap_Convolve", true)) return -1;
+    const size_t len = (size_t)cm->size * cm->size, elemCount = (size_t)cubemapElemCount(cm->size);
+    DevBuf dColor, dConv;
+    if (!dColor.alloc(12 * len * 6) || !dConv.alloc(16 * elemCount * 6)) return -1;
+    cudaStream_t st = nullptr;
+    bool ok = cubeUpload(cm, (float*)dColor.p, (float*)dConv.p, st);
+    KernelTimer timer(st);
+    ok = ok && launchCubeConvolve((const float*)dColor.p, (float*)dConv.p, cm->size, sampleCount, weight, pass, seed, st);
+    timer.stop();
+    ok = ok && cubeDownload(cm, nullptr, (const float*)dConv.p, st);
+    return ok ? 0 : -1;
+}
+
+void Cubemap_Convolve(Cubemap* cm, uint32_t sampleCount, float weight)
+{
+    Cubemap_ConvolvePass(cm, sampleCount, weight, 1u, g_convolvePass++);
+}
+
+int32_t AmbCube_Bake(PtScene* scene, AmbCube_t* pCube, pim_float4 origin, int32_t samples, int32_t prevSampleCount)   // ambcube.c:5-33
+{
+    if (!scene || !pCube || samples < 0 || prevSampleCount < 0) { setError("AmbCube_Bake: bad argument"); return prevSampleCount; }
+    cudaStream_t st = scene->stream;
+    if (samples > 0)
+    {
+        DevBuf c, d, cube;
+        if (!c.alloc(sizeof(float) * 3 * (size_t)samples) || !d.alloc(sizeof(F4) * (size_t)samples) || !cube.alloc(sizeof(F4) * 6)) return prevSampleCount;
+        // Pt_RayGen (path_tracer.c:2615-2644), results left on the device
+        bool ok = launchDistUpdate(scene->view, st);
+        WorkDesc W; memset(&W, 0, sizeof(W));
+        W.kind = Work_Sphere; W.origin = v3(origin.x, origin.y, origin.z); W.count = samples;
+        W.passBase = scene->nextPass++; W.seed = scene->config.seed; W.salt = Salt_RayGen;
+        W.sumColor = (float*)c.p; W.directions = (F4*)d.p; W.accumulate = 0;
+        float ms = 0.0f;
+        ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
+        g_lastKernelMs = ms;
+        ok = ok && PT_CUDA(cudaMemcpyAsync(cube.p, pCube, sizeof(F4) * 6, cudaMemcpyHostToDevice, st));
+        ok = ok && launchAmbCubeFit((F4*)cube.p, (const F4*)d.p, (const float*)c.p, samples, prevSampleCount, st);
+        ok = ok && PT_CUDA(cudaMemcpyAsync(pCube, cube.p, sizeof(F4) * 6, cudaMemcpyDeviceToHost, st));
+        ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+        if (!ok) return prevSampleCount;
+    }
+    return prevSampleCount + 1;
+}
+
+int32_t Pt_BakeSky(Cubemap* cm, const SkyMedium* sky, pim_float3 sunDir, float sunLum, int32_t steps)
+{
+    if (!ensureInit()) return -1;
+    if (!sky) { setError("Pt_BakeSky: null medium"); return -1; }
+    if (!cubeValid(cm, "Pt_BakeSky", false)) return -1;
+    const size_t len = (size_t)cm->size * cm->size;
+    DevBuf dColor;
+    if (!dColor.alloc(12 * len * 6)) return -1;
+    SkyParams A;
+    A.rCrust = sky->rCrust; A.rAtmos = sky->rAtmos; A.muR = v3(sky->muR.x, sky->muR.y, sky->muR.z);
+    A.rhoR = sky->rhoR; A.muM = sky->muM; A.rhoM = sky->rhoM; A.gM = sky->gM;
+    cudaStream_t st = nullptr;
+    KernelTimer timer(st);
+    bool ok = launchSkyBake(A, cm->size, v3(sunDir.x, sunDir.y, sunDir.z), sunLum, steps, (float*)dColor.p, st);
+    timer.stop();
+    ok = ok && cubeDownload(cm, (const float*)dColor.p, nullptr, st);
+    return ok ? 0 : -1;
+}
+
+int32_t Pt_Tonemap(const pim_float4* light, int64_t count, float exposure, uint32_t seed, uint32_t pass, uint32_t* rgba8Out)
+{
+    if (!ensureInit()) return -1;
+    if (count <= 0) return 0;
+    if (!light || !rgba8Out) { setError("Pt_Tonemap: null argument"); return -1; }
+    DevBuf dLight, dOut;
+    if (!dLight.alloc(16 * (size_t)count) || !dOut.alloc(4 * (size_t)count)) return -1;
+    cudaStream_t st = nullptr;
+    bool ok = PT_CUDA(cudaMemcpyAsync(dLight.p, light, 16 * (size_t)count, cudaMemcpyHostToDevice, st));
+    KernelTimer timer(st);
+    ok = ok && launchTonemap((const F4*)dLight.p, count, exposure, pass, seed, (uint32_t*)dOut.p, st);
+    timer.stop();
+    ok = ok && PT_CUDA(cudaMemcpyAsync(rgba8Out, dOut.p, 4 * (size_t)count, cudaMemcpyDeviceToHost, st));
+    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    return ok ? 0 : -1;
+}
+
 int32_t PtScene_GetStats(const PtScene* scene, PtSceneStats* stats)
 {
     if (!scene || !stats) return -1;

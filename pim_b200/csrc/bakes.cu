@@ -1,0 +1,322 @@
+// bakes.cu — the callers either side of the path tracer:
+//   Cubemap_Bake      src/rendering/cubemap.c:138-187   one jittered ray per face texel through the
+//                                                       path wavefront, lerped into the face
+//   Cubemap_Convolve  src/rendering/cubemap.c:189-303   GGX prefilter of every mip texel
+//   AmbCube_Bake      src/math/ambcube.c:5-33           ordered fit of Pt_RayGen's samples
+//   BakeSkyFn         src/rendering/render_system.c:403-425 + src/math/atmosphere.h:79-181
+//   screenshot loop   src/rendering/render_system.c:707-727 (exposure, GT tonemap, sRGB, rgba8)
+// Cubemaps live on the device as 6 contiguous faces: colour float3[size*size] per face,
+// convolved float4[elemCount] per face (mip chain, cubemap.c:102-113).
+#include "pt_device.h"
+#include "kernels_common.cuh"
+
+namespace pt {
+
+namespace {
+
+inline unsigned gridFor(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+// src/rendering/cubemap.c:14-42
+__constant__ float kCubeFwd[6][3] = { { 1, 0, 0 }, { -1, 0, 0 }, { 0, 1, 0 }, { 0, -1, 0 }, { 0, 0, 1 }, { 0, 0, -1 } };
+__constant__ float kCubeUp[6][3] = { { 0, 1, 0 }, { 0, 1, 0 }, { 0, 0, -1 }, { 0, 0, -1 }, { 0, 1, 0 }, { 0, 1, 0 } };
+__constant__ float kCubeRight[6][3] = { { 0, 0, -1 }, { 0, 0, 1 }, { 1, 0, 0 }, { -1, 0, 0 }, { 1, 0, 0 }, { -1, 0, 0 } };
+
+// f2_tent (src/math/float2_funcs.h:630-636). The y lane reads 2 - Xi.x, after Xi.x has
+// already been replaced: kept as the reference has it.
+__device__ __forceinline__ V2 tent(V2 Xi)
+{
+    Xi.x *= 2.0f; Xi.y *= 2.0f;
+    Xi.x = Xi.x < 1.0f ? sqrtf(Xi.x) - 1.0f : 1.0f - sqrtf(2.0f - Xi.x);
+    Xi.y = Xi.y < 1.0f ? sqrtf(Xi.y) - 1.0f : 1.0f - sqrtf(2.0f - Xi.x);
+    return Xi;
+}
+
+// Cubemap_CalcDir (src/rendering/cubemap.h:190-207): BilinearInvert, jitter, snorm, proj_dir
+__device__ __forceinline__ V3 cubeDir(int size, int face, int x, int y, V2 Xi)
+{
+    V2 uv = v2((float)x / (float)(size - 1), (float)y / (float)(size - 1));
+    const float r = 1.0f / size;
+    uv.x += Xi.x * r; uv.y += Xi.y * r;
+    uv.x = uv.x * 2.0f - 1.0f; uv.y = uv.y * 2.0f - 1.0f;
+    const V3 fwd = v3(kCubeFwd[face][0], kCubeFwd[face][1], kCubeFwd[face][2]);
+    const V3 right = v3(kCubeRight[face][0], kCubeRight[face][1], kCubeRight[face][2]);
+    const V3 up = v3(kCubeUp[face][0], kCubeUp[face][1], kCubeUp[face][2]);
+    return normalize((fwd + right * uv.x) + up * uv.y);     // proj_dir, frustum.h:33-47, slope 1
+}
+
+// CalcMipOffset (src/rendering/sampler.h:42-51) for a square image
+__device__ __host__ inline int mipOffset(int size, int m)
+{
+    int y = 0;
+    for (int i = 0; i < m; ++i) { int s = size >> i; if (s < 1) s = 1; y += s * s; }
+    return y;
+}
+
+// cubemap.c BakeFn's ray: one per face texel
+__global__ void __launch_bounds__(256) k_cubeRays(int size, V3 origin, uint32_t pass, uint32_t seed, F4* __restrict__ ro,
+                                                  F4* __restrict__ rd)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int flen = size * size;
+    if (i >= 6 * flen) return;
+    const int face = i / flen, fi = i % flen;
+    Rng rng = seed_prng((uint32_t)i, pass, seed, Salt_CubeBake);
+    const V2 Xi = tent(rng_f2(rng));
+    const V3 dir = cubeDir(size, face, fi % size, fi / size, Xi);
+    ro[i] = f4(origin, 0.0f);
+    rd[i] = f4(dir, 0.0f);
+}
+
+// PrefilterFn + PrefilterEnvMap (cubemap.c:189-260): split-sum N = V approximation
+__global__ void __launch_bounds__(128) k_cubeConvolve(const float* __restrict__ color, float* __restrict__ convolved, int size,
+                                                      int elemCount, int mip, uint32_t sampleCount, float weight,
+                                                      uint32_t pass, uint32_t seed)
+{
+    int mSize = size >> mip;
+    const int len = mSize * mSize;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 6 * len) return;
+    const int face = i / len, fi = i % len;
+    const float roughness = (float)mip / 6.0f;          // MipToRoughness, CUBEMAP_MAX_MIP (cubemap.h:12,66-69)
+    Rng rng = seed_prng((uint32_t)i, pass, seed, Salt_CubeConvolve | (uint32_t)(mip & 0xf));
+    const V2 Xi = tent(rng_f2(rng));
+    const V3 N = cubeDir(mSize, face, fi % mSize, fi / mSize, Xi);
+    const Tbn tbn = NormalToTBN(N);
+    const V3 I = -tbn.c2;
+    const float alpha = BrdfAlpha(roughness);
+    float basisIntegral = 0.0f;
+    F4 light = f4(0, 0, 0, 0);
+    for (uint32_t s = 0; s < sampleCount; ++s)
+    {
+        const V3 H = TbnToWorld(tbn, SampleGGXMicrofacet(rng_f2(rng), alpha));
+        const V3 L = reflect(I, H);
+        const float NoL = dot(L, tbn.c2);
+        if (NoL > 0.0f)
+        {
+            V2 uv;
+            const int f = Cubemap_CalcUv(L, uv);                                   // Cubemap_ReadColor
+            const V3 c = UvBilinearClamp_f3(color + (size_t)f * size * size * 3, size, size, uv);
+            light.x += c.x * NoL; light.y += c.y * NoL; light.z += c.z * NoL; light.w += NoL;
+            basisIntegral += NoL;
+        }
+    }
+    if (basisIntegral > 0.0f)
+    {
+        const float r = 1.0f / basisIntegral;
+        light.x *= r; light.y *= r; light.z *= r; light.w *= r;
+    }
+    // Cubemap_BlendMip (cubemap.h:169-188)
+    F4* dst = reinterpret_cast<F4*>(convolved) + (size_t)face * elemCount + mipOffset(size, mip) + fi;
+    *dst = f4_lerp(*dst, light, weight);
+}
+
+// AmbCube_Bake's loop (ambcube.c:22-29) and AmbCube_Fit (ambcube.h:43-66). The fit is a chain of
+// lerps, so the samples are folded in order by one thread.
+__global__ void k_ambcubeFit(F4* __restrict__ cube, const F4* __restrict__ directions, const float* __restrict__ colors3,
+                             int samples, int prevSampleCount)
+{
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    F4 v[6];
+    for (int k = 0; k < 6; ++k) v[k] = cube[k];
+    float w = 6.0f / (1.0f + samples);
+    w = w / (1.0f + prevSampleCount);
+    for (int i = 0; i < samples; ++i)
+    {
+        const F4 d = directions[i];
+        const F4 rad = f4(colors3[3 * (size_t)i], colors3[3 * (size_t)i + 1], colors3[3 * (size_t)i + 2], 0.0f);
+        const float dx = (d.x * d.x) * w, dy = (d.y * d.y) * w, dz = (d.z * d.z) * w;
+        const int ix = d.x > 0.0f ? 0 : 1, iy = d.y > 0.0f ? 2 : 3, iz = d.z > 0.0f ? 4 : 5;
+        v[ix] = f4_lerp(v[ix], rad, dx);
+        v[iy] = f4_lerp(v[iy], rad, dy);
+        v[iz] = f4_lerp(v[iz], rad, dz);
+    }
+    for (int k = 0; k < 6; ++k) cube[k] = v[k];
+}
+
+// Atmosphere (src/math/atmosphere.h:79-181): single-scattering raymarch with a fixed step of
+// the median free path, marching towards the sun at every view step.
+// The view ray starts exactly on the crust (height 0): the length uses the IEEE square root so that
+// sqrt(r * r) == r there, as on the CPU; the approximate one can land one ulp below and end the march.
+__device__ __forceinline__ float lengthExact(V3 a) { return sqrtr(dot(a, a)); }
+
+__device__ V3 atmosphere(const SkyParams& A, V3 ro, V3 rd, V3 lightDir, V3 luminance, int steps)
+{
+    const float rCrust = A.rCrust;
+    const float rhoR = A.rhoR, rhoM = A.rhoM;
+    const V3 muR = A.muR;
+    const float muM = A.muM;
+    const float majorant = f1_max(muM, hmax(muR)) * steps;
+    const float mfp = SampleFreePath(0.5f, 1.0f / majorant);
+    const float kMinDensity = 1e-5f;
+
+    V3 tr_r = v3s(0.0f), tr_m = v3s(0.0f);
+    float odR_v = 0.0f, odM_v = 0.0f, t_v = 0.0f;
+    while (true)
+    {
+        const V3 pos_v = ro + rd * t_v;
+        const float h_v = lengthExact(pos_v) - rCrust;
+        if (h_v < 0.0f) break;
+        const float densityR_v = expf(-h_v * rhoR);
+        const float densityM_v = expf(-h_v * rhoM);
+        if ((densityR_v + densityM_v) < kMinDensity) break;
+        const float dt_v = mfp;
+        t_v += dt_v;
+        const float odR_vi = densityR_v * dt_v, odM_vi = densityM_v * dt_v;
+        odR_v += odR_vi;
+        odM_v += odM_vi;
+
+        float odR_l = 0.0f, odM_l = 0.0f, t_l = 0.0f;
+        bool hitCrust = false;
+        while (true)
+        {
+            const V3 pos_l = pos_v + lightDir * t_l;
+            const float h_l = lengthExact(pos_l) - rCrust;
+            if (h_l < 0.0f) { hitCrust = true; break; }
+            const float densityR_l = expf(-h_l * rhoR);
+            const float densityM_l = expf(-h_l * rhoM);
+            if ((densityR_l + densityM_l) < kMinDensity) break;
+            const float dt_l = mfp;
+            t_l += dt_l;
+            odR_l += densityR_l * dt_l;
+            odM_l += densityM_l * dt_l;
+        }
+        if (!hitCrust)
+        {
+            const float m = muM * (odM_v + odM_l);
+            const V3 od_i = muR * (odR_v + odR_l) + v3s(m);
+            const V3 tr_i = v3(expf(-od_i.x), expf(-od_i.y), expf(-od_i.z));
+            tr_r = tr_r + tr_i * odR_vi;
+            tr_m = tr_m + tr_i * odM_vi;
+        }
+    }
+    {
+        const float cosTheta = dot(rd, lightDir);
+        const float phR = (3.0f / (16.0f * kPi)) * (1.0f + cosTheta * cosTheta);      // RayleighPhase :31-34
+        const float phM = MiePhase(cosTheta, A.gM);
+        tr_r = tr_r * (muR * phR);
+        tr_m = tr_m * (muM * phM);
+    }
+    return (tr_r + tr_m) * luminance;
+}
+
+// BakeSkyFn (render_system.c:403-425): the view ray starts on the crust at the north pole
+__global__ void __launch_bounds__(128) k_skyBake(SkyParams A, int size, V3 sunDir, float sunLum, int steps, float* __restrict__ color)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int len = size * size;
+    if (i >= 6 * len) return;
+    const int face = i / len, t = i % len;
+    const V3 rd = cubeDir(size, face, t % size, t / size, v2(0.0f, 0.0f));
+    const V3 ro = v3(0.0f, A.rCrust, 0.0f);
+    const V3 c = atmosphere(A, ro, rd, sunDir, v3s(sunLum), steps);
+    color[3 * (size_t)i] = c.x; color[3 * (size_t)i + 1] = c.y; color[3 * (size_t)i + 2] = c.z;
+}
+
+// f1_GTTonemap (src/math/color.h:388-408) with CmdScreenshot's parameters (render_system.c:697-705)
+__device__ __forceinline__ float gtTonemap(float x)
+{
+    const float P = 1.0f, a = 1.0f, m = 0.5f, l = 0.4f, c = 1.33f, b = 0.0f;
+    const float l0 = ((P - m) * l) / a;
+    const float S0 = m + l0;
+    const float S1 = m + a * l0;
+    const float C2 = (a * P) / (P - S1);
+    const float L = m + a * (x - m);
+    const float T = m * powf(x / m, c) + b;
+    const float S = P - (P - S1) * expf(-(C2 * (x - S0)) / P);
+    const float t = f1_sat((x - 0.0f) / (m - 0.0f));         // f1_smoothstep(0, m, x), scalar.h:188-250
+    const float w0 = 1.0f - t * t * ((t * -2.0f) + 3.0f);
+    const float w2 = (x < m + l0) ? 0.0f : 1.0f;
+    const float w1 = 1.0f - w0 - w2;
+    return T * w0 + L * w1 + S * w2;
+}
+__device__ __forceinline__ float srgbInverseEotf(float L)     // color.h:165-172
+{
+    if (L <= 0.0031308f) return L * 12.92f;
+    return 1.055f * powf(L, 1.0f / 2.4f) - 0.055f;
+}
+
+// CmdScreenshot's pixel loop (render_system.c:707-727). Scene colours are Rec709
+// (r_config.h:107), so Color_SceneToSDR is the identity. The 1/255 dither term is seeded per
+// pixel (the reference draws it from the calling thread's serial generator).
+__global__ void __launch_bounds__(256) k_tonemap(const F4* __restrict__ light, int64_t n, float exposure, uint32_t pass,
+                                                 uint32_t seed, uint32_t* __restrict__ rgba8)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    F4 v = light[i];
+    v.x *= exposure; v.y *= exposure; v.z *= exposure;
+    v.x = f1_max(v.x, 0.0f); v.y = f1_max(v.y, 0.0f); v.z = f1_max(v.z, 0.0f);
+    v.x = gtTonemap(v.x); v.y = gtTonemap(v.y); v.z = gtTonemap(v.z);
+    v.x = srgbInverseEotf(v.x); v.y = srgbInverseEotf(v.y); v.z = srgbInverseEotf(v.z);
+    Rng rng = seed_prng((uint32_t)i, pass, seed, Salt_Tonemap);
+    const F4 noise = rng_f4(rng);
+    v = f4_lerp(v, noise, 1.0f / 255.0f);
+    v.w = 1.0f;
+    // f4_rgba8 (color.h:102-112)
+    const uint32_t r = (uint32_t)(f1_sat(v.x) * 255.0f + 0.5f), g = (uint32_t)(f1_sat(v.y) * 255.0f + 0.5f);
+    const uint32_t b = (uint32_t)(f1_sat(v.z) * 255.0f + 0.5f), a = (uint32_t)(f1_sat(v.w) * 255.0f + 0.5f);
+    rgba8[i] = r | (g << 8) | (b << 16) | (a << 24);
+}
+
+} // namespace
+
+int cubemapMipCount(int size)       // CalcMipCount, sampler.h:23-26
+{
+    int m = 0;
+    while ((1 << (m + 1)) <= size) ++m;
+    return 1 + m;
+}
+// cubemap.c:104-105: CalcMipOffset clamps its argument to the last mip, whose one texel is the + 1
+int cubemapElemCount(int size) { return mipOffset(size, cubemapMipCount(size) - 1) + 1; }
+
+bool launchCubeRays(int size, V3 origin, uint32_t pass, uint32_t seed, F4* dRo, F4* dRd, cudaStream_t stream)
+{
+    const int n = 6 * size * size;
+    if (n <= 0) return true;
+    k_cubeRays<<<gridFor(n, 256), 256, 0, stream>>>(size, origin, pass, seed, dRo, dRd);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+bool launchCubeConvolve(const float* dColor, float* dConvolved, int size, uint32_t sampleCount, float weight, uint32_t pass,
+                        uint32_t seed, cudaStream_t stream)
+{
+    const int mipCount = cubemapMipCount(size), elemCount = cubemapElemCount(size);
+    for (int m = 0; m < mipCount; ++m)
+    {
+        const int mSize = size >> m;
+        const int n = 6 * mSize * mSize;
+        if (n <= 0) continue;
+        k_cubeConvolve<<<gridFor(n, 128), 128, 0, stream>>>(dColor, dConvolved, size, elemCount, m, sampleCount, weight, pass, seed);
+        g_counters.kernelLaunches++;
+    }
+    return PT_CUDA(cudaGetLastError());
+}
+
+bool launchAmbCubeFit(F4* dCube, const F4* dDirections, const float* dColors3, int samples, int prevSampleCount,
+                      cudaStream_t stream)
+{
+    k_ambcubeFit<<<1, 32, 0, stream>>>(dCube, dDirections, dColors3, samples, prevSampleCount);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+bool launchSkyBake(const SkyParams& sky, int size, V3 sunDir, float sunLum, int steps, float* dColor, cudaStream_t stream)
+{
+    const int n = 6 * size * size;
+    if (n <= 0) return true;
+    k_skyBake<<<gridFor(n, 128), 128, 0, stream>>>(sky, size, sunDir, sunLum, steps, dColor);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+bool launchTonemap(const F4* dLight, int64_t n, float exposure, uint32_t pass, uint32_t seed, uint32_t* dRgba8,
+                   cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    k_tonemap<<<gridFor(n, 256), 256, 0, stream>>>(dLight, n, exposure, pass, seed, dRgba8);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+} // namespace pt

@@ -160,6 +160,7 @@ enum : uint32_t
 {
     Salt_Emission = 0x10, Salt_LightGrid = 0x11,
     Salt_Trace = 0x21, Salt_RayGen = 0x31, Salt_Bake = 0x41, Salt_Lut = 0x50, Salt_Rays = 0x60,
+    Salt_CubeBake = 0x80, Salt_CubeConvolve = 0x90 /* | mip */, Salt_Tonemap = 0xb0,
 };
 PT_HD Rng seed_ctx(uint32_t item, uint32_t pass, uint32_t seed, uint32_t salt)
 {

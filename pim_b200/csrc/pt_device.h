@@ -87,6 +87,24 @@ bool launchLightGrid(const DScene& S, float ptDistMeters, uint32_t seed, cudaStr
 bool launchDistUpdate(const DScene& S, cudaStream_t stream);
 bool launchBrdfLutBake(float* dLut, int32_t w, int32_t h, int32_t samples, uint32_t seed, cudaStream_t stream);
 
+// ------------------------------------------------------------------ bakes.cu
+struct SkyParams          // SkyMedium, src/math/types.h:531-542
+{
+    float rCrust, rAtmos;
+    V3 muR; float rhoR;
+    float muM, rhoM, gM;
+};
+int cubemapMipCount(int size);
+int cubemapElemCount(int size);
+bool launchCubeRays(int size, V3 origin, uint32_t pass, uint32_t seed, F4* dRo, F4* dRd, cudaStream_t stream);
+bool launchCubeConvolve(const float* dColor, float* dConvolved, int size, uint32_t sampleCount, float weight, uint32_t pass,
+                        uint32_t seed, cudaStream_t stream);
+bool launchAmbCubeFit(F4* dCube, const F4* dDirections, const float* dColors3, int samples, int prevSampleCount,
+                      cudaStream_t stream);
+bool launchSkyBake(const SkyParams& sky, int size, V3 sunDir, float sunLum, int steps, float* dColor, cudaStream_t stream);
+bool launchTonemap(const F4* dLight, int64_t n, float exposure, uint32_t pass, uint32_t seed, uint32_t* dRgba8,
+                   cudaStream_t stream);
+
 // ------------------------------------------------------------------ wavefront
 struct PathPool
 {

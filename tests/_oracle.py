@@ -82,6 +82,11 @@ def lib():
         L.oracle_entity_get.argtypes = [C.c_int, i32p, f32p, i32p, u32p, f32p, f32p, f32p]
         L.oracle_mesh_get.argtypes = [C.c_int, C.POINTER(f32p), C.POINTER(f32p), C.POINTER(f32p)]
         L.oracle_texture_get.argtypes = [C.c_int, i32p, i32p, C.POINTER(C.c_void_p), i32p]
+        L.oracle_cubemap_bake.argtypes = [C.c_void_p, C.c_int, f32p, f32p, C.c_float, C.c_uint32]
+        L.oracle_cubemap_convolve.argtypes = [C.c_int, f32p, f32p, C.c_uint32, C.c_float, C.c_uint32]
+        L.oracle_ambcube_bake.argtypes = [C.c_void_p, f32p, f32p, C.c_int, C.c_int, C.c_uint32]
+        L.oracle_bake_sky.argtypes = [C.c_int, f32p, f32p, f32p, C.c_float, C.c_int]
+        L.oracle_tonemap.argtypes = [f32p, C.c_int, C.c_float, C.c_uint32, u32p]
         L.oracle_sys_init()
         L.oracle_set_threads(min(os.cpu_count() or 1, 64))
         _lib = L
@@ -199,6 +204,46 @@ class Scene:
         colors = np.zeros((count, 4), np.float32); dirs = np.zeros((count, 4), np.float32)
         lib().oracle_raygen(self.h, _ptr(o), count, pass_index, _ptr(colors), _ptr(dirs))
         return colors, dirs
+
+
+    def cubemap_bake(self, color, origin, weight, pass_index=0):
+        """Cubemap_Bake (cubemap.c:162-187) into color[6, size, size, 3], in place."""
+        assert color.dtype == np.float32 and color.flags.c_contiguous and color.shape[0] == 6
+        o = np.asarray(list(origin) + [0.0] * (4 - len(origin)), np.float32)
+        lib().oracle_cubemap_bake(self.h, color.shape[1], _ptr(color), _ptr(o), weight, pass_index)
+        return color
+
+    def ambcube_bake(self, cube, origin, samples, prev_sample_count, pass_index=0):
+        cube = np.ascontiguousarray(cube, np.float32).copy()
+        o = np.asarray(list(origin) + [0.0] * (4 - len(origin)), np.float32)
+        n = lib().oracle_ambcube_bake(self.h, _ptr(cube), _ptr(o), samples, prev_sample_count, pass_index)
+        return n, cube
+
+
+def cubemap_elem_count(size):
+    return lib().oracle_cubemap_elem_count(size)
+
+
+def cubemap_convolve(color, convolved, sample_count, weight, pass_index=0):
+    """Cubemap_Convolve (cubemap.c:262-303): color[6, size, size, 3] -> convolved[6, elemCount, 4], in place."""
+    assert color.dtype == np.float32 and convolved.dtype == np.float32
+    lib().oracle_cubemap_convolve(color.shape[1], _ptr(color), _ptr(convolved), sample_count, weight, pass_index)
+    return convolved
+
+
+def bake_sky(size, sky9, sun_dir, sun_lum, steps):
+    """BakeSkyFn (render_system.c:403-425) over the reference's Atmosphere(); returns color[6, size, size, 3]."""
+    color = np.zeros((6, size, size, 3), np.float32)
+    s = np.asarray(sky9, np.float32); d = np.asarray(sun_dir, np.float32)
+    lib().oracle_bake_sky(size, _ptr(color), _ptr(s), _ptr(d), sun_lum, steps)
+    return color
+
+
+def tonemap(light, exposure=1.0, pass_index=0):
+    light = np.ascontiguousarray(light, np.float32).reshape(-1, 4)
+    out = np.zeros(light.shape[0], np.uint32)
+    lib().oracle_tonemap(_ptr(light), light.shape[0], exposure, pass_index, _ptr(out, u32p))
+    return out
 
 
 def default_dof():

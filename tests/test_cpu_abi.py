@@ -31,6 +31,8 @@ def test_struct_layouts_match_the_reference_abi():
     assert C.sizeof(api.PtTrace) == 48
     assert C.sizeof(api.Camera) == 48            # camera.h:8-15
     assert api.HIT_DTYPE.itemsize == 48
+    assert C.sizeof(api.CubemapStruct) == 8 + 12 * 8      # cubemap.h:28-34
+    assert C.sizeof(api.SkyMedium) == 36                  # types.h:531-542
 
 
 def test_no_cuda_device_fails_loudly():

@@ -99,3 +99,46 @@ def test_pcg32_known_answer():
     """O'Neill's pcg32 demo vector (seed 42, stream 54): first outputs of pcg32-demo."""
     r = scenes.Pcg32(42, 54)
     assert [r.next_u32() for _ in range(3)] == [0xa15c02b7, 0x7b47f409, 0xba1d3330]
+
+
+# ---- SURVEY 8(f) rows: the reference's cubemap / sky / tonemap code in oracle/_ref ----------
+
+SKY9 = [6360e3, 60e3, 1 / 192e3, 1 / 82e3, 1 / 34e3, 1 / 8.5e3, 1 / 48e3, 1 / 1.2e3, 0.758]
+
+
+def test_oracle_sky_bake_is_a_sky(oracle):
+    """BakeSkyFn over the reference's Atmosphere(): finite, positive, brightest towards the (low) sun"""
+    sun = [0.882, 0.195, 0.429]
+    c = oracle.bake_sky(16, SKY9, sun, 3800.0, 2)
+    assert np.isfinite(c).all() and (c >= 0).all()
+    assert c[0].mean() > 3 * c[1].mean()         # +X (towards the sun) much brighter than -X
+    assert c[2].mean() > c[3].mean() > 0         # -Y starts on the crust: one march step, then it ends
+    assert c.max() < 3800.0
+    again = oracle.bake_sky(16, SKY9, sun, 3800.0, 2)
+    assert (again == c).all()                    # no random numbers in this bake
+
+
+def test_oracle_tonemap_known_answers(oracle):
+    """screenshot loop: black stays black (up to the 1/255 dither), huge saturates, monotone in between"""
+    x = np.zeros((256, 4), np.float32)
+    x[:, :3] = np.linspace(0.0, 4.0, 256, dtype=np.float32)[:, None]
+    out = oracle.tonemap(x, 1.0, 0).view(np.uint8).reshape(-1, 4).astype(np.int32)
+    assert (out[:, 3] == 255).all()
+    assert out[0, :3].max() <= 1
+    assert out[-1, :3].min() >= 250
+    assert (np.diff(out[:, 0]) >= -1).all()       # monotone up to the dither
+    mid = oracle.tonemap(np.array([[0.18, 0.18, 0.18, 1.0]], np.float32), 1.0, 0).view(np.uint8)
+    assert abs(int(mid[0]) - 106) <= 2            # sRGB(GT(0.18)): toe 0.5 * (0.18 / 0.5)^1.33 = 0.128 -> 0.415
+
+
+def test_oracle_cubemap_convolve_of_a_constant_is_the_constant(oracle):
+    size = 8
+    color = np.full((6, size, size, 3), 0.5, np.float32)
+    n = oracle.cubemap_elem_count(size)
+    assert n == 64 + 16 + 4 + 1
+    conv = np.zeros((6, n, 4), np.float32)
+    oracle.cubemap_convolve(color, conv, 8, 1.0, 0)
+    assert np.allclose(conv[:, :n - 1, :3], 0.5, atol=1e-5)
+    assert np.allclose(conv[:, :n - 1, 3], 1.0, atol=1e-5)
+    # the 1x1 mip: Cubemap_CalcDir divides by size - 1 = 0, the direction is NaN, no sample passes NoL > 0
+    assert (conv[:, n - 1] == 0).all()

@@ -3,6 +3,8 @@
 
   python tools/configs.py c3 [--spp 256] [--cpu-spp 1]   ~1M-triangle interior, 1080p (configs[2])
   python tools/configs.py c4 [--spp 64] [--cpu]          cornell lightmap bake, 16 texels/m (configs[3])
+  python tools/configs.py bakes [--cpu]                  SURVEY 8(f) rows: sky bake, cubemap bake / convolve,
+                                                         ambient cube, screenshot tonemap
 
 GPU numbers are CUDA-event / wall times around the C-ABI calls; the CPU numbers are the
 reference's own code (oracle/_ref) on the host cores.
@@ -136,9 +138,94 @@ def c4(args):
     scene.close()
 
 
+def bakes(args):
+    """SURVEY 8(f) N2-N4. GPU: kernel time from CUDA events inside the library (Pt_LastKernelMs) and wall time
+    of the whole C-ABI call with host buffers; CPU: the reference's code in oracle/_ref on the host threads."""
+    import _oracle as O
+    from pim_b200 import api, scenes
+    import parity
+    L = api.load()
+    sky9 = [6360e3, 60e3, 1 / 192e3, 1 / 82e3, 1 / 34e3, 1 / 8.5e3, 1 / 48e3, 1 / 1.2e3, 0.758]
+    sun = [0.882, 0.195, 0.429]
+    out = {"config": "bakes (SURVEY 8(f) N2-N4)", "cpu_threads": O.lib().oracle_get_threads() if args.cpu else 0}
+
+    def timed(fn, reps=3):
+        fn()
+        best_wall, best_k = 1e30, 1e30
+        for _ in range(reps):
+            t0 = time.perf_counter(); fn(); dt = time.perf_counter() - t0
+            best_wall = min(best_wall, dt); best_k = min(best_k, L.Pt_LastKernelMs() * 1e-3)
+        return best_wall, best_k
+
+    # N3 sky: the reference's default (size 64, 4 steps) and a large one
+    for size, steps in ((64, 4), (512, 4)):
+        cm = api.Cubemap(size)
+        wall, k = timed(lambda: cm.bake_sky(api.earth_sky(), sun, 3800.0, steps))
+        r = {"texels": 6 * size * size, "gpu_kernel_ms": k * 1e3, "gpu_call_ms": wall * 1e3, "gpu_mtexels_s": 6 * size * size / k / 1e6}
+        if args.cpu and size <= 128:
+            t0 = time.perf_counter(); O.bake_sky(size, sky9, sun, 3800.0, steps); dt = time.perf_counter() - t0
+            r["cpu_ms"] = dt * 1e3; r["cpu_mtexels_s"] = 6 * size * size / dt / 1e6
+        out["sky_%d" % size] = r
+        cm.close()
+
+    # N4 tonemap at 1080p: 16 B in + 4 B out per pixel
+    n = 1920 * 1080
+    light = np.random.default_rng(1).random((n, 4), np.float32) * 4.0
+    wall, k = timed(lambda: api.tonemap(light, 1.0, 1, 0))
+    out["tonemap_1080p"] = {"gpu_kernel_ms": k * 1e3, "gpu_call_ms": wall * 1e3, "gpu_mpixels_s": n / k / 1e6,
+                            "hbm_gbs": n * 20 / k / 1e9}
+    if args.cpu:
+        t0 = time.perf_counter(); O.tonemap(light, 1.0, 0); dt = time.perf_counter() - t0
+        out["tonemap_1080p"].update({"cpu_ms": dt * 1e3, "cpu_mpixels_s": n / dt / 1e6})
+
+    # N2 convolve: 64^2 faces, 64 samples per mip texel (reference: render_system.c uses 64)
+    size, spt = 64, 64
+    color = O.bake_sky(size, sky9, sun, 3800.0, 2) if args.cpu else np.ones((6, size, size, 3), np.float32)
+    cm = api.Cubemap(size)
+    for f in range(6):
+        cm.color(f)[:] = color[f]
+    wall, k = timed(lambda: cm.convolve(spt, 0.5, 1, 0))
+    texels = 6 * sum((size >> m) ** 2 for m in range(7))
+    out["convolve_64"] = {"mip_texels": texels, "samples_per_texel": spt, "gpu_kernel_ms": k * 1e3, "gpu_call_ms": wall * 1e3,
+                          "gpu_msamples_s": texels * spt / k / 1e6}
+    if args.cpu:
+        conv = np.zeros((6, O.cubemap_elem_count(size), 4), np.float32)
+        t0 = time.perf_counter(); O.cubemap_convolve(color, conv, spt, 0.5, 0); dt = time.perf_counter() - t0
+        out["convolve_64"].update({"cpu_ms": dt * 1e3, "cpu_msamples_s": texels * spt / dt / 1e6})
+    cm.close()
+
+    # N2 cubemap bake and ambient cube inside cornell boxes
+    desc = scenes.cornell_box("boxes", brdf_lut=parity.reference_lut(), seed=1)
+    scene = api.Scene(desc)
+    for size in (64, 512):
+        cm = api.Cubemap(size)
+        state = {"p": 0}
+        def bake():
+            cm.bake(scene, [0.3, -0.2, 0.1, 0.0], 0.5, pass_index=state["p"]); state["p"] += 1
+        wall, k = timed(bake)
+        out["cubemap_bake_%d" % size] = {"paths": 6 * size * size, "gpu_kernel_ms": k * 1e3, "gpu_call_ms": wall * 1e3,
+                                         "gpu_mpaths_s": 6 * size * size / k / 1e6}
+        cm.close()
+    cube = np.zeros((6, 4), np.float32)
+    wall, k = timed(lambda: api.ambcube_bake(scene, cube, [0, 0, 0, 0], 4096, 0))
+    out["ambcube_4096"] = {"gpu_call_ms": wall * 1e3}
+    if args.cpu:
+        O.set_seed(1)
+        O.load_scene_desc(desc)
+        ref = O.Scene()
+        want = np.zeros((6, 64, 64, 3), np.float32)
+        t0 = time.perf_counter(); ref.cubemap_bake(want, [0.3, -0.2, 0.1, 0.0], 0.5, 0); dt = time.perf_counter() - t0
+        out["cubemap_bake_64"].update({"cpu_ms": dt * 1e3, "cpu_mpaths_s": 6 * 64 * 64 / dt / 1e6})
+        t0 = time.perf_counter(); ref.ambcube_bake(cube, [0, 0, 0, 0], 4096, 0, 0); dt = time.perf_counter() - t0
+        out["ambcube_4096"]["cpu_ms"] = dt * 1e3
+        ref.close()
+    scene.close()
+    print(json.dumps(out))
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("config", choices=["c3", "c4"])
+    ap.add_argument("config", choices=["c3", "c4", "bakes"])
     ap.add_argument("--spp", type=int, default=0)
     ap.add_argument("--tris", type=int, default=1_000_000)
     ap.add_argument("--emissive", type=float, default=0.001)
@@ -146,7 +233,9 @@ def main():
     ap.add_argument("--cpu", action="store_true")
     ap.add_argument("--sequential", action="store_true", help="c4: PtBake_Sequential")
     args = ap.parse_args()
-    if args.config == "c3":
+    if args.config == "bakes":
+        bakes(args)
+    elif args.config == "c3":
         args.spp = args.spp or 256
         c3(args)
     else:
