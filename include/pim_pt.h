@@ -262,6 +262,29 @@ typedef struct PtLightmapDesc_s
 int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCount,
                         float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass);
 
+/* ---- lightmap attribute embedding --------------------------
+ * EmbedAttributes / EmbedTaskFn (static in src/rendering/lightmap.c:947-1047), the last and
+ * O(texels x triangles) step of LmPack_Pack: for every texel of every page find the
+ * lightmapped triangle nearest in lightmap space (within 2 texels) and store its
+ * interpolated position, normal and a coverage flag. Chart grouping and atlas placement
+ * (lightmap.c:527-945) stay host code and run before this call.
+ * meshes[i]: one drawable in Entities order — the Mesh's own arrays (mesh.h:25-33; uvs.zw
+ * = lightmap uv, texIndices = int4 per vertex, .w = lightmap slot) and its material flags
+ * (drawables with PtMatFlag_Sky or lava, 1 << 4, are skipped as in the reference).
+ * slotIndices[k] = lightmaps[k].slot.index. Writes position, normal and sampleCounts of
+ * every page (probes are left alone); all pages must have the same size. 0 on success. */
+typedef struct PtEmbedMesh_s
+{
+    const pim_float4* positions;
+    const pim_float4* normals;
+    const pim_float4* uvs;
+    const int32_t* texIndices;
+    int32_t length;          /* vertices */
+    uint32_t materialFlags;
+} PtEmbedMesh;
+int32_t LmPack_EmbedDesc(const PtEmbedMesh* meshes, int32_t meshCount, PtLightmapDesc* lightmaps,
+                         const int32_t* slotIndices, int32_t lmCount);
+
 /* ---- callers either side of the path -------------------
  * The reference functions that feed the path tracer (sky) or consume Pt_TraceRay /
  * Pt_RayGen (cubemap and ambient-cube bakes) or its image (screenshot), same names and

@@ -208,6 +208,14 @@ int oracle_mesh_get(int meshId, const float** pos4, const float** nrm4, const fl
     return m->length;
 }
 
+/* int4 per vertex; .w = lightmap slot index after LmPack_Pack (lightmap.c:892-921) */
+const int32_t* oracle_mesh_texindices(int meshId)
+{
+    MeshId id = { 0 }; id.version = 1; id.index = (u32)meshId;
+    const Mesh* m = Mesh_Get(id);
+    return m ? (const int32_t*)m->texIndices : NULL;
+}
+
 int oracle_texture_get(int texId, int* w, int* h, const void** texels, int* vkFormat)
 {
     TextureId id = { 0 }; id.version = 1; id.index = (u32)texId;

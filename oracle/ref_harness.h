@@ -60,6 +60,7 @@ void oracle_entity_get(int i, int* meshId, float* matrix16, int* texIds3,
                        uint32_t* flags, float* meanFreePath4, float* ior, float* bumpiness);
 int oracle_mesh_get(int meshId, const float** pos4, const float** nrm4, const float** uv4);
 int oracle_texture_get(int texId, int* w, int* h, const void** texels, int* vkFormat);
+const int32_t* oracle_mesh_texindices(int meshId);
 
 typedef struct OracleSceneInfo
 {
@@ -122,6 +123,8 @@ void oracle_brute_n(const void* scene, const float* ro4, const float* rd4, float
 int oracle_lm_pack(int atlasSize, float texelsPerUnit, float distThresh, float degThresh);
 int oracle_lm_size(void);
 void oracle_lm_page(int i, float** probes5, float** position3, float** normal3, float** sampleCounts);
+void oracle_lm_embed(void);    /* EmbedAttributes alone, on the pack oracle_lm_pack left */
+int oracle_lm_slot(int i);      /* Lightmap.slot.index: what EmbedTaskFn matches texIndices.w against */
 void oracle_lm_bake(void* scene, float timeSlice, int spp, uint32_t pass);
 
 /* SURVEY 8(f) rows (ref_cm_wrap.c). color: 6 x size*size float3; convolved: 6 x elemCount float4 */

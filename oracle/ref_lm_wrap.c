@@ -27,6 +27,17 @@ void oracle_lm_page(int i, float** probes5, float** position3, float** normal3, 
     *sampleCounts = lm->sampleCounts;
 }
 
+/* EmbedAttributes (lightmap.c:1036-1047) again on the current pack: the step LmPack_EmbedDesc replaces, alone */
+void oracle_lm_embed(void)
+{
+    LmPack* pack = LmPack_Get();
+    oracle_begin(ORACLE_STREAM_LMPACK, 1);
+    EmbedAttributes(pack->lightmaps, pack->lmCount, pack->texelsPerMeter);
+    oracle_frame_end();
+}
+
+int oracle_lm_slot(int i) { return (int)LmPack_Get()->lightmaps[i].slot.index; }
+
 void oracle_lm_bake(void* scene, float timeSlice, int spp, uint32_t pass)
 {
     oracle_begin(ORACLE_STREAM_BAKE, pass);

@@ -471,7 +471,11 @@ bool Crate_Set(Crate *const crate, Guid id, const void* src, i32 size) { (void)c
 vkrTextureId vkrTexTable_Alloc(VkImageViewType type, VkFormat format, VkSamplerAddressMode clamp, i32 width, i32 height, i32 depth, i32 layers, bool mips)
 {
     (void)type; (void)format; (void)clamp; (void)width; (void)height; (void)depth; (void)layers; (void)mips;
+    /* a fresh slot per call, as the engine's table gives: EmbedTaskFn (lightmap.c:968,991) tells the
+     * pages apart by it */
+    static u32 s_nextSlot = 1;
     vkrTextureId id = { 0 };
+    id.index = s_nextSlot++;
     return id;
 }
 bool vkrTexTable_Free(vkrTextureId id) { (void)id; return true; }

@@ -86,6 +86,11 @@ class PtLightmapDesc(C.Structure):
                 ("sampleCounts", C.c_void_p), ("size", C.c_int32)]
 
 
+class PtEmbedMesh(C.Structure):
+    _fields_ = [("positions", C.c_void_p), ("normals", C.c_void_p), ("uvs", C.c_void_p), ("texIndices", C.c_void_p),
+                ("length", C.c_int32), ("materialFlags", C.c_uint32)]
+
+
 class PtSceneStats(C.Structure):
     _fields_ = [("vertCount", C.c_int32), ("matCount", C.c_int32), ("emissiveCount", C.c_int32),
                 ("gridSize", C.c_int32 * 3), ("gridLo", C.c_float * 4), ("gridHi", C.c_float * 4),
@@ -131,7 +136,7 @@ EXPORTS = [
     "Pt_GetCounters", "Pt_ResetCounters", "Pt_LastKernelMs", "Pt_LastError",
     "Pt_SetKernelTiming", "Pt_GetKernelStats", "Pt_IntersectCountN", "Pt_TraceRayN_NoAlloc",
     "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
-    "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap",
+    "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap", "LmPack_EmbedDesc",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -202,6 +207,8 @@ def load():
     L.Pt_BakeSky.restype = C.c_int32
     L.Pt_Tonemap.argtypes = [vp, C.c_int64, C.c_float, C.c_uint32, C.c_uint32, vp]
     L.Pt_Tonemap.restype = C.c_int32
+    L.LmPack_EmbedDesc.argtypes = [C.POINTER(PtEmbedMesh), C.c_int32, C.POINTER(PtLightmapDesc), vp, C.c_int32]
+    L.LmPack_EmbedDesc.restype = C.c_int32
     for name in ("Pt_IntersectN", "Pt_OccludedN", "Pt_TraceRayN", "Pt_TraceSpp", "Pt_IntersectN_Device",
                  "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc", "PtScene_GetStats",
                  "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut"):
@@ -523,4 +530,27 @@ def tonemap(light, exposure=1.0, seed=1, pass_index=0):
     light = np.ascontiguousarray(light, np.float32).reshape(-1, 4)
     out = np.zeros(light.shape[0], np.uint32)
     _check(load().Pt_Tonemap(light.ctypes.data, light.shape[0], exposure, seed, pass_index, out.ctypes.data), "Pt_Tonemap")
+    return out
+
+
+def lm_embed(meshes, slot_indices, size):
+    """LmPack_EmbedDesc. meshes: list of (positions[V,4], normals[V,4], uvs[V,4], texIndices[V,4] int32,
+    materialFlags) in drawable order; returns per page (position[S*S,3], normal[S*S,3], sampleCounts[S*S])."""
+    keep = []
+    arr = (PtEmbedMesh * max(len(meshes), 1))()
+    for i, (pos, nrm, uv, tex, flags) in enumerate(meshes):
+        pos = np.ascontiguousarray(pos, np.float32); nrm = np.ascontiguousarray(nrm, np.float32)
+        uv = np.ascontiguousarray(uv, np.float32); tex = np.ascontiguousarray(tex, np.int32)
+        keep += [pos, nrm, uv, tex]
+        arr[i] = PtEmbedMesh(pos.ctypes.data, nrm.ctypes.data, uv.ctypes.data, tex.ctypes.data, len(pos), int(flags))
+    slots = np.ascontiguousarray(slot_indices, np.int32)
+    pages = (PtLightmapDesc * max(len(slots), 1))()
+    out = []
+    for k in range(len(slots)):
+        position = np.zeros((size * size, 3), np.float32); normal = np.zeros((size * size, 3), np.float32)
+        counts = np.zeros(size * size, np.float32)
+        pages[k].position, pages[k].normal, pages[k].sampleCounts, pages[k].size = (
+            position.ctypes.data, normal.ctypes.data, counts.ctypes.data, size)
+        out.append((position, normal, counts))
+    _check(load().LmPack_EmbedDesc(arr, len(meshes), pages, slots.ctypes.data, len(slots)), "LmPack_EmbedDesc")
     return out

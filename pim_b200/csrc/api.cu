@@ -970,6 +970,75 @@ int32_t AmbCube_Bake(PtScene* scene, AmbCube_t* pCube, pim_float4 origin, int32_
     return prevSampleCount + 1;
 }
 
+int32_t LmPack_EmbedDesc(const PtEmbedMesh* meshes, int32_t meshCount, PtLightmapDesc* lightmaps, const int32_t* slotIndices,
+                         int32_t lmCount)
+{
+    if (!ensureInit()) return -1;
+    if (lmCount <= 0) return 0;
+    if (!lightmaps || !slotIndices || (!meshes && meshCount > 0)) { setError("LmPack_EmbedDesc: null argument"); return -1; }
+    const int32_t lmSize = lightmaps[0].size;
+    for (int32_t k = 0; k < lmCount; ++k)
+    {
+        if (lightmaps[k].size != lmSize || lmSize <= 0) { setError("LmPack_EmbedDesc: pages differ in size"); return -1; }
+        if (!lightmaps[k].position || !lightmaps[k].normal || !lightmaps[k].sampleCounts) { setError("LmPack_EmbedDesc: page %d has no storage", k); return -1; }
+    }
+    // the reference's scan order: drawables in order, whole triangles of each mesh in order
+    const uint32_t kUnmapped = (1u << 1) | (1u << 4);       // kUnmappedMaterials, lightmap.c:38
+    int64_t triCount = 0;
+    for (int32_t i = 0; i < meshCount; ++i)
+    {
+        const PtEmbedMesh& m = meshes[i];
+        if ((m.materialFlags & kUnmapped) || !m.positions || !m.normals || !m.uvs || !m.texIndices) continue;
+        triCount += m.length / 3;
+    }
+    if (triCount > 0xffffffffll) { setError("LmPack_EmbedDesc: more than 2^32 triangles"); return -1; }
+    const size_t texels = (size_t)lmCount * lmSize * lmSize;
+    cudaStream_t st = nullptr;
+    DevBuf dPos, dNor, dUv, dPage, dKeys, dOutPos, dOutNor, dOutCnt;
+    if (!dPos.alloc(16 * 3 * (size_t)triCount) || !dNor.alloc(16 * 3 * (size_t)triCount) || !dUv.alloc(16 * 3 * (size_t)triCount) ||
+        !dPage.alloc(4 * (size_t)triCount) || !dKeys.alloc(8 * texels) || !dOutPos.alloc(12 * texels) || !dOutNor.alloc(12 * texels) ||
+        !dOutCnt.alloc(4 * texels)) return -1;
+    std::vector<int32_t> page((size_t)triCount);
+    bool ok = true;
+    int64_t base = 0;
+    for (int32_t i = 0; ok && i < meshCount; ++i)
+    {
+        const PtEmbedMesh& m = meshes[i];
+        if ((m.materialFlags & kUnmapped) || !m.positions || !m.normals || !m.uvs || !m.texIndices) continue;
+        const int64_t nt = m.length / 3;
+        if (nt <= 0) continue;
+        for (int64_t t = 0; t < nt; ++t)
+        {
+            const int32_t slot = m.texIndices[4 * (3 * t) + 3];     // texIndices[iVert].w, lightmap.c:991
+            int32_t p = -1;
+            for (int32_t k = 0; k < lmCount; ++k) { if (slotIndices[k] == slot) { p = k; break; } }
+            page[(size_t)(base + t)] = p;
+        }
+        const size_t bytes = 16 * 3 * (size_t)nt, off = 3 * (size_t)base;
+        ok = PT_CUDA(cudaMemcpyAsync((F4*)dPos.p + off, m.positions, bytes, cudaMemcpyHostToDevice, st)) &&
+             PT_CUDA(cudaMemcpyAsync((F4*)dNor.p + off, m.normals, bytes, cudaMemcpyHostToDevice, st)) &&
+             PT_CUDA(cudaMemcpyAsync((F4*)dUv.p + off, m.uvs, bytes, cudaMemcpyHostToDevice, st));
+        base += nt;
+    }
+    ok = ok && PT_CUDA(cudaMemcpyAsync(dPage.p, page.data(), 4 * (size_t)triCount, cudaMemcpyHostToDevice, st));
+    ok = ok && PT_CUDA(cudaMemsetAsync(dKeys.p, 0xff, 8 * texels, st));
+    EmbedMesh M;
+    M.positions = (const F4*)dPos.p; M.normals = (const F4*)dNor.p; M.uvs = (const F4*)dUv.p;
+    M.page = (const int32_t*)dPage.p; M.triCount = triCount;
+    KernelTimer timer(st);
+    ok = ok && launchEmbed(M, lmSize, lmCount, (unsigned long long*)dKeys.p, (float*)dOutPos.p, (float*)dOutNor.p, (float*)dOutCnt.p, st);
+    timer.stop();
+    const size_t n = (size_t)lmSize * lmSize;
+    for (int32_t k = 0; ok && k < lmCount; ++k)
+    {
+        ok = PT_CUDA(cudaMemcpyAsync((void*)lightmaps[k].position, (float*)dOutPos.p + 3 * n * k, 12 * n, cudaMemcpyDeviceToHost, st)) &&
+             PT_CUDA(cudaMemcpyAsync((void*)lightmaps[k].normal, (float*)dOutNor.p + 3 * n * k, 12 * n, cudaMemcpyDeviceToHost, st)) &&
+             PT_CUDA(cudaMemcpyAsync(lightmaps[k].sampleCounts, (float*)dOutCnt.p + n * k, 4 * n, cudaMemcpyDeviceToHost, st));
+    }
+    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    return ok ? 0 : -1;
+}
+
 int32_t Pt_BakeSky(Cubemap* cm, const SkyMedium* sky, pim_float3 sunDir, float sunLum, int32_t steps)
 {
     if (!ensureInit()) return -1;

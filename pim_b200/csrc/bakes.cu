@@ -258,6 +258,123 @@ __global__ void __launch_bounds__(256) k_tonemap(const F4* __restrict__ light, i
     rgba8[i] = r | (g << 8) | (b << 16) | (a << 24);
 }
 
+// ---- N1: EmbedTaskFn (src/rendering/lightmap.c:947-1034) --------------------------------------
+// The reference asks, for every texel of every page, every triangle of every drawable for its
+// signed distance in lightmap space (texels x triangles). Here each triangle visits only the
+// texels of its own bounding box grown by the fill padding and bids (distance, triangle index)
+// on them with one 64-bit atomicMin; the lowest distance wins and equal distances go to the
+// lower index — the order the reference's `dist < lmDist` scan keeps. A second pass recomputes
+// the winner's barycentrics per texel. (A triangle with zero area in lightmap space is the one
+// case that differs: sdTriangle2D's sign term is 0 for it, so the reference sees a negative
+// distance on every texel of the page; here it only bids inside its padded box.)
+
+// sdEdge2D, bary2D, sdTriangle2D: src/math/sdf.h:99-156
+__device__ __forceinline__ float sdEdge2D(V2 A, V2 B, V2 P)
+{
+    const float apx = P.x - A.x, apy = P.y - A.y, abx = B.x - A.x, aby = B.y - A.y;
+    return 0.5f * (apy * abx - apx * aby);
+}
+__device__ __forceinline__ float dot2(V2 a, V2 b) { return a.x * b.x + a.y * b.y; }
+__device__ __forceinline__ float sdTriangle2D(V2 a, V2 b, V2 c, V2 p)
+{
+    const V2 ba = v2(b.x - a.x, b.y - a.y), cb = v2(c.x - b.x, c.y - b.y), ac = v2(a.x - c.x, a.y - c.y);
+    const V2 pa = v2(p.x - a.x, p.y - a.y), pb = v2(p.x - b.x, p.y - b.y), pc = v2(p.x - c.x, p.y - c.y);
+    const float h0 = f1_sat(dot2(pa, ba) / dot2(ba, ba));
+    const float h1 = f1_sat(dot2(pb, cb) / dot2(cb, cb));
+    const float h2 = f1_sat(dot2(pc, ac) / dot2(ac, ac));
+    const V2 pq0 = v2(pa.x - ba.x * h0, pa.y - ba.y * h0);
+    const V2 pq1 = v2(pb.x - cb.x * h1, pb.y - cb.y * h1);
+    const V2 pq2 = v2(pc.x - ac.x * h2, pc.y - ac.y * h2);
+    const float s = f1_sign(ba.x * ac.y - ba.y * ac.x);
+    const float dx = f1_min(dot2(pq0, pq0), f1_min(dot2(pq1, pq1), dot2(pq2, pq2)));
+    const float dy = f1_min(s * (pa.x * ba.y - pa.y * ba.x), f1_min(s * (pb.x * cb.y - pb.y * cb.x), s * (pc.x * ac.y - pc.y * ac.x)));
+    const float dySign = (dy >= 0.0f) ? 1.0f : -1.0f;
+    return -sqrtf(f1_max(dx, kEpsilonSq)) * dySign;
+}
+
+constexpr float kFillPadding = 2.0f;                       // lightmap.c:40
+constexpr unsigned long long kEmbedNone = ~0ull;
+
+// float bits -> unsigned with the same order (negative distances are inside the triangle)
+__device__ __forceinline__ uint32_t orderedBits(float f)
+{
+    const uint32_t u = f2u(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__device__ __forceinline__ void embedTriUv(const F4* __restrict__ uvs, int64_t tri, float texelSize, V2& A, V2& B, V2& C)
+{
+    const F4 a = uvs[3 * tri], b = uvs[3 * tri + 1], c = uvs[3 * tri + 2];
+    A = v2(a.z * texelSize, a.w * texelSize);     // f2_mulvs(f2_v(uvs[a].z, uvs[a].w), texelSize)
+    B = v2(b.z * texelSize, b.w * texelSize);
+    C = v2(c.z * texelSize, c.w * texelSize);
+}
+
+// one warp per triangle, lanes stride over the padded bounding box
+__global__ void __launch_bounds__(256) k_embedRaster(const EmbedMesh M, int lmSize, unsigned long long* __restrict__ keys)
+{
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp >= M.triCount) return;
+    const int page = M.page[warp];
+    if (page < 0) return;
+    V2 A, B, C;
+    embedTriUv(M.uvs, warp, (float)lmSize, A, B, C);
+    if (!(isfinite(A.x) && isfinite(A.y) && isfinite(B.x) && isfinite(B.y) && isfinite(C.x) && isfinite(C.y))) return;
+    // texel centres within kFillPadding of the triangle lie inside its box grown by the padding
+    const float pad = kFillPadding + 0.5f;
+    int x0 = (int)floorf(f1_min(A.x, f1_min(B.x, C.x)) - pad), x1 = (int)ceilf(f1_max(A.x, f1_max(B.x, C.x)) + pad);
+    int y0 = (int)floorf(f1_min(A.y, f1_min(B.y, C.y)) - pad), y1 = (int)ceilf(f1_max(A.y, f1_max(B.y, C.y)) + pad);
+    x0 = x0 < 0 ? 0 : x0; y0 = y0 < 0 ? 0 : y0;
+    x1 = x1 > lmSize - 1 ? lmSize - 1 : x1; y1 = y1 > lmSize - 1 ? lmSize - 1 : y1;
+    if (x1 < x0 || y1 < y0) return;
+    const int w = x1 - x0 + 1;
+    const int64_t count = (int64_t)w * (y1 - y0 + 1);
+    unsigned long long* dst = keys + (size_t)page * lmSize * lmSize;
+    for (int64_t i = lane; i < count; i += 32)
+    {
+        const int x = x0 + (int)(i % w), y = y0 + (int)(i / w);
+        const float dist = sdTriangle2D(A, B, C, v2(x + 0.5f, y + 0.5f));
+        if (dist < kFillPadding)
+        {
+            const unsigned long long key = ((unsigned long long)orderedBits(dist) << 32) | (unsigned long long)(uint32_t)warp;
+            atomicMin(dst + (size_t)y * lmSize + x, key);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_embedResolve(const EmbedMesh M, const unsigned long long* __restrict__ keys,
+                                                      int lmSize, int64_t texels, float* __restrict__ position3,
+                                                      float* __restrict__ normal3, float* __restrict__ sampleCounts)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= texels) return;
+    const unsigned long long key = keys[i];
+    V3 pos = v3s(0.0f), nor = v3s(0.0f);
+    float count = 0.0f;
+    if (key != kEmbedNone)
+    {
+        const int64_t tri = (int64_t)(uint32_t)key;
+        const int iTexel = (int)(i % ((int64_t)lmSize * lmSize));
+        const V2 px = v2((iTexel % lmSize) + 0.5f, (iTexel / lmSize) + 0.5f);
+        V2 A, B, C;
+        embedTriUv(M.uvs, tri, (float)lmSize, A, B, C);
+        float area = sdEdge2D(A, B, C);
+        area = f1_max(area, 1e-5f);
+        const float rcpArea = 1.0f / area;
+        float w = sdEdge2D(B, C, px) * rcpArea, u = sdEdge2D(C, A, px) * rcpArea, v = sdEdge2D(A, B, px) * rcpArea;
+        const float r = 1.0f / (w + u + v);                 // f4_divvs
+        w *= r; u *= r; v *= r;
+        pos = (v3(M.positions[3 * tri]) * w + v3(M.positions[3 * tri + 1]) * u) + v3(M.positions[3 * tri + 2]) * v;   // f4_blend
+        nor = normalize((v3(M.normals[3 * tri]) * w + v3(M.normals[3 * tri + 1]) * u) + v3(M.normals[3 * tri + 2]) * v);
+        nor = normalize(nor);                                // lightmap.c:1026-1029
+        count = 1.0f;
+    }
+    sampleCounts[i] = count;
+    position3[3 * i] = pos.x; position3[3 * i + 1] = pos.y; position3[3 * i + 2] = pos.z;
+    normal3[3 * i] = nor.x; normal3[3 * i + 1] = nor.y; normal3[3 * i + 2] = nor.z;
+}
+
 } // namespace
 
 int cubemapMipCount(int size)       // CalcMipCount, sampler.h:23-26
@@ -315,6 +432,22 @@ bool launchTonemap(const F4* dLight, int64_t n, float exposure, uint32_t pass, u
 {
     if (n <= 0) return true;
     k_tonemap<<<gridFor(n, 256), 256, 0, stream>>>(dLight, n, exposure, pass, seed, dRgba8);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+// keys: one 64-bit word per texel of all pages, filled with 0xff.. by the caller
+bool launchEmbed(const EmbedMesh& mesh, int lmSize, int lmCount, unsigned long long* dKeys,
+                 float* dPosition3, float* dNormal3, float* dSampleCounts, cudaStream_t stream)
+{
+    const int64_t texels = (int64_t)lmCount * lmSize * lmSize;
+    if (texels <= 0) return true;
+    if (mesh.triCount > 0)
+    {
+        k_embedRaster<<<gridFor(mesh.triCount * 32, 256), 256, 0, stream>>>(mesh, lmSize, dKeys);
+        g_counters.kernelLaunches++;
+    }
+    k_embedResolve<<<gridFor(texels, 256), 256, 0, stream>>>(mesh, dKeys, lmSize, texels, dPosition3, dNormal3, dSampleCounts);
     g_counters.kernelLaunches++;
     return PT_CUDA(cudaGetLastError());
 }

@@ -102,6 +102,17 @@ bool launchCubeConvolve(const float* dColor, float* dConvolved, int size, uint32
 bool launchAmbCubeFit(F4* dCube, const F4* dDirections, const float* dColors3, int samples, int prevSampleCount,
                       cudaStream_t stream);
 bool launchSkyBake(const SkyParams& sky, int size, V3 sunDir, float sunLum, int steps, float* dColor, cudaStream_t stream);
+// the lightmapped triangles in the reference's scan order (drawable, then vertex), vertices 3t..3t+2:
+// object-space positions and normals and Mesh.uvs (zw = lightmap uv) as EmbedTaskFn reads them;
+// page[t] = index of the lightmap whose slot matches texIndices.w, or -1
+struct EmbedMesh
+{
+    const F4* positions; const F4* normals; const F4* uvs;
+    const int32_t* page;
+    int64_t triCount;
+};
+bool launchEmbed(const EmbedMesh& mesh, int lmSize, int lmCount, unsigned long long* dKeys,
+                 float* dPosition3, float* dNormal3, float* dSampleCounts, cudaStream_t stream);
 bool launchTonemap(const F4* dLight, int64_t n, float exposure, uint32_t pass, uint32_t seed, uint32_t* dRgba8,
                    cudaStream_t stream);
 

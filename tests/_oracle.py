@@ -297,6 +297,33 @@ def lm_page(i):
             np.ctypeslib.as_array(nrm, (n, 3)), np.ctypeslib.as_array(cnt, (n,)))
 
 
+def lm_embed():
+    lib().oracle_lm_embed()
+
+
+def lm_slot(i):
+    return lib().oracle_lm_slot(i)
+
+
+def lm_meshes():
+    """The drawables as EmbedTaskFn reads them after LmPack_Pack, in Entities order:
+    (positions[V,4], normals[V,4], uvs[V,4] (zw = lightmap uv), texIndices[V,4] int32, material flags)."""
+    L = lib()
+    L.oracle_mesh_texindices.restype = i32p
+    L.oracle_mesh_texindices.argtypes = [C.c_int]
+    out = []
+    for i in range(L.oracle_entity_count()):
+        mesh_id = np.zeros(1, np.int32); mat = np.zeros(16, np.float32); tex = np.zeros(3, np.int32)
+        flags = np.zeros(1, np.uint32); mfp = np.zeros(4, np.float32); ior = np.zeros(1, np.float32); bump = np.zeros(1, np.float32)
+        L.oracle_entity_get(i, _ptr(mesh_id, i32p), _ptr(mat), _ptr(tex, i32p), _ptr(flags, u32p), _ptr(mfp), _ptr(ior), _ptr(bump))
+        pos = f32p(); nrm = f32p(); uv = f32p()
+        n = L.oracle_mesh_get(int(mesh_id[0]), C.byref(pos), C.byref(nrm), C.byref(uv))
+        ti = L.oracle_mesh_texindices(int(mesh_id[0]))
+        out.append((np.ctypeslib.as_array(pos, (n, 4)).copy(), np.ctypeslib.as_array(nrm, (n, 4)).copy(),
+                    np.ctypeslib.as_array(uv, (n, 4)).copy(), np.ctypeslib.as_array(ti, (n, 4)).copy(), int(flags[0])))
+    return out
+
+
 def lm_bake(scene, time_slice, spp, pass_index):
     L = lib()
     L.oracle_lm_bake.argtypes = [C.c_void_p, C.c_float, C.c_int, C.c_uint32]

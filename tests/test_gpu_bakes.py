@@ -132,3 +132,64 @@ def test_bake_entry_points_reject_bad_input(api):
     empty = api.CubemapStruct()
     assert L.Pt_BakeSky(empty, api.earth_sky(), api.Float3(0, 1, 0), 1.0, 1) == -1
     assert L.Pt_Tonemap(None, 8, 1.0, 1, 0, None) == -1
+
+
+def _embed_case(api, oracle, kind, atlas, tpm):
+    desc = scenes.cornell_box(kind, brdf_lut=np.zeros((4, 4, 2), np.float32), seed=1)
+    oracle.set_seed(1)
+    oracle.load_scene_desc(desc)
+    pages = oracle.lm_pack(atlas, tpm)
+    assert pages >= 1
+    meshes = oracle.lm_meshes()
+    slots = [oracle.lm_slot(k) for k in range(pages)]
+    assert len(set(slots)) == pages
+    got = api.lm_embed(meshes, slots, atlas)
+    covered = 0
+    for k in range(pages):
+        _, pos, nrm, cnt = oracle.lm_page(k)
+        g_pos, g_nrm, g_cnt = got[k]
+        # coverage: the 2-texel padding test flips only where a distance rounds across 2.0
+        assert (g_cnt != cnt).mean() < 1e-4
+        both = (g_cnt > 0) & (cnt > 0)
+        covered += int(both.sum())
+        # a padding texel exactly half way between two charts has two nearest triangles at distances equal
+        # up to rounding; which one wins differs with the arithmetic (both sides build with fast math)
+        bad = (np.abs(g_pos[both] - pos[both]).max(axis=1) > 2e-4) | (np.abs(g_nrm[both] - nrm[both]).max(axis=1) > 2e-4)
+        assert (not both.any()) or bad.mean() < 2e-3          # metres; positions are O(1..5)
+        assert (g_pos[g_cnt == 0] == 0).all() and (g_nrm[g_cnt == 0] == 0).all()
+    return pages, covered
+
+
+def test_lightmap_embed_matches_reference(api, oracle):
+    """LmPack_EmbedDesc (EmbedTaskFn, lightmap.c:947-1034) on the atlas the reference's own LmPack_Pack laid
+    out: one page, and a small atlas that forces several pages (each drawable's triangles carry their page's slot)"""
+    pages, covered = _embed_case(api, oracle, "boxes", 256, 4.0)
+    assert pages == 1 and covered > 3000
+    pages, covered = _embed_case(api, oracle, "boxes", 256, 12.0)      # five pages, two of them empty
+    assert pages > 1 and covered > 30000          # (the reference's packer never returns for 256 / 16.0 or 128 / 8.0)
+
+
+def test_lightmap_embed_edge_cases(api):
+    """no triangles: every texel is empty; unmapped (sky) drawables are skipped; a triangle with no area in
+    lightmap space bids only inside its padded box (in the reference sdTriangle2D's sign term is 0 for it, the
+    distance comes out negative everywhere and it floods the page; attributes are 0/0 on both sides)"""
+    out = api.lm_embed([], [7], 16)
+    assert (out[0][2] == 0).all() and (out[0][0] == 0).all()
+    pos = np.array([[0, 0, 0, 1], [1, 0, 0, 1], [0, 1, 0, 1]], np.float32)
+    nrm = np.tile(np.array([[0, 0, 1, 0]], np.float32), (3, 1))
+    uv = np.array([[0, 0, 0.25, 0.25], [0, 0, 0.75, 0.25], [0, 0, 0.25, 0.75]], np.float32)
+    tex = np.tile(np.array([[0, 0, 0, 7]], np.int32), (3, 1))
+    sky = api.lm_embed([(pos, nrm, uv, tex, 1 << 1)], [7], 16)
+    assert (sky[0][2] == 0).all()
+    other = api.lm_embed([(pos, nrm, uv, tex, 0)], [3], 16)          # slot does not match any page
+    assert (other[0][2] == 0).all()
+    one = api.lm_embed([(pos, nrm, uv, tex, 0)], [7], 16)
+    assert one[0][2].sum() > 30
+    inside = one[0][2].reshape(16, 16)[5, 5] == 1.0                  # texel centre (5.5, 5.5) / 16 is inside
+    assert inside
+    p = one[0][0].reshape(16, 16, 3)[5, 5]
+    assert np.allclose(p, [(5.5 / 16 - 0.25) / 0.5, (5.5 / 16 - 0.25) / 0.5, 0.0], atol=1e-5)
+    assert np.allclose(one[0][1].reshape(16, 16, 3)[5, 5], [0, 0, 1], atol=1e-6)
+    degenerate = uv.copy(); degenerate[:, 2:] = 0.5
+    d = api.lm_embed([(pos, nrm, degenerate, tex, 0)], [7], 16)
+    assert 4 <= d[0][2].sum() <= 49

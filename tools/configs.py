@@ -194,6 +194,19 @@ def bakes(args):
         out["convolve_64"].update({"cpu_ms": dt * 1e3, "cpu_msamples_s": texels * spt / dt / 1e6})
     cm.close()
 
+    # N1 embed: the C4 atlas (1024^2 at 16 texels/m) the reference's packer lays out for cornell boxes
+    if args.cpu:
+        desc = scenes.cornell_box("boxes", brdf_lut=np.zeros((4, 4, 2), np.float32), seed=1)
+        O.set_seed(1)
+        O.load_scene_desc(desc)
+        pages = O.lm_pack(1024, 16.0)
+        meshes = O.lm_meshes(); slots = [O.lm_slot(k) for k in range(pages)]
+        tris = sum(len(m[0]) // 3 for m in meshes)
+        wall, k = timed(lambda: api.lm_embed(meshes, slots, 1024))
+        t0 = time.perf_counter(); O.lm_embed(); dt = time.perf_counter() - t0
+        out["embed_1024"] = {"pages": pages, "triangles": tris, "texels": pages * 1024 * 1024, "gpu_kernel_ms": k * 1e3,
+                             "gpu_call_ms": wall * 1e3, "cpu_ms": dt * 1e3}
+
     # N2 cubemap bake and ambient cube inside cornell boxes
     desc = scenes.cornell_box("boxes", brdf_lut=parity.reference_lut(), seed=1)
     scene = api.Scene(desc)
