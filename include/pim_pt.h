@@ -261,6 +261,10 @@ typedef struct PtLightmapDesc_s
 
 int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCount,
                         float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass);
+/* the same with every pointer of every page in device memory: the pack stays resident between
+ * passes (a page is 108 B per texel; over PCIe it costs more than the bake itself) */
+int32_t LmPack_BakeDesc_Device(PtScene* scene, const PtLightmapDesc* lightmaps, int32_t lmCount,
+                               float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass);
 
 /* ---- lightmap attribute embedding --------------------------
  * EmbedAttributes / EmbedTaskFn (static in src/rendering/lightmap.c:947-1047), the last and

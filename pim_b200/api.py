@@ -137,6 +137,7 @@ EXPORTS = [
     "Pt_SetKernelTiming", "Pt_GetKernelStats", "Pt_IntersectCountN", "Pt_TraceRayN_NoAlloc",
     "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
     "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap", "LmPack_EmbedDesc",
+    "LmPack_BakeDesc_Device",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -209,6 +210,8 @@ def load():
     L.Pt_Tonemap.restype = C.c_int32
     L.LmPack_EmbedDesc.argtypes = [C.POINTER(PtEmbedMesh), C.c_int32, C.POINTER(PtLightmapDesc), vp, C.c_int32]
     L.LmPack_EmbedDesc.restype = C.c_int32
+    L.LmPack_BakeDesc_Device.argtypes = L.LmPack_BakeDesc.argtypes
+    L.LmPack_BakeDesc_Device.restype = C.c_int32
     for name in ("Pt_IntersectN", "Pt_OccludedN", "Pt_TraceRayN", "Pt_TraceSpp", "Pt_IntersectN_Device",
                  "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc", "PtScene_GetStats",
                  "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut"):
@@ -410,6 +413,17 @@ class Scene:
             d.probes[k] = probes[k].ctypes.data
         d.position, d.normal, d.sampleCounts, d.size = position.ctypes.data, normal.ctypes.data, sample_counts.ctypes.data, size
         _check(load().LmPack_BakeDesc(self.h, C.byref(d), 1, texels_per_meter, time_slice, spp, pass_index), "LmPack_BakeDesc")
+
+
+    def bake_lightmap_device(self, probes, position, normal, sample_counts, size, texels_per_meter, time_slice=1.0, spp=1,
+                             pass_index=0):
+        """LmPack_BakeDesc_Device on one page: the arguments are device pointers (ints), probes a list of five."""
+        d = PtLightmapDesc()
+        for k in range(5):
+            d.probes[k] = probes[k]
+        d.position, d.normal, d.sampleCounts, d.size = position, normal, sample_counts, size
+        _check(load().LmPack_BakeDesc_Device(self.h, C.byref(d), 1, texels_per_meter, time_slice, spp, pass_index),
+               "LmPack_BakeDesc_Device")
 
 
 class Trace:

@@ -392,6 +392,25 @@ struct DevBuf
     ~DevBuf() { if (p) cudaFree(p); }
 };
 
+// CUDA events around a call's kernels on their stream; stop() leaves the time in Pt_LastKernelMs()
+struct KernelTimer
+{
+    cudaEvent_t a = nullptr, b = nullptr;
+    cudaStream_t st;
+    explicit KernelTimer(cudaStream_t s) : st(s)
+    {
+        if (cudaEventCreate(&a) == cudaSuccess && cudaEventCreate(&b) == cudaSuccess) cudaEventRecord(a, st);
+    }
+    void stop()
+    {
+        if (!a || !b) return;
+        cudaEventRecord(b, st);
+        float ms = 0.0f;
+        if (cudaEventSynchronize(b) == cudaSuccess && cudaEventElapsedTime(&ms, a, b) == cudaSuccess) g_lastKernelMs = ms;
+    }
+    ~KernelTimer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+};
+
 static bool traceSppDevice(PtScene* scene, const Camera* camera, PtDofInfo* dof, int w, int h, int sppBegin, int sppCount,
                            float* dColor, float* dAlbedo, float* dNormal, cudaStream_t st)
 {
@@ -771,6 +790,16 @@ PtResults Pt_RayGen(PtScene* scene, pim_float4 origin, int32_t count)      // pa
     return res;
 }
 
+// one page whose arrays are already on the device
+static bool bakePageDevice(PtScene* scene, const LightmapView& view, float texelsPerMeter, float timeSlice, int32_t spp,
+                           uint32_t pass, cudaStream_t st)
+{
+    if (scene->config.bakeMode == PtBake_Sequential)
+        return launchLightmapBake(scene->view, view, 1.0f / texelsPerMeter, timeSlice, spp, pass, scene->config.seed, st);
+    return launchLightmapBakeWavefront(scene->view, scene->pool, view, 1.0f / texelsPerMeter, timeSlice, spp, pass,
+                                       scene->config.seed, st);
+}
+
 int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCount, float texelsPerMeter, float timeSlice,
                         int32_t spp, uint32_t pass)
 {
@@ -796,11 +825,7 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
         ok = ok && PT_CUDA(cudaMemcpyAsync(cnt.p, lm.sampleCounts, 4 * n, cudaMemcpyHostToDevice, st));
         view.position = (const float*)pos.p; view.normal = (const float*)nrm.p; view.sampleCounts = (float*)cnt.p;
         view.texelCount = (int32_t)n; view.texelBase = texelBase;
-        if (scene->config.bakeMode == PtBake_Sequential)
-            ok = ok && launchLightmapBake(scene->view, view, 1.0f / texelsPerMeter, timeSlice, spp, pass, scene->config.seed, st);
-        else
-            ok = ok && launchLightmapBakeWavefront(scene->view, scene->pool, view, 1.0f / texelsPerMeter, timeSlice, spp, pass,
-                                                   scene->config.seed, st);
+        ok = ok && bakePageDevice(scene, view, texelsPerMeter, timeSlice, spp, pass, st);
         for (int k = 0; ok && k < 5; ++k)
             ok = PT_CUDA(cudaMemcpyAsync(lm.probes[k], probes[k].p, sizeof(F4) * n, cudaMemcpyDeviceToHost, st));
         ok = ok && PT_CUDA(cudaMemcpyAsync(lm.sampleCounts, cnt.p, 4 * n, cudaMemcpyDeviceToHost, st));
@@ -810,26 +835,32 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
     return ok ? 0 : -1;
 }
 
-// ---- SURVEY 8(f) N2-N4: cubemap / ambient-cube bakes, sky bake, screenshot tonemap ----
-
-// CUDA events around a call's kernels on their stream; stop() leaves the time in Pt_LastKernelMs()
-struct KernelTimer
+int32_t LmPack_BakeDesc_Device(PtScene* scene, const PtLightmapDesc* lightmaps, int32_t lmCount, float texelsPerMeter,
+                               float timeSlice, int32_t spp, uint32_t pass)
 {
-    cudaEvent_t a = nullptr, b = nullptr;
-    cudaStream_t st;
-    explicit KernelTimer(cudaStream_t s) : st(s)
+    if (!scene || (!lightmaps && lmCount > 0)) { setError("LmPack_BakeDesc_Device: null argument"); return -1; }
+    cudaStream_t st = scene->stream;
+    bool ok = launchDistUpdate(scene->view, st);
+    int32_t texelBase = 0;
+    KernelTimer timer(st);
+    for (int32_t i = 0; ok && i < lmCount; ++i)
     {
-        if (cudaEventCreate(&a) == cudaSuccess && cudaEventCreate(&b) == cudaSuccess) cudaEventRecord(a, st);
+        const PtLightmapDesc& lm = lightmaps[i];
+        const size_t n = (size_t)lm.size * (size_t)lm.size;
+        LightmapView view;
+        for (int k = 0; k < 5; ++k) view.probes[k] = (F4*)lm.probes[k];
+        view.position = (const float*)lm.position; view.normal = (const float*)lm.normal; view.sampleCounts = lm.sampleCounts;
+        view.texelCount = (int32_t)n; view.texelBase = texelBase;
+        if (!view.probes[0] || !view.position || !view.normal || !view.sampleCounts) { setError("LmPack_BakeDesc_Device: page %d has no storage", i); return -1; }
+        ok = bakePageDevice(scene, view, texelsPerMeter, timeSlice, spp, pass, st);
+        texelBase += (int32_t)n;
     }
-    void stop()
-    {
-        if (!a || !b) return;
-        cudaEventRecord(b, st);
-        float ms = 0.0f;
-        if (cudaEventSynchronize(b) == cudaSuccess && cudaEventElapsedTime(&ms, a, b) == cudaSuccess) g_lastKernelMs = ms;
-    }
-    ~KernelTimer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
-};
+    timer.stop();
+    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    return ok ? 0 : -1;
+}
+
+// ---- SURVEY 8(f) N2-N4: cubemap / ambient-cube bakes, sky bake, screenshot tonemap ----
 
 void Cubemap_New(Cubemap* cm, int32_t size)       // cubemap.c:95-114
 {
