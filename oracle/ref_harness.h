@@ -136,6 +136,12 @@ int oracle_ambcube_bake(void* scene, float* cube24, const float* origin4, int sa
 void oracle_bake_sky(int size, float* color, const float* sky9, const float* sunDir3, float sunLum, int steps);
 void oracle_tonemap(const float* light4, int count, float exposure, uint32_t pass, uint32_t* rgba8);
 
+/* known-answer vectors of the 8(a) helpers (ref_kat.c) */
+int oracle_kat_count(void);
+const char* oracle_kat_name(int k, int* kin, int* kout);
+void oracle_kat_run(int k, const float* in, int n, float* out);
+void oracle_sg_axii(float* out20);
+
 /* CalcStdDev (src/rendering/render_system.c:1374-1394) */
 float oracle_stddev(const float* color3, int w, int h);
 

@@ -16,34 +16,6 @@ namespace {
 
 inline unsigned gridFor(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
-// src/rendering/cubemap.c:14-42
-__constant__ float kCubeFwd[6][3] = { { 1, 0, 0 }, { -1, 0, 0 }, { 0, 1, 0 }, { 0, -1, 0 }, { 0, 0, 1 }, { 0, 0, -1 } };
-__constant__ float kCubeUp[6][3] = { { 0, 1, 0 }, { 0, 1, 0 }, { 0, 0, -1 }, { 0, 0, -1 }, { 0, 1, 0 }, { 0, 1, 0 } };
-__constant__ float kCubeRight[6][3] = { { 0, 0, -1 }, { 0, 0, 1 }, { 1, 0, 0 }, { -1, 0, 0 }, { 1, 0, 0 }, { -1, 0, 0 } };
-
-// f2_tent (src/math/float2_funcs.h:630-636). The y lane reads 2 - Xi.x, after Xi.x has
-// already been replaced: kept as the reference has it.
-__device__ __forceinline__ V2 tent(V2 Xi)
-{
-    Xi.x *= 2.0f; Xi.y *= 2.0f;
-    Xi.x = Xi.x < 1.0f ? sqrtf(Xi.x) - 1.0f : 1.0f - sqrtf(2.0f - Xi.x);
-    Xi.y = Xi.y < 1.0f ? sqrtf(Xi.y) - 1.0f : 1.0f - sqrtf(2.0f - Xi.x);
-    return Xi;
-}
-
-// Cubemap_CalcDir (src/rendering/cubemap.h:190-207): BilinearInvert, jitter, snorm, proj_dir
-__device__ __forceinline__ V3 cubeDir(int size, int face, int x, int y, V2 Xi)
-{
-    V2 uv = v2((float)x / (float)(size - 1), (float)y / (float)(size - 1));
-    const float r = 1.0f / size;
-    uv.x += Xi.x * r; uv.y += Xi.y * r;
-    uv.x = uv.x * 2.0f - 1.0f; uv.y = uv.y * 2.0f - 1.0f;
-    const V3 fwd = v3(kCubeFwd[face][0], kCubeFwd[face][1], kCubeFwd[face][2]);
-    const V3 right = v3(kCubeRight[face][0], kCubeRight[face][1], kCubeRight[face][2]);
-    const V3 up = v3(kCubeUp[face][0], kCubeUp[face][1], kCubeUp[face][2]);
-    return normalize((fwd + right * uv.x) + up * uv.y);     // proj_dir, frustum.h:33-47, slope 1
-}
-
 // CalcMipOffset (src/rendering/sampler.h:42-51) for a square image
 __device__ __host__ inline int mipOffset(int size, int m)
 {
@@ -61,8 +33,8 @@ __global__ void __launch_bounds__(256) k_cubeRays(int size, V3 origin, uint32_t 
     if (i >= 6 * flen) return;
     const int face = i / flen, fi = i % flen;
     Rng rng = seed_prng((uint32_t)i, pass, seed, Salt_CubeBake);
-    const V2 Xi = tent(rng_f2(rng));
-    const V3 dir = cubeDir(size, face, fi % size, fi / size, Xi);
+    const V2 Xi = f2_tent(rng_f2(rng));
+    const V3 dir = Cubemap_CalcDir(size, face, fi % size, fi / size, Xi);
     ro[i] = f4(origin, 0.0f);
     rd[i] = f4(dir, 0.0f);
 }
@@ -79,8 +51,8 @@ __global__ void __launch_bounds__(128) k_cubeConvolve(const float* __restrict__ 
     const int face = i / len, fi = i % len;
     const float roughness = (float)mip / 6.0f;          // MipToRoughness, CUBEMAP_MAX_MIP (cubemap.h:12,66-69)
     Rng rng = seed_prng((uint32_t)i, pass, seed, Salt_CubeConvolve | (uint32_t)(mip & 0xf));
-    const V2 Xi = tent(rng_f2(rng));
-    const V3 N = cubeDir(mSize, face, fi % mSize, fi / mSize, Xi);
+    const V2 Xi = f2_tent(rng_f2(rng));
+    const V3 N = Cubemap_CalcDir(mSize, face, fi % mSize, fi / mSize, Xi);
     const Tbn tbn = NormalToTBN(N);
     const V3 I = -tbn.c2;
     const float alpha = BrdfAlpha(roughness);
@@ -206,7 +178,7 @@ __global__ void __launch_bounds__(128) k_skyBake(SkyParams A, int size, V3 sunDi
     const int len = size * size;
     if (i >= 6 * len) return;
     const int face = i / len, t = i % len;
-    const V3 rd = cubeDir(size, face, t % size, t / size, v2(0.0f, 0.0f));
+    const V3 rd = Cubemap_CalcDir(size, face, t % size, t / size, v2(0.0f, 0.0f));
     const V3 ro = v3(0.0f, A.rCrust, 0.0f);
     const V3 c = atmosphere(A, ro, rd, sunDir, v3s(sunLum), steps);
     color[3 * (size_t)i] = c.x; color[3 * (size_t)i + 1] = c.y; color[3 * (size_t)i + 2] = c.z;
@@ -267,30 +239,6 @@ __global__ void __launch_bounds__(256) k_tonemap(const F4* __restrict__ light, i
 // the winner's barycentrics per texel. (A triangle with zero area in lightmap space is the one
 // case that differs: sdTriangle2D's sign term is 0 for it, so the reference sees a negative
 // distance on every texel of the page; here it only bids inside its padded box.)
-
-// sdEdge2D, bary2D, sdTriangle2D: src/math/sdf.h:99-156
-__device__ __forceinline__ float sdEdge2D(V2 A, V2 B, V2 P)
-{
-    const float apx = P.x - A.x, apy = P.y - A.y, abx = B.x - A.x, aby = B.y - A.y;
-    return 0.5f * (apy * abx - apx * aby);
-}
-__device__ __forceinline__ float dot2(V2 a, V2 b) { return a.x * b.x + a.y * b.y; }
-__device__ __forceinline__ float sdTriangle2D(V2 a, V2 b, V2 c, V2 p)
-{
-    const V2 ba = v2(b.x - a.x, b.y - a.y), cb = v2(c.x - b.x, c.y - b.y), ac = v2(a.x - c.x, a.y - c.y);
-    const V2 pa = v2(p.x - a.x, p.y - a.y), pb = v2(p.x - b.x, p.y - b.y), pc = v2(p.x - c.x, p.y - c.y);
-    const float h0 = f1_sat(dot2(pa, ba) / dot2(ba, ba));
-    const float h1 = f1_sat(dot2(pb, cb) / dot2(cb, cb));
-    const float h2 = f1_sat(dot2(pc, ac) / dot2(ac, ac));
-    const V2 pq0 = v2(pa.x - ba.x * h0, pa.y - ba.y * h0);
-    const V2 pq1 = v2(pb.x - cb.x * h1, pb.y - cb.y * h1);
-    const V2 pq2 = v2(pc.x - ac.x * h2, pc.y - ac.y * h2);
-    const float s = f1_sign(ba.x * ac.y - ba.y * ac.x);
-    const float dx = f1_min(dot2(pq0, pq0), f1_min(dot2(pq1, pq1), dot2(pq2, pq2)));
-    const float dy = f1_min(s * (pa.x * ba.y - pa.y * ba.x), f1_min(s * (pb.x * cb.y - pb.y * cb.x), s * (pc.x * ac.y - pc.y * ac.x)));
-    const float dySign = (dy >= 0.0f) ? 1.0f : -1.0f;
-    return -sqrtf(f1_max(dx, kEpsilonSq)) * dySign;
-}
 
 constexpr float kFillPadding = 2.0f;                       // lightmap.c:40
 constexpr unsigned long long kEmbedNone = ~0ull;

@@ -518,6 +518,37 @@ PT_HD int Cubemap_CalcUv(V3 dir, V2& uvOut)
     return face;
 }
 
+// f2_tent (src/math/float2_funcs.h:630-636). The y lane reads 2 - Xi.x after Xi.x has already
+// been replaced: kept as the reference has it.
+PT_HD V2 f2_tent(V2 Xi)
+{
+    Xi.x *= 2.0f; Xi.y *= 2.0f;
+    Xi.x = Xi.x < 1.0f ? sqrtf(Xi.x) - 1.0f : 1.0f - sqrtf(2.0f - Xi.x);
+    Xi.y = Xi.y < 1.0f ? sqrtf(Xi.y) - 1.0f : 1.0f - sqrtf(2.0f - Xi.x);
+    return Xi;
+}
+
+// Cubemap_CalcDir (src/rendering/cubemap.h:190-207): BilinearInvert, jitter, snorm, proj_dir with
+// the face frames of src/rendering/cubemap.c:14-42
+PT_HD V3 Cubemap_CalcDir(int size, int face, int x, int y, V2 Xi)
+{
+    V2 uv = v2((float)x / (float)(size - 1), (float)y / (float)(size - 1));
+    const float r = 1.0f / size;
+    uv.x += Xi.x * r; uv.y += Xi.y * r;
+    uv.x = uv.x * 2.0f - 1.0f; uv.y = uv.y * 2.0f - 1.0f;
+    V3 fwd, up, right;
+    switch (face)
+    {
+    case 0: fwd = v3(1, 0, 0); up = v3(0, 1, 0); right = v3(0, 0, -1); break;
+    case 1: fwd = v3(-1, 0, 0); up = v3(0, 1, 0); right = v3(0, 0, 1); break;
+    case 2: fwd = v3(0, 1, 0); up = v3(0, 0, -1); right = v3(1, 0, 0); break;
+    case 3: fwd = v3(0, -1, 0); up = v3(0, 0, -1); right = v3(-1, 0, 0); break;
+    case 4: fwd = v3(0, 0, 1); up = v3(0, 1, 0); right = v3(1, 0, 0); break;
+    default: fwd = v3(0, 0, -1); up = v3(0, 1, 0); right = v3(-1, 0, 0); break;
+    }
+    return normalize((fwd + right * uv.x) + up * uv.y);     // proj_dir, frustum.h:33-47, slope 1
+}
+
 // --------------------------------------------------------------------- grid
 // src/math/grid.h:8-49
 struct Grid
@@ -565,6 +596,30 @@ PT_HD int FindInterval(const float* cdf, int size, float u)
         }
     }
     return i1_clamp(first - 1, 0, size - 2);
+}
+
+// sdEdge2D, sdTriangle2D: src/math/sdf.h:99-156
+PT_HD float sdEdge2D(V2 A, V2 B, V2 P)
+{
+    const float apx = P.x - A.x, apy = P.y - A.y, abx = B.x - A.x, aby = B.y - A.y;
+    return 0.5f * (apy * abx - apx * aby);
+}
+PT_HD float dot2(V2 a, V2 b) { return a.x * b.x + a.y * b.y; }
+PT_HD float sdTriangle2D(V2 a, V2 b, V2 c, V2 p)
+{
+    const V2 ba = v2(b.x - a.x, b.y - a.y), cb = v2(c.x - b.x, c.y - b.y), ac = v2(a.x - c.x, a.y - c.y);
+    const V2 pa = v2(p.x - a.x, p.y - a.y), pb = v2(p.x - b.x, p.y - b.y), pc = v2(p.x - c.x, p.y - c.y);
+    const float h0 = f1_sat(dot2(pa, ba) / dot2(ba, ba));
+    const float h1 = f1_sat(dot2(pb, cb) / dot2(cb, cb));
+    const float h2 = f1_sat(dot2(pc, ac) / dot2(ac, ac));
+    const V2 pq0 = v2(pa.x - ba.x * h0, pa.y - ba.y * h0);
+    const V2 pq1 = v2(pb.x - cb.x * h1, pb.y - cb.y * h1);
+    const V2 pq2 = v2(pc.x - ac.x * h2, pc.y - ac.y * h2);
+    const float s = f1_sign(ba.x * ac.y - ba.y * ac.x);
+    const float dx = f1_min(dot2(pq0, pq0), f1_min(dot2(pq1, pq1), dot2(pq2, pq2)));
+    const float dy = f1_min(s * (pa.x * ba.y - pa.y * ba.x), f1_min(s * (pb.x * cb.y - pb.y * cb.x), s * (pc.x * ac.y - pc.y * ac.x)));
+    const float dySign = (dy >= 0.0f) ? 1.0f : -1.0f;
+    return -sqrtf(f1_max(dx, kEpsilonSq)) * dySign;
 }
 
 // src/math/sdf.h:158-189

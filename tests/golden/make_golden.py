@@ -4,7 +4,7 @@ where /root/reference is mounted and oracle/_ref is built):
   brdf_lut_128_4096.npy   g_BrdfLut baked by the reference's BakeBrdfFn, 4096 samples/texel
   cornell_boxes_hits.npz  Pt_Intersect on 20000 seeded rays in the cornell boxes scene
   cornell_boxes_64x36.npz two 1-spp passes of Pt_Trace (seed 1) + CalcStdDev
-  pcg_kat.npz             Pcg1/2/4 sequences and sampling helpers from fixed states
+  (kat.npz, the helper known-answer vectors, comes from make_kat.py)
 """
 import os
 import sys

@@ -306,3 +306,132 @@ void hs_trace_rays(void* h, const float* ro4, const float* rd4, int64_t n, uint3
 }
 
 } // extern "C"
+
+// ---- known-answer vectors of the helpers (the counterpart of oracle/ref_kat.c): the same rows
+// through the library's PT_HD functions, compiled for the host
+namespace {
+struct HsKat { const char* name; int kin, kout; void (*fn)(const float* in, float* out); };
+
+void hk_pcg1(const float* i, float* o) { o[0] = u2f(Pcg1(f2u(i[0]))); }
+void hk_pcg2(const float* i, float* o) { uint32_t x = f2u(i[0]), y = f2u(i[1]); Pcg2(x, y); o[0] = u2f(x); o[1] = u2f(y); }
+void hk_pcg4(const float* i, float* o)
+{
+    Rng r = Pcg4(f2u(i[0]), f2u(i[1]), f2u(i[2]), f2u(i[3]));
+    o[0] = u2f(r.x); o[1] = u2f(r.y); o[2] = u2f(r.z); o[3] = u2f(r.w);
+}
+void hk_tbn(const float* i, float* o)
+{
+    Tbn m = NormalToTBN(normalize(v3(i[0], i[1], i[2])));
+    o[0] = m.c0.x; o[1] = m.c0.y; o[2] = m.c0.z; o[3] = m.c1.x; o[4] = m.c1.y; o[5] = m.c1.z; o[6] = m.c2.x; o[7] = m.c2.y; o[8] = m.c2.z;
+}
+void hk_power(const float* i, float* o) { o[0] = PowerHeuristic(i[0], i[1]); }
+void hk_disk(const float* i, float* o) { V2 d = MapSquareToDisk(v2(i[0], i[1])); o[0] = d.x; o[1] = d.y; }
+void hk_bary(const float* i, float* o) { V3 w = SampleBaryCoord(v2(i[0], i[1])); o[0] = w.x; o[1] = w.y; o[2] = w.z; }
+void hk_ngon(const float* i, float* o)
+{
+    V2 p = SampleNGon(v2(i[0], i[1]), f2u(i[2]) % 7u, 7, 0.3f); o[0] = p.x; o[1] = p.y;
+    p = SamplePentagram(v2(i[0], i[1]), f2u(i[2])); o[2] = p.x; o[3] = p.y;
+}
+void hk_sphere(const float* i, float* o) { V3 d = SampleUnitSphere(v2(i[0], i[1])); o[0] = d.x; o[1] = d.y; o[2] = d.z; }
+void hk_coshemi(const float* i, float* o) { V3 d = SampleCosineHemisphere(v2(i[0], i[1])); o[0] = d.x; o[1] = d.y; o[2] = d.z; }
+void hk_ggx(const float* i, float* o)
+{
+    float alpha = BrdfAlpha(i[2]);
+    V3 d = SampleGGXMicrofacet(v2(i[0], i[1]), alpha); o[0] = d.x; o[1] = d.y; o[2] = d.z;
+    o[3] = GGXPdf(i[0], i[1], alpha);
+    o[4] = D_GTR(i[0], alpha);
+    o[5] = V_SmithCorrelated(i[0], i[1], alpha);
+}
+void hk_lightpdf(const float* i, float* o) { o[0] = LightPdf(i[0] + 0.01f, i[1], i[2] * 10.0f); }
+void hk_gauss(const float* i, float* o) { V2 d = SampleGaussPixelFilter(v2(i[0], i[1]), 1.0f); o[0] = d.x; o[1] = d.y; }
+void hk_freepath(const float* i, float* o) { o[0] = SampleFreePath(i[0], 1.0f + 100.0f * i[1]); }
+void hk_fresnel(const float* i, float* o)
+{
+    o[0] = F_Dielectric(i[0], 1.0f, 1.0f + i[1]);
+    o[1] = F_Dielectric(i[0], 1.0f + i[1], 1.0f);
+    V3 f0 = F_0(v3(i[0], i[1], i[2]), i[1]);
+    o[2] = f0.x; o[3] = f0.y; o[4] = f0.z;
+    o[5] = F_90(f0);
+    o[6] = F_Schlick1(i[2], 1.0f, i[0]);
+}
+void hk_burley(const float* i, float* o) { o[0] = Fd_Burley(i[0], i[1], i[2], i[3]); }
+void hk_transmit(const float* i, float* o)
+{
+    V3 t = AlbedoToTransmittance(v3(i[0], i[1], i[2]), i[3], 0.01f + i[3]); o[0] = t.x; o[1] = t.y; o[2] = t.z;
+}
+void hk_gamma(const float* i, float* o) { F4 v = GammaDecode_rgba8(f2u(i[0])); o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; }
+void hk_cubeuv(const float* i, float* o)
+{
+    V2 uv; int f = Cubemap_CalcUv(v3(i[0] - 0.5f, i[1] - 0.5f, i[2] - 0.5f), uv);
+    o[0] = (float)f; o[1] = uv.x; o[2] = uv.y;
+    V3 d = Cubemap_CalcDir(16, (int)(f2u(i[3]) % 6u), (int)(i[0] * 15.99f), (int)(i[1] * 15.99f), f2_tent(v2(i[1], i[2])));
+    o[3] = d.x; o[4] = d.y; o[5] = d.z;
+}
+void hk_grid(const float* i, float* o)
+{
+    // Grid_New (src/math/grid.h:8-16) on the host side of the library: api.cu sceneBuild
+    Grid g; g.lo = v3(-5.0f, -3.0f, -4.0f); g.hi = v3(5.0f, 3.0f, 6.0f); g.cellsPerMeter = 1.0f / 1.5f;
+    g.sx = (int)ceilf((g.hi.x - g.lo.x) * g.cellsPerMeter); g.sy = (int)ceilf((g.hi.y - g.lo.y) * g.cellsPerMeter);
+    g.sz = (int)ceilf((g.hi.z - g.lo.z) * g.cellsPerMeter);
+    V3 p = v3(i[0] * 14.0f - 7.0f, i[1] * 8.0f - 4.0f, i[2] * 12.0f - 5.0f);
+    int idx = Grid_Index(g, p);
+    V3 c = Grid_Position(g, idx);
+    o[0] = (float)idx; o[1] = c.x; o[2] = c.y; o[3] = c.z; o[4] = (float)Grid_Len(g);
+}
+void hk_sdtri(const float* i, float* o)
+{
+    o[0] = sdTriangle3D(v3(i[0], i[1], i[2]), v3(i[3], i[4], i[5]), v3(i[6], i[7], i[8]), v3(i[9] * 2.0f, i[10] * 2.0f, i[11] * 2.0f));
+    o[1] = sdTriangle2D(v2(i[0], i[1]), v2(i[3], i[4]), v2(i[6], i[7]), v2(i[9] * 1.5f, i[10] * 1.5f));
+}
+void hk_mie(const float* i, float* o)
+{
+    float c = i[0] * 2.0f - 1.0f;
+    o[0] = MiePhase(c, 0.758f);
+    o[1] = (3.0f / (16.0f * kPi)) * (1.0f + c * c);        // RayleighPhase as k_skyBake writes it
+}
+void hk_sgfit(const float* i, float* o)
+{
+    F4 axii[5], amps[5];
+    memcpy(axii, i + 2, sizeof(axii));
+    memset(amps, 0, sizeof(amps));
+    Rng s; s.x = f2u(i[0]); s.y = f2u(i[1]); s.z = 7u; s.w = 9u;
+    for (int k = 0; k < 64; ++k)
+    {
+        s = Pcg4(s.x, s.y, s.z, s.w);
+        V2 Xi = v2(ToFloat(s.x), ToFloat(s.y));
+        V3 dir = SampleUnitHemisphere(Xi);
+        V3 rad = v3(ToFloat(s.z), ToFloat(s.w), 0.5f);
+        SG_Accumulate(1.0f / (1.0f + k), dir, rad, axii, amps, 5);
+    }
+    for (int k = 0; k < 5; ++k) { o[4 * k] = amps[k].x; o[4 * k + 1] = amps[k].y; o[4 * k + 2] = amps[k].z; o[4 * k + 3] = amps[k].w; }
+}
+void hk_dist1d(const float* i, float* o)
+{
+    int s = FindInterval(i, 9, i[17]);           // Dist1D_SampleD
+    o[0] = (float)s; o[1] = i[9 + s] / 8.0f;     // Dist1D_PdfD (integrator.h Dist_PdfD)
+}
+
+const HsKat kHsKats[] =
+{
+    { "pcg1", 1, 1, hk_pcg1 }, { "pcg2", 2, 2, hk_pcg2 }, { "pcg4", 4, 4, hk_pcg4 },
+    { "tbn", 3, 9, hk_tbn }, { "power", 2, 1, hk_power }, { "disk", 2, 2, hk_disk }, { "bary", 2, 3, hk_bary },
+    { "ngon", 3, 4, hk_ngon }, { "sphere", 2, 3, hk_sphere }, { "coshemi", 2, 3, hk_coshemi }, { "ggx", 3, 6, hk_ggx },
+    { "lightpdf", 3, 1, hk_lightpdf }, { "gauss", 2, 2, hk_gauss }, { "freepath", 2, 1, hk_freepath },
+    { "fresnel", 3, 7, hk_fresnel }, { "burley", 4, 1, hk_burley }, { "transmit", 4, 3, hk_transmit },
+    { "gamma", 1, 4, hk_gamma }, { "cubeuv", 4, 6, hk_cubeuv }, { "grid", 3, 5, hk_grid }, { "sdtri", 12, 2, hk_sdtri },
+    { "mie", 1, 2, hk_mie }, { "sgfit", 22, 20, hk_sgfit }, { "dist1d", 18, 2, hk_dist1d },
+};
+} // namespace
+
+extern "C" int hs_kat_run(const char* name, const float* in, int n, float* out)
+{
+    for (const HsKat& k : kHsKats)
+    {
+        if (strcmp(k.name, name) == 0)
+        {
+            for (int r = 0; r < n; ++r) k.fn(in + (size_t)r * k.kin, out + (size_t)r * k.kout);
+            return k.kout;
+        }
+    }
+    return -1;
+}
