@@ -106,14 +106,28 @@ __device__ __forceinline__ int warpAlloc(bool pred, int32_t* counter)
 // Path state in HBM: six 16-byte fields per slot. Only two of the RNG's four words ever advance
 // on a path (rng_u32 / rng_f32 / rng_f2), so they ride in the spare lanes of atten and lum — the
 // fields stage A rewrites anyway — and the result index rides with the denoiser accumulators.
-//   ro     = origin.xyz, weight          rd     = direction.xyz, bounce | prevRefractive << 16
+//   ro     = origin.xyz, 0               rd     = direction.xyz, bounce | prevRefractive << 16
 //   atten  = attenuation.xyz, rng.x      lum    = luminance.xyz, rng.y
-//   albedo = albedo.xyz, result index    normal = normal.xyz, 0
-// Stage A needs the first four (plus the last two only when a path ends or scatters in a medium).
+//   albedo = albedo.xyz, result index    normal = normal.xyz, AOV weight
+// Stage A needs the first four (plus the last two only when a path ends or scatters in a medium);
+// stage B needs all but the origin, which it replaces.
 __device__ __forceinline__ void loadPathHot(const PathArrays& P, int slot, Path& p)
 {
     F4 a = P.ro[slot], b = P.rd[slot], c = P.atten[slot], d = P.lum[slot];
-    p.ro = v3(a); p.weight = a.w;
+    p.ro = v3(a);
+    p.rd = v3(b);
+    uint32_t bits = f2u(b.w);
+    p.bounce = (int32_t)(bits & 0xffffu);
+    p.prevFlags = (bits >> 16) ? MatFlag_Refractive : 0u;
+    p.atten = v3(c); p.rng.x = f2u(c.w);
+    p.lum = v3(d); p.rng.y = f2u(d.w);
+    p.rng.z = p.rng.w = 0u;
+}
+
+__device__ __forceinline__ void loadPathNoOrigin(const PathArrays& P, int slot, Path& p)
+{
+    F4 b = P.rd[slot], c = P.atten[slot], d = P.lum[slot];
+    p.ro = v3s(0.0f);
     p.rd = v3(b);
     uint32_t bits = f2u(b.w);
     p.bounce = (int32_t)(bits & 0xffffu);
@@ -127,18 +141,18 @@ __device__ __forceinline__ void loadPathCold(const PathArrays& P, int slot, Path
 {
     F4 e = P.albedo[slot], f = P.normal[slot];
     p.albedo = v3(e); outIndex = f2u(e.w);
-    p.normal = v3(f);
+    p.normal = v3(f); p.weight = f.w;
 }
 
 __device__ __forceinline__ void storePath(const PathArrays& P, int slot, const Path& p, uint32_t outIndex)
 {
-    P.ro[slot] = f4(p.ro, p.weight);
+    P.ro[slot] = f4(p.ro, 0.0f);
     uint32_t bits = (uint32_t)p.bounce | ((p.prevFlags & MatFlag_Refractive) ? 0x10000u : 0u);
     P.rd[slot] = f4(p.rd, u2f(bits));
     P.atten[slot] = f4(p.atten, u2f(p.rng.x));
     P.lum[slot] = f4(p.lum, u2f(p.rng.y));
     P.albedo[slot] = f4(p.albedo, u2f(outIndex));
-    P.normal[slot] = f4(p.normal, 0.0f);
+    P.normal[slot] = f4(p.normal, p.weight);
 }
 
 __device__ __forceinline__ RayHit unpackHit(const DScene& S, V3 rd, U4 h)
@@ -330,7 +344,8 @@ __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_BLOCKS_A) k_wfShadeA(D
     // issue the state loads before the live count is known: they do not depend on it
     Path p;
     loadPathHot(P.cur, slot, p);
-    p.albedo = p.normal = v3s(0.0f);
+    p.albedo = p.normal = v3s(0.0f);    // stage A only ever adds to the AOV accumulators (medium scatter):
+    p.weight = 0.0f;                    // collect the additions, fold them in if the cold fields get loaded
     const U4 h1 = P.hit1[slot];
     const bool active = slot < P.counters[Wf_NumA];
     bool ray2 = false, moved = false;
@@ -344,7 +359,9 @@ __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_BLOCKS_A) k_wfShadeA(D
         if (r == Stage_Done || r == Stage_Next)
         {
             // the path ends here or scattered inside the medium: both need the rest of the state
-            loadPathCold(P.cur, slot, p, outIndex);
+            Path cold;
+            loadPathCold(P.cur, slot, cold, outIndex);
+            p.albedo = cold.albedo + p.albedo; p.normal = cold.normal + p.normal; p.weight = cold.weight + p.weight;
             // scattered: the next bounce starts without a surface interaction
             if (r == Stage_Next && pathAdvance(p)) moved = true;
             else emitResult(W, p, outIndex);
@@ -400,7 +417,7 @@ __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_BLOCKS_B) k_wfShadeB(D
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;     // always below the pool capacity
     // loads that do not depend on the live count go first
     Path p; uint32_t outIndex = 0;
-    loadPathHot(P.cur, slot, p);
+    loadPathNoOrigin(P.cur, slot, p);           // stage B replaces the origin and never reads the old one
     loadPathCold(P.cur, slot, p, outIndex);
     const U4 h2 = P.hit2[slot];
     const F4 o2 = P.ro2[slot], d2 = P.rd2[slot], pa = P.pend[slot];
