@@ -266,6 +266,29 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
 int32_t LmPack_BakeDesc_Device(PtScene* scene, const PtLightmapDesc* lightmaps, int32_t lmCount,
                                float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass);
 
+/* ---- participating medium (PtMediaDesc, src/rendering/path_tracer.c:91-111) -----
+ * The reference edits scene->mediaDesc through its UI (media_desc_gui) or a JSON file
+ * (media_desc_load) and then runs media_desc_update (:1963-1987); this is the same
+ * set of user-facing fields with the same defaults (media_desc_new :1944-1961). The
+ * derived values (mu, noise range, majorant) are recomputed by the call. 0 on success. */
+typedef struct PtMediaParams_s
+{
+    pim_float4 constantColor;   /* default (0.5, 0.5, 0.5, 2) */
+    pim_float4 noiseColor;      /* default (0.5, 0.5, 0.5, 2) */
+    float constantMfp;          /* metres, default 40 km */
+    float noiseMfp;             /* metres, default 40 km */
+    float absorption;           /* 0.1 */
+    int32_t noiseOctaves;       /* 1 */
+    float noiseGain;            /* 0.9 */
+    float noiseLacunarity;      /* 2.0666 */
+    float noiseFreq;            /* 1 */
+    float noiseScale;           /* 1 */
+    float noiseHeight;          /* 20 */
+    float phaseDirA, phaseDirB, phaseBlend;   /* 0, 0, 0.5 */
+} PtMediaParams;
+void PtMediaParams_Default(PtMediaParams* params);
+int32_t PtScene_SetMedia(PtScene* scene, const PtMediaParams* params);
+
 /* ---- lightmap attribute embedding --------------------------
  * EmbedAttributes / EmbedTaskFn (static in src/rendering/lightmap.c:947-1047), the last and
  * O(texels x triangles) step of LmPack_Pack: for every texel of every page find the

@@ -81,6 +81,7 @@ int oracle_sys_init(void);
 void* oracle_scene_new(void);
 void oracle_scene_del(void* scene);
 void oracle_scene_info(const void* scene, OracleSceneInfo* info);
+void oracle_scene_set_media(void* scene, const float* params14, int noiseOctaves, const float* phase3);
 /* copies cell `cell`'s distribution; returns its length (0 = no distribution) */
 int oracle_scene_dist(const void* scene, int cell, float* pdf, float* cdf, uint32_t* live);
 /* overwrite a cell's pdf (length must match or be 0) and re-bake its cdf */

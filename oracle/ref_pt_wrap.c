@@ -51,6 +51,24 @@ void oracle_scene_info(const void* pscene, OracleSceneInfo* info)
     info->emitToVert = scene->emitToVert;
 }
 
+/* what media_desc_gui / media_desc_load do to scene->mediaDesc (path_tracer.c:1989-2026, 2080-2110):
+ * set the user-facing fields, then media_desc_update. params14: constantColor.xyz, noiseColor.xyz,
+ * constantMfp, noiseMfp, absorption, noiseGain, noiseLacunarity, noiseFreq, noiseScale, noiseHeight;
+ * phase3: phaseDirA, phaseDirB, phaseBlend */
+void oracle_scene_set_media(void* pscene, const float* params14, int noiseOctaves, const float* phase3)
+{
+    PtScene* scene = (PtScene*)pscene;
+    PtMediaDesc* d = &scene->mediaDesc;
+    d->constantColor = f4_v(params14[0], params14[1], params14[2], 2.0f);
+    d->noiseColor = f4_v(params14[3], params14[4], params14[5], 2.0f);
+    d->constantMfp = params14[6]; d->noiseMfp = params14[7]; d->absorption = params14[8];
+    d->noiseOctaves = noiseOctaves;
+    d->noiseGain = params14[9]; d->noiseLacunarity = params14[10]; d->noiseFreq = params14[11];
+    d->noiseScale = params14[12]; d->noiseHeight = params14[13];
+    d->phaseDirA = phase3[0]; d->phaseDirB = phase3[1]; d->phaseBlend = phase3[2];
+    media_desc_update(d);
+}
+
 int oracle_scene_dist(const void* pscene, int cell, float* pdf, float* cdf, uint32_t* live)
 {
     const PtScene* scene = (const PtScene*)pscene;

@@ -86,6 +86,13 @@ class PtLightmapDesc(C.Structure):
                 ("sampleCounts", C.c_void_p), ("size", C.c_int32)]
 
 
+class PtMediaParams(C.Structure):       # PtMediaDesc's user-facing fields (path_tracer.c:91-111)
+    _fields_ = [("constantColor", Float4), ("noiseColor", Float4), ("constantMfp", C.c_float), ("noiseMfp", C.c_float),
+                ("absorption", C.c_float), ("noiseOctaves", C.c_int32), ("noiseGain", C.c_float),
+                ("noiseLacunarity", C.c_float), ("noiseFreq", C.c_float), ("noiseScale", C.c_float),
+                ("noiseHeight", C.c_float), ("phaseDirA", C.c_float), ("phaseDirB", C.c_float), ("phaseBlend", C.c_float)]
+
+
 class PtEmbedMesh(C.Structure):
     _fields_ = [("positions", C.c_void_p), ("normals", C.c_void_p), ("uvs", C.c_void_p), ("texIndices", C.c_void_p),
                 ("length", C.c_int32), ("materialFlags", C.c_uint32)]
@@ -137,7 +144,7 @@ EXPORTS = [
     "Pt_SetKernelTiming", "Pt_GetKernelStats", "Pt_IntersectCountN", "Pt_TraceRayN_NoAlloc",
     "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
     "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap", "LmPack_EmbedDesc",
-    "LmPack_BakeDesc_Device",
+    "LmPack_BakeDesc_Device", "PtMediaParams_Default", "PtScene_SetMedia",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -211,6 +218,9 @@ def load():
     L.LmPack_EmbedDesc.argtypes = [C.POINTER(PtEmbedMesh), C.c_int32, C.POINTER(PtLightmapDesc), vp, C.c_int32]
     L.LmPack_EmbedDesc.restype = C.c_int32
     L.LmPack_BakeDesc_Device.argtypes = L.LmPack_BakeDesc.argtypes
+    L.PtMediaParams_Default.argtypes = [C.POINTER(PtMediaParams)]
+    L.PtScene_SetMedia.argtypes = [vp, C.POINTER(PtMediaParams)]
+    L.PtScene_SetMedia.restype = C.c_int32
     L.LmPack_BakeDesc_Device.restype = C.c_int32
     for name in ("Pt_IntersectN", "Pt_OccludedN", "Pt_TraceRayN", "Pt_TraceSpp", "Pt_IntersectN_Device",
                  "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc", "PtScene_GetStats",
@@ -414,6 +424,18 @@ class Scene:
         d.position, d.normal, d.sampleCounts, d.size = position.ctypes.data, normal.ctypes.data, sample_counts.ctypes.data, size
         _check(load().LmPack_BakeDesc(self.h, C.byref(d), 1, texels_per_meter, time_slice, spp, pass_index), "LmPack_BakeDesc")
 
+
+    def set_media(self, **fields):
+        """PtScene_SetMedia: the defaults of media_desc_new with the given PtMediaParams fields replaced."""
+        m = PtMediaParams()
+        load().PtMediaParams_Default(C.byref(m))
+        for k, v in fields.items():
+            if k in ("constantColor", "noiseColor"):
+                setattr(m, k, Float4(float(v[0]), float(v[1]), float(v[2]), 2.0))
+            else:
+                setattr(m, k, v)
+        _check(load().PtScene_SetMedia(self.h, C.byref(m)), "PtScene_SetMedia")
+        return m
 
     def bake_lightmap_device(self, probes, position, normal, sample_counts, size, texels_per_meter, time_slice=1.0, spp=1,
                              pass_index=0):

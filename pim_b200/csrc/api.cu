@@ -1001,6 +1001,42 @@ int32_t AmbCube_Bake(PtScene* scene, AmbCube_t* pCube, pim_float4 origin, int32_
     return prevSampleCount + 1;
 }
 
+void PtMediaParams_Default(PtMediaParams* m)       // media_desc_new, path_tracer.c:1944-1961
+{
+    if (!m) return;
+    memset(m, 0, sizeof(*m));
+    m->constantColor = pim_float4{ 0.5f, 0.5f, 0.5f, 2.0f };
+    m->noiseColor = pim_float4{ 0.5f, 0.5f, 0.5f, 2.0f };
+    m->constantMfp = 40.0f * 1e3f; m->noiseMfp = 40.0f * 1e3f;
+    m->absorption = 0.1f; m->noiseOctaves = 1; m->noiseGain = 0.9f; m->noiseLacunarity = 2.0666f;
+    m->noiseFreq = 1.0f; m->noiseHeight = 20.0f; m->noiseScale = 1.0f;
+    m->phaseDirA = 0.0f; m->phaseDirB = 0.0f; m->phaseBlend = 0.5f;
+}
+
+int32_t PtScene_SetMedia(PtScene* scene, const PtMediaParams* m)      // media_desc_update, path_tracer.c:1963-1987
+{
+    if (!scene || !m) { setError("PtScene_SetMedia: null argument"); return -1; }
+    MediaDesc d;
+    auto mu = [](float mfp, float color) { return 1.0f / (mfp * 0.5f + color * (mfp * 2.0f - mfp * 0.5f)); };   // f4_lerpsv, MeanFreePathToMu
+    d.constantMu = v3(mu(m->constantMfp, m->constantColor.x), mu(m->constantMfp, m->constantColor.y), mu(m->constantMfp, m->constantColor.z));
+    d.noiseMu = v3(mu(m->noiseMfp, m->noiseColor.x), mu(m->noiseMfp, m->noiseColor.y), mu(m->noiseMfp, m->noiseColor.z));
+    d.absorption = m->absorption;
+    d.noiseOctaves = m->noiseOctaves; d.noiseGain = m->noiseGain; d.noiseLacunarity = m->noiseLacunarity;
+    d.noiseFreq = m->noiseFreq; d.noiseScale = m->noiseScale; d.noiseHeight = m->noiseHeight;
+    d.phaseDirA = f1_clamp(m->phaseDirA, -0.99f, 0.99f);
+    d.phaseDirB = f1_clamp(m->phaseDirB, -0.99f, 0.99f);
+    d.phaseBlend = f1_sat(m->phaseBlend);
+    float sum = 0.0f, amplitude = 1.0f;
+    for (int i = 0; i < d.noiseOctaves; ++i) { sum += amplitude; amplitude *= d.noiseGain; }
+    d.noiseRange = sum * d.noiseScale * 1.5f;
+    const float a = 1.0f + d.absorption;
+    const V3 maj = (d.constantMu * a + d.noiseMu * a) * 2.0f;           // CalcMajorant :2190-2196
+    d.rcpMajorant = 1.0f / f1_max(maj.x, f1_max(maj.y, maj.z));
+    cudaStreamSynchronize(scene->stream);
+    scene->view.media = d;
+    return 0;
+}
+
 int32_t LmPack_EmbedDesc(const PtEmbedMesh* meshes, int32_t meshCount, PtLightmapDesc* lightmaps, const int32_t* slotIndices,
                          int32_t lmCount)
 {

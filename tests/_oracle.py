@@ -206,6 +206,17 @@ class Scene:
         return colors, dirs
 
 
+    def set_media(self, m):
+        """the same PtMediaParams (pim_b200.api) on the reference scene, then media_desc_update"""
+        L = lib()
+        L.oracle_scene_set_media.argtypes = [C.c_void_p, f32p, C.c_int, f32p]
+        p = np.array([m.constantColor.x, m.constantColor.y, m.constantColor.z, m.noiseColor.x, m.noiseColor.y, m.noiseColor.z,
+                      m.constantMfp, m.noiseMfp, m.absorption, m.noiseGain, m.noiseLacunarity, m.noiseFreq, m.noiseScale,
+                      m.noiseHeight], np.float32)
+        ph = np.array([m.phaseDirA, m.phaseDirB, m.phaseBlend], np.float32)
+        L.oracle_scene_set_media(self.h, _ptr(p), int(m.noiseOctaves), _ptr(ph))
+        L.oracle_scene_info(self.h, C.byref(self.info))      # rcpMajorant changed
+
     def cubemap_bake(self, color, origin, weight, pass_index=0):
         """Cubemap_Bake (cubemap.c:162-187) into color[6, size, size, 3], in place."""
         assert color.dtype == np.float32 and color.flags.c_contiguous and color.shape[0] == 6

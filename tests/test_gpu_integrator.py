@@ -196,3 +196,48 @@ def test_empty_scene_and_sky(api, lut):
     tr.trace_spp(s, cam, dof, 0, 2)
     assert np.allclose(tr.image("color"), 0.25, atol=1e-6)
     tr.close(); s.close()
+
+
+def test_dense_medium_matches_oracle(api, lut, oracle):
+    """Fog with a 4 m (constant) + 6 m (3-octave noise) mean free path and an anisotropic two-lobe phase
+    function, so that most paths scatter inside the medium: ScatterRay, Media_Sample and its gradient noise,
+    SamplePhaseDir, CalcTransmittance on the NEE rays, and the medium's AOV contributions — the default
+    40 km fog almost never takes those branches. Per path against the reference's Pt_TraceRay, both through
+    the wavefront and the one-thread-per-path kernel, and per pixel for the three images of a frame."""
+    desc = scenes.cornell_box("boxes", brdf_lut=lut, seed=1)
+    s = api.Scene(desc)
+    oracle.load_scene_desc(desc)
+    ref = oracle.Scene()
+    cells = int(np.prod(s.grid_size))
+    dists = [ref.dist(c) for c in range(cells)]
+    _copy_grid(s, [d[1] for d in dists], [d[0] for d in dists])
+    m = s.set_media(constantMfp=4.0, noiseMfp=6.0, constantColor=(0.3, 0.5, 0.8), noiseColor=(0.7, 0.5, 0.4),
+                    absorption=0.2, noiseOctaves=3, noiseScale=1.5, noiseHeight=3.0, noiseFreq=0.7,
+                    phaseDirA=0.6, phaseDirB=-0.3, phaseBlend=0.4)
+    ref.set_media(m)
+    # CalcMajorant: the red channel has the shortest free paths, 2 + 0.3 * 6 and 3 + 0.7 * 9 metres
+    assert abs(1.0 / ref.info.rcpMajorant - 2.0 * 1.2 * (1 / 3.8 + 1 / 9.3)) < 1e-3
+    for n in (1000, 20000):
+        ro, rd = parity.box_rays(n, seed=33, extent=4.0)
+        want = ref.trace_rays(ro, rd, 7)
+        got = s.trace_rays(ro, rd, 7)
+        # more random decisions per path than in clear air: a few more paths flip a branch on rounding
+        assert parity.path_agreement(got[:, 0:3], want[:, 0:3]) >= 0.97
+        assert parity.path_agreement(got[:, 3:6], want[:, 3:6]) >= 0.97
+        assert parity.path_agreement(got[:, 6:9], want[:, 6:9]) >= 0.97
+    # the fog does scatter: the albedo AOV of paths differs from the clear-air run
+    clear = api.Scene(desc)
+    _copy_grid(clear, [d[1] for d in dists], [d[0] for d in dists])
+    ro, rd = parity.box_rays(2000, seed=33, extent=4.0)
+    assert np.abs(clear.trace_rays(ro, rd, 7)[:, 3:6] - s.trace_rays(ro, rd, 7)[:, 3:6]).mean() > 0.01
+    clear.close()
+    cam, dof, ocam, odof = _cams(api, oracle)
+    W, H = 64, 36
+    col = np.zeros((H, W, 3), np.float32); alb = col.copy(); nor = col.copy()
+    ref.trace(col, alb, nor, 1.0, ocam, odof, 0)
+    tr = api.Trace(W, H)
+    tr.trace_spp(s, cam, dof, 0, 1, sums=True)
+    assert parity.path_agreement(tr.image("color"), col) >= 0.97
+    assert parity.path_agreement(tr.image("albedo"), alb) >= 0.97
+    assert parity.path_agreement(tr.image("normal"), nor) >= 0.97
+    tr.close(); ref.close(); s.close()
