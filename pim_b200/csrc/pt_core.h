@@ -457,7 +457,7 @@ PT_HD V3 UvBilinearWrap_xy16(const uint32_t* texels, int w, int h, V2 uv)
     Bilinear bi = BilinearWrap(w, h, uv);
     V3 a = Xy16ToNormalTs(texels[bi.a]), b = Xy16ToNormalTs(texels[bi.b]);
     V3 c = Xy16ToNormalTs(texels[bi.c]), d = Xy16ToNormalTs(texels[bi.d]);
-    return lerp(lerp(a, b, bi.fx), lerp(c, d, bi.fx), bi.fy);
+    return normalize(lerp(lerp(a, b, bi.fx), lerp(c, d, bi.fx), bi.fy));      // BilinearBlend_xy16, sampler.h:250-260
 }
 PT_HD V2 UvBilinearClamp_f2(const float* texels, int w, int h, V2 uv)
 {

@@ -305,6 +305,67 @@ def cornell_box(variant="boxes", brdf_lut=None, seed=1):
     return desc
 
 
+def textured_room(brdf_lut=None, seed=1, tex_seed=5, features=("albedo", "rome", "normal", "emission", "sky")):
+    """Cornell boxes with every material input of GetSurface in play (a parity scene, not one of the
+    reference's): varying RGBA8 albedo textures (true bilinear + gamma decode), ROME textures with varying
+    roughness / metallic and an emission channel that is only partly on (EmissionPdf's texel probes), RG16
+    normal maps, a sky-flagged ceiling and a sky cubemap behind it."""
+    desc = cornell_box("boxes", brdf_lut=brdf_lut, seed=seed)
+    g = np.random.Generator(np.random.PCG64(tex_seed))
+
+    def rgba8(r, gc, b, a):
+        q = lambda x: np.clip(np.rint(np.asarray(x, np.float64) * 255.0), 0, 255).astype(np.uint32)
+        return (q(r) | (q(gc) << 8) | (q(b) << 16) | (q(a) << 24)).astype(np.uint32).reshape(-1)
+
+    def add(tex):
+        desc.textures.append(tex)
+        return len(desc.textures) - 1
+
+    def albedo_tex(n, tint):
+        v = g.uniform(0.35, 0.95, (n, n, 3)) * np.asarray(tint)
+        return add(Texture(n, n, rgba8(v[..., 0], v[..., 1], v[..., 2], np.ones((n, n))), TEX_RGBA8))
+
+    def rome_tex(n, metal_frac, emit=None):
+        rough = g.uniform(0.05, 1.0, (n, n))
+        metal = (g.uniform(0, 1, (n, n)) < metal_frac).astype(np.float64)
+        em = np.zeros((n, n)) if emit is None else emit
+        return add(Texture(n, n, rgba8(rough, np.ones((n, n)), metal, em), TEX_RGBA8))
+
+    def normal_tex(n, tilt):
+        xy = g.uniform(-tilt, tilt, (n, n, 2))
+        q = np.clip(np.rint(xy * 32767.0), -32767, 32767).astype(np.int32)
+        packed = (q[..., 0] & 0xFFFF).astype(np.uint32) | ((q[..., 1] & 0xFFFF).astype(np.uint32) << 16)
+        return add(Texture(n, n, packed.reshape(-1), TEX_RG16))
+
+    e = desc.entities
+    # 0 floor, 1 ceiling, 2 light, 3 -X wall, 4 +X wall, 5 +Z wall, 6 -Z wall, 7 tall box, 8 small box
+    if "albedo" in features:
+        e[0].albedo, e[3].albedo = albedo_tex(32, (1, 1, 1)), albedo_tex(32, (0.3, 1, 0.3))
+        e[4].albedo, e[5].albedo = albedo_tex(16, (1, 0.3, 0.3)), albedo_tex(64, (1, 1, 1))
+        e[7].albedo = albedo_tex(8, (1, 0.9, 0.6))
+    if "rome" in features:
+        e[0].rome, e[3].rome, e[4].rome = rome_tex(16, 0.0), rome_tex(8, 0.5), rome_tex(8, 0.0)
+        e[7].rome, e[8].rome = rome_tex(4, 1.0), rome_tex(16, 0.3)
+    if "normal" in features:
+        e[0].normal, e[4].normal, e[7].normal = normal_tex(16, 0.35), normal_tex(32, 0.5), normal_tex(8, 0.2)
+    if "emission" in features:      # the light: emission on a checkerboard of its texture
+        yy, xx = np.mgrid[0:8, 0:8]
+        e[2].rome = rome_tex(8, 0.0, emit=((xx + yy) % 2).astype(np.float64))
+        e[2].flags |= MATFLAG_EMISSIVE
+    if "sky" in features:           # the ceiling is a window to the sky
+        e[1].flags |= MATFLAG_SKY
+    n = 16
+    yy, xx = np.mgrid[0:n, 0:n]
+    sky = np.zeros((6, n, n, 3), f32)
+    for f in range(6):
+        sky[f, ..., 0] = 0.2 + 0.05 * f + 0.3 * xx / n
+        sky[f, ..., 1] = 0.3 + 0.4 * yy / n
+        sky[f, ..., 2] = 0.8 - 0.03 * f
+    sky[2] *= 3.0       # brighter straight up
+    desc.sky = sky
+    return desc
+
+
 # ------------------------------------------------------------ synthetic inputs
 
 class Pcg32:

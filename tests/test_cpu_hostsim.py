@@ -66,19 +66,24 @@ def _build(hs, oracle, desc):
             pdf[c], cdf[c] = p, cd
     gs = np.array(ref.grid_size, np.int32); glo = np.array(info.gridLo, np.float32); ghi = np.array(info.gridHi, np.float32)
     lut = np.ascontiguousarray(desc.brdf_lut, np.float32)
+    sky = np.ascontiguousarray(desc.sky, np.float32) if desc.sky is not None else None
+    keep.append(sky)
     P = lambda a: a.ctypes.data_as(C.c_void_p)
     hs.hs_new.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                              C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
     h = hs.hs_new(P(pos), P(nrm), P(uv), P(mi), info.vertCount, C.addressof(mats), len(desc.entities), C.addressof(texs),
                   len(desc.textures), P(v2e), P(e2v), E, P(glo), P(ghi), P(gs), info.cellsPerMeter, P(pdf), P(cdf), P(ln),
-                  P(lut), lut.shape[1], lut.shape[0], None, 0)
+                  P(lut), lut.shape[1], lut.shape[0], P(sky) if sky is not None else None, sky.shape[1] if sky is not None else 0)
     return h, ref, keep
 
 
-@pytest.mark.parametrize("variant", ["boxes", "spheres"])
+@pytest.mark.parametrize("variant", ["boxes", "spheres", "textured"])
 def test_device_headers_match_reference(hs, oracle, variant):
-    desc = scenes.cornell_box(variant, brdf_lut=parity.reference_lut(), seed=1)
+    if variant == "textured":       # varying albedo / ROME / normal textures, textured emission, sky ceiling
+        desc = scenes.textured_room(brdf_lut=parity.reference_lut(), seed=1)
+    else:
+        desc = scenes.cornell_box(variant, brdf_lut=parity.reference_lut(), seed=1)
     h, ref, keep = _build(hs, oracle, desc)
     # traversal of the GPU node format, built by the GPU builder's own helpers
     n = 50000
