@@ -125,3 +125,56 @@ def test_device_headers_match_reference(hs, oracle, variant):
     hs.hs_del.argtypes = [C.c_void_p]
     hs.hs_del(h)
     ref.close()
+
+
+def _frame_agreement(hs, oracle, desc, **dof_fields):
+    h, ref, keep = _build(hs, oracle, desc)
+    W, H = 48, 27
+    cam, dof = oracle.camera_lookat([-4, 0, 4], [0, -1, 0]), oracle.default_dof()
+    dof.autoFocus = 0
+    for k, v in dof_fields.items():
+        setattr(dof, k, v)
+    col = np.zeros((H, W, 3), np.float32); alb = col.copy(); nr = col.copy()
+    ref.trace(col, alb, nr, 1.0, cam, dof, 0)
+    q = np.array(cam.rotation, np.float32)
+    hc = Cam()
+    hc.eye[:] = list(cam.position)[:3]
+    hc.right[:] = scenes.quat_mul_dir(q, [1, 0, 0]); hc.up[:] = scenes.quat_mul_dir(q, [0, 1, 0])
+    hc.fwd[:] = scenes.quat_mul_dir(q, [0, 0, -1])
+    th = np.float32(np.tan(np.float32(np.radians(np.float32(90.0))) * np.float32(0.5)))
+    hc.slope[:] = [np.float32(W / H) * th, th]
+    hc.w, hc.h = W, H
+    hc.aperture, hc.focal, hc.blades, hc.rot, hc.curv = dof.aperture, dof.focalLength, dof.bladeCount, dof.bladeRot, dof.focalPlaneCurvature
+    hcol = np.zeros((H, W, 3), np.float32); halb = hcol.copy(); hnr = hcol.copy()
+    hs.hs_trace_frame.argtypes = [C.c_void_p, C.POINTER(Cam), C.c_uint32, C.c_uint32] + [C.c_void_p] * 3
+    hs.hs_trace_frame(h, C.byref(hc), 0, 1, hcol.ctypes.data, halb.ctypes.data, hnr.ctypes.data)
+    hs.hs_del.argtypes = [C.c_void_p]
+    hs.hs_del(h)
+    ref.close()
+    return min(parity.path_agreement(hcol, col), parity.path_agreement(halb, alb), parity.path_agreement(hnr, nr))
+
+
+@pytest.mark.parametrize("dof", [dict(aperture=0.3, focalLength=4.0), dict(aperture=0.3, bladeCount=666),
+                                 dict(aperture=0.2, bladeCount=3, bladeRot=1.0),
+                                 dict(aperture=0.2, focalPlaneCurvature=0.5), dict(aperture=0.0)],
+                         ids=["wide", "pentagram", "triangle-rotated", "curved-focal-plane", "pinhole"])
+def test_depth_of_field_variants(hs, oracle, dof):
+    """CalculateDof (path_tracer.c:2418-2452): n-gon and pentagram apertures, blade rotation, focal plane curvature"""
+    desc = scenes.cornell_box("boxes", brdf_lut=parity.reference_lut(), seed=1)
+    assert _frame_agreement(hs, oracle, desc, **dof) >= 0.99
+
+
+def test_missing_textures_and_sky_only_lighting(hs, oracle):
+    """materials without albedo / ROME textures take SampleAlbedo / SampleRome's defaults (:1328-1352); a scene
+    whose only light is a sky-flagged ceiling"""
+    lut = parity.reference_lut()
+    desc = scenes.cornell_box("boxes", brdf_lut=lut, seed=1)
+    for e in desc.entities[3:]:
+        e.albedo = -1
+    desc.entities[0].rome = -1
+    assert _frame_agreement(hs, oracle, desc) >= 0.99
+    desc = scenes.cornell_box("boxes", brdf_lut=lut, seed=1)
+    del desc.entities[2]
+    desc.sky = np.full((6, 4, 4, 3), 0.5, np.float32)
+    desc.entities[1].flags |= scenes.MATFLAG_SKY
+    assert _frame_agreement(hs, oracle, desc) >= 0.99
