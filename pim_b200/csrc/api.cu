@@ -91,7 +91,8 @@ static bool ensureInit()
     int n = 0;
     if (!PT_CUDA(cudaGetDeviceCount(&n))) return false;
     if (n <= 0) { setError("no CUDA device: libpimpt has no CPU path"); return false; }
-    if (const char* e = getenv("PIMPT_PERSISTENT")) g_persistentTraversal = atoi(e);   // tuning switch
+    if (const char* e = getenv("PIMPT_PERSISTENT")) g_persistentTraversal = atoi(e);   // tuning switches
+    if (const char* e = getenv("PIMPT_FINISH")) g_finishKernel = atoi(e) != 0;
     g_initialised = true;
     return true;
 }

@@ -29,7 +29,8 @@ struct KernelStats
     unsigned long long extendRays, connectRays;
 };
 extern bool g_kernelTiming;
-extern int g_persistentTraversal;   // 0: one thread per ray, 1: persistent warps that refill idle lanes, -1: by BVH size
+extern int g_persistentTraversal;
+extern bool g_finishKernel;   // 0: one thread per ray, 1: persistent warps that refill idle lanes, -1: by BVH size
 bool usePersistent(int32_t bvhNodeCount);
 extern KernelStats g_kernelStats;
 
@@ -152,7 +153,8 @@ enum WfCounter : int
     Wf_NumNext = 32,             // survivors written to the other buffer (one atomic per CTA of stage B)
     Wf_NumConnect = 64,          // slots asking for a second ray (one atomic per CTA of stage A)
     Wf_ExtendCursor = 96, Wf_ConnectCursor = 128,    // ray fetch cursors of the persistent traversal kernels
-    Wf_COUNT = 160
+    Wf_FinishExtend = 160, Wf_FinishConnect = 161,   // rays traced by the finishing kernel
+    Wf_COUNT = 192
 };
 constexpr size_t kWfCounterBytes = 1024;
 

@@ -31,6 +31,7 @@ namespace pt {
 
 bool g_kernelTiming = false;
 int g_persistentTraversal = -1;   // -1: by scene size (see usePersistent)
+bool g_finishKernel = true;       // PIMPT_FINISH=0 keeps iterating to the last path (experiments)
 KernelStats g_kernelStats = {};
 
 // Refilling idle lanes pays off only when rays take very many steps: +22 % on the 10 M-triangle
@@ -469,6 +470,70 @@ __global__ void k_wfEndIteration(PoolView P, int32_t* status)
     P.counters[Wf_NumNext] = 0;
 }
 
+// The tail of a call: once the work items are used up the live paths thin out geometrically, and
+// an iteration of seven launches over a few thousand paths is all launch latency. Below
+// kFinishThreshold live paths one launch runs each remaining path to its end in its own thread
+// (Pt_TraceRay's loop, as k_traceRays does), from the state the last iteration left.
+constexpr int kFinishThreshold = 16384;
+
+__global__ void __launch_bounds__(kTravThreads) k_wfFinish(DScene S, PoolView P, WorkDesc W)
+{
+    PT_DECLARE_STACK(st);
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t nExtend = 0, nConnect = 0;
+    if (slot < P.counters[Wf_NumA])
+    {
+        Path p; uint32_t outIndex = 0;
+        loadPathHot(P.cur, slot, p);
+        loadPathCold(P.cur, slot, p, outIndex);
+        bool alive = true;
+        while (alive)
+        {
+            RayHit hit = intersectLocal(S, p.ro, p.rd, 0.0f, kRcpEpsilon, st);
+            ++nExtend;
+            Pending pend; SurfHit surf;
+            int r = pathStageA(S, p, hit, pend, surf, st);
+            if (r == Stage_Done) break;
+            if (r != Stage_Next)
+            {
+                RayHit hit2;
+                hit2.type = Hit_Nothing; hit2.iVert = -1; hit2.t = -1.0f; hit2.flags = 0;
+                hit2.normal = v3s(0.0f); hit2.w = hit2.u = hit2.v = 0.0f;
+                if (r == Stage_Ray2)
+                {
+                    hit2 = intersectLocal(S, pend.ro2, pend.rd2, 0.0f, pend.tFar2, st);
+                    ++nConnect;
+                }
+                r = pathStageB(S, p, surf, pend, hit2, st);
+                if (r == Stage_Done) break;
+            }
+            alive = pathAdvance(p);
+        }
+        emitResult(W, p, outIndex);
+    }
+    // ray statistics: one atomic pair per warp
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        nExtend += __shfl_down_sync(0xffffffffu, nExtend, o);
+        nConnect += __shfl_down_sync(0xffffffffu, nConnect, o);
+    }
+    if ((threadIdx.x & 31) == 0 && (nExtend | nConnect))
+    {
+        atomicAdd(&P.counters[Wf_FinishExtend], (int32_t)nExtend);
+        atomicAdd(&P.counters[Wf_FinishConnect], (int32_t)nConnect);
+    }
+}
+
+__global__ void k_wfEndFinish(PoolView P, int32_t* status)
+{
+    status[0] = 0;
+    status[1] = 0;
+    status[2] = P.counters[Wf_FinishExtend];
+    status[3] = P.counters[Wf_FinishConnect];
+    P.counters[Wf_NumA] = 0;
+    P.counters[Wf_NumNext] = 0;
+}
+
 PoolView makeView(const PathPool& pool)
 {
     PoolView v;
@@ -594,6 +659,19 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     while (ok && !finished)
     {
         const int r = (int)(iterations % kRing);
+        if (!workLeft && bound <= kFinishThreshold && g_finishKernel)
+        {
+            // the few paths still alive (after the iterations already queued) finish in one launch
+            if (timing) { cudaEventRecord(ev[r][0], stream); cudaEventRecord(ev[r][1], stream); }
+            k_wfFinish<<<(unsigned)((bound + kTravThreads - 1) / kTravThreads), kTravThreads, 0, stream>>>(S, P, work);
+            if (timing) for (int k = 2; k < 6; ++k) cudaEventRecord(ev[r][k], stream);
+            k_wfEndFinish<<<1, 1, 0, stream>>>(P, dStatus);
+            g_counters.kernelLaunches += 2;
+            ok = ok && PT_CUDA(cudaMemcpyAsync(pool.hostCounters + 4 * r, dStatus, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+            ok = ok && PT_CUDA(cudaEventRecord(done[r], stream));
+            ++iterations;
+            break;
+        }
         const unsigned gridLive = (unsigned)((bound + kTravThreads - 1) / kTravThreads);
         const unsigned gridRegen = workLeft ? grid : 1u;
         const unsigned gridPersist = std::min<unsigned>(gridLive, gridP);
