@@ -92,7 +92,7 @@ static bool ensureInit()
     if (!PT_CUDA(cudaGetDeviceCount(&n))) return false;
     if (n <= 0) { setError("no CUDA device: libpimpt has no CPU path"); return false; }
     if (const char* e = getenv("PIMPT_PERSISTENT")) g_persistentTraversal = atoi(e);   // tuning switches
-    if (const char* e = getenv("PIMPT_FINISH")) g_finishKernel = atoi(e) != 0;
+    if (const char* e = getenv("PIMPT_FINISH")) g_finishThreshold = atoi(e);
     g_initialised = true;
     return true;
 }

@@ -30,7 +30,7 @@ struct KernelStats
 };
 extern bool g_kernelTiming;
 extern int g_persistentTraversal;
-extern bool g_finishKernel;   // 0: one thread per ray, 1: persistent warps that refill idle lanes, -1: by BVH size
+extern int g_finishThreshold;   // 0: one thread per ray, 1: persistent warps that refill idle lanes, -1: by BVH size
 bool usePersistent(int32_t bvhNodeCount);
 extern KernelStats g_kernelStats;
 

@@ -31,7 +31,7 @@ namespace pt {
 
 bool g_kernelTiming = false;
 int g_persistentTraversal = -1;   // -1: by scene size (see usePersistent)
-bool g_finishKernel = true;       // PIMPT_FINISH=0 keeps iterating to the last path (experiments)
+int g_finishThreshold = 131072;    // live paths at which the tail is finished in one launch; PIMPT_FINISH=n overrides, 0 disables
 KernelStats g_kernelStats = {};
 
 // Refilling idle lanes pays off only when rays take very many steps: +22 % on the 10 M-triangle
@@ -472,9 +472,8 @@ __global__ void k_wfEndIteration(PoolView P, int32_t* status)
 
 // The tail of a call: once the work items are used up the live paths thin out geometrically, and
 // an iteration of seven launches over a few thousand paths is all launch latency. Below
-// kFinishThreshold live paths one launch runs each remaining path to its end in its own thread
+// g_finishThreshold live paths one launch runs each remaining path to its end in its own thread
 // (Pt_TraceRay's loop, as k_traceRays does), from the state the last iteration left.
-constexpr int kFinishThreshold = 16384;
 
 __global__ void __launch_bounds__(kTravThreads) k_wfFinish(DScene S, PoolView P, WorkDesc W)
 {
@@ -659,10 +658,20 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     while (ok && !finished)
     {
         const int r = (int)(iterations % kRing);
-        if (!workLeft && bound <= kFinishThreshold && g_finishKernel)
+        const bool smallCall = iterations == 0 && work.count <= (int64_t)g_finishThreshold && work.count <= (int64_t)cap;
+        if ((!workLeft && bound <= g_finishThreshold) || smallCall)
         {
-            // the few paths still alive (after the iterations already queued) finish in one launch
-            if (timing) { cudaEventRecord(ev[r][0], stream); cudaEventRecord(ev[r][1], stream); }
+            // the few paths still alive (after the iterations already queued) finish in one launch;
+            // a call that small to begin with generates its paths and goes straight there
+            if (timing) cudaEventRecord(ev[r][0], stream);
+            if (smallCall)
+            {
+                k_wfRegen<<<grid, 128, 0, stream>>>(S, P, work);
+                k_wfAfterRegen<<<1, 1, 0, stream>>>(P);
+                g_counters.kernelLaunches += 2;
+                bound = (int)work.count;
+            }
+            if (timing) cudaEventRecord(ev[r][1], stream);
             k_wfFinish<<<(unsigned)((bound + kTravThreads - 1) / kTravThreads), kTravThreads, 0, stream>>>(S, P, work);
             if (timing) for (int k = 2; k < 6; ++k) cudaEventRecord(ev[r][k], stream);
             k_wfEndFinish<<<1, 1, 0, stream>>>(P, dStatus);
