@@ -192,6 +192,13 @@ def bakes(args):
     if args.cpu:
         t0 = time.perf_counter(); O.tonemap(light, 1.0, 0); dt = time.perf_counter() - t0
         out["tonemap_1080p"].update({"cpu_ms": dt * 1e3, "cpu_mpixels_s": n / dt / 1e6})
+    # the same kernel on an image larger than L2 (8192 x 4096): its HBM rate
+    nbig = 8192 * 4096
+    big = np.tile(light[:1 << 20], (nbig >> 20, 1))
+    wall, k = timed(lambda: api.tonemap(big, 1.0, 1, 0), reps=2)
+    out["tonemap_8192x4096"] = {"gpu_kernel_ms": k * 1e3, "gpu_call_ms": wall * 1e3, "gpu_mpixels_s": nbig / k / 1e6,
+                                "hbm_gbs": nbig * 20 / k / 1e9}
+    del big
 
     # N2 convolve: 64^2 faces, 64 samples per mip texel (reference: render_system.c uses 64)
     size, spt = 64, 64
