@@ -39,15 +39,25 @@ __global__ void __launch_bounds__(256) k_cubeRays(int size, V3 origin, uint32_t 
     rd[i] = f4(dir, 0.0f);
 }
 
-// PrefilterFn + PrefilterEnvMap (cubemap.c:189-260): split-sum N = V approximation
+// PrefilterFn + PrefilterEnvMap (cubemap.c:189-260): split-sum N = V approximation.
+// kLanes lanes share a mip texel (a 64^2 cubemap has 32 766 mip texels in all, a tenth of the GPU's
+// threads): every lane runs the texel's random stream — a hash chain, so nobody can skip ahead — but
+// evaluates only samples s = lane (mod kLanes); the partial sums are added across the lanes.
+template <int kLanes>
 __global__ void __launch_bounds__(128) k_cubeConvolve(const float* __restrict__ color, float* __restrict__ convolved, int size,
-                                                      int elemCount, int mip, uint32_t sampleCount, float weight,
+                                                      int elemCount, int mipCount, uint32_t sampleCount, float weight,
                                                       uint32_t pass, uint32_t seed)
 {
-    int mSize = size >> mip;
+    // all mips in one launch: find this lane group's mip (the reference runs one task per mip, and the
+    // texel index inside the mip seeds the stream, cubemap.c:271-287)
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t rest = tid / kLanes;
+    const int lane = (int)(tid % kLanes);
+    int mip = 0, mSize = size;
+    while (mip < mipCount && rest >= 6ll * mSize * mSize) { rest -= 6ll * mSize * mSize; ++mip; mSize >>= 1; }
+    if (mip >= mipCount) return;        // whole lane groups leave together
     const int len = mSize * mSize;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 6 * len) return;
+    const int i = (int)rest;
     const int face = i / len, fi = i % len;
     const float roughness = (float)mip / 6.0f;          // MipToRoughness, CUBEMAP_MAX_MIP (cubemap.h:12,66-69)
     Rng rng = seed_prng((uint32_t)i, pass, seed, Salt_CubeConvolve | (uint32_t)(mip & 0xf));
@@ -58,9 +68,19 @@ __global__ void __launch_bounds__(128) k_cubeConvolve(const float* __restrict__ 
     const float alpha = BrdfAlpha(roughness);
     float basisIntegral = 0.0f;
     F4 light = f4(0, 0, 0, 0);
-    for (uint32_t s = 0; s < sampleCount; ++s)
+    for (uint32_t s0 = 0; s0 < sampleCount; s0 += kLanes)
     {
-        const V3 H = TbnToWorld(tbn, SampleGGXMicrofacet(rng_f2(rng), alpha));
+        // kLanes draws of the stream in lockstep, lane j keeps draw j; then all lanes evaluate side by side
+        V2 u = v2(0.0f, 0.0f);
+        bool mine = false;
+        for (int j = 0; j < kLanes; ++j)
+        {
+            if (s0 + (uint32_t)j >= sampleCount) break;
+            const V2 d = rng_f2(rng);
+            if (j == lane) { u = d; mine = true; }
+        }
+        if (!mine) continue;
+        const V3 H = TbnToWorld(tbn, SampleGGXMicrofacet(u, alpha));
         const V3 L = reflect(I, H);
         const float NoL = dot(L, tbn.c2);
         if (NoL > 0.0f)
@@ -71,6 +91,17 @@ __global__ void __launch_bounds__(128) k_cubeConvolve(const float* __restrict__ 
             light.x += c.x * NoL; light.y += c.y * NoL; light.z += c.z * NoL; light.w += NoL;
             basisIntegral += NoL;
         }
+    }
+    if (kLanes > 1)
+    {
+        // lane groups are aligned sub-warps: xor shuffles below kLanes stay inside the group
+        for (int o = kLanes >> 1; o > 0; o >>= 1)
+        {
+            light.x += __shfl_xor_sync(0xffffffffu, light.x, o); light.y += __shfl_xor_sync(0xffffffffu, light.y, o);
+            light.z += __shfl_xor_sync(0xffffffffu, light.z, o); light.w += __shfl_xor_sync(0xffffffffu, light.w, o);
+            basisIntegral += __shfl_xor_sync(0xffffffffu, basisIntegral, o);
+        }
+        if (lane != 0) return;
     }
     if (basisIntegral > 0.0f)
     {
@@ -384,14 +415,16 @@ bool launchCubeConvolve(const float* dColor, float* dConvolved, int size, uint32
                         uint32_t seed, cudaStream_t stream)
 {
     const int mipCount = cubemapMipCount(size), elemCount = cubemapElemCount(size);
-    for (int m = 0; m < mipCount; ++m)
-    {
-        const int mSize = size >> m;
-        const int n = 6 * mSize * mSize;
-        if (n <= 0) continue;
-        k_cubeConvolve<<<gridFor(n, 128), 128, 0, stream>>>(dColor, dConvolved, size, elemCount, m, sampleCount, weight, pass, seed);
-        g_counters.kernelLaunches++;
-    }
+    int64_t n = 0;
+    for (int m = 0; m < mipCount; ++m) n += 6ll * (size >> m) * (size >> m);
+    if (n <= 0) return true;
+    // small cubemaps: 8 lanes per mip texel (every mip's texel count x 8 is a multiple of 8, so lane
+    // groups never straddle a mip or the end of the range)
+    if (n < 148 * 2048)
+        k_cubeConvolve<8><<<gridFor(n * 8, 128), 128, 0, stream>>>(dColor, dConvolved, size, elemCount, mipCount, sampleCount, weight, pass, seed);
+    else
+        k_cubeConvolve<1><<<gridFor(n, 128), 128, 0, stream>>>(dColor, dConvolved, size, elemCount, mipCount, sampleCount, weight, pass, seed);
+    g_counters.kernelLaunches++;
     return PT_CUDA(cudaGetLastError());
 }
 
