@@ -8,19 +8,19 @@
 //   K6a shadeA    Pt_TraceRay from the hit up to EstimateDirect's ray
 //   K4' connect   the NEE / MIS ray (closest hit + primitive id, as the reference does)
 //   K6b shadeB    rest of EstimateDirect, BSDF scatter, roulette for the next bounce
+//   K6f finish    once the work is used up and few paths are left: one thread per path to its end
 //   K7  (in shade) finished paths add their result to the per-pixel sums
-//   K8  (in regen/shade) work claims and live counts are warp-aggregated with
-//                 ballot/popc: one atomic per warp
+//   K8  (in regen/shade) work claims and live counts: ballot/popc per warp, one atomic per CTA
 //
-// Compaction moves state, not indices: the seven persistent state arrays are double
-// buffered, stage B writes each surviving path to the next free position of the other
-// buffer (one atomic per warp, so a warp's survivors land contiguously) and regen appends
-// the new paths behind them. Every kernel therefore runs over a dense range [0, N) with
-// full warps, fully coalesced 16-byte fields (512 contiguous bytes per warp and array) and
-// the freshly generated, coherent camera rays side by side. Index queues over fixed slots
-// (an earlier version) paid a 32-byte sector per 16-byte field once slot order had decayed;
-// regenerating in place instead scattered the camera rays among old paths and slowed the
-// traversal kernels (profiles/README.md has the three measurements).
+// Compaction moves state, not indices: the six persistent state fields are double buffered,
+// stage B writes each surviving path to the next free position of the other buffer (one atomic
+// per CTA, so a CTA's survivors land contiguously) and regen appends the new paths behind them.
+// Every kernel therefore runs over a dense range [0, N) with full warps, fully coalesced 16-byte
+// fields (512 contiguous bytes per warp and array) and the freshly generated, coherent camera
+// rays side by side. Index queues over fixed slots (an earlier version) paid a 32-byte sector
+// per 16-byte field once slot order had decayed; regenerating in place instead scattered the
+// camera rays among old paths and slowed the traversal kernels (profiles/README.md has the
+// three measurements).
 #include "pt_device.h"
 #include "kernels_common.cuh"
 
