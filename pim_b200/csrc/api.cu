@@ -304,7 +304,7 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
     // BVH (RtcNewScene)
     const int32_t triCount = vertCount / 3;
     ok = ok && buildBvh(dPos, triCount, s->bvh, st);
-    V.bvh.nodes = s->bvh.nodes; V.bvh.tris = s->bvh.tris;
+    V.bvh.nodes = s->bvh.nodes; V.bvh.tris = s->bvh.tris; V.bvh.nodesF = s->bvh.nodesF;
     V.bvh.nodeCount = s->bvh.nodeCount; V.bvh.triCount = s->bvh.triCount;
 
     phase(1);

@@ -39,12 +39,30 @@ struct alignas(16) PackedTri
 };
 static_assert(sizeof(PackedTri) == 48, "48-byte triangle");
 
+// The same wide node with its plane bytes already converted: plane = q * 2^e in fp32, still relative
+// to the node origin, so the traversal computes the very same t = plane * idir + (origin - ro) * idir
+// as it does from the bytes (scaling by a power of two commutes with the rounding) and both forms
+// visit the same nodes and return the same hits. 224 bytes, fourteen 128-bit loads, no byte-to-float
+// conversion in the traversal loop. Built next to the quantised nodes for trees small enough that
+// node bytes do not matter (kFloatNodeMaxNodes).
+struct alignas(16) WideNodeF
+{
+    uint32_t childBase;
+    uint32_t triBaseImask;  // triangle base | internal-mask << 24
+    uint32_t meta[2];
+    float ox, oy, oz, pad;
+    float plane[6][8];      // lox, loy, loz, hix, hiy, hiz of the eight children, relative to the origin
+};
+static_assert(sizeof(WideNodeF) == 224, "224-byte node");
+constexpr int kFloatNodeMaxNodes = 16384;      // 3.7 MB: stays in L2 whatever else streams through
+
 struct Bvh
 {
     const WideNode* nodes;
     const PackedTri* tris;
     int32_t nodeCount;
     int32_t triCount;
+    const WideNodeF* nodesF;    // null above kFloatNodeMaxNodes nodes (or 2^24 triangles)
 };
 
 struct Hit

@@ -38,6 +38,13 @@ int sahMaxTris()
     return e ? atoi(e) : kSahMaxTris;
 }
 
+// PIMPT_FLOAT_NODES overrides kFloatNodeMaxNodes (0 = never build the fp32 node form)
+int floatNodeMaxNodes()
+{
+    const char* e = getenv("PIMPT_FLOAT_NODES");
+    return e ? atoi(e) : kFloatNodeMaxNodes;
+}
+
 __device__ __forceinline__ int floatToOrdered(float f)
 {
     int i = __float_as_int(f);
@@ -576,11 +583,38 @@ bool devAlloc(T*& p, size_t count)
     return PT_CUDA(cudaMalloc((void**)&p, sizeof(T) * count));
 }
 
+// WideNode -> WideNodeF: the plane bytes as floats, scaled by the node's power-of-two cell size
+__global__ void __launch_bounds__(256) k_expandNodes(const WideNode* __restrict__ nodes, int32_t n, WideNodeF* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const WideNode w = nodes[i];
+    WideNodeF f;
+    f.childBase = w.childBase;
+    f.triBaseImask = (w.triBase & 0xffffffu) | ((w.exyzImask >> 24) << 24);
+    f.meta[0] = w.meta[0]; f.meta[1] = w.meta[1];
+    f.ox = w.ox; f.oy = w.oy; f.oz = w.oz; f.pad = 0.0f;
+    const float sx = u2f((w.exyzImask & 0xffu) << 23), sy = u2f(((w.exyzImask >> 8) & 0xffu) << 23);
+    const float sz = u2f(((w.exyzImask >> 16) & 0xffu) << 23);
+    for (int c = 0; c < 8; ++c)
+    {
+        const int wd = c >> 2, sh = 8 * (c & 3);
+        f.plane[0][c] = (float)((w.qlox[wd] >> sh) & 0xffu) * sx;       // exact: an 8-bit integer times 2^e
+        f.plane[1][c] = (float)((w.qloy[wd] >> sh) & 0xffu) * sy;
+        f.plane[2][c] = (float)((w.qloz[wd] >> sh) & 0xffu) * sz;
+        f.plane[3][c] = (float)((w.qhix[wd] >> sh) & 0xffu) * sx;
+        f.plane[4][c] = (float)((w.qhiy[wd] >> sh) & 0xffu) * sy;
+        f.plane[5][c] = (float)((w.qhiz[wd] >> sh) & 0xffu) * sz;
+    }
+    out[i] = f;
+}
+
 } // namespace
 
 void freeBvh(BvhBuffers& b)
 {
     if (b.nodes) cudaFree(b.nodes);
+    if (b.nodesF) cudaFree(b.nodesF);
     if (b.tris) cudaFree(b.tris);
     b = BvhBuffers();
 }
@@ -684,6 +718,16 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
                 ub.i = (b >= 0) ? b : (b ^ 0x7fffffff);
                 out.sceneLo[k] = ua.f; out.sceneHi[k] = ub.f;
             }
+        }
+    }
+    if (ok && out.nodeCount > 0 && out.nodeCount <= floatNodeMaxNodes() && out.triCount < (1 << 24))
+    {
+        ok = devAlloc(out.nodesF, out.nodeCount);
+        if (ok)
+        {
+            k_expandNodes<<<(out.nodeCount + 255) / 256, 256, 0, stream>>>(out.nodes, out.nodeCount, out.nodesF);
+            g_counters.kernelLaunches++;
+            ok = PT_CUDA(cudaGetLastError()) && PT_CUDA(cudaStreamSynchronize(stream));
         }
     }
     cudaFree(leafLo); cudaFree(leafHi); cudaFree(lo); cudaFree(hi); cudaFree(bounds);

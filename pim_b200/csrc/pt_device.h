@@ -40,6 +40,7 @@ constexpr int kSmCount = 148;           // B200: 2 dies x 74 SMs
 struct BvhBuffers
 {
     WideNode* nodes = nullptr;
+    WideNodeF* nodesF = nullptr;    // fp32 form of the same nodes, small trees only
     PackedTri* tris = nullptr;
     int32_t nodeCount = 0;
     int32_t triCount = 0;

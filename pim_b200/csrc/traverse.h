@@ -224,13 +224,150 @@ PT_D bool travStep(const Bvh& bvh, TravRay& r, Stack& st, TravCounters* cnt)
     return r.haveCur || st.sp != 0;
 }
 
-template <bool kAnyHit, bool kCount, class Stack>
+// One wide node of the fp32 form (Bvh::nodesF). Same arithmetic as travStep from the plane onwards
+// (t = plane * idir + (origin - ro) * idir), so the same nodes are visited in the same order; the
+// planes arrive as floats, near / far picked by address instead of by select.
+template <bool kAnyHit, class Stack>
+PT_D bool travStepF(const Bvh& bvh, TravRay& r, Stack& st)
+{
+    while (!r.haveCur)
+    {
+        if (st.sp == 0) return false;
+        unsigned long long e = st.pop();
+        uint32_t key = (uint32_t)(e >> 32);
+        if (u2f((key - 8u) & ~7u) > r.tBest) continue;
+        r.cur = (uint32_t)e;
+        r.haveCur = true;
+    }
+    r.haveCur = false;
+
+    const WideNodeF* np = bvh.nodesF + r.cur;
+    const U4 hdr = ldg128(&np->childBase);
+    const U4 org = ldg128(&np->ox);
+    const float bx = (u2f(org.x) - r.ro.x) * r.idir.x;
+    const float by = (u2f(org.y) - r.ro.y) * r.idir.y;
+    const float bz = (u2f(org.z) - r.ro.z) * r.idir.z;
+    const uint32_t imask = hdr.y >> 24;
+    const uint32_t triBase = hdr.y & 0xffffffu;
+    const uint32_t metaw[2] = { hdr.z, hdr.w };
+    // plane sets: 0 lox, 1 loy, 2 loz, 3 hix, 4 hiy, 5 hiz; each 8 floats = two 128-bit loads
+    const float* pl = &np->plane[0][0];
+    const float* nx = pl + (r.negx ? 24 : 0);
+    const float* fx = pl + (r.negx ? 0 : 24);
+    const float* ny = pl + (r.negy ? 32 : 8);
+    const float* fy = pl + (r.negy ? 8 : 32);
+    const float* nz = pl + (r.negz ? 40 : 16);
+    const float* fz = pl + (r.negz ? 16 : 40);
+
+    uint32_t keys[8];
+    uint32_t hitMask = 0;
+#if defined(__CUDA_ARCH__)
+    #pragma unroll
+#endif
+    for (int half = 0; half < 2; ++half)
+    {
+        const U4 anx = ldg128(nx + 4 * half), afx = ldg128(fx + 4 * half);
+        const U4 any_ = ldg128(ny + 4 * half), afy = ldg128(fy + 4 * half);
+        const U4 anz = ldg128(nz + 4 * half), afz = ldg128(fz + 4 * half);
+        const uint32_t vnx[4] = { anx.x, anx.y, anx.z, anx.w }, vfx[4] = { afx.x, afx.y, afx.z, afx.w };
+        const uint32_t vny[4] = { any_.x, any_.y, any_.z, any_.w }, vfy[4] = { afy.x, afy.y, afy.z, afy.w };
+        const uint32_t vnz[4] = { anz.x, anz.y, anz.z, anz.w }, vfz[4] = { afz.x, afz.y, afz.z, afz.w };
+#if defined(__CUDA_ARCH__)
+        #pragma unroll
+#endif
+        for (int k = 0; k < 4; ++k)
+        {
+            const int i = 4 * half + k;
+            float tnx = u2f(vnx[k]) * r.idir.x + bx;
+            float tfx = u2f(vfx[k]) * r.idir.x + bx;
+            float tny = u2f(vny[k]) * r.idir.y + by;
+            float tfy = u2f(vfy[k]) * r.idir.y + by;
+            float tnz = u2f(vnz[k]) * r.idir.z + bz;
+            float tfz = u2f(vfz[k]) * r.idir.z + bz;
+            float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tNear));
+            float tmax = fminf(fminf(tfx, tfy), fminf(tfz, r.tBest));
+            bool h = tmin <= tmax * 1.0000004f;
+            keys[i] = h ? (((f2u(tmin) & ~7u) | (uint32_t)i) + 8u) : 0u;
+            hitMask |= h ? (1u << i) : 0u;
+        }
+    }
+
+    uint32_t leafMask = hitMask & ~imask;
+    while (leafMask)
+    {
+        uint32_t lk = 0xffffffffu;
+#if defined(__CUDA_ARCH__)
+        #pragma unroll
+#endif
+        for (int k = 0; k < 8; ++k) { const uint32_t kk = ((leafMask >> k) & 1u) ? keys[k] : 0xffffffffu; lk = kk < lk ? kk : lk; }
+        const int i = (int)((lk - 8u) & 7u);
+        leafMask &= ~(1u << i);
+        if (!kAnyHit && u2f((lk - 8u) & ~7u) > r.tBest) break;
+        const uint32_t m = (metaw[i >> 2] >> (8 * (i & 3))) & 0xffu;
+        const uint32_t count = m >> 5, first = triBase + (m & 31u);
+        for (uint32_t j = 0; j < count; ++j)
+        {
+            float t, u, v; uint32_t prim; V3 ng;
+            if (triTest(bvh.tris + first + j, r.ro, r.rd, r.tNear, r.tBest, t, u, v, prim, ng))
+            {
+                if (kAnyHit) { r.found = true; return false; }
+                if (!r.found || t < r.tBest || prim < r.bestPrim)
+                {
+                    r.found = true;
+                    r.tBest = t; r.bestPrim = prim;
+                    r.hit.t = t; r.hit.u = u; r.hit.v = v; r.hit.prim = (int32_t)prim; r.hit.ng = ng;
+                }
+            }
+        }
+    }
+
+    uint32_t intMask = hitMask & imask;
+    if (intMask)
+    {
+#if defined(__CUDA_ARCH__)
+        #pragma unroll
+#endif
+        for (int i = 0; i < 8; ++i) keys[i] = ((intMask >> i) & 1u) ? keys[i] : 0u;
+        int n = popc32(intMask);
+        while (n > 1)
+        {
+            const uint32_t best = max8(keys);
+            const uint32_t idx = (best - 8u) & 7u;
+            st.push(hdr.x + (uint32_t)popc32(imask & ((1u << idx) - 1u)), best);
+#if defined(__CUDA_ARCH__)
+            #pragma unroll
+#endif
+            for (int i = 0; i < 8; ++i) keys[i] = (keys[i] == best) ? 0u : keys[i];
+            --n;
+        }
+        const uint32_t best = max8(keys);
+        if (u2f((best - 8u) & ~7u) <= r.tBest)
+        {
+            const uint32_t idx = (best - 8u) & 7u;
+            r.cur = hdr.x + (uint32_t)popc32(imask & ((1u << idx) - 1u));
+            r.haveCur = true;
+        }
+    }
+    return r.haveCur || st.sp != 0;
+}
+
+// kFloatNodes: take the fp32 node form when the tree has one. Only the two wavefront traversal
+// kernels ask for it: in kernels that also shade, the second traversal body costs more in
+// registers and code than it saves (stage A went from 75 to 93 ms with it).
+template <bool kAnyHit, bool kCount, bool kFloatNodes = false, class Stack>
 PT_D bool traverse(const Bvh& bvh, V3 ro, V3 rd, float tNear, float tFar, Hit& hit, Stack& st,
                    TravCounters* cnt)
 {
     TravRay r;
     travBegin(bvh, r, ro, rd, tNear, tFar, st);
-    while (travStep<kAnyHit, kCount>(bvh, r, st, cnt)) {}
+    if (kFloatNodes && !kCount && bvh.nodesF)
+    {
+        while (travStepF<kAnyHit>(bvh, r, st)) {}
+    }
+    else
+    {
+        while (travStep<kAnyHit, kCount>(bvh, r, st, cnt)) {}
+    }
     hit = r.hit;
     return r.found;
 }

@@ -267,14 +267,17 @@ __global__ void k_wfAfterRegen(PoolView P)
 }
 
 // K3'
-__global__ void __launch_bounds__(kTravThreads) k_wfExtend(DScene S, PoolView P)
+#ifndef PT_TRAV_BLOCKS
+#define PT_TRAV_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(kTravThreads, PT_TRAV_BLOCKS) k_wfExtend(DScene S, PoolView P)
 {
     PT_DECLARE_STACK(st);
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= P.counters[Wf_NumA]) return;
     F4 o = P.cur.ro[slot], d = P.cur.rd[slot];
     Hit hit;
-    traverse<false, false>(S.bvh, v3(o), v3(d), 0.0f, kRcpEpsilon, hit, st, (TravCounters*)nullptr);
+    traverse<false, false, true>(S.bvh, v3(o), v3(d), 0.0f, kRcpEpsilon, hit, st, (TravCounters*)nullptr);
     U4 h; h.x = f2u(hit.t); h.y = f2u(hit.u); h.z = f2u(hit.v); h.w = (uint32_t)hit.prim;
     P.hit1[slot] = h;
 }
@@ -397,7 +400,7 @@ __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_BLOCKS_A) k_wfShadeA(D
 }
 
 // K4'
-__global__ void __launch_bounds__(kTravThreads) k_wfConnect(DScene S, PoolView P)
+__global__ void __launch_bounds__(kTravThreads, PT_TRAV_BLOCKS) k_wfConnect(DScene S, PoolView P)
 {
     PT_DECLARE_STACK(st);
     // dense over the slots that asked for a ray (shadeA's list is ascending within each CTA's chunk)
@@ -406,7 +409,7 @@ __global__ void __launch_bounds__(kTravThreads) k_wfConnect(DScene S, PoolView P
     const int slot = P.connectList[i];
     F4 o = P.ro2[slot], d = P.rd2[slot];
     Hit hit;
-    traverse<false, false>(S.bvh, v3(o), v3(d), 0.0f, o.w, hit, st, (TravCounters*)nullptr);
+    traverse<false, false, true>(S.bvh, v3(o), v3(d), 0.0f, o.w, hit, st, (TravCounters*)nullptr);
     U4 h; h.x = f2u(hit.t); h.y = f2u(hit.u); h.z = f2u(hit.v); h.w = (uint32_t)hit.prim;
     P.hit2[slot] = h;
 }
