@@ -27,7 +27,9 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHit(DScene S, const F4*
     if (i >= n) return;
     U4 o = ldg128(ro + i), d = ldg128(rd + i);
     V3 dir = v3(u2f(d.x), u2f(d.y), u2f(d.z));
-    RayHit h = intersectLocal(S, v3(u2f(o.x), u2f(o.y), u2f(o.z)), dir, tNear, u2f(d.w), st);
+    Hit th;
+    traverse<false, false, true>(S.bvh, v3(u2f(o.x), u2f(o.y), u2f(o.z)), dir, tNear, u2f(d.w), th, st, (TravCounters*)nullptr);
+    RayHit h = finishHit(S, dir, th);
     // PtRayHit is 48 bytes: three 128-bit stores
     U4* dst = reinterpret_cast<U4*>(out + i);
     U4 a; a.x = f2u(h.w); a.y = f2u(h.u); a.z = f2u(h.v); a.w = f2u(h.t);
@@ -96,7 +98,7 @@ __global__ void __launch_bounds__(kTravThreads) k_anyHit(DScene S, const F4* __r
     if (i >= n) return;
     U4 o = ldg128(ro + i), d = ldg128(rd + i);
     Hit hit;
-    bool occ = traverse<true, false>(S.bvh, v3(u2f(o.x), u2f(o.y), u2f(o.z)), v3(u2f(d.x), u2f(d.y), u2f(d.z)),
+    bool occ = traverse<true, false, true>(S.bvh, v3(u2f(o.x), u2f(o.y), u2f(o.z)), v3(u2f(d.x), u2f(d.y), u2f(d.z)),
                                      tNear, u2f(d.w), hit, st, (TravCounters*)nullptr);
     out[i] = occ ? 1 : 0;
 }
