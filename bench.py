@@ -298,7 +298,7 @@ def run_ours(args, rank, world, local_rank):
             "config": {"workload": WORKLOAD, "spp_per_step": spp, "width": WIDTH, "height": HEIGHT,
                        "sharding": "sample index per rank, scene replicated, NCCL reduce of the sums per step",
                        "l2": "256 MB buffer written between timed steps (L2 flush)",
-                       "path_pool_slots": args.pool or (1 << 22)},
+                       "path_pool_slots": args.pool or (1 << 23)},
             "mrays_per_s": value * total_rays / max(counters["paths"], 1),      # all ranks, from rank 0's rays per sample
             "rays_per_sample": total_rays / max(counters["paths"], 1),
             "gpu_launches": int(counters["kernelLaunches"]),

@@ -363,13 +363,13 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
     }
 
     phase(3);
-    // wavefront pool: 4 M slots x 324 B = 1.36 GB. Measured on cornell 1080p (Msamples/s): 128 K 599,
-    // 512 K 1030, 1 M 1213, 2 M 1344, 4 M 1401, 8 M 1389 - the state streams through HBM fully
-    // coalesced either way, and fewer, larger iterations amortise launches and the drain at the
+    // wavefront pool: 8 M slots x 324 B = 2.7 GB. Measured on cornell 1080p, 64 spp per call (Msamples/s):
+    // 2 M 2161, 4 M 2336, 6 M 2392, 8 M 2424, 12 M 2427, 16 M 2418, 24 M 2407 - the state streams through
+    // HBM fully coalesced either way, and fewer, larger iterations amortise launches and the drain at the
     // end of a call. Calls with less work than slots run a correspondingly smaller range.
     if (ok)
     {
-        int32_t cap = s->config.pathPoolSize > 0 ? s->config.pathPoolSize : (1 << 22);
+        int32_t cap = s->config.pathPoolSize > 0 ? s->config.pathPoolSize : (1 << 23);
         cap = (cap + 255) & ~255;
         ok = poolAlloc(s->pool, cap);
     }
