@@ -72,7 +72,10 @@ struct Hit
     V3 ng;          // unnormalised (v1-v0)x(v2-v0), only valid on a hit
 };
 
-constexpr int kLeafMaxTris = 3;
+#ifndef PT_LEAF_MAX_TRIS
+#define PT_LEAF_MAX_TRIS 3
+#endif
+constexpr int kLeafMaxTris = PT_LEAF_MAX_TRIS;
 constexpr uint32_t kMetaInternal = 0xffu;
 
 // ---------------------------------------------------------------- build math
