@@ -363,6 +363,14 @@ int32_t Pt_BakeSky(Cubemap* cm, const SkyMedium* sky, pim_float3 sunDir, float s
 int32_t Pt_Tonemap(const pim_float4* light, int64_t count, float exposure, uint32_t seed, uint32_t pass,
                    uint32_t* rgba8Out);
 
+/* CreateRomeTexture's texel loop (static in src/rendering/gltf_model.c:1118-1139): resamples the
+ * glTF metallic-roughness, occlusion and emission images (host float4, each of its own size; pass a
+ * 1x1 default where the material has none: (0, 0.5, 0, 0), (1, 0, 0, 0), (0, 0, 0, 0)) onto one
+ * size x size RGBA8 "ROME" texture (roughness, occlusion, metallic, packed emission) in
+ * romeOut[size*size]. `size` is the reference's NextPow2(max side), at most 2048. 0 on success. */
+int32_t Pt_RepackRome(const pim_float4* metallicRoughness, pim_int2 mrSize, const pim_float4* occlusion, pim_int2 occSize,
+                      const pim_float4* emission, pim_int2 emSize, int32_t size, uint32_t* romeOut);
+
 /* ---- introspection ----------------------------------------------------------- */
 typedef struct PtSceneStats_s
 {

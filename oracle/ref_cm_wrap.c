@@ -28,6 +28,8 @@
 #include "math/ambcube.h"
 #include "math/atmosphere.h"
 #include "math/color.h"
+#include "rendering/texture.h"
+#include "rendering/sampler.h"
 #include "ref_harness.h"
 
 /* layout of one cubemap handed across the harness: color = 6 faces of size*size float3,
@@ -140,5 +142,42 @@ void oracle_tonemap(const float* light4, int count, float exposure, uint32_t pas
     t.light = (const float4*)light4; t.color = (R8G8B8A8_t*)rgba8; t.exposure = exposure;
     oracle_begin(ORACLE_STREAM_TONEMAP, pass);
     Task_Run(&t.task, ToneFn, count);
+    oracle_frame_end();
+}
+
+/* CreateRomeTexture's texel loop (src/rendering/gltf_model.c:1118-1139; the file itself needs cgltf and
+ * stb_image and does not compile here), restated around the reference's own UvBilinearClamp_f4
+ * (sampler.h:327-331), PackEmission (color.h:582-586) and f4_rgba8 (color.h:102-112). */
+typedef struct RomeTask { Task task; Texture mr, occ, em; i32 size; R8G8B8A8_t* dst; } RomeTask;
+static void RomeFn(void* p, i32 begin, i32 end)
+{
+    RomeTask* t = (RomeTask*)p;
+    const i32 size = t->size;
+    const float rcpSize = 1.0f / (size - 1);
+    for (i32 index = begin; index < end; ++index)
+    {
+        i32 x = index % size, y = index / size;
+        float2 uv = { x * rcpSize, y * rcpSize };
+        float4 rome = f4_0;
+        {
+            float4 mr = UvBilinearClamp_f4(t->mr.texels, t->mr.size, uv);
+            rome.x = mr.y;
+            rome.z = mr.x;
+        }
+        rome.y = UvBilinearClamp_f4(t->occ.texels, t->occ.size, uv).x;
+        rome.w = PackEmission(UvBilinearClamp_f4(t->em.texels, t->em.size, uv));
+        t->dst[index] = f4_rgba8(rome);
+    }
+}
+void oracle_repack_rome(const float* mr4, int mrW, int mrH, const float* occ4, int occW, int occH,
+                        const float* em4, int emW, int emH, int size, uint32_t* rgba8)
+{
+    RomeTask t; memset(&t, 0, sizeof(t));
+    t.mr.texels = (void*)mr4; t.mr.size = i2_v(mrW, mrH);
+    t.occ.texels = (void*)occ4; t.occ.size = i2_v(occW, occH);
+    t.em.texels = (void*)em4; t.em.size = i2_v(emW, emH);
+    t.size = size; t.dst = (R8G8B8A8_t*)rgba8;
+    oracle_begin(ORACLE_STREAM_SKY, 1);
+    Task_Run(&t.task, RomeFn, size * size);
     oracle_frame_end();
 }

@@ -136,6 +136,8 @@ void oracle_cubemap_convolve(int size, float* color, float* convolved, uint32_t 
 int oracle_ambcube_bake(void* scene, float* cube24, const float* origin4, int samples, int prevSampleCount, uint32_t pass);
 void oracle_bake_sky(int size, float* color, const float* sky9, const float* sunDir3, float sunLum, int steps);
 void oracle_tonemap(const float* light4, int count, float exposure, uint32_t pass, uint32_t* rgba8);
+void oracle_repack_rome(const float* mr4, int mrW, int mrH, const float* occ4, int occW, int occH,
+                        const float* em4, int emW, int emH, int size, uint32_t* rgba8);
 
 /* known-answer vectors of the 8(a) helpers (ref_kat.c) */
 int oracle_kat_count(void);

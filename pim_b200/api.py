@@ -145,6 +145,7 @@ EXPORTS = [
     "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
     "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap", "LmPack_EmbedDesc",
     "LmPack_BakeDesc_Device", "PtMediaParams_Default", "PtScene_SetMedia",
+    "Pt_RepackRome",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -218,6 +219,8 @@ def load():
     L.LmPack_EmbedDesc.argtypes = [C.POINTER(PtEmbedMesh), C.c_int32, C.POINTER(PtLightmapDesc), vp, C.c_int32]
     L.LmPack_EmbedDesc.restype = C.c_int32
     L.LmPack_BakeDesc_Device.argtypes = L.LmPack_BakeDesc.argtypes
+    L.Pt_RepackRome.argtypes = [vp, Int2, vp, Int2, vp, Int2, C.c_int32, vp]
+    L.Pt_RepackRome.restype = C.c_int32
     L.PtMediaParams_Default.argtypes = [C.POINTER(PtMediaParams)]
     L.PtScene_SetMedia.argtypes = [vp, C.POINTER(PtMediaParams)]
     L.PtScene_SetMedia.restype = C.c_int32
@@ -589,4 +592,16 @@ def lm_embed(meshes, slot_indices, size):
             position.ctypes.data, normal.ctypes.data, counts.ctypes.data, size)
         out.append((position, normal, counts))
     _check(load().LmPack_EmbedDesc(arr, len(meshes), pages, slots.ctypes.data, len(slots)), "LmPack_EmbedDesc")
+    return out
+
+
+def repack_rome(mr, occ, em, size):
+    """Pt_RepackRome: float4 images [h, w, 4] (metallic-roughness, occlusion, emission) -> RGBA8 ROME texture
+    [size*size] (uint32, roughness in the low byte)."""
+    imgs = [np.ascontiguousarray(t, np.float32) for t in (mr, occ, em)]
+    out = np.zeros(size * size, np.uint32)
+    args = []
+    for t in imgs:
+        args += [t.ctypes.data, Int2(t.shape[1], t.shape[0])]
+    _check(load().Pt_RepackRome(*args, size, out.ctypes.data), "Pt_RepackRome")
     return out

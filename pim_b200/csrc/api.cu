@@ -1143,6 +1143,33 @@ int32_t Pt_Tonemap(const pim_float4* light, int64_t count, float exposure, uint3
     return ok ? 0 : -1;
 }
 
+int32_t Pt_RepackRome(const pim_float4* mr, pim_int2 mrSize, const pim_float4* occ, pim_int2 occSize, const pim_float4* em,
+                      pim_int2 emSize, int32_t size, uint32_t* romeOut)
+{
+    if (!ensureInit()) return -1;
+    if (!mr || !occ || !em || !romeOut || size <= 0 || mrSize.x <= 0 || mrSize.y <= 0 || occSize.x <= 0 || occSize.y <= 0 ||
+        emSize.x <= 0 || emSize.y <= 0)
+    {
+        setError("Pt_RepackRome: null or empty argument");
+        return -1;
+    }
+    const size_t nMr = (size_t)mrSize.x * mrSize.y, nOcc = (size_t)occSize.x * occSize.y, nEm = (size_t)emSize.x * emSize.y;
+    const size_t n = (size_t)size * size;
+    DevBuf dMr, dOcc, dEm, dOut;
+    if (!dMr.alloc(16 * nMr) || !dOcc.alloc(16 * nOcc) || !dEm.alloc(16 * nEm) || !dOut.alloc(4 * n)) return -1;
+    cudaStream_t st = nullptr;
+    bool ok = PT_CUDA(cudaMemcpyAsync(dMr.p, mr, 16 * nMr, cudaMemcpyHostToDevice, st)) &&
+              PT_CUDA(cudaMemcpyAsync(dOcc.p, occ, 16 * nOcc, cudaMemcpyHostToDevice, st)) &&
+              PT_CUDA(cudaMemcpyAsync(dEm.p, em, 16 * nEm, cudaMemcpyHostToDevice, st));
+    KernelTimer timer(st);
+    ok = ok && launchRepackRome((const F4*)dMr.p, mrSize.x, mrSize.y, (const F4*)dOcc.p, occSize.x, occSize.y, (const F4*)dEm.p,
+                                emSize.x, emSize.y, size, (uint32_t*)dOut.p, st);
+    timer.stop();
+    ok = ok && PT_CUDA(cudaMemcpyAsync(romeOut, dOut.p, 4 * n, cudaMemcpyDeviceToHost, st));
+    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    return ok ? 0 : -1;
+}
+
 int32_t PtScene_GetStats(const PtScene* scene, PtSceneStats* stats)
 {
     if (!scene || !stats) return -1;

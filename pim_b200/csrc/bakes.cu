@@ -391,6 +391,33 @@ __global__ void __launch_bounds__(256) k_embedResolve(const EmbedMesh M, const u
     normal3[3 * i] = nor.x; normal3[3 * i + 1] = nor.y; normal3[3 * i + 2] = nor.z;
 }
 
+// CreateRomeTexture's texel loop (src/rendering/gltf_model.c:1118-1139): the glTF metallic-roughness,
+// occlusion and emission images, each already float4 and of its own size, resampled onto one
+// size x size RGBA8 texture: R roughness (mr.y), O occlusion (occ.x), M metallic (mr.x), E packed emission.
+__device__ __forceinline__ F4 bilinearClampF4(const F4* __restrict__ tex, int w, int h, V2 uv)
+{
+    const Bilinear bi = BilinearClamp(w, h, uv);
+    return f4_bilerp(tex[bi.a], tex[bi.b], tex[bi.c], tex[bi.d], bi.fx, bi.fy);
+}
+__global__ void __launch_bounds__(256) k_repackRome(const F4* __restrict__ mr, int mrW, int mrH, const F4* __restrict__ occ, int occW,
+                                                    int occH, const F4* __restrict__ em, int emW, int emH, int size,
+                                                    uint32_t* __restrict__ dst)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= size * size) return;
+    const float rcpSize = 1.0f / (size - 1);
+    const V2 uv = v2((i % size) * rcpSize, (i / size) * rcpSize);
+    const F4 m = bilinearClampF4(mr, mrW, mrH, uv);
+    const float o = bilinearClampF4(occ, occW, occH, uv).x;
+    const F4 e = bilinearClampF4(em, emW, emH, uv);
+    // PackEmission (src/math/color.h:582-586)
+    const float pe = f1_sat(fmaxf(e.x, fmaxf(e.y, e.z)) * (1.0f / kEmissionScale));
+    const float w = (pe > kEpsilon) ? sqrtf(pe) : 0.0f;
+    const uint32_t r = (uint32_t)(f1_sat(m.y) * 255.0f + 0.5f), g = (uint32_t)(f1_sat(o) * 255.0f + 0.5f);
+    const uint32_t b = (uint32_t)(f1_sat(m.x) * 255.0f + 0.5f), a = (uint32_t)(f1_sat(w) * 255.0f + 0.5f);
+    dst[i] = r | (g << 8) | (b << 16) | (a << 24);         // f4_rgba8
+}
+
 } // namespace
 
 int cubemapMipCount(int size)       // CalcMipCount, sampler.h:23-26
@@ -453,6 +480,15 @@ bool launchTonemap(const F4* dLight, int64_t n, float exposure, uint32_t pass, u
 {
     if (n <= 0) return true;
     k_tonemap<<<gridFor(n, 256), 256, 0, stream>>>(dLight, n, exposure, pass, seed, dRgba8);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+bool launchRepackRome(const F4* dMr, int mrW, int mrH, const F4* dOcc, int occW, int occH, const F4* dEm, int emW, int emH,
+                      int size, uint32_t* dDst, cudaStream_t stream)
+{
+    if (size <= 0) return true;
+    k_repackRome<<<gridFor((int64_t)size * size, 256), 256, 0, stream>>>(dMr, mrW, mrH, dOcc, occW, occH, dEm, emW, emH, size, dDst);
     g_counters.kernelLaunches++;
     return PT_CUDA(cudaGetLastError());
 }

@@ -115,6 +115,8 @@ struct EmbedMesh
 };
 bool launchEmbed(const EmbedMesh& mesh, int lmSize, int lmCount, unsigned long long* dKeys,
                  float* dPosition3, float* dNormal3, float* dSampleCounts, cudaStream_t stream);
+bool launchRepackRome(const F4* dMr, int mrW, int mrH, const F4* dOcc, int occW, int occH, const F4* dEm, int emW, int emH,
+                      int size, uint32_t* dDst, cudaStream_t stream);
 bool launchTonemap(const F4* dLight, int64_t n, float exposure, uint32_t pass, uint32_t seed, uint32_t* dRgba8,
                    cudaStream_t stream);
 

@@ -257,6 +257,19 @@ def tonemap(light, exposure=1.0, pass_index=0):
     return out
 
 
+def repack_rome(mr, occ, em, size):
+    """CreateRomeTexture's texel loop (gltf_model.c:1118-1139) over float4 images [h, w, 4]"""
+    L = lib()
+    L.oracle_repack_rome.argtypes = [f32p, C.c_int, C.c_int, f32p, C.c_int, C.c_int, f32p, C.c_int, C.c_int, C.c_int, u32p]
+    imgs = [np.ascontiguousarray(t, np.float32) for t in (mr, occ, em)]
+    out = np.zeros(size * size, np.uint32)
+    args = []
+    for t in imgs:
+        args += [_ptr(t), t.shape[1], t.shape[0]]
+    L.oracle_repack_rome(*args, size, _ptr(out, u32p))
+    return out
+
+
 def default_dof():
     d = Dof()
     lib().oracle_dof_default(C.byref(d))

@@ -193,3 +193,25 @@ def test_lightmap_embed_edge_cases(api):
     degenerate = uv.copy(); degenerate[:, 2:] = 0.5
     d = api.lm_embed([(pos, nrm, degenerate, tex, 0)], [7], 16)
     assert 4 <= d[0][2].sum() <= 49
+
+
+def test_rome_repack_matches_reference(api, oracle):
+    """Pt_RepackRome (CreateRomeTexture's loop, gltf_model.c:1118-1139): three float4 images of different
+    sizes onto one RGBA8 texture; every channel within one code value, 99 % equal; 1x1 defaults work"""
+    g = np.random.default_rng(11)
+    mr = g.uniform(0, 1, (48, 64, 4)).astype(np.float32)
+    occ = g.uniform(0, 1, (16, 16, 4)).astype(np.float32)
+    em = (g.uniform(0, 1, (32, 8, 4)) * np.array([150.0, 80.0, 20.0, 0.0])).astype(np.float32)
+    em[:8] = 0.0                                       # no emission: packs to exactly 0
+    for size in (64, 256):
+        got = api.repack_rome(mr, occ, em, size).view(np.uint8).reshape(-1, 4).astype(np.int32)
+        want = oracle.repack_rome(mr, occ, em, size).view(np.uint8).reshape(-1, 4).astype(np.int32)
+        d = np.abs(got - want)
+        assert d.max() <= 1 and (d == 0).mean() > 0.99
+        assert want[:, 3].max() > 200 and (want[:size, 3] == 0).all()
+    d_mr = np.array([[[0.0, 0.5, 0.0, 0.0]]], np.float32); d_occ = np.array([[[1.0, 0, 0, 0]]], np.float32)
+    d_em = np.zeros((1, 1, 4), np.float32)
+    got = api.repack_rome(d_mr, d_occ, d_em, 4).view(np.uint8).reshape(-1, 4)
+    assert (got == np.array([128, 255, 0, 0], np.uint8)).all()
+    assert (got == oracle.repack_rome(d_mr, d_occ, d_em, 4).view(np.uint8).reshape(-1, 4)).all()
+    assert api.load().Pt_RepackRome(None, api.Int2(1, 1), None, api.Int2(1, 1), None, api.Int2(1, 1), 4, None) == -1
