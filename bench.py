@@ -287,10 +287,18 @@ def run_ours(args, rank, world, local_rank):
         sample_gbs = value * 1e6 / world * b_sample / 1e9
         # measured DRAM bytes per ray of k_wfExtend from the committed ncu capture (path state in, hit out)
         traffic = None
+        l2 = None
         tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
         if os.path.exists(tpath):
             with open(tpath) as f:
-                traffic = json.load(f)["k_wfExtend"]["dram_bytes_per_ray"] * rays_per_launch
+                tj = json.load(f)
+            traffic = tj["k_wfExtend"]["dram_bytes_per_ray"] * rays_per_launch
+            if "l2_bytes_per_ray" in tj["k_wfExtend"] and "l2_copy_peak_gbs" in tj:
+                # the tree is cache resident: the kernel's L2 traffic (ncu capture) at this run's ray rate
+                # against the L2-resident copy rate measured with tools/l2peak.py
+                l2_gbs = tj["k_wfExtend"]["l2_bytes_per_ray"] * rays_per_launch / avg_s / 1e9
+                l2 = {"achieved": l2_gbs, "peak": tj["l2_copy_peak_gbs"], "unit": "GB/s", "frac": l2_gbs / tj["l2_copy_peak_gbs"],
+                      "bytes_per_ray": tj["k_wfExtend"]["l2_bytes_per_ray"], "source": "profiles/r01_traffic.json"}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
@@ -307,7 +315,7 @@ def run_ours(args, rank, world, local_rank):
             "roofline": {"bound": "hbm", "kernel": "k_wfExtend", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "bytes_per_ray": b_ray, "rays_per_launch": rays_per_launch,
-                         "avg_launch_ms": avg_s * 1e3,
+                         "avg_launch_ms": avg_s * 1e3, "l2": l2,
                          "note": "108-triangle BVH is L1/L2 resident: algorithmic bytes never reach HBM, "
                                  "so frac can exceed 1 (SURVEY.md 8(d))"},
             "roofline_sample": {"bound": "hbm", "bytes_per_sample": b_sample, "bounces_per_path": bounces,
