@@ -38,6 +38,14 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHit(DScene S, const F4*
     dst[0] = a; dst[1] = b; dst[2] = c;
 }
 
+#ifndef PT_POSTPONED_LEAVES
+#define PT_POSTPONED_LEAVES 1
+#endif
+#ifndef PT_LEAF_VOTES
+#define PT_LEAF_VOTES 12
+#endif
+constexpr int kLeafVotes = PT_LEAF_VOTES;
+
 // persistent form: warps refill finished lanes with the next rays of the batch (one atomic per warp)
 __global__ void __launch_bounds__(kTravThreads) k_closestHitPersistent(DScene S, const F4* __restrict__ ro,
                                                                         const F4* __restrict__ rd, float tNear,
@@ -76,7 +84,21 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHitPersistent(DScene S,
             if (exhausted) break;
             continue;
         }
+#if PT_POSTPONED_LEAVES
+        // lanes holding a popped leaf wait; the others take a node step; once kLeafVotes lanes wait (or
+        // nobody can take a node step) the waiting lanes test their triangles side by side
+        const bool waiting = busy && r.pendCount != 0u;
+        const unsigned waitMask = __ballot_sync(0xffffffffu, waiting);
+        const unsigned nodeMask = __ballot_sync(0xffffffffu, busy && !waiting);
+        if (__popc(waitMask) >= kLeafVotes || nodeMask == 0u)
+        {
+            if (waiting) travLeafStepP(S.bvh, r);
+            continue;
+        }
+        if (busy && !waiting && !travNodeStepP(S.bvh, r, st))
+#else
         if (busy && !travStep<false, false>(S.bvh, r, st, (TravCounters*)nullptr))
+#endif
         {
             RayHit h = finishHit(S, r.rd, r.hit);
             U4* dst = reinterpret_cast<U4*>(out + idx);

@@ -17,21 +17,23 @@ struct TravStack
     unsigned long long* base;
     int stride;
     int sp;
-    unsigned long long spill[40];
+    // 7 pushes per wide node at most; postponed leaves (below) put leaf children here as well
+    static constexpr int kSpillDepth = 72;
+    unsigned long long spill[kSpillDepth];
 
     PT_D void init(unsigned long long* b, int s) { base = b; stride = s; sp = 0; }
     PT_D void push(uint32_t node, uint32_t key)
     {
         unsigned long long e = ((unsigned long long)key << 32) | node;
         if (sp < kSharedDepth) base[sp * stride] = e;
-        else if (sp - kSharedDepth < 40) spill[sp - kSharedDepth] = e;
+        else if (sp - kSharedDepth < kSpillDepth) spill[sp - kSharedDepth] = e;
         ++sp;
     }
     PT_D unsigned long long pop()
     {
         --sp;
         if (sp < kSharedDepth) return base[sp * stride];
-        return (sp - kSharedDepth < 40) ? spill[sp - kSharedDepth] : 0ull;
+        return (sp - kSharedDepth < kSpillDepth) ? spill[sp - kSharedDepth] : 0ull;
     }
 };
 
@@ -74,6 +76,7 @@ struct TravRay
     uint32_t bestPrim;
     uint32_t cur;
     bool haveCur, found, negx, negy, negz;
+    uint32_t pendFirst, pendCount;      // a popped leaf waiting for its triangle tests (travNodeStepP)
     Hit hit;
 };
 
@@ -92,6 +95,7 @@ PT_D void travBegin(const Bvh& bvh, TravRay& r, V3 ro, V3 rd, float tNear, float
     r.bestPrim = 0xffffffffu;
     r.cur = 0;
     r.haveCur = bvh.nodeCount > 0;
+    r.pendFirst = 0u; r.pendCount = 0u;
     st.sp = 0;
 }
 
@@ -349,6 +353,133 @@ PT_D bool travStepF(const Bvh& bvh, TravRay& r, Stack& st)
         }
     }
     return r.haveCur || st.sp != 0;
+}
+
+// ---- postponed leaves (the persistent kernels, large incoherent trees) ------------------------
+// In travStep a lane tests the triangles of a node's leaf children on the spot, while the other
+// lanes of the warp wait: on the 10 M-triangle soup 2.3 of 32 lanes were inside a triangle test
+// at any time, for a third of all instructions. Here leaf children go onto the stack like inner
+// children (node field: kLeafEntry | count << 28 | first triangle); a lane that pops one only
+// records it (TravRay::pendCount) and stops taking node steps. The kernel lets the other lanes go
+// on and runs travLeafStepP for the waiting ones once enough of them wait (Aila and Laine's
+// postponed leaves), so triangle tests execute with many lanes side by side. Children are pushed
+// nearest-last but otherwise unsorted: popping culls by distance anyway, and the sort loop ran with
+// 2.8 lanes. Results are those of travStep: the closest hit does not depend on the visiting order,
+// ties go to the lowest primitive id.
+constexpr uint32_t kLeafEntry = 0x80000000u;
+
+// the triangles of the pending leaf
+PT_D void travLeafStepP(const Bvh& bvh, TravRay& r)
+{
+    const uint32_t first = r.pendFirst, count = r.pendCount;
+    r.pendCount = 0u;
+    for (uint32_t j = 0; j < count; ++j)
+    {
+        float t, u, v; uint32_t prim; V3 ng;
+        if (triTest(bvh.tris + first + j, r.ro, r.rd, r.tNear, r.tBest, t, u, v, prim, ng))
+        {
+            if (!r.found || t < r.tBest || prim < r.bestPrim)
+            {
+                r.found = true;
+                r.tBest = t; r.bestPrim = prim;
+                r.hit.t = t; r.hit.u = u; r.hit.v = v; r.hit.prim = (int32_t)prim; r.hit.ng = ng;
+            }
+        }
+    }
+}
+
+// one node step; returns false when the ray is finished (stack empty, nothing pending)
+template <class Stack>
+PT_D bool travNodeStepP(const Bvh& bvh, TravRay& r, Stack& st)
+{
+    while (!r.haveCur)
+    {
+        if (st.sp == 0) return false;
+        unsigned long long e = st.pop();
+        uint32_t key = (uint32_t)(e >> 32);
+        if (u2f((key - 8u) & ~7u) > r.tBest) continue;
+        const uint32_t id = (uint32_t)e;
+        if (id & kLeafEntry) { r.pendFirst = id & 0x0fffffffu; r.pendCount = (id >> 28) & 7u; return true; }
+        r.cur = id;
+        r.haveCur = true;
+    }
+    r.haveCur = false;
+
+    const WideNode* np = bvh.nodes + r.cur;
+    const U4 n0 = ldg128(&np->ox);
+    const U4 n1 = ldg128(&np->childBase);
+    const U4 n2 = ldg128(&np->qlox[0]);
+    const U4 n3 = ldg128(&np->qloz[0]);
+    const U4 n4 = ldg128(&np->qhiy[0]);
+    const uint32_t imask = n0.w >> 24;
+    const float sx = u2f((n0.w & 0xffu) << 23) * r.idir.x;
+    const float sy = u2f(((n0.w >> 8) & 0xffu) << 23) * r.idir.y;
+    const float sz = u2f(((n0.w >> 16) & 0xffu) << 23) * r.idir.z;
+    const float bx = (u2f(n0.x) - r.ro.x) * r.idir.x;
+    const float by = (u2f(n0.y) - r.ro.y) * r.idir.y;
+    const float bz = (u2f(n0.z) - r.ro.z) * r.idir.z;
+    uint32_t nxw[2], fxw[2], nyw[2], fyw[2], nzw[2], fzw[2];
+    nxw[0] = r.negx ? n3.z : n2.x; nxw[1] = r.negx ? n3.w : n2.y;
+    fxw[0] = r.negx ? n2.x : n3.z; fxw[1] = r.negx ? n2.y : n3.w;
+    nyw[0] = r.negy ? n4.x : n2.z; nyw[1] = r.negy ? n4.y : n2.w;
+    fyw[0] = r.negy ? n2.z : n4.x; fyw[1] = r.negy ? n2.w : n4.y;
+    nzw[0] = r.negz ? n4.z : n3.x; nzw[1] = r.negz ? n4.w : n3.y;
+    fzw[0] = r.negz ? n3.x : n4.z; fzw[1] = r.negz ? n3.y : n4.w;
+    const uint32_t metaw[2] = { n1.z, n1.w };
+
+    uint32_t keys[8];
+    uint32_t hitMask = 0;
+    uint32_t nearest = 0xffffffffu;
+#if defined(__CUDA_ARCH__)
+    #pragma unroll
+#endif
+    for (int i = 0; i < 8; ++i)
+    {
+        const int w = i >> 2;
+        float tnx = byteToFloat(nxw[w], i & 3) * sx + bx;
+        float tfx = byteToFloat(fxw[w], i & 3) * sx + bx;
+        float tny = byteToFloat(nyw[w], i & 3) * sy + by;
+        float tfy = byteToFloat(fyw[w], i & 3) * sy + by;
+        float tnz = byteToFloat(nzw[w], i & 3) * sz + bz;
+        float tfz = byteToFloat(fzw[w], i & 3) * sz + bz;
+        float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tNear));
+        float tmax = fminf(fminf(tfx, tfy), fminf(tfz, r.tBest));
+        bool h = tmin <= tmax * 1.0000004f;
+        // a leaf slot with no triangles (an empty slot let through by the slack) is dropped here
+        const uint32_t m = (metaw[w] >> (8 * (i & 3))) & 0xffu;
+        h = h && (((imask >> i) & 1u) || (m >> 5) != 0u);
+        keys[i] = h ? (((f2u(tmin) & ~7u) | (uint32_t)i) + 8u) : 0xffffffffu;
+        nearest = keys[i] < nearest ? keys[i] : nearest;
+        hitMask |= h ? (1u << i) : 0u;
+    }
+    if (hitMask == 0u) return r.haveCur || st.sp != 0;
+
+    // stack id of child i: inner node index, or a leaf entry
+    auto childId = [&](int i) -> uint32_t
+    {
+        if ((imask >> i) & 1u) return n1.x + (uint32_t)popc32(imask & ((1u << i) - 1u));
+        const uint32_t m = (metaw[i >> 2] >> (8 * (i & 3))) & 0xffu;
+        return kLeafEntry | ((m >> 5) << 28) | (n1.y + (m & 31u));
+    };
+    // every hit child but the nearest goes onto the stack (unrolled and predicated: all lanes in step);
+    // the nearest becomes the current node, or the pending leaf
+    const uint32_t rest = hitMask & ~(1u << ((nearest - 8u) & 7u));
+    uint32_t idNear = 0u;
+#if defined(__CUDA_ARCH__)
+    #pragma unroll
+#endif
+    for (int i = 0; i < 8; ++i)
+    {
+        if ((hitMask >> i) & 1u)
+        {
+            const uint32_t id = childId(i);
+            if ((rest >> i) & 1u) st.push(id, keys[i]);
+            else idNear = id;
+        }
+    }
+    if (idNear & kLeafEntry) { r.pendFirst = idNear & 0x0fffffffu; r.pendCount = (idNear >> 28) & 7u; }
+    else { r.cur = idNear; r.haveCur = true; }
+    return true;
 }
 
 // kFloatNodes: take the fp32 node form when the tree has one. Only the two wavefront traversal

@@ -291,6 +291,10 @@ __global__ void __launch_bounds__(kTravThreads, PT_TRAV_BLOCKS) k_wfExtend(DScen
 #endif
 constexpr int kRefillLanes = PT_REFILL_LANES;
 constexpr int kPersistentBlocksPerSm = 12;
+#ifndef PT_LEAF_VOTES
+#define PT_LEAF_VOTES 12
+#endif
+constexpr int kLeafVotes = PT_LEAF_VOTES;
 
 template <bool kConnect>
 __global__ void __launch_bounds__(kTravThreads) k_wfTracePersistent(DScene S, PoolView P)
@@ -331,7 +335,17 @@ __global__ void __launch_bounds__(kTravThreads) k_wfTracePersistent(DScene S, Po
             if (exhausted) break;
             continue;
         }
-        if (busy && !travStep<false, false>(S.bvh, r, st, (TravCounters*)nullptr))
+        // postponed leaves (traverse.h): lanes holding a popped leaf wait while the others take node steps;
+        // the triangles are tested once kLeafVotes lanes wait or nobody can take a node step
+        const bool waiting = busy && r.pendCount != 0u;
+        const unsigned waitMask = __ballot_sync(0xffffffffu, waiting);
+        const unsigned nodeMask = __ballot_sync(0xffffffffu, busy && !waiting);
+        if (__popc(waitMask) >= kLeafVotes || nodeMask == 0u)
+        {
+            if (waiting) travLeafStepP(S.bvh, r);
+            continue;
+        }
+        if (busy && !waiting && !travNodeStepP(S.bvh, r, st))
         {
             U4 h; h.x = f2u(r.hit.t); h.y = f2u(r.hit.u); h.z = f2u(r.hit.v); h.w = (uint32_t)r.hit.prim;
             if (kConnect) P.hit2[slot] = h; else P.hit1[slot] = h;
