@@ -125,6 +125,61 @@ __global__ void __launch_bounds__(kTravThreads) k_anyHit(DScene S, const F4* __r
     out[i] = occ ? 1 : 0;
 }
 
+// any hit on large trees: persistent warps with postponed leaves; a ray stops at its first hit
+__global__ void __launch_bounds__(kTravThreads) k_anyHitPersistent(DScene S, const F4* __restrict__ ro,
+                                                                    const F4* __restrict__ rd, float tNear,
+                                                                    uint8_t* __restrict__ out, int64_t n,
+                                                                    unsigned long long* cursor)
+{
+    PT_DECLARE_STACK(st);
+    const int lane = threadIdx.x & 31;
+    const uint32_t ltMask = (1u << lane) - 1u;
+    TravRay r;
+    bool busy = false, exhausted = false;
+    long long idx = -1;
+    for (;;)
+    {
+        const unsigned idle = __ballot_sync(0xffffffffu, !busy);
+        if (!exhausted && __popc(idle) >= 8)
+        {
+            const int leader = __ffs((int)idle) - 1;
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(cursor, (unsigned long long)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!busy)
+            {
+                idx = (long long)base + __popc(idle & ltMask);
+                if (idx < n)
+                {
+                    U4 o = ldg128(ro + idx), d = ldg128(rd + idx);
+                    travBegin(S.bvh, r, v3(u2f(o.x), u2f(o.y), u2f(o.z)), v3(u2f(d.x), u2f(d.y), u2f(d.z)), tNear, u2f(d.w), st);
+                    busy = true;
+                }
+            }
+            exhausted = (long long)base + __popc(idle) >= n;
+        }
+        if (__ballot_sync(0xffffffffu, busy) == 0u)
+        {
+            if (exhausted) break;
+            continue;
+        }
+        const bool waiting = busy && r.pendCount != 0u;
+        const unsigned waitMask = __ballot_sync(0xffffffffu, waiting);
+        const unsigned nodeMask = __ballot_sync(0xffffffffu, busy && !waiting);
+        bool done = false;
+        if (__popc(waitMask) >= kLeafVotes || nodeMask == 0u)
+        {
+            if (waiting) { travLeafStepP<true>(S.bvh, r); done = r.found; }
+        }
+        else if (busy && !waiting) done = !travNodeStepP(S.bvh, r, st);
+        if (done)
+        {
+            out[idx] = r.found ? 1 : 0;
+            busy = false;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kTravThreads) k_closestHitCount(DScene S, const F4* __restrict__ ro,
                                                                    const F4* __restrict__ rd, float tNear, int64_t n,
                                                                    unsigned long long* totals)
@@ -177,6 +232,15 @@ bool launchOccluded(const DScene& S, const F4* dRo, const F4* dRd, float tNear, 
                     cudaStream_t stream)
 {
     if (n <= 0) return true;
+    if (usePersistent(S.bvh.nodeCount))
+    {
+        static unsigned long long* dCursor = nullptr;
+        if (!dCursor && !PT_CUDA(cudaMalloc((void**)&dCursor, 8))) return false;
+        cudaMemsetAsync(dCursor, 0, 8, stream);
+        const unsigned grid = (unsigned)std::min<int64_t>(gridFor(n, kTravThreads), kSmCount * 12);
+        k_anyHitPersistent<<<grid, kTravThreads, 0, stream>>>(S, dRo, dRd, tNear, dOut, n, dCursor);
+    }
+    else
     k_anyHit<<<gridFor(n, kTravThreads), kTravThreads, 0, stream>>>(S, dRo, dRd, tNear, dOut, n);
     g_counters.kernelLaunches++;
     g_counters.occlusionRays += (unsigned long long)n;

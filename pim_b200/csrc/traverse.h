@@ -369,6 +369,7 @@ PT_D bool travStepF(const Bvh& bvh, TravRay& r, Stack& st)
 constexpr uint32_t kLeafEntry = 0x80000000u;
 
 // the triangles of the pending leaf
+template <bool kAnyHit = false>
 PT_D void travLeafStepP(const Bvh& bvh, TravRay& r)
 {
     const uint32_t first = r.pendFirst, count = r.pendCount;
@@ -378,6 +379,7 @@ PT_D void travLeafStepP(const Bvh& bvh, TravRay& r)
         float t, u, v; uint32_t prim; V3 ng;
         if (triTest(bvh.tris + first + j, r.ro, r.rd, r.tNear, r.tBest, t, u, v, prim, ng))
         {
+            if (kAnyHit) { r.found = true; return; }      // occlusion query: the caller stops the ray
             if (!r.found || t < r.tBest || prim < r.bestPrim)
             {
                 r.found = true;
