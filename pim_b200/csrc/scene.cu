@@ -213,7 +213,7 @@ bool launchIntersect(const DScene& S, const F4* dRo, const F4* dRd, float tNear,
                      cudaStream_t stream)
 {
     if (n <= 0) return true;
-    if (usePersistent(S.bvh.nodeCount))
+    if (usePersistentBatch(S.bvh.nodeCount))
     {
         static unsigned long long* dCursor = nullptr;
         if (!dCursor && !PT_CUDA(cudaMalloc((void**)&dCursor, 8))) return false;
@@ -232,7 +232,7 @@ bool launchOccluded(const DScene& S, const F4* dRo, const F4* dRd, float tNear, 
                     cudaStream_t stream)
 {
     if (n <= 0) return true;
-    if (usePersistent(S.bvh.nodeCount))
+    if (usePersistentBatch(S.bvh.nodeCount))
     {
         static unsigned long long* dCursor = nullptr;
         if (!dCursor && !PT_CUDA(cudaMalloc((void**)&dCursor, 8))) return false;

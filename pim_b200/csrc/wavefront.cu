@@ -44,6 +44,17 @@ bool usePersistent(int32_t bvhNodeCount)
     return bvhNodeCount >= (1 << 20);
 }
 
+// The batch entry points (Pt_IntersectN / Pt_OccludedN) carry rays in the caller's order, usually
+// unrelated ones: there the persistent kernels with postponed leaves win from small trees on
+// (closest / any hit, Mrays/s: cornell spheres, 5 K nodes, 4259 -> 6739 / 5222 -> 9987; 1 M-triangle soup
+// 323 -> 569; only the 19-node cornell boxes lose, 16.9 -> 13.3 G). The wavefront's rays are the paths of
+// neighbouring pixels and keep the higher switch above.
+bool usePersistentBatch(int32_t bvhNodeCount)
+{
+    if (g_persistentTraversal >= 0) return g_persistentTraversal != 0;
+    return bvhNodeCount >= 2048;
+}
+
 namespace {
 
 // shading kernels are latency bound (dependent loads through hit -> vertex -> material ->
