@@ -169,11 +169,20 @@ void PtSys_Init(void);
 void PtSys_Update(void);
 void PtSys_Shutdown(void);
 
-/* PtScene_New(void) builds from the description registered with
- * PtSys_SetSceneDesc (the adapter's stand-in for the engine globals). */
+/* PtScene_New(void) (path_tracer.c:1083-1093) builds from the description registered with
+ * PtSys_SetSceneDesc, the adapter's stand-in for the engine globals the reference reads.
+ * The call copies everything the description points to (entity table, mesh arrays, texels,
+ * sky faces, BRDF table), so the caller may fill it from per-frame memory; NULL clears it.
+ * Registering again is the equivalent of a changed Entities_Get()->modtime: the next
+ * PtScene_Update / Pt_Trace / Pt_RayGen / LmPack_Bake on a scene made by PtScene_New(void)
+ * rebuilds that scene in place (path_tracer.c:1028-1032) before it goes on. Scenes made by
+ * PtScene_NewFromDesc are never rebuilt; that call reads the description's arrays only
+ * until it returns. */
 void PtSys_SetSceneDesc(const PtSceneDesc* desc);
 PtScene* PtScene_New(void);
 PtScene* PtScene_NewFromDesc(const PtSceneDesc* desc);
+/* rebuild if the registered description changed, then relearn the light-grid distributions
+ * (UpdateDists, path_tracer.c:2472-2483) */
 void PtScene_Update(PtScene* scene);
 void PtScene_Del(PtScene* scene);
 void PtScene_Gui(PtScene* scene);   /* no-op */
@@ -198,6 +207,10 @@ int32_t Pt_IntersectN(const PtScene* scene, const pim_float4* ro, const pim_floa
  * RtcOccluded16 (path_tracer.c:524-553). */
 int32_t Pt_OccludedN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd,
                      float tNear, uint8_t* occludedOut, int64_t n);
+/* nearest-surface query: points[i] = (x, y, z, radius); distanceOut[i] = unsigned distance to the
+ * nearest triangle closer than the radius, 8388608 (kRcpEpsilon) when there is none. Replaces
+ * RtcPointQuery / rtcPointQuery (path_tracer.c:597-616, :614), which the light-grid set-up runs per cell. */
+int32_t Pt_PointQueryN(const PtScene* scene, const pim_float4* points, float* distanceOut, int64_t n);
 /* n calls of Pt_TraceRay; path i is seeded from (i, pass, seed). */
 int32_t Pt_TraceRayN(PtScene* scene, const pim_float4* ro, const pim_float4* rd,
                      uint32_t pass, PtResult* resultsOut, int64_t n);
@@ -233,13 +246,15 @@ int32_t Pt_TraceSpp_Device(PtScene* scene, const Camera* camera, PtDofInfo* dof,
  *    same scene, rays and pass.
  *  - n may not exceed PT_NOALLOC_MAX_PATHS; larger batches fail with -1 and a message in
  *    Pt_LastError() — split them, or use Pt_TraceRayN.
+ *  - The scene's device must be the current one; otherwise the call fails with a message.
  *  - The first call on each device looks up the array's device address (with that device
- *    current, as it is for the scene's owner). Make that first call outside any CUDA
- *    stream capture.
+ *    current). Make that first call before any CUDA stream capture begins.
  *  - All calls on a device share the one array. It is not cleared between calls (the call
  *    resets the counters it depends on), so two calls that overlap on the GPU — different
- *    streams, different host threads — corrupt each other. Serialise them.
- *  - Blocking: returns after the stream has drained. */
+ *    streams, different host threads — corrupt each other. Serialise them, first calls
+ *    included.
+ *  - Blocking: every call synchronises the stream several times and returns after it has
+ *    drained. */
 #define PT_NOALLOC_MAX_PATHS 32768
 int32_t Pt_TraceRayN_NoAlloc(PtScene* scene, const void* dRo, const void* dRd, uint32_t pass,
                              void* dColor3, void* dAlbedo3, void* dNormal3, int64_t n, void* stream);
@@ -259,8 +274,20 @@ typedef struct PtLightmapDesc_s
     int32_t size;           /* page is size x size texels */
 } PtLightmapDesc;
 
+/* Only the texels a chart covers (sampleCounts != 0; BakeFn skips the others, lightmap.c:1145)
+ * cross the bus, compacted, each way. */
 int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCount,
                         float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass);
+
+/* LmPack_Bake under the reference's own name and signature (src/rendering/lightmap.h:69, body
+ * lightmap.c:1204-1223; caller render_system.c:198). The reference bakes the engine's global
+ * pack (LmPack_Get(), lightmap.c:136); PtSys_SetLmPack is the adapter's stand-in for that
+ * global: it remembers the pack's pages (the descriptions are copied, the arrays stay the
+ * engine's and must live until the pack is registered again or cleared with NULL / 0) and
+ * pack->texelsPerMeter. LmPack_Bake then runs PtScene_Update and one bake pass over those
+ * pages, spp clamped to >= 1, results written into the engine's arrays before it returns. */
+void PtSys_SetLmPack(const PtLightmapDesc* lightmaps, int32_t lmCount, float texelsPerMeter);
+void LmPack_Bake(PtScene* scene, float timeSlice, int32_t spp);
 /* the same with every pointer of every page in device memory: the pack stays resident between
  * passes (a page is 108 B per texel; over PCIe it costs more than the bake itself) */
 int32_t LmPack_BakeDesc_Device(PtScene* scene, const PtLightmapDesc* lightmaps, int32_t lmCount,
@@ -421,6 +448,13 @@ void Pt_GetKernelStats(PtKernelStats* out);
 /* closest-hit batch that only counts wide-node and triangle fetches (bytes-per-ray bookkeeping) */
 int32_t Pt_IntersectCountN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd, float tNear,
                            int64_t n, uint64_t* nodeFetches, uint64_t* triFetches);
+
+/* Tuning switches, also readable from the environment at PtSys_Init (PIMPT_PERSISTENT, PIMPT_FINISH):
+ *   "persistent"  -1 choose the traversal kernels by BVH size (default), 0 one thread per ray, 1 persistent
+ *                 warps with postponed leaves
+ *   "finish"      live paths below which the tail of a wavefront call finishes in one launch (0 = never)
+ * Results do not depend on either. 0 on success. */
+int32_t Pt_SetOption(const char* name, int32_t value);
 
 const char* Pt_LastError(void);
 

@@ -558,3 +558,237 @@ void cpubvh_intersect_batch(const CpuBvh* bvh, const float* ro4, const float* rd
         *nodes += args[t].nodes; *tris += args[t].tris;
     }
 }
+
+/* ---- fp64 ground truth at scale --------------------------------------------------------------
+ * The all-triangles loop above is O(rays x triangles): fine for a few thousand rays against
+ * 10 M triangles, not for 100 K. f64grid_* is a second ground truth that shares no code or
+ * structure with any BVH: triangles are binned (by their slightly padded boxes) into every cell
+ * of a uniform grid they overlap, a ray walks the cells it crosses in order (3-D DDA in fp64)
+ * and runs the same fp64 Moller-Trumbore on each cell's triangles, stopping once the next cell
+ * starts beyond the closest hit. The tests check it ray for ray against the all-triangles loop
+ * on a subsample before using it as the reference for the rest. */
+
+static int mt_f64(const float* a, const float* b, const float* c, const float ro[3], const float rd[3],
+                  double tnear, double tfar, double* tOut, double* uOut, double* vOut)
+{
+    double e1x = (double)b[0] - a[0], e1y = (double)b[1] - a[1], e1z = (double)b[2] - a[2];
+    double e2x = (double)c[0] - a[0], e2y = (double)c[1] - a[1], e2z = (double)c[2] - a[2];
+    double px = rd[1] * e2z - rd[2] * e2y;
+    double py = rd[2] * e2x - rd[0] * e2z;
+    double pz = rd[0] * e2y - rd[1] * e2x;
+    double det = e1x * px + e1y * py + e1z * pz;
+    if (det == 0.0) return 0;
+    double inv = 1.0 / det;
+    double tx = (double)ro[0] - a[0], ty = (double)ro[1] - a[1], tz = (double)ro[2] - a[2];
+    double u = (tx * px + ty * py + tz * pz) * inv;
+    if (!(u >= 0.0 && u <= 1.0)) return 0;
+    double qx = ty * e1z - tz * e1y;
+    double qy = tz * e1x - tx * e1z;
+    double qz = tx * e1y - ty * e1x;
+    double v = (rd[0] * qx + rd[1] * qy + rd[2] * qz) * inv;
+    if (!(v >= 0.0 && u + v <= 1.0)) return 0;
+    double t = (e2x * qx + e2y * qy + e2z * qz) * inv;
+    if (!(t >= tnear && t <= tfar)) return 0;
+    *tOut = t; *uOut = u; *vOut = v;
+    return 1;
+}
+
+typedef struct F64Grid
+{
+    const float* verts; int stride; int64_t ntris;
+    double lo[3], cell; int n[3];
+    int64_t* start;     /* n[0]*n[1]*n[2] + 1 */
+    int32_t* items;
+} F64Grid;
+
+static void tri_cells(const F64Grid* g, int64_t i, int c0[3], int c1[3])
+{
+    const float* a = g->verts + (size_t)(3 * i + 0) * g->stride;
+    const float* b = g->verts + (size_t)(3 * i + 1) * g->stride;
+    const float* c = g->verts + (size_t)(3 * i + 2) * g->stride;
+    const double pad = 1e-3 * g->cell;
+    for (int k = 0; k < 3; ++k)
+    {
+        double lo = fmin(a[k], fmin(b[k], c[k])) - pad, hi = fmax(a[k], fmax(b[k], c[k])) + pad;
+        int i0 = (int)floor((lo - g->lo[k]) / g->cell), i1 = (int)floor((hi - g->lo[k]) / g->cell);
+        c0[k] = i0 < 0 ? 0 : (i0 >= g->n[k] ? g->n[k] - 1 : i0);
+        c1[k] = i1 < 0 ? 0 : (i1 >= g->n[k] ? g->n[k] - 1 : i1);
+    }
+}
+
+F64Grid* f64grid_build(const float* verts, int stride, int64_t ntris, double cell)
+{
+    F64Grid* g = (F64Grid*)calloc(1, sizeof(F64Grid));
+    g->verts = verts; g->stride = stride; g->ntris = ntris; g->cell = cell;
+    double lo[3] = { DBL_MAX, DBL_MAX, DBL_MAX }, hi[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
+    for (int64_t v = 0; v < 3 * ntris; ++v)
+        for (int k = 0; k < 3; ++k)
+        {
+            double x = verts[(size_t)v * stride + k];
+            if (x < lo[k]) lo[k] = x;
+            if (x > hi[k]) hi[k] = x;
+        }
+    for (int k = 0; k < 3; ++k)
+    {
+        g->lo[k] = lo[k] - 0.01 * cell;
+        int n = (int)ceil((hi[k] + 0.01 * cell - g->lo[k]) / cell);
+        g->n[k] = n < 1 ? 1 : n;
+    }
+    const int64_t cells = (int64_t)g->n[0] * g->n[1] * g->n[2];
+    g->start = (int64_t*)calloc((size_t)cells + 1, sizeof(int64_t));
+    for (int64_t i = 0; i < ntris; ++i)
+    {
+        int c0[3], c1[3];
+        tri_cells(g, i, c0, c1);
+        for (int z = c0[2]; z <= c1[2]; ++z) for (int y = c0[1]; y <= c1[1]; ++y) for (int x = c0[0]; x <= c1[0]; ++x)
+            g->start[((int64_t)z * g->n[1] + y) * g->n[0] + x + 1]++;
+    }
+    for (int64_t c = 0; c < cells; ++c) g->start[c + 1] += g->start[c];
+    g->items = (int32_t*)malloc(sizeof(int32_t) * (size_t)(g->start[cells] > 0 ? g->start[cells] : 1));
+    int64_t* fill = (int64_t*)malloc(sizeof(int64_t) * (size_t)cells);
+    memcpy(fill, g->start, sizeof(int64_t) * (size_t)cells);
+    for (int64_t i = 0; i < ntris; ++i)
+    {
+        int c0[3], c1[3];
+        tri_cells(g, i, c0, c1);
+        for (int z = c0[2]; z <= c1[2]; ++z) for (int y = c0[1]; y <= c1[1]; ++y) for (int x = c0[0]; x <= c1[0]; ++x)
+            g->items[fill[((int64_t)z * g->n[1] + y) * g->n[0] + x]++] = (int32_t)i;
+    }
+    free(fill);
+    return g;
+}
+
+void f64grid_free(F64Grid* g)
+{
+    if (!g) return;
+    free(g->start); free(g->items); free(g);
+}
+
+/* same contract as brute_intersect_f64 */
+int f64grid_intersect(const F64Grid* g, const float ro[3], const float rd[3], float tnear, float tfar, CpuHit* hit)
+{
+    hit->prim = -1; hit->t = tfar; hit->u = hit->v = 0.0f;
+    double bestT = (double)tfar, second = DBL_MAX;
+    int found = 0;
+    /* clip the ray to the grid's box */
+    double t0 = (double)tnear, t1 = (double)tfar;
+    for (int k = 0; k < 3; ++k)
+    {
+        const double lo = g->lo[k], hi = g->lo[k] + g->cell * g->n[k];
+        if (rd[k] == 0.0f) { if (ro[k] < lo || ro[k] > hi) return 0; continue; }
+        double a = (lo - ro[k]) / rd[k], b = (hi - ro[k]) / rd[k];
+        if (a > b) { double s = a; a = b; b = s; }
+        if (a > t0) t0 = a;
+        if (b < t1) t1 = b;
+    }
+    if (t0 > t1) return 0;
+    int c[3], step[3]; double tMax[3], tDelta[3];
+    for (int k = 0; k < 3; ++k)
+    {
+        const double p = (double)ro[k] + t0 * (double)rd[k];
+        int i = (int)floor((p - g->lo[k]) / g->cell);
+        c[k] = i < 0 ? 0 : (i >= g->n[k] ? g->n[k] - 1 : i);
+        if (rd[k] > 0.0f) { step[k] = 1; tDelta[k] = g->cell / rd[k]; tMax[k] = (g->lo[k] + (c[k] + 1) * g->cell - ro[k]) / rd[k]; }
+        else if (rd[k] < 0.0f) { step[k] = -1; tDelta[k] = -g->cell / rd[k]; tMax[k] = (g->lo[k] + c[k] * g->cell - ro[k]) / rd[k]; }
+        else { step[k] = 0; tDelta[k] = DBL_MAX; tMax[k] = DBL_MAX; }
+    }
+    double tEnter = t0;
+    for (;;)
+    {
+        if (tEnter > bestT + 1e-6 * fmax(1.0, fabs(bestT))) break;     /* nothing closer (or tying) can start here */
+        const int64_t cellIdx = ((int64_t)c[2] * g->n[1] + c[1]) * g->n[0] + c[0];
+        for (int64_t j = g->start[cellIdx]; j < g->start[cellIdx + 1]; ++j)
+        {
+            const int32_t i = g->items[j];
+            if (found && i == hit->prim) continue;
+            const float* a = g->verts + (size_t)(3 * (int64_t)i + 0) * g->stride;
+            const float* b = g->verts + (size_t)(3 * (int64_t)i + 1) * g->stride;
+            const float* cc = g->verts + (size_t)(3 * (int64_t)i + 2) * g->stride;
+            double t, u, v;
+            if (!mt_f64(a, b, cc, ro, rd, (double)tnear, (double)tfar, &t, &u, &v)) continue;
+            if (!found || t < bestT || (t == bestT && i < hit->prim))
+            {
+                if (found) second = bestT;
+                bestT = t; found = 1;
+                hit->t = (float)t; hit->u = (float)u; hit->v = (float)v; hit->prim = i;
+                double e1x = (double)b[0] - a[0], e1y = (double)b[1] - a[1], e1z = (double)b[2] - a[2];
+                double e2x = (double)cc[0] - a[0], e2y = (double)cc[1] - a[1], e2z = (double)cc[2] - a[2];
+                hit->ng[0] = (float)(e1y * e2z - e1z * e2y);
+                hit->ng[1] = (float)(e1z * e2x - e1x * e2z);
+                hit->ng[2] = (float)(e1x * e2y - e1y * e2x);
+            }
+            else if (t < second) second = t;
+        }
+        /* next cell */
+        int k = (tMax[0] <= tMax[1]) ? ((tMax[0] <= tMax[2]) ? 0 : 2) : ((tMax[1] <= tMax[2]) ? 1 : 2);
+        if (tMax[k] > t1 || step[k] == 0) break;
+        tEnter = tMax[k];
+        c[k] += step[k];
+        if (c[k] < 0 || c[k] >= g->n[k]) break;
+        tMax[k] += tDelta[k];
+    }
+    if (!found) return 0;
+    if (second < DBL_MAX && (second - bestT) <= 1e-6 * fmax(1.0, fabs(bestT))) return 2;
+    return 1;
+}
+
+typedef struct TruthArg
+{
+    const F64Grid* grid; const CpuBvh* bvh;
+    const float* verts; int stride; int64_t ntris;
+    const float* ro4; const float* rd4; float tnear; int64_t begin, end;
+    CpuHit* hits; int32_t* flags; uint8_t* occ;
+} TruthArg;
+
+static void* truth_main(void* p)
+{
+    TruthArg* a = (TruthArg*)p;
+    for (int64_t i = a->begin; i < a->end; ++i)
+    {
+        const float* ro = a->ro4 + 4 * i; const float* rd = a->rd4 + 4 * i;
+        if (a->occ) a->occ[i] = (uint8_t)(cpubvh_occluded(a->bvh, ro, rd, a->tnear, rd[3]) ? 1 : 0);
+        else if (a->grid) a->flags[i] = f64grid_intersect(a->grid, ro, rd, a->tnear, rd[3], &a->hits[i]);
+        else a->flags[i] = brute_intersect_f64(a->verts, a->stride, a->ntris, ro, rd, a->tnear, rd[3], &a->hits[i]);
+    }
+    return NULL;
+}
+
+static void truth_run(TruthArg proto, int64_t n, int threads)
+{
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    pthread_t th[256]; TruthArg args[256];
+    for (int t = 0; t < threads; ++t)
+    {
+        args[t] = proto;
+        args[t].begin = n * t / threads; args[t].end = n * (t + 1) / threads;
+        pthread_create(&th[t], NULL, truth_main, &args[t]);
+    }
+    for (int t = 0; t < threads; ++t) pthread_join(th[t], NULL);
+}
+
+/* rd4[i].w = tFar; flags[i] = 0 miss, 1 hit, 2 hit with a tie */
+void brute_intersect_f64_batch(const float* verts, int stride, int64_t ntris, const float* ro4, const float* rd4,
+                               float tnear, int64_t n, int threads, CpuHit* hits, int32_t* flags)
+{
+    TruthArg a; memset(&a, 0, sizeof(a));
+    a.verts = verts; a.stride = stride; a.ntris = ntris; a.ro4 = ro4; a.rd4 = rd4; a.tnear = tnear; a.hits = hits; a.flags = flags;
+    truth_run(a, n, threads);
+}
+
+void f64grid_intersect_batch(const F64Grid* g, const float* ro4, const float* rd4, float tnear, int64_t n, int threads,
+                             CpuHit* hits, int32_t* flags)
+{
+    TruthArg a; memset(&a, 0, sizeof(a));
+    a.grid = g; a.ro4 = ro4; a.rd4 = rd4; a.tnear = tnear; a.hits = hits; a.flags = flags;
+    truth_run(a, n, threads);
+}
+
+/* cpubvh_occluded (what the shim's rtcOccluded16 calls per lane) over a batch; rd4[i].w = tFar */
+void cpubvh_occluded_batch(const CpuBvh* bvh, const float* ro4, const float* rd4, float tnear, int64_t n, int threads,
+                           uint8_t* occluded)
+{
+    TruthArg a; memset(&a, 0, sizeof(a));
+    a.bvh = bvh; a.ro4 = ro4; a.rd4 = rd4; a.tnear = tnear; a.occ = occluded;
+    truth_run(a, n, threads);
+}

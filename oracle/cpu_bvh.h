@@ -74,6 +74,21 @@ int brute_intersect_f64(const float* verts, int stride, int64_t ntris,
 void cpubvh_intersect_batch(const CpuBvh* bvh, const float* ro4, const float* rd4, float tnear, int64_t n,
                             int threads, int32_t* prim, uint64_t* nodes, uint64_t* tris);
 
+
+/* threaded batches of the two ground truths and of the occlusion query; rd4[i].w = tFar,
+ * flags[i] = 0 miss, 1 hit, 2 hit whose runner-up lies within 1e-6 relative (tie, exempt) */
+void brute_intersect_f64_batch(const float* verts, int stride, int64_t ntris, const float* ro4, const float* rd4,
+                               float tnear, int64_t n, int threads, CpuHit* hits, int32_t* flags);
+/* fp64 ground truth over a uniform grid instead of all triangles (no BVH involved): see cpu_bvh.c */
+typedef struct F64Grid F64Grid;
+F64Grid* f64grid_build(const float* verts, int stride, int64_t ntris, double cell);
+void f64grid_free(F64Grid* g);
+int f64grid_intersect(const F64Grid* g, const float ro[3], const float rd[3], float tnear, float tfar, CpuHit* hit);
+void f64grid_intersect_batch(const F64Grid* g, const float* ro4, const float* rd4, float tnear, int64_t n, int threads,
+                             CpuHit* hits, int32_t* flags);
+void cpubvh_occluded_batch(const CpuBvh* bvh, const float* ro4, const float* rd4, float tnear, int64_t n, int threads,
+                           uint8_t* occluded);
+
 #ifdef __cplusplus
 }
 #endif

@@ -112,6 +112,10 @@ void oracle_raygen(void* scene, const float* origin4, int count, uint32_t pass,
                    float* colors4, float* directions4);
 
 /* fetch counters of the canonical BVH, summed over worker threads since reset */
+/* RtcOccluded16 (path_tracer.c:524-553) and RtcPointQuery (:597-616) as the reference calls them */
+void oracle_occluded_n(const void* scene, const float* ro4, const float* rd4, float tNear, int64_t n, uint8_t* out);
+void oracle_point_query_n(const void* scene, const float* pts4, int64_t n, float* distOut, int32_t* primOut);
+
 void oracle_counters_reset(void);
 void oracle_counters_get(uint64_t* nodes, uint64_t* tris, uint64_t* rays);
 

@@ -259,3 +259,35 @@ void oracle_brute_n(const void* pscene, const float* ro4, const float* rd4, floa
     oracle_begin(ORACLE_STREAM_RAYS, 0);
     Task_Run(&t, BruteFn, (i32)n);
 }
+
+/* the reference's RtcOccluded16 (path_tracer.c:524-553) over the shim's rtcOccluded16, 16 rays at a
+ * time: ro4.w unused (tNear is a parameter), rd4.w = tFar; out[i] = 1 when occluded */
+void oracle_occluded_n(const void* pscene, const float* ro4, const float* rd4, float tNear, int64_t n, uint8_t* out)
+{
+    const PtScene* scene = (const PtScene*)pscene;
+    for (int64_t base = 0; base < n; base += 16)
+    {
+        float4 ros[16]; float4 rds[16]; bool visibles[16];
+        for (int i = 0; i < 16; ++i)
+        {
+            const int64_t j = (base + i < n) ? base + i : n - 1;
+            ros[i] = f4_v(ro4[4 * j], ro4[4 * j + 1], ro4[4 * j + 2], tNear);
+            rds[i] = f4_v(rd4[4 * j], rd4[4 * j + 1], rd4[4 * j + 2], rd4[4 * j + 3]);
+        }
+        RtcOccluded16(scene->rtcScene, ros, rds, visibles);
+        for (int i = 0; i < 16 && base + i < n; ++i) out[base + i] = visibles[i] ? 0 : 1;
+    }
+}
+
+/* the reference's RtcPointQuery (path_tracer.c:597-616): pts4 = (x, y, z, radius); distOut = usr.distance
+ * (kRcpEpsilon when nothing lies within the radius), primOut = usr.primID (-1 for none) */
+void oracle_point_query_n(const void* pscene, const float* pts4, int64_t n, float* distOut, int32_t* primOut)
+{
+    const PtScene* scene = (const PtScene*)pscene;
+    for (int64_t i = 0; i < n; ++i)
+    {
+        PointQueryUserData usr = RtcPointQuery(scene, f4_v(pts4[4 * i], pts4[4 * i + 1], pts4[4 * i + 2], pts4[4 * i + 3]));
+        distOut[i] = usr.distance;
+        primOut[i] = (usr.primID == RTC_INVALID_GEOMETRY_ID) ? -1 : (int32_t)usr.primID;
+    }
+}

@@ -145,7 +145,7 @@ EXPORTS = [
     "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
     "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap", "LmPack_EmbedDesc",
     "LmPack_BakeDesc_Device", "PtMediaParams_Default", "PtScene_SetMedia",
-    "Pt_RepackRome",
+    "Pt_RepackRome", "PtSys_SetLmPack", "LmPack_Bake", "Pt_PointQueryN", "Pt_SetOption",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -225,6 +225,14 @@ def load():
     L.PtScene_SetMedia.argtypes = [vp, C.POINTER(PtMediaParams)]
     L.PtScene_SetMedia.restype = C.c_int32
     L.LmPack_BakeDesc_Device.restype = C.c_int32
+    L.Pt_PointQueryN.argtypes = [vp, vp, vp, C.c_int64]
+    L.Pt_PointQueryN.restype = C.c_int32
+    L.Pt_SetOption.argtypes = [C.c_char_p, C.c_int32]
+    L.Pt_SetOption.restype = C.c_int32
+    L.PtSys_SetLmPack.argtypes = [C.POINTER(PtLightmapDesc), C.c_int32, C.c_float]
+    L.PtSys_SetLmPack.restype = None
+    L.LmPack_Bake.argtypes = [vp, C.c_float, C.c_int32]
+    L.LmPack_Bake.restype = None
     for name in ("Pt_IntersectN", "Pt_OccludedN", "Pt_TraceRayN", "Pt_TraceSpp", "Pt_IntersectN_Device",
                  "Pt_OccludedN_Device", "Pt_TraceSpp_Device", "LmPack_BakeDesc", "PtScene_GetStats",
                  "PtScene_Download", "PtScene_GetDist", "PtScene_SetDist", "PtScene_GetBrdfLut"):
@@ -267,6 +275,10 @@ def default_dof(auto_focus=True):
     return d
 
 
+def set_option(name, value):
+    _check(load().Pt_SetOption(name.encode(), int(value)), "Pt_SetOption")
+
+
 def counters():
     c = PtCounters()
     load().Pt_GetCounters(C.byref(c))
@@ -281,61 +293,114 @@ def kernel_stats():
     return out
 
 
-class Scene:
-    """PtScene built from a scenes.SceneDesc (PtScene_NewFromDesc)."""
+def marshal_desc(desc):
+    """scenes.SceneDesc -> (PtSceneDesc, objects that keep its arrays alive)"""
+    keep = []
+    ents = (PtEntityDesc * max(len(desc.entities), 1))()
+    for i, e in enumerate(desc.entities):
+        pos = np.ascontiguousarray(e.positions, np.float32)
+        nrm = np.ascontiguousarray(e.normals, np.float32)
+        uvs = np.ascontiguousarray(e.uvs, np.float32)
+        # entities that share one mesh object share one upload (keyed by the source array)
+        key = id(e.positions)
+        cached = next((k for k in keep if isinstance(k, tuple) and k[0] == key), None)
+        if cached is None:
+            cached = (key, pos, nrm, uvs)
+            keep.append(cached)
+        _, pos, nrm, uvs = cached
+        ents[i].positions = pos.ctypes.data
+        ents[i].normals = nrm.ctypes.data
+        ents[i].uvs = uvs.ctypes.data
+        ents[i].length = len(pos)
+        ents[i].matrix[:] = [float(x) for x in np.asarray(e.matrix, np.float32).reshape(-1)]
+        m = ents[i].material
+        m.albedo, m.rome, m.normal, m.flags = e.albedo, e.rome, e.normal, e.flags
+        m.meanFreePath[:] = [float(x) for x in e.mean_free_path]
+        m.ior, m.bumpiness = e.ior, e.bumpiness
+    texs = (PtTextureDesc * max(len(desc.textures), 1))()
+    for i, t in enumerate(desc.textures):
+        arr = np.ascontiguousarray(t.texels, np.uint32)
+        keep.append(arr)
+        texs[i].width, texs[i].height, texs[i].format, texs[i].texels = t.width, t.height, t.format, arr.ctypes.data
+    d = PtSceneDesc()
+    d.entities = ents
+    d.entityCount = len(desc.entities)
+    d.textures = texs
+    d.textureCount = len(desc.textures)
+    if desc.sky is not None:
+        sky = np.ascontiguousarray(desc.sky, np.float32)
+        keep.append(sky)
+        d.skyFaces, d.skySize = sky.ctypes.data, sky.shape[1]
+    if desc.brdf_lut is not None:
+        lut = np.ascontiguousarray(desc.brdf_lut, np.float32)
+        keep.append(lut)
+        d.brdfLut, d.lutWidth, d.lutHeight = lut.ctypes.data, lut.shape[1], lut.shape[0]
+    d.config.ptDistMeters = desc.pt_dist_meters
+    d.config.seed = desc.seed
+    d.config.pathPoolSize = desc.path_pool_size
+    d.config.bakeMode = desc.bake_mode
+    keep += [ents, texs]
+    return d, keep
 
-    def __init__(self, desc):
+
+def set_scene_desc(desc):
+    """PtSys_SetSceneDesc: register (a copy of) the description PtScene_New(void) builds from; None clears it."""
+    L = load()
+    L.PtSys_Init()
+    if desc is None:
+        L.PtSys_SetSceneDesc(None)
+        return
+    d, keep = marshal_desc(desc)
+    L.PtSys_SetSceneDesc(C.byref(d))
+    del keep        # the library copied everything
+
+
+def set_lm_pack(pages, texels_per_meter):
+    """PtSys_SetLmPack. pages: list of (probes[5] arrays, position, normal, sample_counts) host arrays that stay alive
+    (and are written) while the pack is registered; [] clears it."""
+    arr = (PtLightmapDesc * max(len(pages), 1))()
+    for i, (probes, position, normal, counts) in enumerate(pages):
+        for k in range(5):
+            arr[i].probes[k] = probes[k].ctypes.data
+        arr[i].position, arr[i].normal, arr[i].sampleCounts = position.ctypes.data, normal.ctypes.data, counts.ctypes.data
+        arr[i].size = int(round(np.sqrt(len(counts))))
+    load().PtSys_SetLmPack(arr, len(pages), float(texels_per_meter))
+
+
+class Scene:
+    """PtScene built from a scenes.SceneDesc: PtScene_NewFromDesc, or with desc=None the reference's
+    PtScene_New(void) over the description registered with set_scene_desc()."""
+
+    def __init__(self, desc=None):
         L = load()
         L.PtSys_Init()
-        self._keep = []
-        ents = (PtEntityDesc * max(len(desc.entities), 1))()
-        for i, e in enumerate(desc.entities):
-            pos = np.ascontiguousarray(e.positions, np.float32)
-            nrm = np.ascontiguousarray(e.normals, np.float32)
-            uvs = np.ascontiguousarray(e.uvs, np.float32)
-            # entities that share one mesh object share one upload (keyed by the source array)
-            key = id(e.positions)
-            cached = next((k for k in self._keep if isinstance(k, tuple) and k[0] == key), None)
-            if cached is None:
-                cached = (key, pos, nrm, uvs)
-                self._keep.append(cached)
-            _, pos, nrm, uvs = cached
-            ents[i].positions = pos.ctypes.data
-            ents[i].normals = nrm.ctypes.data
-            ents[i].uvs = uvs.ctypes.data
-            ents[i].length = len(pos)
-            ents[i].matrix[:] = [float(x) for x in np.asarray(e.matrix, np.float32).reshape(-1)]
-            m = ents[i].material
-            m.albedo, m.rome, m.normal, m.flags = e.albedo, e.rome, e.normal, e.flags
-            m.meanFreePath[:] = [float(x) for x in e.mean_free_path]
-            m.ior, m.bumpiness = e.ior, e.bumpiness
-        texs = (PtTextureDesc * max(len(desc.textures), 1))()
-        for i, t in enumerate(desc.textures):
-            arr = np.ascontiguousarray(t.texels, np.uint32)
-            self._keep.append(arr)
-            texs[i].width, texs[i].height, texs[i].format, texs[i].texels = t.width, t.height, t.format, arr.ctypes.data
-        d = PtSceneDesc()
-        d.entities = ents
-        d.entityCount = len(desc.entities)
-        d.textures = texs
-        d.textureCount = len(desc.textures)
-        if desc.sky is not None:
-            sky = np.ascontiguousarray(desc.sky, np.float32)
-            self._keep.append(sky)
-            d.skyFaces, d.skySize = sky.ctypes.data, sky.shape[1]
-        if desc.brdf_lut is not None:
-            lut = np.ascontiguousarray(desc.brdf_lut, np.float32)
-            self._keep.append(lut)
-            d.brdfLut, d.lutWidth, d.lutHeight = lut.ctypes.data, lut.shape[1], lut.shape[0]
-        d.config.ptDistMeters = desc.pt_dist_meters
-        d.config.seed = desc.seed
-        d.config.pathPoolSize = desc.path_pool_size
-        d.config.bakeMode = desc.bake_mode
-        self.h = L.PtScene_NewFromDesc(C.byref(d))
-        if not self.h:
-            raise PtError("PtScene_NewFromDesc failed: " + last_error())
+        if desc is None:
+            self.h = L.PtScene_New()
+            if not self.h:
+                raise PtError("PtScene_New failed: " + last_error())
+        else:
+            d, keep = marshal_desc(desc)
+            self.h = L.PtScene_NewFromDesc(C.byref(d))
+            del keep
+            if not self.h:
+                raise PtError("PtScene_NewFromDesc failed: " + last_error())
         self.stats = PtSceneStats()
         _check(L.PtScene_GetStats(self.h, C.byref(self.stats)), "PtScene_GetStats")
+
+    def refresh_stats(self):
+        _check(load().PtScene_GetStats(self.h, C.byref(self.stats)), "PtScene_GetStats")
+        return self.stats
+
+    def update(self):
+        load().PtScene_Update(self.h)
+        return self.refresh_stats()
+
+    def bake(self, time_slice, spp):
+        """LmPack_Bake over the pack registered with set_lm_pack()."""
+        load().LmPack_Bake(self.h, time_slice, spp)
+        err = last_error()
+        if err:
+            raise PtError("LmPack_Bake failed: " + err)
 
     def close(self):
         if getattr(self, "h", None):
@@ -394,6 +459,13 @@ class Scene:
         ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)
         out = np.zeros(len(ro), np.uint8)
         _check(load().Pt_OccludedN(self.h, ro.ctypes.data, rd.ctypes.data, t_near, out.ctypes.data, len(ro)), "Pt_OccludedN")
+        return out
+
+    def point_query(self, pts):
+        """Pt_PointQueryN: pts[:, 3] = radius -> distance to the nearest triangle within it (8388608 if none)"""
+        pts = np.ascontiguousarray(pts, np.float32)
+        out = np.zeros(len(pts), np.float32)
+        _check(load().Pt_PointQueryN(self.h, pts.ctypes.data, out.ctypes.data, len(pts)), "Pt_PointQueryN")
         return out
 
     def fetch_counts(self, ro, rd, t_near=0.0):

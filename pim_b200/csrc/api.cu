@@ -6,7 +6,9 @@
 #define PIM_PT_NO_VECTOR_TYPES 1
 #include "../../include/pim_pt.h"
 #include "pt_device.h"
+#include "arena.h"
 
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -35,6 +37,18 @@ bool cudaOk(cudaError_t e, const char* what)
     if (e == cudaSuccess) return true;
     setError("CUDA error %s (%d) at %s", cudaGetErrorString(e), (int)e, what);
     return false;
+}
+
+Arena& stagingArena(int device)
+{
+    static Arena arenas[kMaxDevices];
+    return arenas[(device >= 0 && device < kMaxDevices) ? device : 0];
+}
+int currentDevice()
+{
+    int d = 0;
+    cudaGetDevice(&d);
+    return d;
 }
 
 } // namespace pt
@@ -67,13 +81,96 @@ struct PtScene_s
     pim_float4* rayGenDirs[2] = { nullptr, nullptr };
     int32_t rayGenCap[2] = { 0, 0 };
     int rayGenFlip = 0;
+    int device = 0;                 // the CUDA device the scene lives on (current when it was built)
+    uint64_t descVersion = 0;       // PtSys_SetSceneDesc generation the scene was built from (0: an explicit description)
+    // ray cursors of the persistent batch kernels: one 128-byte line per call in flight, handed out
+    // round robin, so two batches on different streams never share a cursor
+    static constexpr uint32_t kCursorRing = 64;
+    unsigned long long* cursorRing = nullptr;
+    unsigned long long* nextCursor() const;
 };
+static std::atomic<uint32_t> g_cursorNext{ 0 };
+unsigned long long* PtScene_s::nextCursor() const
+{
+    return cursorRing + 16 * (size_t)(g_cursorNext.fetch_add(1u) % kCursorRing);
+}
 
 static bool g_initialised = false;
-static PtSceneDesc g_sceneDesc;
-static bool g_haveSceneDesc = false;
 static std::map<PtTrace*, DeviceImages> g_traces;
 static std::mutex g_mutex;
+
+// PtSys_SetSceneDesc keeps its own copy of everything the description points to (the adapter of
+// INTEGRATION.md fills it from per-frame memory): mesh arrays once per distinct pointer, so
+// instanced meshes stay shared, texel blocks, sky faces and the BRDF table.
+struct SceneDescCopy
+{
+    PtSceneDesc desc;
+    std::vector<PtEntityDesc> entities;
+    std::vector<PtTextureDesc> textures;
+    std::vector<std::vector<pim_float4>> meshArrays;
+    std::vector<std::vector<uint32_t>> texelBlocks;
+    std::vector<float> sky, lut;
+    bool valid = false;
+    uint64_t version = 0;
+
+    void clear()
+    {
+        entities.clear(); textures.clear(); meshArrays.clear(); texelBlocks.clear(); sky.clear(); lut.clear();
+        memset(&desc, 0, sizeof(desc));
+        valid = false;
+    }
+    void assign(const PtSceneDesc* src)
+    {
+        clear();
+        ++version;
+        if (!src) return;
+        desc = *src;
+        std::map<const void*, const pim_float4*> seen;
+        auto dup = [&](const pim_float4* p, int32_t n) -> const pim_float4*
+        {
+            if (!p || n <= 0) return nullptr;
+            auto it = seen.find(p);
+            if (it != seen.end()) return it->second;
+            meshArrays.emplace_back(p, p + n);
+            seen[p] = meshArrays.back().data();
+            return meshArrays.back().data();
+        };
+        entities.assign(src->entities, src->entities + std::max(src->entityCount, 0));
+        for (PtEntityDesc& e : entities)
+        {
+            e.positions = dup(e.positions, e.length);
+            e.normals = dup(e.normals, e.length);
+            e.uvs = dup(e.uvs, e.length);
+        }
+        textures.assign(src->textures, src->textures + std::max(src->textureCount, 0));
+        for (PtTextureDesc& t : textures)
+        {
+            const size_t n = (size_t)std::max(t.width, 0) * (size_t)std::max(t.height, 0);
+            const uint32_t* q = (const uint32_t*)t.texels;
+            texelBlocks.emplace_back(q ? q : nullptr, q ? q + n : nullptr);     // RGBA8 and RG16 texels are both 4 bytes
+            t.texels = texelBlocks.back().data();
+        }
+        if (src->skyFaces && src->skySize > 0)
+        {
+            sky.assign(src->skyFaces, src->skyFaces + (size_t)6 * src->skySize * src->skySize * 3);
+            desc.skyFaces = sky.data();
+        }
+        if (src->brdfLut && src->lutWidth > 0 && src->lutHeight > 0)
+        {
+            lut.assign(src->brdfLut, src->brdfLut + (size_t)2 * src->lutWidth * src->lutHeight);
+            desc.brdfLut = lut.data();
+        }
+        desc.entities = entities.data();
+        desc.textures = textures.data();
+        valid = true;
+    }
+};
+static SceneDescCopy g_sceneDesc;
+
+// the lightmap pack LmPack_Bake works on (the reference's LmPack_Get(), lightmap.c:136): page
+// descriptions copied, the arrays stay the engine's (they are where the result has to appear)
+static std::vector<PtLightmapDesc> g_lmPack;
+static float g_lmTexelsPerMeter = 0.0f;
 
 template <class T>
 static bool sceneAlloc(PtScene* s, T*& p, size_t count)
@@ -195,12 +292,14 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
         tPhase = now;
     };
     memset(&s->view, 0, sizeof(s->view));
+    cudaGetDevice(&s->device);
     s->config = desc->config;
     if (s->config.ptDistMeters <= 0.0f) s->config.ptDistMeters = 1.5f;
     bool ok = PT_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     cudaStream_t st = s->stream;
     DScene& V = s->view;
     V.media = MediaDesc_Default();
+    ok = ok && sceneAlloc(s, s->cursorRing, (size_t)16 * PtScene_s::kCursorRing);
 
     // textures
     std::vector<DTexture> texTable((size_t)std::max(desc->textureCount, 0));
@@ -386,21 +485,15 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
 
 // ---- helpers for host <-> device batches ---------------------------------------
 
-struct DevBuf
-{
-    void* p = nullptr;
-    bool alloc(size_t bytes) { return PT_CUDA(cudaMalloc(&p, bytes ? bytes : 1)); }
-    ~DevBuf() { if (p) cudaFree(p); }
-};
-
-// CUDA events around a call's kernels on their stream; stop() leaves the time in Pt_LastKernelMs()
+// CUDA events around a call's kernels on their stream; stop() leaves the time in Pt_LastKernelMs().
+// The two events belong to the staging arena of the call's lease (created once per device).
 struct KernelTimer
 {
-    cudaEvent_t a = nullptr, b = nullptr;
+    cudaEvent_t a, b;
     cudaStream_t st;
-    explicit KernelTimer(cudaStream_t s) : st(s)
+    KernelTimer(Lease& lease, cudaStream_t s) : a(lease.arena().evA), b(lease.arena().evB), st(s)
     {
-        if (cudaEventCreate(&a) == cudaSuccess && cudaEventCreate(&b) == cudaSuccess) cudaEventRecord(a, st);
+        if (a && b) cudaEventRecord(a, st);
     }
     void stop()
     {
@@ -409,13 +502,36 @@ struct KernelTimer
         float ms = 0.0f;
         if (cudaEventSynchronize(b) == cudaSuccess && cudaEventElapsedTime(&ms, a, b) == cudaSuccess) g_lastKernelMs = ms;
     }
-    ~KernelTimer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
 };
+
+static PtScene* sceneBuild(const PtSceneDesc* desc);
+
+// PtScene_Update (path_tracer.c:1024-1037): a scene built from the registered description is rebuilt in
+// place when the description has changed since (the reference compares Entities_Get()->modtime), then
+// the light-grid distributions relearn (UpdateDists)
+static bool sceneRefresh(PtScene* scene, cudaStream_t st)
+{
+    if (scene->descVersion != 0 && g_sceneDesc.valid && scene->descVersion != g_sceneDesc.version)
+    {
+        PtScene* fresh = sceneBuild(&g_sceneDesc.desc);
+        if (!fresh) return false;
+        fresh->descVersion = g_sceneDesc.version;
+        fresh->nextPass = scene->nextPass;
+        cudaStreamSynchronize(scene->stream);
+        const bool ownStream = st == scene->stream;
+        std::swap(*scene, *fresh);          // the caller's handle now owns the new scene
+        sceneFree(fresh);
+        if (ownStream) st = scene->stream;
+    }
+    return launchDistUpdate(scene->view, st);
+}
 
 static bool traceSppDevice(PtScene* scene, const Camera* camera, PtDofInfo* dof, int w, int h, int sppBegin, int sppCount,
                            float* dColor, float* dAlbedo, float* dNormal, cudaStream_t st)
 {
-    if (!launchDistUpdate(scene->view, st)) return false;       // PtScene_Update -> UpdateDists
+    const bool own = st == scene->stream;
+    if (!sceneRefresh(scene, st)) return false;       // PtScene_Update -> UpdateDists
+    if (own) st = scene->stream;
     WorkDesc W; memset(&W, 0, sizeof(W));
     W.kind = Work_Camera;
     W.cam = makeCam(camera, dof, w, h);
@@ -451,19 +567,36 @@ static bool dofUpdate(PtScene* scene, PtDofInfo* dof, const Camera* camera)
     return true;
 }
 
+static void freeImages(DeviceImages& im)
+{
+    for (int k = 0; k < 3; ++k)
+    {
+        if (im.image[k]) cudaFree(im.image[k]);
+        if (im.sum[k]) cudaFree(im.sum[k]);
+        im.image[k] = im.sum[k] = nullptr;
+    }
+}
+
+// The running-mean images of a PtTrace live on the device (the host arrays are refreshed from
+// them at the end of every Pt_Trace / Pt_TraceSpp; edits the host makes to them are not read back).
 static DeviceImages* traceImages(PtTrace* trace)
 {
     std::lock_guard<std::mutex> lock(g_mutex);
     auto it = g_traces.find(trace);
     const int64_t texels = (int64_t)trace->imageSize.x * trace->imageSize.y;
     if (it != g_traces.end() && it->second.texels == texels) return &it->second;
+    if (it != g_traces.end()) { freeImages(it->second); g_traces.erase(it); }      // the image size changed
     DeviceImages im;
     im.texels = texels;
     for (int k = 0; k < 3; ++k)
     {
-        if (!PT_CUDA(cudaMalloc((void**)&im.image[k], sizeof(float) * 3 * texels))) return nullptr;
-        if (!PT_CUDA(cudaMalloc((void**)&im.sum[k], sizeof(float) * 3 * texels))) return nullptr;
-        cudaMemset(im.image[k], 0, sizeof(float) * 3 * texels);
+        if (!PT_CUDA(cudaMalloc((void**)&im.image[k], sizeof(float) * 3 * texels)) ||
+            !PT_CUDA(cudaMalloc((void**)&im.sum[k], sizeof(float) * 3 * texels)) ||
+            !PT_CUDA(cudaMemset(im.image[k], 0, sizeof(float) * 3 * texels)))
+        {
+            freeImages(im);
+            return nullptr;
+        }
     }
     g_traces[trace] = im;
     return &g_traces[trace];
@@ -474,8 +607,20 @@ static void releaseImages(PtTrace* trace)
     std::lock_guard<std::mutex> lock(g_mutex);
     auto it = g_traces.find(trace);
     if (it == g_traces.end()) return;
-    for (int k = 0; k < 3; ++k) { cudaFree(it->second.image[k]); cudaFree(it->second.sum[k]); }
+    freeImages(it->second);
     g_traces.erase(it);
+}
+
+static bool onSceneDevice(const PtScene* scene, const char* who)
+{
+    int dev = 0;
+    if (!PT_CUDA(cudaGetDevice(&dev))) return false;
+    if (dev != scene->device)
+    {
+        setError("%s: the scene lives on device %d but device %d is current", who, scene->device, dev);
+        return false;
+    }
+    return true;
 }
 
 // ================================================================== C ABI =====
@@ -491,33 +636,47 @@ void PtSys_Shutdown(void)
     std::vector<PtTrace*> keys;
     { std::lock_guard<std::mutex> lock(g_mutex); for (auto& kv : g_traces) keys.push_back(kv.first); }
     for (PtTrace* t : keys) releaseImages(t);
+    // staging arenas of every device that was used
+    int count = 0, cur = 0;
+    if (cudaGetDeviceCount(&count) == cudaSuccess && cudaGetDevice(&cur) == cudaSuccess)
+    {
+        for (int d = 0; d < count && d < kMaxDevices; ++d)
+        {
+            Arena& A = stagingArena(d);
+            std::lock_guard<std::mutex> lock(A.mutex);
+            if (!A.dev && !A.host && !A.evA) continue;
+            cudaSetDevice(d);
+            A.release();
+        }
+        cudaSetDevice(cur);
+    }
+    g_sceneDesc.clear();
+    g_lmPack.clear();
     g_initialised = false;
 }
 
-void PtSys_SetSceneDesc(const PtSceneDesc* desc)
-{
-    g_haveSceneDesc = desc != nullptr;
-    if (desc) g_sceneDesc = *desc;
-}
+void PtSys_SetSceneDesc(const PtSceneDesc* desc) { g_sceneDesc.assign(desc); }
 
 PtScene* PtScene_New(void)
 {
-    if (!g_haveSceneDesc) { setError("PtScene_New: no scene description registered (PtSys_SetSceneDesc)"); return nullptr; }
-    return sceneBuild(&g_sceneDesc);
+    if (!g_sceneDesc.valid) { setError("PtScene_New: no scene description registered (PtSys_SetSceneDesc)"); return nullptr; }
+    PtScene* s = sceneBuild(&g_sceneDesc.desc);
+    if (s) s->descVersion = g_sceneDesc.version;
+    return s;
 }
 PtScene* PtScene_NewFromDesc(const PtSceneDesc* desc) { return sceneBuild(desc); }
 
 void PtScene_Update(PtScene* scene)
 {
     if (!scene) return;
-    launchDistUpdate(scene->view, scene->stream);
-    PT_CUDA(cudaStreamSynchronize(scene->stream));
+    if (sceneRefresh(scene, scene->stream)) PT_CUDA(cudaStreamSynchronize(scene->stream));
 }
 void PtScene_Del(PtScene* scene) { sceneFree(scene); }
 void PtScene_Gui(PtScene* scene) { (void)scene; }
 
 void PtTrace_New(PtTrace* trace, pim_int2 imageSize)      // path_tracer.c:1117-1130
 {
+    releaseImages(trace);       // a PtTrace re-initialised at the same address starts from empty device images
     memset(trace, 0, sizeof(*trace));
     const size_t texels = (size_t)imageSize.x * (size_t)imageSize.y;
     trace->imageSize = imageSize;
@@ -560,7 +719,7 @@ int32_t Pt_IntersectN_Device(const PtScene* scene, const void* dRo, const void* 
 {
     if (!scene) { setError("Pt_IntersectN_Device: null scene"); return -1; }
     cudaStream_t st = stream ? (cudaStream_t)stream : scene->stream;
-    return launchIntersect(scene->view, (const F4*)dRo, (const F4*)dRd, tNear, (RayHitOut*)dHitsOut, n, st) ? 0 : -1;
+    return launchIntersect(scene->view, (const F4*)dRo, (const F4*)dRd, tNear, (RayHitOut*)dHitsOut, n, scene->nextCursor(), st) ? 0 : -1;
 }
 
 int32_t Pt_OccludedN_Device(const PtScene* scene, const void* dRo, const void* dRd, float tNear, void* dOccludedOut,
@@ -568,7 +727,7 @@ int32_t Pt_OccludedN_Device(const PtScene* scene, const void* dRo, const void* d
 {
     if (!scene) { setError("Pt_OccludedN_Device: null scene"); return -1; }
     cudaStream_t st = stream ? (cudaStream_t)stream : scene->stream;
-    return launchOccluded(scene->view, (const F4*)dRo, (const F4*)dRd, tNear, (uint8_t*)dOccludedOut, n, st) ? 0 : -1;
+    return launchOccluded(scene->view, (const F4*)dRo, (const F4*)dRd, tNear, (uint8_t*)dOccludedOut, n, scene->nextCursor(), st) ? 0 : -1;
 }
 
 int32_t Pt_IntersectN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd, float tNear, PtRayHit* hitsOut,
@@ -577,19 +736,20 @@ int32_t Pt_IntersectN(const PtScene* scene, const pim_float4* ro, const pim_floa
     if (!scene) { setError("Pt_IntersectN: null scene"); return -1; }
     if (n <= 0) return 0;
     const int64_t chunk = 1 << 24;
-    DevBuf dRo, dRd, dOut;
     const int64_t m = std::min(n, chunk);
-    if (!dRo.alloc(sizeof(F4) * m) || !dRd.alloc(sizeof(F4) * m) || !dOut.alloc(sizeof(RayHitOut) * m)) return -1;
+    F4 *dRo = nullptr, *dRd = nullptr; RayHitOut* dOut = nullptr;
+    Lease lease;
+    if (!lease.dev(dRo, (size_t)m).dev(dRd, (size_t)m).dev(dOut, (size_t)m).commit()) return -1;
     cudaStream_t st = scene->stream;
     for (int64_t base = 0; base < n; base += chunk)
     {
         const int64_t c = std::min(chunk, n - base);
-        bool ok = PT_CUDA(cudaMemcpyAsync(dRo.p, ro + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
-                  PT_CUDA(cudaMemcpyAsync(dRd.p, rd + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
-                  launchIntersect(scene->view, (const F4*)dRo.p, (const F4*)dRd.p, tNear, (RayHitOut*)dOut.p, c, st) &&
-                  PT_CUDA(cudaMemcpyAsync(hitsOut + base, dOut.p, sizeof(RayHitOut) * c, cudaMemcpyDeviceToHost, st)) &&
+        bool ok = PT_CUDA(cudaMemcpyAsync(dRo, ro + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+                  PT_CUDA(cudaMemcpyAsync(dRd, rd + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+                  launchIntersect(scene->view, dRo, dRd, tNear, dOut, c, scene->nextCursor(), st) &&
+                  PT_CUDA(cudaMemcpyAsync(hitsOut + base, dOut, sizeof(RayHitOut) * c, cudaMemcpyDeviceToHost, st)) &&
                   PT_CUDA(cudaStreamSynchronize(st));
-        if (!ok) return -1;
+        if (!ok) { cudaStreamSynchronize(st); return -1; }
     }
     return 0;
 }
@@ -600,21 +760,37 @@ int32_t Pt_OccludedN(const PtScene* scene, const pim_float4* ro, const pim_float
     if (!scene) { setError("Pt_OccludedN: null scene"); return -1; }
     if (n <= 0) return 0;
     const int64_t chunk = 1 << 24;
-    DevBuf dRo, dRd, dOut;
     const int64_t m = std::min(n, chunk);
-    if (!dRo.alloc(sizeof(F4) * m) || !dRd.alloc(sizeof(F4) * m) || !dOut.alloc(m)) return -1;
+    F4 *dRo = nullptr, *dRd = nullptr; uint8_t* dOut = nullptr;
+    Lease lease;
+    if (!lease.dev(dRo, (size_t)m).dev(dRd, (size_t)m).dev(dOut, (size_t)m).commit()) return -1;
     cudaStream_t st = scene->stream;
     for (int64_t base = 0; base < n; base += chunk)
     {
         const int64_t c = std::min(chunk, n - base);
-        bool ok = PT_CUDA(cudaMemcpyAsync(dRo.p, ro + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
-                  PT_CUDA(cudaMemcpyAsync(dRd.p, rd + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
-                  launchOccluded(scene->view, (const F4*)dRo.p, (const F4*)dRd.p, tNear, (uint8_t*)dOut.p, c, st) &&
-                  PT_CUDA(cudaMemcpyAsync(occludedOut + base, dOut.p, c, cudaMemcpyDeviceToHost, st)) &&
+        bool ok = PT_CUDA(cudaMemcpyAsync(dRo, ro + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+                  PT_CUDA(cudaMemcpyAsync(dRd, rd + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+                  launchOccluded(scene->view, dRo, dRd, tNear, dOut, c, scene->nextCursor(), st) &&
+                  PT_CUDA(cudaMemcpyAsync(occludedOut + base, dOut, c, cudaMemcpyDeviceToHost, st)) &&
                   PT_CUDA(cudaStreamSynchronize(st));
-        if (!ok) return -1;
+        if (!ok) { cudaStreamSynchronize(st); return -1; }
     }
     return 0;
+}
+
+int32_t Pt_PointQueryN(const PtScene* scene, const pim_float4* points, float* distanceOut, int64_t n)
+{
+    if (!scene) { setError("Pt_PointQueryN: null scene"); return -1; }
+    if (n <= 0) return 0;
+    F4* dPts = nullptr; float* dDist = nullptr;
+    Lease lease;
+    if (!lease.dev(dPts, (size_t)n).dev(dDist, (size_t)n).commit()) return -1;
+    cudaStream_t st = scene->stream;
+    bool ok = PT_CUDA(cudaMemcpyAsync(dPts, points, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
+              launchPointQuery(scene->view, dPts, dDist, n, st) &&
+              PT_CUDA(cudaMemcpyAsync(distanceOut, dDist, sizeof(float) * n, cudaMemcpyDeviceToHost, st));
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
+    return ok ? 0 : -1;
 }
 
 PtRayHit Pt_Intersect(const PtScene* scene, pim_float4 ro, pim_float4 rd, float tNear, float tFar)
@@ -632,35 +808,36 @@ int32_t Pt_TraceRayN(PtScene* scene, const pim_float4* ro, const pim_float4* rd,
 {
     if (!scene) { setError("Pt_TraceRayN: null scene"); return -1; }
     if (n <= 0) return 0;
-    DevBuf dRo, dRd, dOut;
-    if (!dRo.alloc(sizeof(F4) * n) || !dRd.alloc(sizeof(F4) * n) || !dOut.alloc(sizeof(float) * 9 * n)) return -1;
+    const bool small = n < 4096;
+    F4 *dRo = nullptr, *dRd = nullptr; float *dOut = nullptr, *c = nullptr, *a = nullptr, *nr = nullptr;
+    Lease lease;
+    lease.dev(dRo, (size_t)n).dev(dRd, (size_t)n).dev(dOut, 9 * (size_t)n);
+    if (!small) lease.dev(c, 3 * (size_t)n).dev(a, 3 * (size_t)n).dev(nr, 3 * (size_t)n);
+    if (!lease.commit()) return -1;
     cudaStream_t st = scene->stream;
-    bool ok = PT_CUDA(cudaMemcpyAsync(dRo.p, ro, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
-              PT_CUDA(cudaMemcpyAsync(dRd.p, rd, sizeof(F4) * n, cudaMemcpyHostToDevice, st));
-    if (ok && n < 4096)
+    bool ok = PT_CUDA(cudaMemcpyAsync(dRo, ro, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
+              PT_CUDA(cudaMemcpyAsync(dRd, rd, sizeof(F4) * n, cudaMemcpyHostToDevice, st));
+    if (ok && small)
     {
-        ok = launchTraceRays(scene->view, (const F4*)dRo.p, (const F4*)dRd.p, n, pass, scene->config.seed, (float*)dOut.p, st);
+        ok = launchTraceRays(scene->view, dRo, dRd, n, pass, scene->config.seed, dOut, st);
     }
     else if (ok)
     {
         // results are per item: colour, albedo, normal triples interleaved as PtResult
-        DevBuf c, a, nr;
-        ok = c.alloc(sizeof(float) * 3 * n) && a.alloc(sizeof(float) * 3 * n) && nr.alloc(sizeof(float) * 3 * n);
         WorkDesc W; memset(&W, 0, sizeof(W));
-        W.kind = Work_Rays; W.ro = (const F4*)dRo.p; W.rd = (const F4*)dRd.p; W.count = n;
+        W.kind = Work_Rays; W.ro = dRo; W.rd = dRd; W.count = n;
         W.passBase = pass; W.seed = scene->config.seed; W.salt = Salt_Rays;
-        W.sumColor = (float*)c.p; W.sumAlbedo = (float*)a.p; W.sumNormal = (float*)nr.p; W.accumulate = 0;
+        W.sumColor = c; W.sumAlbedo = a; W.sumNormal = nr; W.accumulate = 0;
         float ms = 0.0f;
-        ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
+        ok = runWavefront(scene->view, scene->pool, W, st, &ms);
         g_lastKernelMs = ms;
-        // interleave on the host side of the copy: three strided 2D copies into PtResult
-        ok = ok && PT_CUDA(cudaMemcpy2DAsync((float*)dOut.p + 0, 36, c.p, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
-        ok = ok && PT_CUDA(cudaMemcpy2DAsync((float*)dOut.p + 3, 36, a.p, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
-        ok = ok && PT_CUDA(cudaMemcpy2DAsync((float*)dOut.p + 6, 36, nr.p, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
-        ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+        // interleave on the device side of the copy: three strided 2D copies into PtResult
+        ok = ok && PT_CUDA(cudaMemcpy2DAsync(dOut + 0, 36, c, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
+        ok = ok && PT_CUDA(cudaMemcpy2DAsync(dOut + 3, 36, a, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
+        ok = ok && PT_CUDA(cudaMemcpy2DAsync(dOut + 6, 36, nr, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
     }
-    ok = ok && PT_CUDA(cudaMemcpyAsync(resultsOut, dOut.p, sizeof(float) * 9 * n, cudaMemcpyDeviceToHost, st));
-    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    ok = ok && PT_CUDA(cudaMemcpyAsync(resultsOut, dOut, sizeof(float) * 9 * n, cudaMemcpyDeviceToHost, st));
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
 }
 
@@ -674,6 +851,8 @@ int32_t Pt_TraceRayN_NoAlloc(PtScene* scene, const void* dRo, const void* dRd, u
                  (long long)n, PT_NOALLOC_MAX_PATHS);
         return -1;
     }
+    // the scratch array is per device: the one resolved is the current device's, which must be the scene's
+    if (!onSceneDevice(scene, "Pt_TraceRayN_NoAlloc")) return -1;
     cudaStream_t st = stream ? (cudaStream_t)stream : scene->stream;
     return runWavefrontNoAlloc(scene->view, (const F4*)dRo, (const F4*)dRd, n, pass, scene->config.seed, (float*)dColor3,
                                (float*)dAlbedo3, (float*)dNormal3, st) ? 0 : -1;
@@ -703,12 +882,12 @@ int32_t Pt_TraceSpp(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera
     if (sppCount <= 0) return 0;
     DeviceImages* im = traceImages(trace);
     if (!im) return -1;
-    cudaStream_t st = scene->stream;
     const int w = trace->imageSize.x, h = trace->imageSize.y;
     const int64_t n3 = im->texels * 3;
     bool ok = true;
-    for (int k = 0; k < 3; ++k) ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[k], 0, sizeof(float) * n3, st));
-    ok = ok && traceSppDevice(scene, camera, dof, w, h, sppBegin, sppCount, im->sum[0], im->sum[1], im->sum[2], st);
+    for (int k = 0; k < 3; ++k) ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[k], 0, sizeof(float) * n3, scene->stream));
+    ok = ok && traceSppDevice(scene, camera, dof, w, h, sppBegin, sppCount, im->sum[0], im->sum[1], im->sum[2], scene->stream);
+    cudaStream_t st = scene->stream;
     float* host[3] = { (float*)trace->color, (float*)trace->albedo, (float*)trace->normal };
     for (int k = 0; ok && k < 3; ++k)
     {
@@ -722,7 +901,7 @@ int32_t Pt_TraceSpp(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera
             ok = PT_CUDA(cudaMemcpyAsync(host[k], im->sum[k], sizeof(float) * n3, cudaMemcpyDeviceToHost, st));
         }
     }
-    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
 }
 
@@ -732,13 +911,28 @@ void Pt_Trace(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera* came
     if (!trace || !dof || !scene || !camera || !trace->color) { setError("Pt_Trace: null argument"); return; }
     DeviceImages* im = traceImages(trace);
     if (!im) return;
-    cudaStream_t st = scene->stream;
     const int w = trace->imageSize.x, h = trace->imageSize.y;
     const int64_t n3 = im->texels * 3;
+    if (!sceneRefresh(scene, scene->stream)) return;    // PtScene_Update first (:2573), so that DofUpdate sees the current scene
     if (!dofUpdate(scene, dof, camera)) return;
+    cudaStream_t st = scene->stream;
     bool ok = true;
     for (int k = 0; k < 3; ++k) ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[k], 0, sizeof(float) * n3, st));
-    ok = ok && traceSppDevice(scene, camera, dof, w, h, (int32_t)scene->nextPass, 1, im->sum[0], im->sum[1], im->sum[2], st);
+    {
+        // the CDFs were relearned just above: trace without a second PtScene_Update
+        WorkDesc W; memset(&W, 0, sizeof(W));
+        W.kind = Work_Camera;
+        W.cam = makeCam(camera, dof, w, h);
+        W.count = (int64_t)w * h;
+        W.passBase = scene->nextPass;
+        W.seed = scene->config.seed;
+        W.salt = Salt_Trace;
+        W.sumColor = im->sum[0]; W.sumAlbedo = im->sum[1]; W.sumNormal = im->sum[2];
+        W.accumulate = 1;
+        float ms = 0.0f;
+        ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
+        g_lastKernelMs = ms;
+    }
     scene->nextPass++;
     float* host[3] = { (float*)trace->color, (float*)trace->albedo, (float*)trace->normal };
     for (int k = 0; ok && k < 3; ++k)
@@ -746,7 +940,7 @@ void Pt_Trace(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera* came
         ok = launchLerp(im->image[k], im->sum[k], n3, trace->sampleWeight, st);
         ok = ok && PT_CUDA(cudaMemcpyAsync(host[k], im->image[k], sizeof(float) * n3, cudaMemcpyDeviceToHost, st));
     }
-    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
 }
 
 PtResults Pt_RayGen(PtScene* scene, pim_float4 origin, int32_t count)      // path_tracer.c:2615-2644
@@ -764,27 +958,27 @@ PtResults Pt_RayGen(PtScene* scene, pim_float4 origin, int32_t count)      // pa
         if (!PT_CUDA(cudaMallocHost((void**)&scene->rayGenDirs[slot], sizeof(F4) * (size_t)count))) return res;
         scene->rayGenCap[slot] = count;
     }
+    float *c = nullptr, *hc = nullptr; F4* d = nullptr;
+    Lease lease;
+    if (!lease.dev(c, 3 * (size_t)count).dev(d, (size_t)count).host(hc, 3 * (size_t)count).commit()) return res;
+    bool ok = sceneRefresh(scene, scene->stream);
     cudaStream_t st = scene->stream;
-    DevBuf c, d;
-    if (!c.alloc(sizeof(float) * 3 * (size_t)count) || !d.alloc(sizeof(F4) * (size_t)count)) return res;
-    bool ok = launchDistUpdate(scene->view, st);
     WorkDesc W; memset(&W, 0, sizeof(W));
     W.kind = Work_Sphere; W.origin = v3(origin.x, origin.y, origin.z); W.count = count;
     W.passBase = scene->nextPass++; W.seed = scene->config.seed; W.salt = Salt_RayGen;
-    W.sumColor = (float*)c.p; W.directions = (F4*)d.p; W.accumulate = 0;
+    W.sumColor = c; W.directions = d; W.accumulate = 0;
     float ms = 0.0f;
     ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
     g_lastKernelMs = ms;
     // colours come back as float3; widen to the reference's float4 (w = 0)
-    ok = ok && PT_CUDA(cudaMemcpyAsync(scene->rayGenDirs[slot], d.p, sizeof(F4) * (size_t)count, cudaMemcpyDeviceToHost, st));
-    std::vector<float> tmp((size_t)count * 3);
-    ok = ok && PT_CUDA(cudaMemcpyAsync(tmp.data(), c.p, sizeof(float) * 3 * (size_t)count, cudaMemcpyDeviceToHost, st));
-    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    ok = ok && PT_CUDA(cudaMemcpyAsync(scene->rayGenDirs[slot], d, sizeof(F4) * (size_t)count, cudaMemcpyDeviceToHost, st));
+    ok = ok && PT_CUDA(cudaMemcpyAsync(hc, c, sizeof(float) * 3 * (size_t)count, cudaMemcpyDeviceToHost, st));
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     if (!ok) return res;
     for (int32_t i = 0; i < count; ++i)
     {
-        scene->rayGenColors[slot][i].x = tmp[3 * (size_t)i]; scene->rayGenColors[slot][i].y = tmp[3 * (size_t)i + 1];
-        scene->rayGenColors[slot][i].z = tmp[3 * (size_t)i + 2]; scene->rayGenColors[slot][i].w = 0.0f;
+        scene->rayGenColors[slot][i].x = hc[3 * (size_t)i]; scene->rayGenColors[slot][i].y = hc[3 * (size_t)i + 1];
+        scene->rayGenColors[slot][i].z = hc[3 * (size_t)i + 2]; scene->rayGenColors[slot][i].w = 0.0f;
     }
     res.colors = scene->rayGenColors[slot];
     res.directions = scene->rayGenDirs[slot];
@@ -801,38 +995,86 @@ static bool bakePageDevice(PtScene* scene, const LightmapView& view, float texel
                                        scene->config.seed, st);
 }
 
+// Host pages move sparsely. BakeFn skips every texel whose sampleCounts entry is 0 (lightmap.c:1145-1149)
+// — the texels no chart covers, usually most of an atlas page (cornell at 16 texels/m: 54 437 of 1 048 576)
+// — so only the covered texels' 108 bytes travel: the host compacts them into page-locked staging, one
+// copy takes them to the device, a kernel scatters them into a full-size device page whose sampleCounts
+// were zeroed, the bake runs on that page exactly as it would on a resident one, and probes + counts of
+// the same texels come back the same way. A dense page costs the same bytes as a plain copy plus 4 B of
+// index per texel; the cornell page costs 5.9 MB each way instead of 113 MB.
 int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCount, float texelsPerMeter, float timeSlice,
                         int32_t spp, uint32_t pass)
 {
     if (!scene || (!lightmaps && lmCount > 0)) { setError("LmPack_BakeDesc: null argument"); return -1; }
+    if (lmCount <= 0) return 0;
+    size_t maxTexels = 0;
+    for (int32_t i = 0; i < lmCount; ++i)
+    {
+        const PtLightmapDesc& lm = lightmaps[i];
+        if (lm.size <= 0 || !lm.position || !lm.normal || !lm.sampleCounts || !lm.probes[0] || !lm.probes[1] || !lm.probes[2] ||
+            !lm.probes[3] || !lm.probes[4]) { setError("LmPack_BakeDesc: page %d has no storage", i); return -1; }
+        maxTexels = std::max(maxTexels, (size_t)lm.size * (size_t)lm.size);
+    }
+    // worst case: every texel of the largest page is covered
+    F4* dProbes = nullptr; float *dPos = nullptr, *dNrm = nullptr, *dCnt = nullptr;          // the full-size device page
+    int32_t *dIdx = nullptr, *hIdx = nullptr;
+    F4 *dCProbes = nullptr, *hCProbes = nullptr;                                             // compacted staging, both sides
+    float *dCPos = nullptr, *hCPos = nullptr, *dCNrm = nullptr, *hCNrm = nullptr, *dCCnt = nullptr, *hCCnt = nullptr;
+    Lease lease;
+    lease.dev(dProbes, 5 * maxTexels).dev(dPos, 3 * maxTexels).dev(dNrm, 3 * maxTexels).dev(dCnt, maxTexels)
+         .dev(dIdx, maxTexels).dev(dCProbes, 5 * maxTexels).dev(dCPos, 3 * maxTexels).dev(dCNrm, 3 * maxTexels).dev(dCCnt, maxTexels)
+         .host(hIdx, maxTexels).host(hCProbes, 5 * maxTexels).host(hCPos, 3 * maxTexels).host(hCNrm, 3 * maxTexels).host(hCCnt, maxTexels);
+    if (!lease.commit()) return -1;
+    bool ok = sceneRefresh(scene, scene->stream);       // LmPack_Bake -> PtScene_Update (lightmap.c:1209)
     cudaStream_t st = scene->stream;
-    bool ok = launchDistUpdate(scene->view, st);       // LmPack_Bake -> PtScene_Update (lightmap.c:1209)
     int32_t texelBase = 0;
     for (int32_t i = 0; ok && i < lmCount; ++i)
     {
         PtLightmapDesc& lm = lightmaps[i];
         const size_t n = (size_t)lm.size * (size_t)lm.size;
-        DevBuf probes[5], pos, nrm, cnt;
-        LightmapView view;
-        for (int k = 0; ok && k < 5; ++k)
+        // covered texels, compacted on the host
+        int32_t m = 0;
+        for (size_t t = 0; t < n; ++t) if (lm.sampleCounts[t] != 0.0f) hIdx[m++] = (int32_t)t;
+        const float* pos = (const float*)lm.position; const float* nrm = (const float*)lm.normal;
+        for (int32_t j = 0; j < m; ++j)
         {
-            ok = probes[k].alloc(sizeof(F4) * n) &&
-                 PT_CUDA(cudaMemcpyAsync(probes[k].p, lm.probes[k], sizeof(F4) * n, cudaMemcpyHostToDevice, st));
-            view.probes[k] = (F4*)probes[k].p;
+            const size_t t = (size_t)hIdx[j];
+            for (int k = 0; k < 5; ++k) hCProbes[(size_t)k * m + j] = *(const F4*)&lm.probes[k][t];
+            hCPos[3 * j] = pos[3 * t]; hCPos[3 * j + 1] = pos[3 * t + 1]; hCPos[3 * j + 2] = pos[3 * t + 2];
+            hCNrm[3 * j] = nrm[3 * t]; hCNrm[3 * j + 1] = nrm[3 * t + 1]; hCNrm[3 * j + 2] = nrm[3 * t + 2];
+            hCCnt[j] = lm.sampleCounts[t];
         }
-        ok = ok && pos.alloc(12 * n) && nrm.alloc(12 * n) && cnt.alloc(4 * n);
-        ok = ok && PT_CUDA(cudaMemcpyAsync(pos.p, lm.position, 12 * n, cudaMemcpyHostToDevice, st));
-        ok = ok && PT_CUDA(cudaMemcpyAsync(nrm.p, lm.normal, 12 * n, cudaMemcpyHostToDevice, st));
-        ok = ok && PT_CUDA(cudaMemcpyAsync(cnt.p, lm.sampleCounts, 4 * n, cudaMemcpyHostToDevice, st));
-        view.position = (const float*)pos.p; view.normal = (const float*)nrm.p; view.sampleCounts = (float*)cnt.p;
+        LightmapView view;
+        for (int k = 0; k < 5; ++k) view.probes[k] = dProbes + (size_t)k * n;
+        view.position = dPos; view.normal = dNrm; view.sampleCounts = dCnt;
         view.texelCount = (int32_t)n; view.texelBase = texelBase;
-        ok = ok && bakePageDevice(scene, view, texelsPerMeter, timeSlice, spp, pass, st);
-        for (int k = 0; ok && k < 5; ++k)
-            ok = PT_CUDA(cudaMemcpyAsync(lm.probes[k], probes[k].p, sizeof(F4) * n, cudaMemcpyDeviceToHost, st));
-        ok = ok && PT_CUDA(cudaMemcpyAsync(lm.sampleCounts, cnt.p, 4 * n, cudaMemcpyDeviceToHost, st));
-        ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+        ok = PT_CUDA(cudaMemsetAsync(dCnt, 0, sizeof(float) * n, st));
+        if (ok && m > 0)
+        {
+            ok = PT_CUDA(cudaMemcpyAsync(dIdx, hIdx, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, st)) &&
+                 PT_CUDA(cudaMemcpyAsync(dCProbes, hCProbes, sizeof(F4) * 5 * (size_t)m, cudaMemcpyHostToDevice, st)) &&
+                 PT_CUDA(cudaMemcpyAsync(dCPos, hCPos, 12 * (size_t)m, cudaMemcpyHostToDevice, st)) &&
+                 PT_CUDA(cudaMemcpyAsync(dCNrm, hCNrm, 12 * (size_t)m, cudaMemcpyHostToDevice, st)) &&
+                 PT_CUDA(cudaMemcpyAsync(dCCnt, hCCnt, 4 * (size_t)m, cudaMemcpyHostToDevice, st)) &&
+                 launchLightmapScatter(view, dIdx, m, dCProbes, dCPos, dCNrm, dCCnt, st);
+            ok = ok && bakePageDevice(scene, view, texelsPerMeter, timeSlice, spp, pass, st);
+            ok = ok && launchLightmapGather(view, dIdx, m, dCProbes, dCCnt, st);
+            ok = ok && PT_CUDA(cudaMemcpyAsync(hCProbes, dCProbes, sizeof(F4) * 5 * (size_t)m, cudaMemcpyDeviceToHost, st));
+            ok = ok && PT_CUDA(cudaMemcpyAsync(hCCnt, dCCnt, 4 * (size_t)m, cudaMemcpyDeviceToHost, st));
+            ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
+            if (ok)
+            {
+                for (int32_t j = 0; j < m; ++j)
+                {
+                    const size_t t = (size_t)hIdx[j];
+                    for (int k = 0; k < 5; ++k) *(F4*)&lm.probes[k][t] = hCProbes[(size_t)k * m + j];
+                    lm.sampleCounts[t] = hCCnt[j];
+                }
+            }
+        }
         texelBase += (int32_t)n;
     }
+    if (!ok) cudaStreamSynchronize(st);
     return ok ? 0 : -1;
 }
 
@@ -840,10 +1082,12 @@ int32_t LmPack_BakeDesc_Device(PtScene* scene, const PtLightmapDesc* lightmaps, 
                                float timeSlice, int32_t spp, uint32_t pass)
 {
     if (!scene || (!lightmaps && lmCount > 0)) { setError("LmPack_BakeDesc_Device: null argument"); return -1; }
+    Lease lease;                                // only for the timer's events and the lock
+    if (!lease.commit()) return -1;
+    bool ok = sceneRefresh(scene, scene->stream);
     cudaStream_t st = scene->stream;
-    bool ok = launchDistUpdate(scene->view, st);
     int32_t texelBase = 0;
-    KernelTimer timer(st);
+    KernelTimer timer(lease, st);
     for (int32_t i = 0; ok && i < lmCount; ++i)
     {
         const PtLightmapDesc& lm = lightmaps[i];
@@ -857,8 +1101,32 @@ int32_t LmPack_BakeDesc_Device(PtScene* scene, const PtLightmapDesc* lightmaps, 
         texelBase += (int32_t)n;
     }
     timer.stop();
-    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
+}
+
+// LmPack_Bake under the reference's name and signature (src/rendering/lightmap.h:69, body lightmap.c:1204-1223).
+// The reference bakes the engine's global pack (LmPack_Get()); PtSys_SetLmPack is the adapter's stand-in for
+// that global. The pass index is the scene's running counter (the reference draws from its thread generators).
+void PtSys_SetLmPack(const PtLightmapDesc* lightmaps, int32_t lmCount, float texelsPerMeter)
+{
+    g_lmPack.clear();
+    g_lmTexelsPerMeter = texelsPerMeter;
+    if (lightmaps && lmCount > 0) g_lmPack.assign(lightmaps, lightmaps + lmCount);
+}
+
+void LmPack_Bake(PtScene* scene, float timeSlice, int32_t spp)
+{
+    t_error[0] = 0;
+    if (!scene) { setError("LmPack_Bake: null scene"); return; }
+    if (g_lmPack.empty())
+    {
+        PtScene_Update(scene);      // an empty pack still relearns the light grid (lightmap.c:1209)
+        return;
+    }
+    if (!(g_lmTexelsPerMeter > 0.0f)) { setError("LmPack_Bake: the registered pack has no texel density"); return; }
+    LmPack_BakeDesc(scene, g_lmPack.data(), (int32_t)g_lmPack.size(), g_lmTexelsPerMeter, timeSlice, spp < 1 ? 1 : spp,
+                    scene->nextPass++);
 }
 
 // ---- cubemap / ambient-cube bakes, sky bake, screenshot tonemap ----
@@ -931,20 +1199,22 @@ int32_t Cubemap_BakePass(Cubemap* cm, PtScene* scene, pim_float4 origin, float w
     if (!cubeValid(cm, "Cubemap_Bake", false)) return -1;
     const int64_t n = 6ll * cm->size * cm->size;
     cudaStream_t st = scene->stream;
-    DevBuf dColor, dRo, dRd, dRes;
-    if (!dColor.alloc(12 * n) || !dRo.alloc(16 * n) || !dRd.alloc(16 * n) || !dRes.alloc(12 * n)) return -1;
-    bool ok = cubeUpload(cm, (float*)dColor.p, nullptr, st);
-    KernelTimer timer(st);
-    ok = ok && launchCubeRays(cm->size, v3(origin.x, origin.y, origin.z), pass, scene->config.seed, (F4*)dRo.p, (F4*)dRd.p, st);
+    float *dColor = nullptr, *dRes = nullptr; F4 *dRo = nullptr, *dRd = nullptr;
+    Lease lease;
+    if (!lease.dev(dColor, 3 * (size_t)n).dev(dRo, (size_t)n).dev(dRd, (size_t)n).dev(dRes, 3 * (size_t)n).commit()) return -1;
+    bool ok = cubeUpload(cm, dColor, nullptr, st);
+    KernelTimer timer(lease, st);
+    ok = ok && launchCubeRays(cm->size, v3(origin.x, origin.y, origin.z), pass, scene->config.seed, dRo, dRd, st);
     WorkDesc W; memset(&W, 0, sizeof(W));
-    W.kind = Work_Rays; W.ro = (const F4*)dRo.p; W.rd = (const F4*)dRd.p; W.count = n;
+    W.kind = Work_Rays; W.ro = dRo; W.rd = dRd; W.count = n;
     W.passBase = pass; W.seed = scene->config.seed; W.salt = Salt_CubeBake;
-    W.sumColor = (float*)dRes.p; W.accumulate = 0;
+    W.sumColor = dRes; W.accumulate = 0;
     float ms = 0.0f;
     ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
-    ok = ok && launchLerp((float*)dColor.p, (const float*)dRes.p, 3 * n, weight, st);      // f3_lerpvs, cubemap.c:158
+    ok = ok && launchLerp(dColor, dRes, 3 * n, weight, st);      // f3_lerpvs, cubemap.c:158
     timer.stop();
-    ok = ok && cubeDownload(cm, (const float*)dColor.p, nullptr, st);
+    ok = ok && cubeDownload(cm, dColor, nullptr, st);
+    if (!ok) cudaStreamSynchronize(st);
     return ok ? 0 : -1;
 }
 
@@ -960,14 +1230,16 @@ int32_t Cubemap_ConvolvePass(Cubemap* cm, uint32_t sampleCount, float weight, ui
     if (!ensureInit()) return -1;
     if (!cubeValid(cm, "Cubemap_Convolve", true)) return -1;
     const size_t len = (size_t)cm->size * cm->size, elemCount = (size_t)cubemapElemCount(cm->size);
-    DevBuf dColor, dConv;
-    if (!dColor.alloc(12 * len * 6) || !dConv.alloc(16 * elemCount * 6)) return -1;
+    float *dColor = nullptr, *dConv = nullptr;
+    Lease lease;
+    if (!lease.dev(dColor, 3 * len * 6).dev(dConv, 4 * elemCount * 6).commit()) return -1;
     cudaStream_t st = nullptr;
-    bool ok = cubeUpload(cm, (float*)dColor.p, (float*)dConv.p, st);
-    KernelTimer timer(st);
-    ok = ok && launchCubeConvolve((const float*)dColor.p, (float*)dConv.p, cm->size, sampleCount, weight, pass, seed, st);
+    bool ok = cubeUpload(cm, dColor, dConv, st);
+    KernelTimer timer(lease, st);
+    ok = ok && launchCubeConvolve(dColor, dConv, cm->size, sampleCount, weight, pass, seed, st);
     timer.stop();
-    ok = ok && cubeDownload(cm, nullptr, (const float*)dConv.p, st);
+    ok = ok && cubeDownload(cm, nullptr, dConv, st);
+    if (!ok) cudaStreamSynchronize(st);
     return ok ? 0 : -1;
 }
 
@@ -979,24 +1251,25 @@ void Cubemap_Convolve(Cubemap* cm, uint32_t sampleCount, float weight)
 int32_t AmbCube_Bake(PtScene* scene, AmbCube_t* pCube, pim_float4 origin, int32_t samples, int32_t prevSampleCount)   // ambcube.c:5-33
 {
     if (!scene || !pCube || samples < 0 || prevSampleCount < 0) { setError("AmbCube_Bake: bad argument"); return prevSampleCount; }
-    cudaStream_t st = scene->stream;
     if (samples > 0)
     {
-        DevBuf c, d, cube;
-        if (!c.alloc(sizeof(float) * 3 * (size_t)samples) || !d.alloc(sizeof(F4) * (size_t)samples) || !cube.alloc(sizeof(F4) * 6)) return prevSampleCount;
+        float* c = nullptr; F4 *d = nullptr, *cube = nullptr;
+        Lease lease;
+        if (!lease.dev(c, 3 * (size_t)samples).dev(d, (size_t)samples).dev(cube, 6).commit()) return prevSampleCount;
         // Pt_RayGen (path_tracer.c:2615-2644), results left on the device
-        bool ok = launchDistUpdate(scene->view, st);
+        bool ok = sceneRefresh(scene, scene->stream);
+        cudaStream_t st = scene->stream;
         WorkDesc W; memset(&W, 0, sizeof(W));
         W.kind = Work_Sphere; W.origin = v3(origin.x, origin.y, origin.z); W.count = samples;
         W.passBase = scene->nextPass++; W.seed = scene->config.seed; W.salt = Salt_RayGen;
-        W.sumColor = (float*)c.p; W.directions = (F4*)d.p; W.accumulate = 0;
+        W.sumColor = c; W.directions = d; W.accumulate = 0;
         float ms = 0.0f;
         ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
         g_lastKernelMs = ms;
-        ok = ok && PT_CUDA(cudaMemcpyAsync(cube.p, pCube, sizeof(F4) * 6, cudaMemcpyHostToDevice, st));
-        ok = ok && launchAmbCubeFit((F4*)cube.p, (const F4*)d.p, (const float*)c.p, samples, prevSampleCount, st);
-        ok = ok && PT_CUDA(cudaMemcpyAsync(pCube, cube.p, sizeof(F4) * 6, cudaMemcpyDeviceToHost, st));
-        ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+        ok = ok && PT_CUDA(cudaMemcpyAsync(cube, pCube, sizeof(F4) * 6, cudaMemcpyHostToDevice, st));
+        ok = ok && launchAmbCubeFit(cube, d, c, samples, prevSampleCount, st);
+        ok = ok && PT_CUDA(cudaMemcpyAsync(pCube, cube, sizeof(F4) * 6, cudaMemcpyDeviceToHost, st));
+        ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
         if (!ok) return prevSampleCount;
     }
     return prevSampleCount + 1;
@@ -1062,10 +1335,11 @@ int32_t LmPack_EmbedDesc(const PtEmbedMesh* meshes, int32_t meshCount, PtLightma
     if (triCount > 0xffffffffll) { setError("LmPack_EmbedDesc: more than 2^32 triangles"); return -1; }
     const size_t texels = (size_t)lmCount * lmSize * lmSize;
     cudaStream_t st = nullptr;
-    DevBuf dPos, dNor, dUv, dPage, dKeys, dOutPos, dOutNor, dOutCnt;
-    if (!dPos.alloc(16 * 3 * (size_t)triCount) || !dNor.alloc(16 * 3 * (size_t)triCount) || !dUv.alloc(16 * 3 * (size_t)triCount) ||
-        !dPage.alloc(4 * (size_t)triCount) || !dKeys.alloc(8 * texels) || !dOutPos.alloc(12 * texels) || !dOutNor.alloc(12 * texels) ||
-        !dOutCnt.alloc(4 * texels)) return -1;
+    F4 *dPos = nullptr, *dNor = nullptr, *dUv = nullptr; int32_t* dPage = nullptr; unsigned long long* dKeys = nullptr;
+    float *dOutPos = nullptr, *dOutNor = nullptr, *dOutCnt = nullptr;
+    Lease lease;
+    if (!lease.dev(dPos, 3 * (size_t)triCount).dev(dNor, 3 * (size_t)triCount).dev(dUv, 3 * (size_t)triCount).dev(dPage, (size_t)triCount)
+              .dev(dKeys, texels).dev(dOutPos, 3 * texels).dev(dOutNor, 3 * texels).dev(dOutCnt, texels).commit()) return -1;
     std::vector<int32_t> page((size_t)triCount);
     bool ok = true;
     int64_t base = 0;
@@ -1083,27 +1357,27 @@ int32_t LmPack_EmbedDesc(const PtEmbedMesh* meshes, int32_t meshCount, PtLightma
             page[(size_t)(base + t)] = p;
         }
         const size_t bytes = 16 * 3 * (size_t)nt, off = 3 * (size_t)base;
-        ok = PT_CUDA(cudaMemcpyAsync((F4*)dPos.p + off, m.positions, bytes, cudaMemcpyHostToDevice, st)) &&
-             PT_CUDA(cudaMemcpyAsync((F4*)dNor.p + off, m.normals, bytes, cudaMemcpyHostToDevice, st)) &&
-             PT_CUDA(cudaMemcpyAsync((F4*)dUv.p + off, m.uvs, bytes, cudaMemcpyHostToDevice, st));
+        ok = PT_CUDA(cudaMemcpyAsync(dPos + off, m.positions, bytes, cudaMemcpyHostToDevice, st)) &&
+             PT_CUDA(cudaMemcpyAsync(dNor + off, m.normals, bytes, cudaMemcpyHostToDevice, st)) &&
+             PT_CUDA(cudaMemcpyAsync(dUv + off, m.uvs, bytes, cudaMemcpyHostToDevice, st));
         base += nt;
     }
-    ok = ok && PT_CUDA(cudaMemcpyAsync(dPage.p, page.data(), 4 * (size_t)triCount, cudaMemcpyHostToDevice, st));
-    ok = ok && PT_CUDA(cudaMemsetAsync(dKeys.p, 0xff, 8 * texels, st));
+    ok = ok && PT_CUDA(cudaMemcpyAsync(dPage, page.data(), 4 * (size_t)triCount, cudaMemcpyHostToDevice, st));
+    ok = ok && PT_CUDA(cudaMemsetAsync(dKeys, 0xff, 8 * texels, st));
     EmbedMesh M;
-    M.positions = (const F4*)dPos.p; M.normals = (const F4*)dNor.p; M.uvs = (const F4*)dUv.p;
-    M.page = (const int32_t*)dPage.p; M.triCount = triCount;
-    KernelTimer timer(st);
-    ok = ok && launchEmbed(M, lmSize, lmCount, (unsigned long long*)dKeys.p, (float*)dOutPos.p, (float*)dOutNor.p, (float*)dOutCnt.p, st);
+    M.positions = dPos; M.normals = dNor; M.uvs = dUv;
+    M.page = dPage; M.triCount = triCount;
+    KernelTimer timer(lease, st);
+    ok = ok && launchEmbed(M, lmSize, lmCount, dKeys, dOutPos, dOutNor, dOutCnt, st);
     timer.stop();
     const size_t n = (size_t)lmSize * lmSize;
     for (int32_t k = 0; ok && k < lmCount; ++k)
     {
-        ok = PT_CUDA(cudaMemcpyAsync((void*)lightmaps[k].position, (float*)dOutPos.p + 3 * n * k, 12 * n, cudaMemcpyDeviceToHost, st)) &&
-             PT_CUDA(cudaMemcpyAsync((void*)lightmaps[k].normal, (float*)dOutNor.p + 3 * n * k, 12 * n, cudaMemcpyDeviceToHost, st)) &&
-             PT_CUDA(cudaMemcpyAsync(lightmaps[k].sampleCounts, (float*)dOutCnt.p + n * k, 4 * n, cudaMemcpyDeviceToHost, st));
+        ok = PT_CUDA(cudaMemcpyAsync((void*)lightmaps[k].position, dOutPos + 3 * n * k, 12 * n, cudaMemcpyDeviceToHost, st)) &&
+             PT_CUDA(cudaMemcpyAsync((void*)lightmaps[k].normal, dOutNor + 3 * n * k, 12 * n, cudaMemcpyDeviceToHost, st)) &&
+             PT_CUDA(cudaMemcpyAsync(lightmaps[k].sampleCounts, dOutCnt + n * k, 4 * n, cudaMemcpyDeviceToHost, st));
     }
-    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
 }
 
@@ -1113,16 +1387,18 @@ int32_t Pt_BakeSky(Cubemap* cm, const SkyMedium* sky, pim_float3 sunDir, float s
     if (!sky) { setError("Pt_BakeSky: null medium"); return -1; }
     if (!cubeValid(cm, "Pt_BakeSky", false)) return -1;
     const size_t len = (size_t)cm->size * cm->size;
-    DevBuf dColor;
-    if (!dColor.alloc(12 * len * 6)) return -1;
+    float* dColor = nullptr;
+    Lease lease;
+    if (!lease.dev(dColor, 3 * len * 6).commit()) return -1;
     SkyParams A;
     A.rCrust = sky->rCrust; A.rAtmos = sky->rAtmos; A.muR = v3(sky->muR.x, sky->muR.y, sky->muR.z);
     A.rhoR = sky->rhoR; A.muM = sky->muM; A.rhoM = sky->rhoM; A.gM = sky->gM;
     cudaStream_t st = nullptr;
-    KernelTimer timer(st);
-    bool ok = launchSkyBake(A, cm->size, v3(sunDir.x, sunDir.y, sunDir.z), sunLum, steps, (float*)dColor.p, st);
+    KernelTimer timer(lease, st);
+    bool ok = launchSkyBake(A, cm->size, v3(sunDir.x, sunDir.y, sunDir.z), sunLum, steps, dColor, st);
     timer.stop();
-    ok = ok && cubeDownload(cm, (const float*)dColor.p, nullptr, st);
+    ok = ok && cubeDownload(cm, dColor, nullptr, st);
+    if (!ok) cudaStreamSynchronize(st);
     return ok ? 0 : -1;
 }
 
@@ -1131,15 +1407,16 @@ int32_t Pt_Tonemap(const pim_float4* light, int64_t count, float exposure, uint3
     if (!ensureInit()) return -1;
     if (count <= 0) return 0;
     if (!light || !rgba8Out) { setError("Pt_Tonemap: null argument"); return -1; }
-    DevBuf dLight, dOut;
-    if (!dLight.alloc(16 * (size_t)count) || !dOut.alloc(4 * (size_t)count)) return -1;
+    F4* dLight = nullptr; uint32_t* dOut = nullptr;
+    Lease lease;
+    if (!lease.dev(dLight, (size_t)count).dev(dOut, (size_t)count).commit()) return -1;
     cudaStream_t st = nullptr;
-    bool ok = PT_CUDA(cudaMemcpyAsync(dLight.p, light, 16 * (size_t)count, cudaMemcpyHostToDevice, st));
-    KernelTimer timer(st);
-    ok = ok && launchTonemap((const F4*)dLight.p, count, exposure, pass, seed, (uint32_t*)dOut.p, st);
+    bool ok = PT_CUDA(cudaMemcpyAsync(dLight, light, 16 * (size_t)count, cudaMemcpyHostToDevice, st));
+    KernelTimer timer(lease, st);
+    ok = ok && launchTonemap(dLight, count, exposure, pass, seed, dOut, st);
     timer.stop();
-    ok = ok && PT_CUDA(cudaMemcpyAsync(rgba8Out, dOut.p, 4 * (size_t)count, cudaMemcpyDeviceToHost, st));
-    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    ok = ok && PT_CUDA(cudaMemcpyAsync(rgba8Out, dOut, 4 * (size_t)count, cudaMemcpyDeviceToHost, st));
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
 }
 
@@ -1155,18 +1432,18 @@ int32_t Pt_RepackRome(const pim_float4* mr, pim_int2 mrSize, const pim_float4* o
     }
     const size_t nMr = (size_t)mrSize.x * mrSize.y, nOcc = (size_t)occSize.x * occSize.y, nEm = (size_t)emSize.x * emSize.y;
     const size_t n = (size_t)size * size;
-    DevBuf dMr, dOcc, dEm, dOut;
-    if (!dMr.alloc(16 * nMr) || !dOcc.alloc(16 * nOcc) || !dEm.alloc(16 * nEm) || !dOut.alloc(4 * n)) return -1;
+    F4 *dMr = nullptr, *dOcc = nullptr, *dEm = nullptr; uint32_t* dOut = nullptr;
+    Lease lease;
+    if (!lease.dev(dMr, nMr).dev(dOcc, nOcc).dev(dEm, nEm).dev(dOut, n).commit()) return -1;
     cudaStream_t st = nullptr;
-    bool ok = PT_CUDA(cudaMemcpyAsync(dMr.p, mr, 16 * nMr, cudaMemcpyHostToDevice, st)) &&
-              PT_CUDA(cudaMemcpyAsync(dOcc.p, occ, 16 * nOcc, cudaMemcpyHostToDevice, st)) &&
-              PT_CUDA(cudaMemcpyAsync(dEm.p, em, 16 * nEm, cudaMemcpyHostToDevice, st));
-    KernelTimer timer(st);
-    ok = ok && launchRepackRome((const F4*)dMr.p, mrSize.x, mrSize.y, (const F4*)dOcc.p, occSize.x, occSize.y, (const F4*)dEm.p,
-                                emSize.x, emSize.y, size, (uint32_t*)dOut.p, st);
+    bool ok = PT_CUDA(cudaMemcpyAsync(dMr, mr, 16 * nMr, cudaMemcpyHostToDevice, st)) &&
+              PT_CUDA(cudaMemcpyAsync(dOcc, occ, 16 * nOcc, cudaMemcpyHostToDevice, st)) &&
+              PT_CUDA(cudaMemcpyAsync(dEm, em, 16 * nEm, cudaMemcpyHostToDevice, st));
+    KernelTimer timer(lease, st);
+    ok = ok && launchRepackRome(dMr, mrSize.x, mrSize.y, dOcc, occSize.x, occSize.y, dEm, emSize.x, emSize.y, size, dOut, st);
     timer.stop();
-    ok = ok && PT_CUDA(cudaMemcpyAsync(romeOut, dOut.p, 4 * n, cudaMemcpyDeviceToHost, st));
-    ok = ok && PT_CUDA(cudaStreamSynchronize(st));
+    ok = ok && PT_CUDA(cudaMemcpyAsync(romeOut, dOut, 4 * n, cudaMemcpyDeviceToHost, st));
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
 }
 
@@ -1283,16 +1560,28 @@ int32_t Pt_IntersectCountN(const PtScene* scene, const pim_float4* ro, const pim
                            uint64_t* nodeFetches, uint64_t* triFetches)
 {
     if (!scene || n <= 0) { setError("Pt_IntersectCountN: bad argument"); return -1; }
-    DevBuf dRo, dRd;
-    if (!dRo.alloc(sizeof(F4) * n) || !dRd.alloc(sizeof(F4) * n)) return -1;
+    F4 *dRo = nullptr, *dRd = nullptr; unsigned long long* dTotals = nullptr;
+    Lease lease;
+    if (!lease.dev(dRo, (size_t)n).dev(dRd, (size_t)n).dev(dTotals, 2).commit()) return -1;
     cudaStream_t st = scene->stream;
     unsigned long long a = 0, b = 0;
-    bool ok = PT_CUDA(cudaMemcpyAsync(dRo.p, ro, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
-              PT_CUDA(cudaMemcpyAsync(dRd.p, rd, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
-              launchIntersectCount(scene->view, (const F4*)dRo.p, (const F4*)dRd.p, tNear, n, &a, &b, st);
+    bool ok = PT_CUDA(cudaMemcpyAsync(dRo, ro, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
+              PT_CUDA(cudaMemcpyAsync(dRd, rd, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
+              launchIntersectCount(scene->view, dRo, dRd, tNear, n, dTotals, &a, &b, st);
+    if (!ok) cudaStreamSynchronize(st);
     *nodeFetches = a; *triFetches = b;
     return ok ? 0 : -1;
 }
 float Pt_LastKernelMs(void) { return g_lastKernelMs; }
+
+int32_t Pt_SetOption(const char* name, int32_t value)
+{
+    if (!name) return -1;
+    if (!ensureInit()) return -1;       // the environment's values are read first, then overridden here
+    if (!strcmp(name, "persistent")) { g_persistentTraversal = value; return 0; }
+    if (!strcmp(name, "finish")) { g_finishThreshold = value; return 0; }
+    setError("Pt_SetOption: unknown option '%s'", name);
+    return -1;
+}
 
 } // extern "C"

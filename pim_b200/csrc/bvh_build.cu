@@ -700,6 +700,7 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
             ok = ok && PT_CUDA(cudaMemcpyAsync(h, counters, sizeof(h), cudaMemcpyDeviceToHost, stream));
             ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
             levelCount = (int)h[2];
+            out.depth++;
             out.nodeCount = (int32_t)h[0];
             out.triCount = (int32_t)h[1];
             ok = ok && PT_CUDA(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), stream));

@@ -99,6 +99,53 @@ bool launchLightmapBake(const DScene& S, const LightmapView& lm, float metersPer
     return PT_CUDA(cudaGetLastError());
 }
 
+// ---------------------------------------------------------------- sparse page transfer
+// LmPack_BakeDesc moves only the texels a chart covers (sampleCounts != 0): idx[j] is the texel of
+// compact entry j; probes are lobe-major (5 x count), positions and normals float3, counts float.
+
+__global__ void __launch_bounds__(256) k_lmScatter(LightmapView lm, const int32_t* __restrict__ idx, int count,
+                                                   const F4* __restrict__ probes, const float* __restrict__ pos3,
+                                                   const float* __restrict__ nrm3, const float* __restrict__ cnt)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= count) return;
+    const int t = idx[j];
+    for (int k = 0; k < 5; ++k) lm.probes[k][t] = probes[(size_t)k * count + j];
+    float* p = const_cast<float*>(lm.position) + 3 * (size_t)t;
+    float* n = const_cast<float*>(lm.normal) + 3 * (size_t)t;
+    p[0] = pos3[3 * j]; p[1] = pos3[3 * j + 1]; p[2] = pos3[3 * j + 2];
+    n[0] = nrm3[3 * j]; n[1] = nrm3[3 * j + 1]; n[2] = nrm3[3 * j + 2];
+    lm.sampleCounts[t] = cnt[j];
+}
+
+__global__ void __launch_bounds__(256) k_lmGather(LightmapView lm, const int32_t* __restrict__ idx, int count,
+                                                  F4* __restrict__ probes, float* __restrict__ cnt)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= count) return;
+    const int t = idx[j];
+    for (int k = 0; k < 5; ++k) probes[(size_t)k * count + j] = lm.probes[k][t];
+    cnt[j] = lm.sampleCounts[t];
+}
+
+bool launchLightmapScatter(const LightmapView& lm, const int32_t* dIdx, int32_t count, const F4* dProbes, const float* dPos3,
+                           const float* dNrm3, const float* dCnt, cudaStream_t stream)
+{
+    if (count <= 0) return true;
+    k_lmScatter<<<(count + 255) / 256, 256, 0, stream>>>(lm, dIdx, count, dProbes, dPos3, dNrm3, dCnt);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
+bool launchLightmapGather(const LightmapView& lm, const int32_t* dIdx, int32_t count, F4* dProbes, float* dCnt,
+                          cudaStream_t stream)
+{
+    if (count <= 0) return true;
+    k_lmGather<<<(count + 255) / 256, 256, 0, stream>>>(lm, dIdx, count, dProbes, dCnt);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
 // ---------------------------------------------------------------- wavefront bake
 // The same BakeFn, arranged for the GPU: (1) pick the texels that bake this pass (covered,
 // time-slice draw) and compact them, (2) one thread per picked texel writes the hemisphere
@@ -189,10 +236,13 @@ bool launchLightmapBakeWavefront(const DScene& S, PathPool& pool, const Lightmap
 {
     if (lm.texelCount <= 0) return true;
     if (spp < 1) spp = 1;
-    int32_t* dActive = nullptr;
-    int32_t* dCount = nullptr;
-    bool ok = PT_CUDA(cudaMalloc((void**)&dActive, sizeof(int32_t) * (size_t)lm.texelCount)) &&
-              PT_CUDA(cudaMalloc((void**)&dCount, sizeof(int32_t)));
+    // scratch comes from the pool's growable block: [picked texels][counter][ray origins][directions]
+    // [colours][rng ids]; a steady-state pass allocates nothing
+    auto align = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t activeBytes = align(sizeof(int32_t) * (size_t)lm.texelCount), headBytes = activeBytes + 256;
+    bool ok = poolAux(pool, headBytes, 0, stream);
+    int32_t* dActive = (int32_t*)pool.aux;
+    int32_t* dCount = (int32_t*)((char*)pool.aux + activeBytes);
     ok = ok && PT_CUDA(cudaMemsetAsync(dCount, 0, sizeof(int32_t), stream));
     int32_t nActive = 0;
     if (ok)
@@ -204,13 +254,16 @@ bool launchLightmapBakeWavefront(const DScene& S, PathPool& pool, const Lightmap
     }
     // texels per chunk: at most ~8 M rays (76 B each) in flight
     const int chunkTexels = std::max(1, (8 << 20) / spp);
-    F4 *dRo = nullptr, *dRd = nullptr;
-    float* dColor = nullptr;
-    uint32_t* dIds = nullptr;
     const size_t chunkRays = (size_t)std::min(chunkTexels, std::max(nActive, 1)) * (size_t)spp;
-    ok = ok && PT_CUDA(cudaMalloc((void**)&dRo, sizeof(F4) * chunkRays)) && PT_CUDA(cudaMalloc((void**)&dRd, sizeof(F4) * chunkRays)) &&
-         PT_CUDA(cudaMalloc((void**)&dColor, sizeof(float) * 3 * chunkRays)) &&
-         PT_CUDA(cudaMalloc((void**)&dIds, sizeof(uint32_t) * chunkRays));
+    const size_t roBytes = align(sizeof(F4) * chunkRays), colBytes = align(sizeof(float) * 3 * chunkRays),
+                 idBytes = align(sizeof(uint32_t) * chunkRays);
+    ok = ok && poolAux(pool, headBytes + 2 * roBytes + colBytes + idBytes, headBytes, stream);
+    dActive = (int32_t*)pool.aux;       // the block may have moved (the picked texels moved with it)
+    char* q = (char*)pool.aux + headBytes;
+    F4* dRo = (F4*)q; q += roBytes;
+    F4* dRd = (F4*)q; q += roBytes;
+    float* dColor = (float*)q; q += colBytes;
+    uint32_t* dIds = (uint32_t*)q;
     for (int first = 0; ok && first < nActive; first += chunkTexels)
     {
         const int count = std::min(chunkTexels, nActive - first);
@@ -231,13 +284,7 @@ bool launchLightmapBakeWavefront(const DScene& S, PathPool& pool, const Lightmap
             ok = PT_CUDA(cudaGetLastError());
         }
     }
-    ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
-    if (dActive) cudaFree(dActive);
-    if (dCount) cudaFree(dCount);
-    if (dRo) cudaFree(dRo);
-    if (dRd) cudaFree(dRd);
-    if (dColor) cudaFree(dColor);
-    if (dIds) cudaFree(dIds);
+    ok = PT_CUDA(cudaStreamSynchronize(stream)) && ok;
     return ok;
 }
 

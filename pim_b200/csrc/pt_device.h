@@ -45,6 +45,7 @@ struct BvhBuffers
     PackedTri* tris = nullptr;
     int32_t nodeCount = 0;
     int32_t triCount = 0;
+    int32_t depth = 0;              // levels of the wide tree (the traversal stack holds at most 7 entries per level)
     float sceneLo[3] = { 0, 0, 0 }, sceneHi[3] = { 0, 0, 0 };   // bounds of all vertices
 };
 // positions: device float4[3*triCount]. Allocates nodes/tris with cudaMalloc.
@@ -64,13 +65,17 @@ struct RayHitOut      // PtRayHit, 48 bytes
     int32_t type, iVert;
     uint32_t flags, pad;
 };
+// dCursor: 8 bytes of device memory for the persistent kernels' ray cursor, private to this call
+// until its kernel has finished (the scene hands them out from a ring, api.cu)
 bool launchIntersect(const DScene& S, const F4* dRo, const F4* dRd, float tNear, RayHitOut* dOut, int64_t n,
-                     cudaStream_t stream);
+                     unsigned long long* dCursor, cudaStream_t stream);
 bool launchOccluded(const DScene& S, const F4* dRo, const F4* dRd, float tNear, uint8_t* dOut, int64_t n,
-                    cudaStream_t stream);
+                    unsigned long long* dCursor, cudaStream_t stream);
+bool launchPointQuery(const DScene& S, const F4* dPts, float* dDist, int64_t n, cudaStream_t stream);
 // counting variant for the bytes-per-ray roofline: returns total node / triangle fetches
 bool launchIntersectCount(const DScene& S, const F4* dRo, const F4* dRd, float tNear, int64_t n,
-                          unsigned long long* nodesOut, unsigned long long* trisOut, cudaStream_t stream);
+                          unsigned long long* dTotals, unsigned long long* nodesOut, unsigned long long* trisOut,
+                          cudaStream_t stream);
 
 // ---------------------------------------------------------------- scene build
 struct EntityUpload
@@ -145,7 +150,18 @@ struct PathPool
     int32_t* counters = nullptr; // device: see WfCounter
     int32_t* hostCounters = nullptr; // pinned mirror of the per-iteration status
     void* all = nullptr;
+    // events of the host loop, created once with the pool (runWavefront creates none per call)
+    static constexpr int kRing = 8;
+    cudaEvent_t evBegin = nullptr, evEnd = nullptr;
+    cudaEvent_t evDone[kRing] = {};
+    cudaEvent_t evKernel[kRing][6] = {};    // per-kernel timing, created the first time timing is on
+    // growable device scratch owned by the pool for callers that feed it (lightmap bake: picked
+    // texels, their rays and colours), so that a steady-state bake pass allocates nothing
+    void* aux = nullptr;
+    size_t auxBytes = 0;
 };
+// makes pool.aux at least `bytes` large; when it has to grow, the first keepBytes are carried over
+bool poolAux(PathPool& pool, size_t bytes, size_t keepBytes, cudaStream_t stream);
 // The counters many CTAs bump with atomics each sit in a 128-byte line of their own, away from
 // the values every thread only reads (Wf_NumA, the work cursor): same-address atomics serialise
 // in one L2 slice at about one per two clocks, and neighbours in the line queue behind them.
@@ -214,6 +230,12 @@ bool launchLightmapBake(const DScene& S, const LightmapView& lm, float metersPer
 // the same bake through the path wavefront: all samples of all picked texels trace in parallel
 bool launchLightmapBakeWavefront(const DScene& S, PathPool& pool, const LightmapView& lm, float metersPerTexel,
                                  float timeSlice, int32_t spp, uint32_t pass, uint32_t seed, cudaStream_t stream);
+
+// covered texels of a host page to / from a full-size device page (LmPack_BakeDesc)
+bool launchLightmapScatter(const LightmapView& lm, const int32_t* dIdx, int32_t count, const F4* dProbes, const float* dPos3,
+                           const float* dNrm3, const float* dCnt, cudaStream_t stream);
+bool launchLightmapGather(const LightmapView& lm, const int32_t* dIdx, int32_t count, F4* dProbes, float* dCnt,
+                          cudaStream_t stream);
 
 // image helpers
 bool launchResolve(float* dImage, const float* dSum, int64_t n, float prevCount, float addCount, cudaStream_t stream);

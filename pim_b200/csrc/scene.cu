@@ -210,14 +210,15 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHitCount(DScene S, cons
 static inline unsigned gridFor(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
 bool launchIntersect(const DScene& S, const F4* dRo, const F4* dRd, float tNear, RayHitOut* dOut, int64_t n,
-                     cudaStream_t stream)
+                     unsigned long long* dCursor, cudaStream_t stream)
 {
     if (n <= 0) return true;
     if (usePersistentBatch(S.bvh.nodeCount))
     {
-        static unsigned long long* dCursor = nullptr;
-        if (!dCursor && !PT_CUDA(cudaMalloc((void**)&dCursor, 8))) return false;
-        cudaMemsetAsync(dCursor, 0, 8, stream);
+        // the ray cursor belongs to this call alone (two batches in flight on different streams must
+        // not share one: the other batch's claims would run this one's cursor past its rays)
+        if (!dCursor) { setError("launchIntersect: no cursor for the persistent kernel"); return false; }
+        if (!PT_CUDA(cudaMemsetAsync(dCursor, 0, 8, stream))) return false;
         const unsigned grid = (unsigned)std::min<int64_t>(gridFor(n, kTravThreads), kSmCount * 12);
         k_closestHitPersistent<<<grid, kTravThreads, 0, stream>>>(S, dRo, dRd, tNear, dOut, n, dCursor);
     }
@@ -229,14 +230,13 @@ bool launchIntersect(const DScene& S, const F4* dRo, const F4* dRd, float tNear,
 }
 
 bool launchOccluded(const DScene& S, const F4* dRo, const F4* dRd, float tNear, uint8_t* dOut, int64_t n,
-                    cudaStream_t stream)
+                    unsigned long long* dCursor, cudaStream_t stream)
 {
     if (n <= 0) return true;
     if (usePersistentBatch(S.bvh.nodeCount))
     {
-        static unsigned long long* dCursor = nullptr;
-        if (!dCursor && !PT_CUDA(cudaMalloc((void**)&dCursor, 8))) return false;
-        cudaMemsetAsync(dCursor, 0, 8, stream);
+        if (!dCursor) { setError("launchOccluded: no cursor for the persistent kernel"); return false; }
+        if (!PT_CUDA(cudaMemsetAsync(dCursor, 0, 8, stream))) return false;
         const unsigned grid = (unsigned)std::min<int64_t>(gridFor(n, kTravThreads), kSmCount * 12);
         k_anyHitPersistent<<<grid, kTravThreads, 0, stream>>>(S, dRo, dRd, tNear, dOut, n, dCursor);
     }
@@ -248,10 +248,9 @@ bool launchOccluded(const DScene& S, const F4* dRo, const F4* dRd, float tNear, 
 }
 
 bool launchIntersectCount(const DScene& S, const F4* dRo, const F4* dRd, float tNear, int64_t n,
-                          unsigned long long* nodesOut, unsigned long long* trisOut, cudaStream_t stream)
+                          unsigned long long* dTotals, unsigned long long* nodesOut, unsigned long long* trisOut,
+                          cudaStream_t stream)
 {
-    unsigned long long* dTotals = nullptr;
-    if (!PT_CUDA(cudaMalloc((void**)&dTotals, 16))) return false;
     bool ok = PT_CUDA(cudaMemsetAsync(dTotals, 0, 16, stream));
     if (ok && n > 0)
     {
@@ -261,9 +260,27 @@ bool launchIntersectCount(const DScene& S, const F4* dRo, const F4* dRd, float t
     unsigned long long h[2] = { 0, 0 };
     ok = ok && PT_CUDA(cudaMemcpyAsync(h, dTotals, 16, cudaMemcpyDeviceToHost, stream));
     ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
-    cudaFree(dTotals);
     *nodesOut = h[0]; *trisOut = h[1];
     return ok;
+}
+
+// RtcPointQuery (path_tracer.c:597-616) over a batch: pts = (x, y, z, radius); dist = distance to the
+// nearest triangle within the radius, kRcpEpsilon when there is none
+__global__ void __launch_bounds__(kTravThreads) k_pointQuery(DScene S, const F4* __restrict__ pts, float* __restrict__ dist, int64_t n)
+{
+    PT_DECLARE_STACK(st);
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    U4 p = ldg128(pts + i);
+    dist[i] = pointQuery(S.bvh, v3(u2f(p.x), u2f(p.y), u2f(p.z)), u2f(p.w), st);
+}
+
+bool launchPointQuery(const DScene& S, const F4* dPts, float* dDist, int64_t n, cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    k_pointQuery<<<gridFor(n, kTravThreads), kTravThreads, 0, stream>>>(S, dPts, dDist, n);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
 }
 
 // -------------------------------------------------------------------- flatten

@@ -29,11 +29,16 @@ struct TravStack
         else if (sp - kSharedDepth < kSpillDepth) spill[sp - kSharedDepth] = e;
         ++sp;
     }
+    // An entry pushed beyond the capacity was dropped; popping it yields kDropped, whose key decodes to
+    // +inf so every traversal loop culls it (the subtree is skipped instead of the ray restarting at the
+    // root, which is what a zero entry would mean) and whose node id pointQuery recognises. buildBvh
+    // reports the wide tree's depth (BvhBuffers::depth) so that a tree deep enough to get here is visible.
+    static constexpr unsigned long long kDropped = (0x7f800008ull << 32) | 0xffffffffull;
     PT_D unsigned long long pop()
     {
         --sp;
         if (sp < kSharedDepth) return base[sp * stride];
-        return (sp - kSharedDepth < kSpillDepth) ? spill[sp - kSharedDepth] : 0ull;
+        return (sp - kSharedDepth < kSpillDepth) ? spill[sp - kSharedDepth] : kDropped;
     }
 };
 
@@ -518,6 +523,7 @@ PT_D float pointQuery(const Bvh& bvh, V3 p, float radius, Stack& st)
     while (st.sp > 0)
     {
         const uint32_t cur = (uint32_t)st.pop();
+        if (cur == 0xffffffffu) continue;       // TravStack::kDropped
         const WideNode* np = bvh.nodes + cur;
         const U4 n0 = ldg128(&np->ox);
         const U4 n1 = ldg128(&np->childBase);

@@ -26,6 +26,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 
 namespace pt {
 
@@ -608,13 +609,41 @@ bool poolAlloc(PathPool& pool, int32_t capacity)
     pool.connectList = (int32_t*)take(cap * sizeof(int32_t));
     pool.counters = (int32_t*)take(counterBytes);
     if (!PT_CUDA(cudaMallocHost((void**)&pool.hostCounters, 64 * sizeof(int32_t)))) { poolFree(pool); return false; }
+    bool ok = PT_CUDA(cudaEventCreate(&pool.evBegin)) && PT_CUDA(cudaEventCreate(&pool.evEnd));
+    for (int r = 0; ok && r < PathPool::kRing; ++r) ok = PT_CUDA(cudaEventCreateWithFlags(&pool.evDone[r], cudaEventDisableTiming));
+    if (!ok) { poolFree(pool); return false; }
     return true;
+}
+
+bool poolAux(PathPool& pool, size_t bytes, size_t keepBytes, cudaStream_t stream)
+{
+    if (bytes <= pool.auxBytes) return true;
+    const size_t cap = (bytes + bytes / 4 + (1u << 20)) & ~(size_t)((1u << 20) - 1);
+    void* grown = nullptr;
+    if (!PT_CUDA(cudaMalloc(&grown, cap))) return false;
+    bool ok = true;
+    if (pool.aux)
+    {
+        if (keepBytes) ok = PT_CUDA(cudaMemcpyAsync(grown, pool.aux, std::min(keepBytes, pool.auxBytes), cudaMemcpyDeviceToDevice, stream));
+        ok = PT_CUDA(cudaStreamSynchronize(stream)) && ok;      // nothing in flight may still use the old block
+        cudaFree(pool.aux);
+    }
+    pool.aux = grown; pool.auxBytes = cap;
+    return ok;
 }
 
 void poolFree(PathPool& pool)
 {
     if (pool.all) cudaFree(pool.all);
+    if (pool.aux) cudaFree(pool.aux);
     if (pool.hostCounters) cudaFreeHost(pool.hostCounters);
+    if (pool.evBegin) cudaEventDestroy(pool.evBegin);
+    if (pool.evEnd) cudaEventDestroy(pool.evEnd);
+    for (int r = 0; r < PathPool::kRing; ++r)
+    {
+        if (pool.evDone[r]) cudaEventDestroy(pool.evDone[r]);
+        for (int k = 0; k < 6; ++k) if (pool.evKernel[r][k]) cudaEventDestroy(pool.evKernel[r][k]);
+    }
     pool = PathPool();
 }
 
@@ -628,8 +657,10 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     if ((long long)P.capacity > (long long)work.count) P.capacity = (int32_t)((work.count + 127) & ~127ll);
     const int cap = P.capacity;
     const unsigned grid = (unsigned)((cap + kTravThreads - 1) / kTravThreads);
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    bool ok = PT_CUDA(cudaEventCreate(&e0)) && PT_CUDA(cudaEventCreate(&e1));
+    // the events live in the pool (created with it): a call creates and destroys none
+    cudaEvent_t e0 = pool.evBegin, e1 = pool.evEnd;
+    bool ok = e0 && e1;
+    if (!ok) setError("runWavefront: pool has no events");
     int32_t* dStatus = pool.counters + Wf_Status;     // 4 ints inside the counter block
     k_wfInit<<<(cap + 255) / 256, 256, 0, stream>>>(P, (unsigned long long)work.count);
     g_counters.kernelLaunches++;
@@ -638,17 +669,17 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     // left) is copied to a pinned ring and read kLag iterations later, so the stream never
     // drains between iterations. The few iterations launched after the last path ended find
     // empty ranges and cost a few microseconds each.
-    constexpr int kRing = 8, kLag = 3;
+    constexpr int kRing = PathPool::kRing, kLag = 3;
     const bool persistent = usePersistent(S.bvh.nodeCount);
     const unsigned gridP = std::min<unsigned>(grid, (unsigned)(kSmCount * kPersistentBlocksPerSm));
     unsigned long long iterations = 0, consumed = 0, extendRays = 0, connectRays = 0;
     const bool timing = g_kernelTiming;
-    cudaEvent_t done[kRing] = {};
-    cudaEvent_t ev[kRing][6] = {};
-    for (int r = 0; ok && r < kRing; ++r)
+    cudaEvent_t* done = pool.evDone;
+    cudaEvent_t (*ev)[6] = pool.evKernel;
+    if (timing && !ev[0][0])
     {
-        ok = PT_CUDA(cudaEventCreateWithFlags(&done[r], cudaEventDisableTiming));
-        if (timing) for (int k = 0; ok && k < 6; ++k) ok = PT_CUDA(cudaEventCreate(&ev[r][k]));
+        for (int r = 0; ok && r < kRing; ++r)
+            for (int k = 0; ok && k < 6; ++k) ok = PT_CUDA(cudaEventCreate(&ev[r][k]));
     }
     bool finished = false;
     // Upper bound on the live range of the iterations still to be launched. While work items
@@ -704,6 +735,7 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
             if (timing) for (int k = 2; k < 6; ++k) cudaEventRecord(ev[r][k], stream);
             k_wfEndFinish<<<1, 1, 0, stream>>>(P, dStatus);
             g_counters.kernelLaunches += 2;
+            ok = ok && PT_CUDA(cudaGetLastError());
             ok = ok && PT_CUDA(cudaMemcpyAsync(pool.hostCounters + 4 * r, dStatus, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
             ok = ok && PT_CUDA(cudaEventRecord(done[r], stream));
             ++iterations;
@@ -729,6 +761,7 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
         if (timing) cudaEventRecord(ev[r][5], stream);
         k_wfEndIteration<<<1, 1, 0, stream>>>(P, dStatus);
         g_counters.kernelLaunches += 7;
+        ok = ok && PT_CUDA(cudaGetLastError());     // a failed launch of any of the seven shows up here
         ok = ok && PT_CUDA(cudaMemcpyAsync(pool.hostCounters + 4 * r, dStatus, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
         ok = ok && PT_CUDA(cudaEventRecord(done[r], stream));
         ++iterations;
@@ -737,16 +770,10 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
         if (iterations > 1000000ull) { setError("runWavefront: iteration limit"); ok = false; }
     }
     while (ok && consumed < iterations) ok = consume(consumed++);
-    for (int r = 0; r < kRing; ++r)
-    {
-        if (done[r]) cudaEventDestroy(done[r]);
-        for (int k = 0; k < 6; ++k) if (ev[r][k]) cudaEventDestroy(ev[r][k]);
-    }
     ok = ok && PT_CUDA(cudaEventRecord(e1, stream));
     ok = ok && PT_CUDA(cudaEventSynchronize(e1));
     if (ok && kernelMsOut) cudaEventElapsedTime(kernelMsOut, e0, e1);
-    if (e0) cudaEventDestroy(e0);
-    if (e1) cudaEventDestroy(e1);
+    if (!ok) cudaStreamSynchronize(stream);      // leave nothing in flight that still uses the pool
     g_counters.iterations += iterations;
     g_counters.paths += (unsigned long long)work.count;
     g_counters.rays += extendRays + connectRays;
@@ -772,6 +799,7 @@ static __device__ __align__(256) unsigned char g_noAllocScratch[kNoAllocBytes];
 // In host code `g_noAllocScratch` is only a handle for the runtime, not a device address;
 // the address a kernel can use comes from cudaGetSymbolAddress, once per device.
 static unsigned char* g_noAllocPtr[64] = {};
+static std::mutex g_noAllocMutex;       // guards the first-call fill of g_noAllocPtr
 
 int32_t noAllocMaxPaths() { return kNoAllocMaxPaths; }
 
@@ -788,12 +816,17 @@ bool runWavefrontNoAlloc(const DScene& S, const F4* dRo, const F4* dRd, int64_t 
     int dev = 0;
     if (!PT_CUDA(cudaGetDevice(&dev))) return false;
     if (dev < 0 || dev >= 64) { setError("Pt_TraceRayN_NoAlloc: device index %d out of range", dev); return false; }
-    if (!g_noAllocPtr[dev])
     {
-        // first call on this device (it is the current one): resolve the array's device address
-        void* p = nullptr;
-        if (!PT_CUDA(cudaGetSymbolAddress(&p, g_noAllocScratch))) return false;
-        g_noAllocPtr[dev] = (unsigned char*)p;
+        // first call on this device (it is the current one): resolve the array's device address.
+        // The lock only makes the look-up safe when first calls arrive from several host threads;
+        // the calls themselves still have to be serialised by the caller (one shared array).
+        std::lock_guard<std::mutex> lock(g_noAllocMutex);
+        if (!g_noAllocPtr[dev])
+        {
+            void* p = nullptr;
+            if (!PT_CUDA(cudaGetSymbolAddress(&p, g_noAllocScratch))) return false;
+            g_noAllocPtr[dev] = (unsigned char*)p;
+        }
     }
     // carve the same layout poolAlloc uses out of the static array
     const size_t cap = (size_t)kNoAllocMaxPaths;

@@ -193,6 +193,24 @@ class Scene:
         lib().oracle_brute_n(self.h, _ptr(ro), _ptr(rd), t_near, n, _ptr(tuv), _ptr(prim, i32p), _ptr(flags, i32p))
         return tuv, prim, flags
 
+    def occluded(self, ro, rd, t_near=0.0):
+        """the reference's RtcOccluded16 (path_tracer.c:524-553), rd[:, 3] = tFar; 1 = occluded"""
+        ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)
+        out = np.zeros(len(ro), np.uint8)
+        L = lib()
+        L.oracle_occluded_n.argtypes = [C.c_void_p, f32p, f32p, C.c_float, C.c_int64, C.c_void_p]
+        L.oracle_occluded_n(self.h, _ptr(ro), _ptr(rd), t_near, len(ro), out.ctypes.data)
+        return out
+
+    def point_query(self, pts):
+        """the reference's RtcPointQuery (path_tracer.c:597-616), pts[:, 3] = radius -> (distance, primitive)"""
+        pts = np.ascontiguousarray(pts, np.float32)
+        dist = np.zeros(len(pts), np.float32); prim = np.zeros(len(pts), np.int32)
+        L = lib()
+        L.oracle_point_query_n.argtypes = [C.c_void_p, f32p, C.c_int64, f32p, i32p]
+        L.oracle_point_query_n(self.h, _ptr(pts), len(pts), _ptr(dist), _ptr(prim, i32p))
+        return dist, prim
+
     def trace_rays(self, ro, rd, pass_index=0):
         ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)
         out = np.zeros((len(ro), 9), np.float32)

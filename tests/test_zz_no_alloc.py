@@ -25,9 +25,14 @@ def test_no_alloc_matches_trace_ray_n_twice():
         d_ro, d_rd = torch.from_numpy(ro).to(dev), torch.from_numpy(rd).to(dev)
         out = [torch.full((n, 3), -1.0, dtype=torch.float32, device=dev) for _ in range(3)]
         torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info(dev)[0]          # cudaMemGetInfo: bytes the driver still has to give
         rc = L.Pt_TraceRayN_NoAlloc(scene.h, d_ro.data_ptr(), d_rd.data_ptr(), pass_index, out[0].data_ptr(),
                                     out[1].data_ptr(), out[2].data_ptr(), n, None)
         assert rc == 0, api.last_error()
+        if call > 0:
+            # the property in the name, on a warm call (the first one may have loaded the kernels' code):
+            # the device's free memory is what it was before the call
+            assert torch.cuda.mem_get_info(dev)[0] == free_before
         got = np.concatenate([o.cpu().numpy() for o in out], axis=1)
         # same kernels, same per-path seeds: the tolerance of the other path-parity tests, and tighter
         assert parity.path_agreement(got[:, 0:3], want[:, 0:3]) >= 0.999, call
