@@ -738,11 +738,13 @@ typedef struct TruthArg
     const float* verts; int stride; int64_t ntris;
     const float* ro4; const float* rd4; float tnear; int64_t begin, end;
     CpuHit* hits; int32_t* flags; uint8_t* occ;
+    uint64_t nodes, tris;       /* wide-node / triangle fetches of this thread's occlusion rays */
 } TruthArg;
 
 static void* truth_main(void* p)
 {
     TruthArg* a = (TruthArg*)p;
+    cpubvh_counters_reset();
     for (int64_t i = a->begin; i < a->end; ++i)
     {
         const float* ro = a->ro4 + 4 * i; const float* rd = a->rd4 + 4 * i;
@@ -750,8 +752,12 @@ static void* truth_main(void* p)
         else if (a->grid) a->flags[i] = f64grid_intersect(a->grid, ro, rd, a->tnear, rd[3], &a->hits[i]);
         else a->flags[i] = brute_intersect_f64(a->verts, a->stride, a->ntris, ro, rd, a->tnear, rd[3], &a->hits[i]);
     }
+    uint64_t rays;
+    cpubvh_counters_get(&a->nodes, &a->tris, &rays);
     return NULL;
 }
+
+static uint64_t g_truthNodes, g_truthTris;     /* summed over the threads of the last batch */
 
 static void truth_run(TruthArg proto, int64_t n, int threads)
 {
@@ -764,7 +770,12 @@ static void truth_run(TruthArg proto, int64_t n, int threads)
         args[t].begin = n * t / threads; args[t].end = n * (t + 1) / threads;
         pthread_create(&th[t], NULL, truth_main, &args[t]);
     }
-    for (int t = 0; t < threads; ++t) pthread_join(th[t], NULL);
+    g_truthNodes = g_truthTris = 0;
+    for (int t = 0; t < threads; ++t)
+    {
+        pthread_join(th[t], NULL);
+        g_truthNodes += args[t].nodes; g_truthTris += args[t].tris;
+    }
 }
 
 /* rd4[i].w = tFar; flags[i] = 0 miss, 1 hit, 2 hit with a tie */
@@ -792,3 +803,4 @@ void cpubvh_occluded_batch(const CpuBvh* bvh, const float* ro4, const float* rd4
     a.bvh = bvh; a.ro4 = ro4; a.rd4 = rd4; a.tnear = tnear; a.occ = occluded;
     truth_run(a, n, threads);
 }
+void cpubvh_last_batch_counts(uint64_t* nodes, uint64_t* tris) { *nodes = g_truthNodes; *tris = g_truthTris; }

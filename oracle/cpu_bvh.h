@@ -88,6 +88,7 @@ void f64grid_intersect_batch(const F64Grid* g, const float* ro4, const float* rd
                              CpuHit* hits, int32_t* flags);
 void cpubvh_occluded_batch(const CpuBvh* bvh, const float* ro4, const float* rd4, float tnear, int64_t n, int threads,
                            uint8_t* occluded);
+void cpubvh_last_batch_counts(uint64_t* nodes, uint64_t* tris);   /* fetches of the last occlusion batch */
 
 #ifdef __cplusplus
 }

@@ -85,6 +85,9 @@ class CpuBvh:
         ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)
         occ = np.zeros(len(ro), np.uint8)
         lib().cpubvh_occluded_batch(self.h, ro.ctypes.data, rd.ctypes.data, t_near, len(ro), threads(), occ.ctypes.data)
+        a, b = C.c_uint64(), C.c_uint64()
+        lib().cpubvh_last_batch_counts(C.byref(a), C.byref(b))
+        self.last_counts = (a.value, b.value)
         return occ
 
     def close(self):
