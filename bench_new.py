@@ -1,0 +1,271 @@
+#!/usr/bin/env python
+"""bench.py — Msamples/s of the path-tracing hot path on cornell_box at 1920x1080.
+
+A step is one progressive pass of the hot path: `--spp-per-step` samples of every
+pixel of the 1080p frame (BASELINE.json configs[1]; the full config is 1024 spp =
+16 steps of 64 spp). `value` times Pt_TraceSpp_Device with the scene and the
+accumulation images resident in HBM; `e2e` times the reference-facing call with host
+PtTrace buffers (Pt_TraceSpp: device->host copies of the three images inside). With
+N > 1 every rank renders its own sample indices of the full frame (scene replicated)
+into per-step sums, one NCCL reduce per step adds them on rank 0, and `e2e` is
+render + reduce + one device->host copy of the three images on rank 0.
+
+The other BASELINE configs ride along in `extra` (C1 320x180x64 spp, C3 1 M-triangle
+interior 1080p x 256 spp, C4 lightmap bake 16 texels/m x 64 spp, C5 10 M triangles x
+100 M rays closest / any hit), each with its own roofline and CPU baseline; `verify`
+holds the N-rank image against the 1-rank image over the same (pixel, sample) set.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--extras LIST|none]
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WIDTH, HEIGHT = 1920, 1080
+EYE, AT, FOVY = [-4.0, 0.0, 4.0], [0.0, -1.0, 0.0], 90.0    # pt_test camera (render_system.c:1360-1361)
+C3_EYE, C3_AT = [3.0, 1.5, 3.0], [30.0, 1.2, 27.0]
+METRIC, UNIT = "Msamples/s (1080p cornell_box)", "Msamples/s"
+WORKLOAD = "cornell_box boxes 1920x1080 progressive accumulation (BASELINE configs[1])"
+TRAVERSAL_COUNTS = os.path.join(ROOT, "baseline", "traversal_counts.json")
+TRAFFIC = os.path.join(ROOT, "profiles", "r02_traffic.json")
+DEFAULT_EXTRAS = "c1,c3,c4,c5"
+BACKEND = "reference path_tracer.c over the CPU BVH restatement (Embree 3.13.5 binary unavailable)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--spp-per-step", type=int, default=64)
+    ap.add_argument("--pool", type=int, default=0, help="path pool slots (0 = library default)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--extras", default=DEFAULT_EXTRAS,
+                    help="comma list of c1,c3,c4,c5 or 'none' (N > 1 runs only c3 and c4: the configs BASELINE.md shards)")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def traversal_counts(key):
+    """mean wide-node / triangle fetches per ray and rays per sample of the canonical CPU
+    BVH on a workload; written by baseline/make_traversal_counts.py"""
+    with open(TRAVERSAL_COUNTS) as f:
+        return json.load(f)[key]
+
+
+def bytes_per_ray(tc, prefix=""):
+    return 32 + 16 + tc[prefix + "nodes_per_ray"] * 80 + tc[prefix + "tris_per_ray"] * 48
+
+
+def host_cores():
+    return min(os.cpu_count() or 1, 64)
+
+
+class ClockSampler:
+    """nvidia-smi clocks line of B200_PROFILING.md, sampled while the timed region runs."""
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index):
+        self.tmp = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(device_index), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=self.tmp, stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        self.tmp.flush()
+        self.tmp.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.tmp.read().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        self.tmp.close()
+        os.unlink(self.tmp.name)
+        if sm:
+            out["sm_mhz"] = float(np.median(sm))
+            out["sm_max_mhz"] = float(max(mx))
+            out["samples"] = len(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def _oracle():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle as O
+    return O
+
+
+def _oracle_cornell(O, seed=1, lut_samples=1024):
+    from pim_b200 import scenes
+    O.set_threads(host_cores())
+    O.set_seed(seed)
+    lut = O.bake_brdf_lut(128, lut_samples)
+    desc = scenes.cornell_box("boxes", brdf_lut=lut, seed=seed)
+    O.load_scene_desc(desc)
+    return desc
+
+
+# ---------------------------------------------------------------- CPU baselines (reference code on the host cores)
+
+def _cpu_frames(O, ref, eye, at, width, height, min_seconds, max_frames):
+    cam, dof = O.camera_lookat(eye, at, FOVY), O.default_dof()
+    dof.autoFocus = 0
+    col = np.zeros((height, width, 3), np.float32); alb = col.copy(); nor = col.copy()
+    ref.trace(col, alb, nor, 1.0, cam, dof, 0)          # warm-up frame (page faults, caches)
+    O.lib().oracle_counters_reset()
+    frames, t0 = 0, time.perf_counter()
+    while True:
+        ref.trace(col, alb, nor, 1.0 / (frames + 2), cam, dof, frames + 1)
+        frames += 1
+        dt = time.perf_counter() - t0
+        if dt >= min_seconds or frames >= max_frames:
+            break
+    _, _, rays = O.counters()
+    return frames, dt, rays, float(col.mean())
+
+
+def cpu_baseline(width, height, min_seconds=10.0, max_frames=64):
+    """The reference's own Pt_Trace (oracle/_ref) on the host cores, same scene and camera."""
+    O = _oracle()
+    if not O.available():
+        return None
+    _oracle_cornell(O)
+    ref = O.Scene()
+    frames, dt, rays, _ = _cpu_frames(O, ref, EYE, AT, width, height, min_seconds, max_frames)
+    ref.close()
+    samples = frames * width * height
+    return {"value": samples / dt / 1e6, "unit": UNIT, "cores": host_cores(), "kind": "reference",
+            "sample": "%d frames of 1 spp at %dx%d, %s" % (frames, width, height, BACKEND),
+            "seconds": dt, "mrays_per_s": rays / dt / 1e6, "rays_per_sample": rays / samples}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path on the host cores, on the arm's own
+    config: a step is 1 spp of the full 1920x1080 frame, same scene and camera (one step is a few tenths of a
+    second on 16 threads, so K steps + W warm-ups stay within minutes)."""
+    if rank != 0:
+        return
+    O = _oracle()
+    if not O.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libpim_ref.so not built"}))
+        return
+    w, h = WIDTH, HEIGHT
+    cores = host_cores()
+    _oracle_cornell(O)
+    ref = O.Scene()
+    cam, dof = O.camera_lookat(EYE, AT, FOVY), O.default_dof()
+    dof.autoFocus = 0
+    col = np.zeros((h, w, 3), np.float32); alb = col.copy(); nor = col.copy()
+    for i in range(args.warmup):
+        ref.trace(col, alb, nor, 1.0 / (i + 1), cam, dof, i)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        ref.trace(col, alb, nor, 1.0 / (args.warmup + i + 1), cam, dof, args.warmup + i)
+    dt = time.perf_counter() - t0
+    ref.close()
+    value = args.steps * w * h / dt / 1e6
+    sample = "per step: 1 spp of the full %dx%d frame, same scene and camera" % (w, h)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "spp_per_step": 1, "width": w, "height": h, "sample": sample, "threads": cores,
+                   "backend": BACKEND},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "mean_luminance": float(col.mean()),
+    }))
+
+
+# ---------------------------------------------------------------- the GPU arm
+
+class Ctx:
+    """what every measurement of the GPU arm shares"""
+    def __init__(self, args, rank, world, local_rank):
+        import torch
+        import torch.distributed as dist
+        from pim_b200 import api, scenes, multigpu
+        self.torch, self.dist, self.api, self.scenes, self.multigpu = torch, dist, api, scenes, multigpu
+        self.args, self.rank, self.world = args, rank, world
+        torch.cuda.set_device(local_rank)
+        self.dev = torch.device("cuda", local_rank)
+        if world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.L = api.load()
+        self.stream = torch.cuda.Stream(device=self.dev)   # the library launches on this stream; events are recorded on it
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)     # > 126 MB L2
+        torch.cuda.synchronize()
+        torch.cuda.set_stream(self.stream)
+        self.peak, self.peak_src = measured_peaks()
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def images(self, w, h):
+        return [self.torch.zeros(w * h * 3, dtype=self.torch.float32, device=self.dev) for _ in range(3)]
+
+    def trace(self, scene, cam, dof, w, h, begin, spp, sums):
+        rc = self.L.Pt_TraceSpp_Device(scene.h, C.byref(cam), C.byref(dof), w, h, begin, spp,
+                                       sums[0].data_ptr(), sums[1].data_ptr(), sums[2].data_ptr(), self.stream.cuda_stream)
+        if rc != 0:
+            raise RuntimeError("Pt_TraceSpp_Device: " + self.api.last_error())
+
+    def timed_steps(self, fn, steps, warmup):
+        """W untimed + K timed calls of fn(i); each timed call between two events on the launching stream, an L2
+        flush before it (outside the events); returns the max over ranks of the summed milliseconds"""
+        torch = self.torch
+        for i in range(warmup):
+            fn(i)
+        self.barrier()
+        total_ms = 0.0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for i in range(steps):
+            self.flush.fill_(i & 0xFF)
+            e0.record(self.stream)
+            fn(warmup + i)
+            e1.record(self.stream)
+            e1.synchronize()
+            total_ms += e0.elapsed_time(e1)
+        self.barrier()
+        return self.multigpu.max_over_ranks(total_ms, self.dev)
