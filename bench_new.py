@@ -269,3 +269,101 @@ class Ctx:
             total_ms += e0.elapsed_time(e1)
         self.barrier()
         return self.multigpu.max_over_ranks(total_ms, self.dev)
+
+
+def sample_roofline(ctx, value_per_gpu, tc_key, kstats, counters):
+    """whole-step figure of SURVEY.md 8(d): B_sample = 72 + L*(R*B_ray + 192), L = bounces per path and R = rays
+    per bounce as this run traced them, B_ray from the canonical CPU BVH's committed counts"""
+    tc = traversal_counts(tc_key)
+    b_ray = bytes_per_ray(tc)
+    paths = max(counters["paths"], 1)
+    total_rays = kstats["extendRays"] + kstats["connectRays"]
+    bounces = kstats["extendRays"] / paths
+    rays_per_bounce = total_rays / max(kstats["extendRays"], 1)
+    b_sample = 72 + bounces * (rays_per_bounce * b_ray + 192)
+    gbs = value_per_gpu * 1e6 * b_sample / 1e9
+    return {"bound": "hbm", "bytes_per_sample": b_sample, "bytes_per_ray": b_ray, "bounces_per_path": bounces,
+            "rays_per_bounce": rays_per_bounce, "rays_per_sample": total_rays / paths, "achieved": gbs,
+            "peak": ctx.peak, "unit": "GB/s", "frac": gbs / ctx.peak, "peak_source": ctx.peak_src,
+            "counts": "baseline/traversal_counts.json:" + tc_key,
+            "note": "per GPU; whole step by SURVEY.md 8(d) B_sample"}
+
+
+def kernel_table(api, kstats):
+    total = max(sum(kstats[n]["ms"] for n in api.KERNEL_NAMES), 1e-9)
+    return {n: {"ms": kstats[n]["ms"], "launches": kstats[n]["launches"], "share": kstats[n]["ms"] / total,
+                "us_per_launch": kstats[n]["ms"] / max(kstats[n]["launches"], 1) * 1e3} for n in api.KERNEL_NAMES}
+
+
+def dominant_kernel_roofline(ctx, kstats, counters):
+    """`roofline` of the line: the kernel with the largest share of the step (CUDA events on the launching stream
+    inside the library). Traversal kernels by B_ray x rays per launch; shading kernels by the path state they are
+    specified to move per slot (96 B state read + 96 B written per bounce, shared by the two
+    shading stages, plus the two rays' 48 B in / out)."""
+    api = ctx.api
+    tab = kernel_table(api, kstats)
+    name = max(api.KERNEL_NAMES, key=lambda n: tab[n]["ms"])
+    launches = max(kstats[name]["launches"], 1)
+    avg_s = kstats[name]["ms"] * 1e-3 / launches
+    tc = traversal_counts("cornell_boxes_camera_paths")
+    b_ray = bytes_per_ray(tc)
+    slots = kstats["extendRays"] / max(kstats["extend"]["launches"], 1)        # live paths per iteration
+    if name in ("extend", "connect"):
+        units = kstats[name + "Rays"] / launches
+        per_unit, what = b_ray, "B_ray = 32 + 16 + N_node*80 + N_tri*48 per ray (canonical CPU BVH counts)"
+    else:
+        units = slots
+        per_unit = {"shadeA": 96.0 + 48.0, "shadeB": 96.0 + 48.0, "regen": 96.0}[name]
+        what = ("path state per slot: 96 B (one read or one write of the state of SURVEY 8(d)) + 48 B (a ray in, a hit out)"
+                if name != "regen" else "96 B of new path state per slot")
+    achieved = units * per_unit / max(avg_s, 1e-12) / 1e9
+    traffic = None
+    if os.path.exists(TRAFFIC):
+        with open(TRAFFIC) as f:
+            tj = json.load(f)
+        key = "k_wf" + name[0].upper() + name[1:]
+        if key in tj and "dram_bytes_per_slot" in tj[key]:
+            traffic = tj[key]["dram_bytes_per_slot"] * units
+    return {"bound": "hbm", "kernel": "k_wf" + name[0].upper() + name[1:], "achieved": achieved, "peak": ctx.peak,
+            "unit": "GB/s", "frac": achieved / ctx.peak, "traffic": traffic, "peak_source": ctx.peak_src,
+            "algorithmic_bytes_per_unit": per_unit, "units_per_launch": units, "avg_launch_ms": avg_s * 1e3,
+            "share_of_step": tab[name]["share"], "definition": what,
+            "traffic_source": "profiles/r02_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture, per slot)"
+                              if traffic is not None else None}
+
+
+def verify_ranks(ctx, scene_desc_fn):
+    """The N-rank image against the 1-rank image over the same (pixel, sample) set: 32 samples per pixel of the 1080p
+    frame, split by sample index over the ranks (fresh replicas, so every rank samples the light grid as built),
+    summed with the bench's reduce, against the same 32 samples rendered by rank 0 alone in one call. Differences
+    are the order of the float atomics only. mean_luminance is over that fixed sample set, so it is the same
+    number at every N."""
+    torch, api, mg = ctx.torch, ctx.api, ctx.multigpu
+    total_spp = 32
+    per_rank = total_spp // ctx.world
+    cam, dof = api.make_camera(EYE, AT, FOVY), api.default_dof(auto_focus=False)
+    scene = api.Scene(scene_desc_fn())
+    sums = ctx.images(WIDTH, HEIGHT)
+    ctx.trace(scene, cam, dof, WIDTH, HEIGHT, ctx.rank * per_rank, per_rank, sums)
+    torch.cuda.synchronize()
+    mg.reduce_sums(sums, dst=0)
+    ctx.barrier()
+    scene.close()
+    out = None
+    if ctx.rank == 0:
+        n_rank = sums[0] / total_spp
+        out = {"samples_per_pixel": total_spp, "mean_luminance": float(n_rank.mean().item())}
+        if ctx.world > 1:
+            solo = api.Scene(scene_desc_fn())
+            one = ctx.images(WIDTH, HEIGHT)
+            ctx.trace(solo, cam, dof, WIDTH, HEIGHT, 0, total_spp, one)
+            torch.cuda.synchronize()
+            solo.close()
+            ref = one[0] / total_spp
+            diff = (n_rank - ref).abs()
+            out.update({"mean_luminance_1_rank": float(ref.mean().item()),
+                        "max_abs_diff": float(diff.max().item()),
+                        "rel_diff_of_means": float(abs(n_rank.mean().item() - ref.mean().item()) / ref.mean().item()),
+                        "pixels_beyond_1e-4_rel": int((diff > 1e-4 * (ref.abs() + 1e-3)).sum().item())})
+    ctx.barrier()
+    return out
