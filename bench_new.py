@@ -367,3 +367,146 @@ def verify_ranks(ctx, scene_desc_fn):
                         "pixels_beyond_1e-4_rel": int((diff > 1e-4 * (ref.abs() + 1e-3)).sum().item())})
     ctx.barrier()
     return out
+
+
+def run_ours(args, rank, world, local_rank):
+    ctx = Ctx(args, rank, world, local_rank)
+    torch, api, scenes, mg, L = ctx.torch, ctx.api, ctx.scenes, ctx.multigpu, ctx.L
+    spp = args.spp_per_step
+
+    def cornell():
+        # the same seed on every rank: a path's random stream is a function of (pixel, sample index, seed), and
+        # the ranks render disjoint sample indices (multigpu.sample_range)
+        d = scenes.cornell_box("boxes", brdf_lut=None, seed=1)      # BRDF table baked on the device
+        d.path_pool_size = args.pool
+        return d
+
+    scene = api.Scene(cornell())
+    cam = api.make_camera(EYE, AT, FOVY)
+    dof = api.default_dof(auto_focus=False)
+    n3 = WIDTH * HEIGHT * 3
+    sums = ctx.images(WIDTH, HEIGHT)                 # this step's samples of this rank
+    total = ctx.images(WIDTH, HEIGHT) if rank == 0 else None     # rank 0: everything rendered so far, all ranks
+
+    def step(i):
+        begin, _ = mg.sample_range(i, rank, world, spp)
+        for t in sums:
+            t.zero_()
+        ctx.trace(scene, cam, dof, WIDTH, HEIGHT, begin, spp, sums)
+        mg.reduce_sums(sums, dst=0)                  # per-step sums, not running totals
+        if rank == 0:
+            for a, b in zip(total, sums):
+                a += b
+
+    for i in range(args.warmup):
+        step(i)
+    ctx.barrier()
+    L.Pt_ResetCounters()
+    L.Pt_SetKernelTiming(1)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    total_ms = ctx.timed_steps(lambda i: step(args.warmup + i), args.steps, 0)
+    clocks = sampler.stop() if sampler else None
+    counters = api.counters()
+    kstats = api.kernel_stats()
+    L.Pt_SetKernelTiming(0)
+    samples_per_step = WIDTH * HEIGHT * spp * world
+    value = samples_per_step * args.steps / (total_ms * 1e-3) / 1e6
+    steps_done = args.warmup + args.steps
+    image_mean = float((total[0] / (steps_done * spp * world)).mean().item()) if rank == 0 else None
+
+    # ---- end to end
+    e2e_steps = max(2, min(args.steps, 8))
+    if world == 1:
+        # through the reference-facing call with host buffers (Pt_TraceSpp): the step's inputs (camera + dof
+        # structs) go host->device, the three images come back device->host
+        trace = api.Trace(WIDTH, HEIGHT)
+        for i in range(2):
+            trace.trace_spp(scene, cam, dof, i * spp, spp)
+        ctx.barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            trace.trace_spp(scene, cam, dof, (2 + i) * spp, spp)
+        ctx.barrier()
+        e2e_s = time.perf_counter() - t0
+        e2e_lum = float(trace.image("color").mean())
+        trace.close()
+        e2e_how = "Pt_TraceSpp with host PtTrace buffers"
+    else:
+        # one image on one host: every rank renders its samples, the sums are reduced to rank 0, rank 0 adds them
+        # to the frame's total and copies the three images to page-locked host memory
+        host = [torch.empty(n3, dtype=torch.float32, pin_memory=True) for _ in range(3)] if rank == 0 else None
+
+        def e2e_step(i):
+            step(steps_done + i)
+            if rank == 0:
+                for h, t in zip(host, total):
+                    h.copy_(t, non_blocking=True)
+            torch.cuda.synchronize()
+        for i in range(2):
+            e2e_step(i)
+        ctx.barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            e2e_step(2 + i)
+        ctx.barrier()
+        e2e_s = time.perf_counter() - t0
+        e2e_lum = float((host[0] / ((steps_done + 2 + e2e_steps) * spp * world)).mean().item()) if rank == 0 else None
+        e2e_how = "Pt_TraceSpp_Device per rank + NCCL reduce to rank 0 + device->host copy of the three images on rank 0"
+    e2e_s = mg.max_over_ranks(e2e_s, ctx.dev)
+    e2e_value = WIDTH * HEIGHT * spp * world * e2e_steps / e2e_s / 1e6
+
+    verify = verify_ranks(ctx, cornell)
+
+    line = None
+    if rank == 0:
+        total_rays = kstats["extendRays"] + kstats["connectRays"]
+        paths = max(counters["paths"], 1)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "spp_per_step": spp, "width": WIDTH, "height": HEIGHT,
+                       "sharding": "sample index per rank, scene replicated, NCCL reduce of the per-step sums to rank 0",
+                       "l2": "256 MB buffer written between timed steps (L2 flush)",
+                       "path_pool_slots": args.pool or (1 << 23)},
+            "mrays_per_s": value * total_rays / paths,      # all ranks, from rank 0's rays per sample
+            "rays_per_sample": total_rays / paths,
+            "gpu_launches": int(counters["kernelLaunches"]),
+            "mean_luminance": image_mean,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": C.sizeof(api.Camera) + C.sizeof(api.PtDofInfo),
+                    "d2h_bytes_per_step": 3 * n3 * 4, "steps": e2e_steps, "mean_luminance": e2e_lum, "how": e2e_how},
+            "roofline": dominant_kernel_roofline(ctx, kstats, counters),
+            "roofline_sample": sample_roofline(ctx, value / world, "cornell_boxes_camera_paths", kstats, counters),
+            "kernels": kernel_table(api, kstats),
+            "clocks": clocks,
+            "verify": verify,
+        }
+    scene.close()
+
+    # ---- the other BASELINE configs
+    wanted = [] if args.extras in ("none", "") else [x.strip() for x in args.extras.split(",") if x.strip()]
+    if world > 1:
+        wanted = [x for x in wanted if x in ("c3", "c4")]
+    extra = {}
+    for name in wanted:
+        fn = {"c1": extra_c1, "c3": extra_c3, "c4": extra_c4, "c5": extra_c5}.get(name)
+        if fn is None:
+            continue
+        try:
+            r = fn(ctx)
+        except Exception as e:      # an extra never takes the headline down with it
+            r = {"error": "%s: %s" % (type(e).__name__, e)}
+        if rank == 0:
+            extra[name] = r
+        ctx.barrier()
+
+    if rank == 0:
+        line["extra"] = extra
+        if not args.no_cpu_baseline and world == 1:
+            try:
+                line["cpu_baseline"] = cpu_baseline(WIDTH, HEIGHT)
+            except Exception as e:      # the baseline is reported, never required for the GPU number
+                line["cpu_baseline"] = {"error": str(e)}
+        print(json.dumps(line))
+    if world > 1:
+        ctx.dist.destroy_process_group()
