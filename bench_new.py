@@ -510,3 +510,120 @@ def run_ours(args, rank, world, local_rank):
         print(json.dumps(line))
     if world > 1:
         ctx.dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------- the other BASELINE configs
+
+def _timed_trace(ctx, scene, cam, dof, w, h, total_spp, chunk, warm_spp):
+    """device-timed Pt_TraceSpp_Device over total_spp samples per pixel in calls of `chunk` (this rank's sample
+    indices), after warm_spp untimed samples; per-call sums reduced to rank 0 like the main step"""
+    torch, api, mg, L = ctx.torch, ctx.api, ctx.multigpu, ctx.L
+    sums = ctx.images(w, h)
+    total = ctx.images(w, h) if ctx.rank == 0 else None
+    calls = total_spp // chunk
+
+    def call(i):
+        begin, _ = mg.sample_range(i, ctx.rank, ctx.world, chunk)
+        for t in sums:
+            t.zero_()
+        ctx.trace(scene, cam, dof, w, h, begin, chunk, sums)
+        mg.reduce_sums(sums, dst=0)
+        if ctx.rank == 0:
+            for a, b in zip(total, sums):
+                a += b
+    warm_calls = max(1, warm_spp // chunk)
+    for i in range(warm_calls):
+        call(i)
+    ctx.barrier()
+    L.Pt_ResetCounters(); L.Pt_SetKernelTiming(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx.flush.fill_(1)
+    e0.record(ctx.stream)
+    for i in range(calls):
+        call(warm_calls + i)
+    e1.record(ctx.stream)
+    e1.synchronize()
+    ms = mg.max_over_ranks(e0.elapsed_time(e1), ctx.dev)
+    ctx.barrier()
+    counters, kstats = api.counters(), api.kernel_stats()
+    L.Pt_SetKernelTiming(0)
+    lum = float((total[0] / ((warm_calls + calls) * chunk * ctx.world)).mean().item()) if ctx.rank == 0 else None
+    return ms, counters, kstats, lum
+
+
+def extra_c1(ctx):
+    """BASELINE configs[0]: cornell boxes via pt_test at 320x180, 64 spp (the reference's CPU-runnable case)"""
+    api, scenes = ctx.api, ctx.scenes
+    W, H, spp = 320, 180, 64
+    scene = api.Scene(scenes.cornell_box("boxes", brdf_lut=None, seed=1))
+    cam, dof = api.make_camera(EYE, AT, FOVY), api.default_dof(auto_focus=False)
+    ms, counters, kstats, lum = _timed_trace(ctx, scene, cam, dof, W, H, spp, spp, spp)
+    value = W * H * spp / ms / 1e3
+    # end to end as pt_test runs it: 64 calls of Pt_Trace (1 spp each, host images refreshed every call)
+    tr = api.Trace(W, H)
+    tr.trace(scene, cam, dof, 1.0)
+    t0 = time.perf_counter()
+    for p in range(spp):
+        tr.trace(scene, cam, dof, 1.0 / (p + 1))
+    e2e_s = time.perf_counter() - t0
+    tr.close(); scene.close()
+    out = {"workload": "cornell_box boxes via pt_test 320x180, 64 spp (BASELINE configs[0])", "metric": "Msamples/s",
+           "value": value, "ms": ms, "mean_luminance": lum,
+           "e2e": {"value": W * H * spp / e2e_s / 1e6, "unit": "Msamples/s", "how": "64 calls of Pt_Trace with host PtTrace buffers",
+                   "d2h_bytes_per_step": 3 * W * H * 12},
+           "roofline": sample_roofline(ctx, value, "cornell_boxes_camera_paths", kstats, counters)}
+    if not ctx.args.no_cpu_baseline:
+        O = _oracle()
+        if O.available():
+            _oracle_cornell(O)
+            ref = O.Scene()
+            frames, dt, rays, clum = _cpu_frames(O, ref, EYE, AT, W, H, 1e9, spp)
+            ref.close()
+            out["cpu_baseline"] = {"value": frames * W * H / dt / 1e6, "unit": "Msamples/s", "cores": host_cores(), "kind": "reference",
+                                   "sample": "the whole config: %d frames of 1 spp at %dx%d, %s" % (frames, W, H, BACKEND),
+                                   "mrays_per_s": rays / dt / 1e6, "mean_luminance": clum}
+    return out
+
+
+def extra_c3(ctx):
+    """BASELINE configs[2]: ~1 M-triangle procedural interior with emissive panels, 1080p, 256 spp"""
+    api, scenes = ctx.api, ctx.scenes
+    t0 = time.perf_counter()
+    desc = scenes.interior(1_000_000, seed=7, emissive_fraction=0.001)
+    gen_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    scene = api.Scene(desc)
+    build_s = time.perf_counter() - t0
+    st = scene.stats
+    cam, dof = api.make_camera(C3_EYE, C3_AT, FOVY), api.default_dof(auto_focus=False)
+    spp, chunk = 256, 16
+    ms, counters, kstats, lum = _timed_trace(ctx, scene, cam, dof, WIDTH, HEIGHT, spp, chunk, chunk)
+    value = WIDTH * HEIGHT * spp * ctx.world / ms / 1e3
+    total_rays = kstats["extendRays"] + kstats["connectRays"]
+    out = {"workload": "procedural interior, %d triangles, %d emissive, 1920x1080, 256 spp per rank (BASELINE configs[2])"
+                       % (desc.tri_count, st.emissiveCount),
+           "metric": "Msamples/s", "value": value, "ms": ms, "n_gpus": ctx.world, "mean_luminance": lum,
+           "mrays_per_s": value * total_rays / max(counters["paths"], 1),
+           "scene": {"generate_s": gen_s, "build_s": build_s, "bvh_nodes": st.bvhNodeCount, "grid": list(st.gridSize),
+                     "build_phase_ms": dict(zip(["upload_flatten", "bvh", "emissive", "grid", "lut", "pool"],
+                                                [round(x, 1) for x in st.phaseMs]))},
+           "roofline": sample_roofline(ctx, value / ctx.world, "interior_1m_camera_paths", kstats, counters),
+           "kernels": kernel_table(api, kstats)}
+    lut = scene.brdf_lut()
+    scene.close()
+    if ctx.world == 1 and not ctx.args.no_cpu_baseline:
+        O = _oracle()
+        if O.available():
+            O.set_threads(host_cores()); O.set_seed(1)
+            desc.brdf_lut = lut
+            t0 = time.perf_counter()
+            O.load_scene_desc(desc)
+            ref = O.Scene()
+            cpu_build = time.perf_counter() - t0
+            w, h = WIDTH // 4, HEIGHT // 4
+            frames, dt, rays, clum = _cpu_frames(O, ref, C3_EYE, C3_AT, w, h, 4.0, 16)
+            ref.close()
+            out["cpu_baseline"] = {"value": frames * w * h / dt / 1e6, "unit": "Msamples/s", "cores": host_cores(), "kind": "reference",
+                                   "sample": "%d frames of 1 spp at %dx%d (1/16 of the frame), same scene and camera, %s" % (frames, w, h, BACKEND),
+                                   "scene_build_s": cpu_build, "mrays_per_s": rays / dt / 1e6, "mean_luminance": clum}
+    return out
