@@ -627,3 +627,119 @@ def extra_c3(ctx):
                                    "sample": "%d frames of 1 spp at %dx%d (1/16 of the frame), same scene and camera, %s" % (frames, w, h, BACKEND),
                                    "scene_build_s": cpu_build, "mrays_per_s": rays / dt / 1e6, "mean_luminance": clum}
     return out
+
+
+def extra_c4(ctx):
+    """BASELINE configs[3]: lm_gen bake of cornell_box at 16 texels/m, 64 spp. LmPack_Pack(1024, 16.0, 0.1, 15 deg) runs
+    as reference code on rank 0's host (the shared input); the pack then lives on the device(s). With N ranks the covered
+    texels are split into N contiguous ranges (the fit is sequential per texel, so texels, never samples, are sharded),
+    every rank bakes its range and the disjoint slabs are gathered on rank 0: no reduction."""
+    torch, api, scenes, mg, L = ctx.torch, ctx.api, ctx.scenes, ctx.multigpu, ctx.L
+    O = _oracle()
+    if not O.available():
+        return {"error": "oracle/_ref not built: no LmPack_Pack to make the shared input"}
+    size, tpm, spp = 1024, 16.0, 64
+    n = size * size
+    pack_s = 0.0
+    if ctx.rank == 0:
+        desc = _oracle_cornell(O)
+        t0 = time.perf_counter()
+        pages = O.lm_pack(size, tpm, 0.1, 15.0)
+        pack_s = time.perf_counter() - t0
+        assert pages == 1
+        probes, pos, nrm, cnt = O.lm_page(0)
+        h_probes = [np.ascontiguousarray(p.copy()) for p in probes]
+        h_pos, h_nrm, h_cnt = pos.copy(), nrm.copy(), cnt.copy()
+        d_probes = torch.from_numpy(np.stack(h_probes)).to(ctx.dev)
+        d_pos, d_nrm, d_cnt = torch.from_numpy(h_pos).to(ctx.dev), torch.from_numpy(h_nrm).to(ctx.dev), torch.from_numpy(h_cnt).to(ctx.dev)
+    else:
+        d_probes = torch.zeros((5, n, 4), dtype=torch.float32, device=ctx.dev)
+        d_pos = torch.zeros((n, 3), dtype=torch.float32, device=ctx.dev); d_nrm = torch.zeros_like(d_pos)
+        d_cnt = torch.zeros(n, dtype=torch.float32, device=ctx.dev)
+    if ctx.world > 1:
+        for t in (d_probes, d_pos, d_nrm, d_cnt):
+            ctx.dist.broadcast(t, src=0)
+    covered_idx = torch.nonzero(d_cnt > 0).flatten()
+    covered = int(covered_idx.numel())
+    begin, count = mg.texel_range(covered, ctx.rank, ctx.world)
+    mine = covered_idx[begin:begin + count]
+    start_cnt = d_cnt.clone()
+    scene = api.Scene(scenes.cornell_box("boxes", brdf_lut=None, seed=1))
+
+    def bake(pass_index):
+        # this rank's range: every other texel is switched off through its sample count (BakeFn skips those)
+        work = torch.zeros_like(d_cnt)
+        work[mine] = d_cnt[mine]
+        scene.bake_lightmap_device([d_probes[k].data_ptr() for k in range(5)], d_pos.data_ptr(), d_nrm.data_ptr(), work.data_ptr(),
+                                   size, tpm, 1.0, spp, pass_index)
+        d_cnt[mine] = work[mine]
+        if ctx.world > 1:
+            # disjoint slabs to rank 0 (equal sizes up to one texel: pad to the largest)
+            m = (covered + ctx.world - 1) // ctx.world
+            slab = torch.zeros((m, 21), dtype=torch.float32, device=ctx.dev)
+            slab[:count, :20] = d_probes[:, mine, :].permute(1, 0, 2).reshape(count, 20)
+            slab[:count, 20] = d_cnt[mine]
+            parts = [torch.zeros_like(slab) for _ in range(ctx.world)] if ctx.rank == 0 else None
+            ctx.dist.gather(slab, parts, dst=0)
+            if ctx.rank == 0:
+                for r, part in enumerate(parts):
+                    b, c = mg.texel_range(covered, r, ctx.world)
+                    idx = covered_idx[b:b + c]
+                    d_probes[:, idx, :] = part[:c, :20].reshape(c, 5, 4).permute(1, 0, 2)
+                    d_cnt[idx] = part[:c, 20]
+    bake(99)                                            # warm-up pass (also grows the library's scratch once)
+    ctx.barrier()
+    L.Pt_ResetCounters(); L.Pt_SetKernelTiming(1)
+    reps = 3
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ctx.stream)
+    for p in range(reps):
+        bake(p)
+    e1.record(ctx.stream)
+    e1.synchronize()
+    ms = mg.max_over_ranks(e0.elapsed_time(e1), ctx.dev) / reps
+    ctx.barrier()
+    counters, kstats = api.counters(), api.kernel_stats()
+    L.Pt_SetKernelTiming(0)
+    value = covered * spp / ms / 1e3
+    out = None
+    if ctx.rank == 0:
+        advanced = bool(((d_cnt - start_cnt)[covered_idx] == (reps + 1) * spp).all().item())
+        tc = traversal_counts("cornell_lightmap_16tpm_bake_paths")
+        b_ray = bytes_per_ray(tc)
+        paths = max(counters["paths"], 1)
+        total_rays = kstats["extendRays"] + kstats["connectRays"]
+        bounces = kstats["extendRays"] / paths
+        rpb = total_rays / max(kstats["extendRays"], 1)
+        b_sample = 2 * 108.0 / spp + 32 + 12 + bounces * (rpb * b_ray + 192)     # page in/out amortised + ray in, colour out
+        gbs = value / ctx.world * 1e6 * b_sample / 1e9
+        out = {"workload": "lm_gen bake of cornell_box, LmPack_Pack(1024, 16.0, 0.1, 15), 64 spp, pack resident on the device (BASELINE configs[3])",
+               "metric": "M texel-samples/s", "value": value, "ms_per_pass": ms, "n_gpus": ctx.world, "covered_texels": covered,
+               "bake_mode": "PtBake_Wavefront (default; statistically, not texel for texel, equal to the seeded reference: tests/test_gpu_configs.py)",
+               "sharding": "contiguous ranges of the covered texels per rank, slabs gathered on rank 0",
+               "all_texels_advanced": advanced, "lm_pack_cpu_s": pack_s,
+               "mrays_per_s": value * total_rays / paths,
+               "roofline": {"bound": "hbm", "bytes_per_sample": b_sample, "bytes_per_ray": b_ray, "bounces_per_path": bounces,
+                            "rays_per_bounce": rpb, "achieved": gbs, "peak": ctx.peak, "unit": "GB/s", "frac": gbs / ctx.peak,
+                            "counts": "baseline/traversal_counts.json:cornell_lightmap_16tpm_bake_paths", "note": "per GPU"}}
+        if ctx.world == 1:
+            # end to end through the reference-facing form: LmPack_BakeDesc on the host page (covered texels cross the bus)
+            g_probes = [p.copy() for p in h_probes]; g_cnt = h_cnt.copy()
+            scene.bake_lightmap(g_probes, h_pos, h_nrm, g_cnt, tpm, 1.0, spp, 50)
+            t0 = time.perf_counter()
+            for p in range(reps):
+                scene.bake_lightmap(g_probes, h_pos, h_nrm, g_cnt, tpm, 1.0, spp, 51 + p)
+            dt = (time.perf_counter() - t0) / reps
+            out["e2e"] = {"value": covered * spp / dt / 1e6, "unit": "M texel-samples/s", "how": "LmPack_BakeDesc with the host page",
+                          "h2d_bytes_per_step": covered * 112, "d2h_bytes_per_step": covered * 84}
+            if not ctx.args.no_cpu_baseline:
+                ref = O.Scene()
+                O.lm_bake(ref, 1.0, 1, 0)
+                t0 = time.perf_counter()
+                O.lm_bake(ref, 1.0, spp, 1)
+                dt = time.perf_counter() - t0
+                ref.close()
+                out["cpu_baseline"] = {"value": covered * spp / dt / 1e6, "unit": "M texel-samples/s", "cores": host_cores(), "kind": "reference",
+                                       "sample": "the whole config: one LmPack_Bake(scene, 1, 64) pass, reference lightmap.c + path_tracer.c over the CPU BVH restatement"}
+    scene.close()
+    return out
