@@ -670,6 +670,7 @@ def extra_c4(ctx):
         # this rank's range: every other texel is switched off through its sample count (BakeFn skips those)
         work = torch.zeros_like(d_cnt)
         work[mine] = d_cnt[mine]
+        ctx.stream.synchronize()                        # the bake runs on the scene's own stream and blocks
         scene.bake_lightmap_device([d_probes[k].data_ptr() for k in range(5)], d_pos.data_ptr(), d_nrm.data_ptr(), work.data_ptr(),
                                    size, tpm, 1.0, spp, pass_index)
         d_cnt[mine] = work[mine]
@@ -743,3 +744,104 @@ def extra_c4(ctx):
                                        "sample": "the whole config: one LmPack_Bake(scene, 1, 64) pass, reference lightmap.c + path_tracer.c over the CPU BVH restatement"}
     scene.close()
     return out
+
+
+def extra_c5(ctx):
+    """BASELINE configs[4]: incoherent-ray intersection microbench, 100 M random rays against a 10 M-triangle soup,
+    closest hit (Pt_IntersectN_Device) and any hit (Pt_OccludedN_Device), rays resident on the device"""
+    torch, api, scenes, L = ctx.torch, ctx.api, ctx.scenes, ctx.L
+    tris, batch, batches = 10_000_000, 1 << 24, 6           # 6 x 16.8 M = 100.7 M rays
+    t0 = time.perf_counter()
+    desc = scenes.random_soup(tris, seed=11)
+    gen_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    scene = api.Scene(desc)
+    build_s = time.perf_counter() - t0
+    st = scene.stats
+    ro, rd = scenes.random_rays(batch, seed=13)
+    _, rd_o = scenes.random_rays(batch, seed=13, occlusion=True)
+    d_ro, d_rd, d_rdo = torch.from_numpy(ro).to(ctx.dev), torch.from_numpy(rd).to(ctx.dev), torch.from_numpy(rd_o).to(ctx.dev)
+    d_hits = torch.empty((batch, 12), dtype=torch.float32, device=ctx.dev)
+    d_occ = torch.empty(batch, dtype=torch.uint8, device=ctx.dev)
+    torch.cuda.synchronize()
+
+    def timed(fn):
+        fn()
+        ctx.stream.synchronize()
+        best = None
+        for _ in range(2):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ctx.flush.fill_(3)
+            e0.record(ctx.stream)
+            for _ in range(batches):
+                fn()
+            e1.record(ctx.stream)
+            e1.synchronize()
+            ms = e0.elapsed_time(e1)
+            best = ms if best is None else min(best, ms)
+        return best
+    sp = ctx.stream.cuda_stream
+    ms_c = timed(lambda: L.Pt_IntersectN_Device(scene.h, d_ro.data_ptr(), d_rd.data_ptr(), 0.0, d_hits.data_ptr(), batch, sp))
+    ms_o = timed(lambda: L.Pt_OccludedN_Device(scene.h, d_ro.data_ptr(), d_rdo.data_ptr(), 0.0, d_occ.data_ptr(), batch, sp))
+    total = batch * batches
+    closest, anyhit = total / ms_c / 1e3, total / ms_o / 1e3
+    own_nodes, own_tris = scene.fetch_counts(ro[:1 << 20], rd[:1 << 20])
+    hits = d_hits.cpu().numpy().view(np.uint32)
+    tc = traversal_counts("soup_10m_random_rays")
+    b_ray, b_any = bytes_per_ray(tc), 32 + 1 + tc["anyhit_nodes_per_ray"] * 80 + tc["anyhit_tris_per_ray"] * 48
+    out = {"workload": "100.7 M random rays (6 batches of 2^24, seed 13) vs 10 M-triangle soup (seed 11) (BASELINE configs[4])",
+           "metric": "Mrays/s", "closest_hit_mrays_s": closest, "any_hit_mrays_s": anyhit, "value": closest,
+           "hit_fraction": float((hits[:, 8] != 0).mean()), "occluded_fraction": float(d_occ.float().mean().item()),
+           "scene": {"generate_s": gen_s, "build_s": build_s, "bvh_build_ms": st.phaseMs[1], "bvh_nodes": st.bvhNodeCount},
+           "tree": {"own_nodes_per_ray": own_nodes / (1 << 20), "own_tris_per_ray": own_tris / (1 << 20),
+                    "canonical_nodes_per_ray": tc["nodes_per_ray"], "canonical_tris_per_ray": tc["tris_per_ray"]},
+           "roofline": {"bound": "hbm", "kernel": "k_closestHitPersistent", "bytes_per_ray": b_ray,
+                        "achieved": closest * 1e6 * b_ray / 1e9, "peak": ctx.peak, "unit": "GB/s",
+                        "frac": closest * 1e6 * b_ray / 1e9 / ctx.peak, "counts": "baseline/traversal_counts.json:soup_10m_random_rays"},
+           "roofline_any_hit": {"bound": "hbm", "kernel": "k_anyHitPersistent", "bytes_per_ray": b_any,
+                                "achieved": anyhit * 1e6 * b_any / 1e9, "peak": ctx.peak, "unit": "GB/s",
+                                "frac": anyhit * 1e6 * b_any / 1e9 / ctx.peak}}
+    # end to end with host rays and host hits (Pt_IntersectN): 32 B in, 48 B out per ray over PCIe
+    n_e2e = 1 << 22
+    scene.intersect(ro[:1 << 16], rd[:1 << 16])
+    t0 = time.perf_counter()
+    scene.intersect(ro[:n_e2e], rd[:n_e2e])
+    dt = time.perf_counter() - t0
+    out["e2e"] = {"value": n_e2e / dt / 1e6, "unit": "Mrays/s", "how": "Pt_IntersectN, 4.2 M host rays in, PtRayHit out",
+                  "h2d_bytes_per_step": n_e2e * 32, "d2h_bytes_per_step": n_e2e * 48}
+    scene.close()
+    if not ctx.args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import truth
+        verts = desc.entities[0].positions
+        t0 = time.perf_counter()
+        bvh = truth.CpuBvh(verts)
+        cpu_build = time.perf_counter() - t0
+        n = 2_000_000
+        t0 = time.perf_counter()
+        prim, _, _ = bvh.intersect(ro[:n], rd[:n])
+        dt = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        bvh.occluded(ro[:n], rd_o[:n])
+        dt_o = time.perf_counter() - t0
+        bvh.close()
+        gpu_prim = np.where(hits[:n, 8] != 0, hits[:n, 9].view(np.int32) // 3, -1)
+        out["cpu_baseline"] = {"value": n / dt / 1e6, "unit": "Mrays/s", "any_hit_mrays_s": n / dt_o / 1e6, "cores": truth.threads(), "kind": "port",
+                               "sample": "2 M of the same rays against the same mesh, CPU BVH restatement of Embree's rtcIntersect1 / rtcOccluded (binary unavailable)",
+                               "bvh_build_s": cpu_build, "agreement_with_gpu": float((gpu_prim == prim).mean())}
+    return out
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
