@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 
 namespace pt {
 
@@ -36,6 +37,18 @@ int sahMaxTris()
 {
     const char* e = getenv("PIMPT_SAH_MAX_TRIS");
     return e ? atoi(e) : kSahMaxTris;
+}
+
+// PIMPT_SAH_LARGE_NODE overrides kLargeNode: nodes above it take the many-CTAs-per-node levels
+// (a huge value turns them off, which is how the tests compare the two paths)
+#ifndef PT_SAH_LARGE_NODE
+#define PT_SAH_LARGE_NODE 8192
+#endif
+int largeNodeMin()
+{
+    const char* e = getenv("PIMPT_SAH_LARGE_NODE");
+    const int v = e ? atoi(e) : PT_SAH_LARGE_NODE;
+    return v < 2 * 2048 ? 2 * 2048 : v;       // at least two tiles
 }
 
 // PIMPT_FLOAT_NODES overrides kFloatNodeMaxNodes (0 = never build the fp32 node form)
@@ -497,6 +510,339 @@ __global__ void k_sahInit(BinTree T, int n, const int* __restrict__ bounds, int*
     }
 }
 
+// ---- binned SAH, large nodes: many CTAs per node -----------------------------------------------
+// One warp per node is fine for the thousands of small nodes deep in the tree, but the first levels
+// have a handful of nodes with millions of primitives each (the root of the 10 M-triangle soup was
+// binned and partitioned by 32 lanes). Nodes above PT_SAH_LARGE_NODE primitives are therefore processed level
+// by level with the work spread over tiles of kLargeTile primitives:
+//   plan       tile ranges of this level's large nodes, their bin mapping, cleared bins
+//   bin        every tile bins its primitives in shared memory and adds its bins to the node's
+//   pick       a warp per node evaluates the 45 planes, allocates the two children
+//   partition  every tile sends its primitives left or right (one atomic pair per tile for its two
+//              output ranges) and accumulates the children's centroid bounds
+//   copy       the partitioned ranges go back from tmp to order
+// Children above that size go to the next level's list, the others to the queue of the warp-per-node
+// kernel above, which finishes the tree. Tiles claim their output ranges in arrival order, so the order
+// of primitives inside a node's range can differ from run to run; the split planes, and with them the
+// tree and every hit, do not depend on it (only the pathological all-centroids-equal node splits by
+// position, and such a node is handed to the warp-per-node kernel unsplit).
+
+constexpr int kLargeTile = 2048;
+constexpr int kLargeThreads = 256;
+constexpr int kLargeItems = kLargeTile / kLargeThreads;
+
+struct LargeNode
+{
+    int node, first, count;
+    int tileStart;              // first tile of this node in the level's grid (plan)
+    int parent, side;           // where the centroid bounds come from: parent's slot in the previous level's list (-1: scene bounds)
+    float cmin[3], scale[3];    // centroid -> bin (plan); scale 0: no extent on that axis
+    int axis, plane, nLeft;     // the split (pick); axis < 0: not split here
+    int curL, curR;             // output cursors of the partition
+    int clo[2][3], chi[2][3];   // children's centroid bounds, ordered ints (partition)
+};
+
+__device__ __forceinline__ int sahBinOf(float c, float cmin, float scale)
+{
+    int bin = (int)((c - cmin) * scale);
+    return bin < 0 ? 0 : (bin > kSahBins - 1 ? kSahBins - 1 : bin);
+}
+
+// tile -> slot of its node in the level's list (tileStart is ascending)
+__device__ __forceinline__ int largeSlotOfTile(const LargeNode* __restrict__ L, int nLarge, int tile)
+{
+    int lo = 0, hi = nLarge - 1;
+    while (lo < hi)
+    {
+        const int mid = (lo + hi + 1) >> 1;
+        if (L[mid].tileStart <= tile) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+// one block: tile ranges and bin mappings of the level's nodes; counters[4] = tiles of the level
+__global__ void __launch_bounds__(256) k_sahPlanLarge(LargeNode* L, int nLarge, const LargeNode* __restrict__ prev,
+                                                     const int* __restrict__ bounds, SahBins* bins, uint32_t* counters)
+{
+    __shared__ int sTiles[256];
+    // tiles per node, scanned in chunks of 256 nodes
+    int running = 0;
+    for (int base = 0; base < nLarge; base += 256)
+    {
+        const int i = base + threadIdx.x;
+        const int tiles = i < nLarge ? (L[i].count + kLargeTile - 1) / kLargeTile : 0;
+        sTiles[threadIdx.x] = tiles;
+        __syncthreads();
+        for (int o = 1; o < 256; o <<= 1)
+        {
+            const int v = threadIdx.x >= o ? sTiles[threadIdx.x - o] : 0;
+            __syncthreads();
+            sTiles[threadIdx.x] += v;
+            __syncthreads();
+        }
+        if (i < nLarge) L[i].tileStart = running + sTiles[threadIdx.x] - tiles;
+        running += sTiles[255];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) counters[4] = (uint32_t)running;
+    for (int i = threadIdx.x; i < nLarge; i += 256)
+    {
+        LargeNode& n = L[i];
+        float lo[3], hi[3];
+        for (int k = 0; k < 3; ++k)
+        {
+            if (n.parent < 0) { lo[k] = orderedToFloat(bounds[k]); hi[k] = orderedToFloat(bounds[3 + k]); }
+            else { lo[k] = orderedToFloat(prev[n.parent].clo[n.side][k]); hi[k] = orderedToFloat(prev[n.parent].chi[n.side][k]); }
+            const float ext = hi[k] - lo[k];
+            n.cmin[k] = lo[k];
+            n.scale[k] = ext > 0.0f ? (float)kSahBins / ext : 0.0f;
+        }
+        n.axis = -1; n.plane = 0; n.nLeft = 0; n.curL = 0; n.curR = 0;
+        for (int s2 = 0; s2 < 2; ++s2)
+            for (int k = 0; k < 3; ++k) { n.clo[s2][k] = floatToOrdered(3.0e38f); n.chi[s2][k] = floatToOrdered(-3.0e38f); }
+    }
+    // cleared bins
+    int* b = reinterpret_cast<int*>(bins);
+    const int words = (int)(sizeof(SahBins) / sizeof(int));
+    for (int i = threadIdx.x; i < nLarge * words; i += 256)
+    {
+        const int w = i % words;
+        b[i] = w < 3 * kSahBins * 3 ? floatToOrdered(3.0e38f) : (w < 2 * 3 * kSahBins * 3 ? floatToOrdered(-3.0e38f) : 0);
+    }
+}
+
+__global__ void __launch_bounds__(kLargeThreads) k_sahBinLarge(const LargeNode* __restrict__ L, int nLarge,
+                                                                const F4* __restrict__ leafLo, const F4* __restrict__ leafHi,
+                                                                const int* __restrict__ order, SahBins* bins,
+                                                                const uint32_t* __restrict__ counters)
+{
+    __shared__ SahBins B;
+    const int tile = blockIdx.x;
+    if (tile >= (int)counters[4]) return;
+    const int slot = largeSlotOfTile(L, nLarge, tile);
+    const LargeNode n = L[slot];
+    for (int i = threadIdx.x; i < 3 * kSahBins; i += kLargeThreads)
+    {
+        const int a = i / kSahBins, b = i % kSahBins;
+        for (int k = 0; k < 3; ++k) { B.lo[a][b][k] = floatToOrdered(3.0e38f); B.hi[a][b][k] = floatToOrdered(-3.0e38f); }
+        B.cnt[a][b] = 0;
+    }
+    __syncthreads();
+    const int begin = n.first + (tile - n.tileStart) * kLargeTile, end = min(begin + kLargeTile, n.first + n.count);
+    for (int i = begin + threadIdx.x; i < end; i += kLargeThreads)
+    {
+        const int t = order[i];
+        const F4 a = leafLo[t], b = leafHi[t];
+        const float c[3] = { (a.x + b.x) * 0.5f, (a.y + b.y) * 0.5f, (a.z + b.z) * 0.5f };
+        const int lo3[3] = { floatToOrdered(a.x), floatToOrdered(a.y), floatToOrdered(a.z) };
+        const int hi3[3] = { floatToOrdered(b.x), floatToOrdered(b.y), floatToOrdered(b.z) };
+        for (int ax = 0; ax < 3; ++ax)
+        {
+            if (n.scale[ax] == 0.0f) continue;
+            const int bin = sahBinOf(c[ax], n.cmin[ax], n.scale[ax]);
+            for (int k = 0; k < 3; ++k) { atomicMin(&B.lo[ax][bin][k], lo3[k]); atomicMax(&B.hi[ax][bin][k], hi3[k]); }
+            atomicAdd(&B.cnt[ax][bin], 1);
+        }
+    }
+    __syncthreads();
+    SahBins& G = bins[slot];
+    for (int i = threadIdx.x; i < 3 * kSahBins; i += kLargeThreads)
+    {
+        const int a = i / kSahBins, b = i % kSahBins;
+        const int c = B.cnt[a][b];
+        if (c == 0) continue;
+        for (int k = 0; k < 3; ++k) { atomicMin(&G.lo[a][b][k], B.lo[a][b][k]); atomicMax(&G.hi[a][b][k], B.hi[a][b][k]); }
+        atomicAdd(&G.cnt[a][b], c);
+    }
+}
+
+// counters: [0] nodes allocated, [2] next level's large nodes, [3] nodes handed to the warp-per-node kernel
+__global__ void __launch_bounds__(kSahWarps * 32) k_sahPickLarge(BinTree T, LargeNode* L, int nLarge, const SahBins* __restrict__ bins,
+                                                                  LargeNode* next, int* smallQ, uint32_t* counters, int largeMin)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * kSahWarps + warp;
+    if (slot >= nLarge) return;
+    LargeNode& n = L[slot];
+    const SahBins& B = bins[slot];
+    float bestCost = 3.0e38f;
+    int bestCand = -1;
+    for (int cand = lane; cand < 3 * (kSahBins - 1); cand += 32)
+    {
+        const int ax = cand / (kSahBins - 1), sp = cand % (kSahBins - 1);
+        if (n.scale[ax] == 0.0f) continue;
+        float llo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, lhi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+        float rlo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, rhi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
+        int nl = 0, nr = 0;
+        for (int b = 0; b < kSahBins; ++b)
+        {
+            const int c = B.cnt[ax][b];
+            if (c == 0) continue;
+            if (b <= sp)
+            {
+                nl += c;
+                for (int k = 0; k < 3; ++k) { llo[k] = fminf(llo[k], orderedToFloat(B.lo[ax][b][k])); lhi[k] = fmaxf(lhi[k], orderedToFloat(B.hi[ax][b][k])); }
+            }
+            else
+            {
+                nr += c;
+                for (int k = 0; k < 3; ++k) { rlo[k] = fminf(rlo[k], orderedToFloat(B.lo[ax][b][k])); rhi[k] = fmaxf(rhi[k], orderedToFloat(B.hi[ax][b][k])); }
+            }
+        }
+        if (nl == 0 || nr == 0) continue;
+        const float al = boxArea(f4(llo[0], llo[1], llo[2], 0), f4(lhi[0], lhi[1], lhi[2], 0));
+        const float ar = boxArea(f4(rlo[0], rlo[1], rlo[2], 0), f4(rhi[0], rhi[1], rhi[2], 0));
+        const float cost = al * (float)nl + ar * (float)nr;
+        if (cost < bestCost) { bestCost = cost; bestCand = cand; }
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const float oc = __shfl_xor_sync(0xffffffffu, bestCost, o);
+        const int ocand = __shfl_xor_sync(0xffffffffu, bestCand, o);
+        if (oc < bestCost || (oc == bestCost && ocand >= 0 && (bestCand < 0 || ocand < bestCand))) { bestCost = oc; bestCand = ocand; }
+    }
+    if (lane != 0) return;
+    if (bestCand < 0)
+    {
+        // every centroid in one bin on every axis: the warp-per-node kernel splits such a node by position
+        smallQ[atomicAdd(&counters[3], 1u)] = n.node;
+        return;
+    }
+    const int ax = bestCand / (kSahBins - 1), sp = bestCand % (kSahBins - 1);
+    float clo[2][3], chi[2][3];
+    for (int side = 0; side < 2; ++side)
+        for (int k = 0; k < 3; ++k) { clo[side][k] = 3.0e38f; chi[side][k] = -3.0e38f; }
+    int nLeft = 0;
+    for (int b = 0; b < kSahBins; ++b)
+    {
+        if (B.cnt[ax][b] == 0) continue;
+        const int side = b <= sp ? 0 : 1;
+        if (side == 0) nLeft += B.cnt[ax][b];
+        for (int k = 0; k < 3; ++k)
+        {
+            clo[side][k] = fminf(clo[side][k], orderedToFloat(B.lo[ax][b][k]));
+            chi[side][k] = fmaxf(chi[side][k], orderedToFloat(B.hi[ax][b][k]));
+        }
+    }
+    n.axis = ax; n.plane = sp; n.nLeft = nLeft;
+    const uint32_t base = atomicAdd(&counters[0], 2u);
+    T.lo[n.node].w = u2f(base);
+    T.hi[n.node].w = u2f(base + 1u);
+    const int kf[2] = { n.first, n.first + nLeft }, kc[2] = { nLeft, n.count - nLeft };
+    for (int side = 0; side < 2; ++side)
+    {
+        const int k = (int)base + side;
+        T.lo[k] = f4(clo[side][0], clo[side][1], clo[side][2], 0.0f);
+        T.hi[k] = f4(chi[side][0], chi[side][1], chi[side][2], 0.0f);
+        T.first[k] = kf[side]; T.last[k] = kf[side] + kc[side] - 1;
+        if (kc[side] > largeMin)
+        {
+            LargeNode c;
+            c.node = k; c.first = kf[side]; c.count = kc[side]; c.tileStart = 0; c.parent = slot; c.side = side;
+            next[atomicAdd(&counters[2], 1u)] = c;
+        }
+        else if (kc[side] > kLeafMaxTris) smallQ[atomicAdd(&counters[3], 1u)] = k;
+    }
+}
+
+__global__ void __launch_bounds__(kLargeThreads) k_sahPartitionLarge(LargeNode* L, int nLarge, const F4* __restrict__ leafLo,
+                                                                      const F4* __restrict__ leafHi, const int* __restrict__ order,
+                                                                      int* __restrict__ tmp, const uint32_t* __restrict__ counters)
+{
+    __shared__ int sCount[2], sBase[2], sFill[2];
+    __shared__ int sClo[2][3], sChi[2][3];
+    const int tile = blockIdx.x;
+    if (tile >= (int)counters[4]) return;
+    const int slot = largeSlotOfTile(L, nLarge, tile);
+    LargeNode& n = L[slot];
+    const int axis = n.axis;
+    if (axis < 0) return;                   // not split here: its range stays as it is
+    const int plane = n.plane, nodeFirst = n.first, nLeft = n.nLeft;
+    const float cminA = n.cmin[axis], scaleA = n.scale[axis];
+    if (threadIdx.x < 2) { sCount[threadIdx.x] = 0; sFill[threadIdx.x] = 0; }
+    if (threadIdx.x < 6) { (&sClo[0][0])[threadIdx.x] = floatToOrdered(3.0e38f); (&sChi[0][0])[threadIdx.x] = floatToOrdered(-3.0e38f); }
+    __syncthreads();
+    const int begin = nodeFirst + (tile - n.tileStart) * kLargeTile, end = min(begin + kLargeTile, nodeFirst + n.count);
+    int prim[kLargeItems];
+    uint32_t leftBits = 0, validBits = 0;
+    float clo[2][3], chi[2][3];
+    for (int s2 = 0; s2 < 2; ++s2)
+        for (int k = 0; k < 3; ++k) { clo[s2][k] = 3.0e38f; chi[s2][k] = -3.0e38f; }
+    int myLeft = 0, myRight = 0;
+    #pragma unroll
+    for (int r = 0; r < kLargeItems; ++r)
+    {
+        const int i = begin + r * kLargeThreads + threadIdx.x;
+        prim[r] = 0;
+        if (i < end)
+        {
+            const int t = order[i];
+            prim[r] = t;
+            const F4 a = leafLo[t], b = leafHi[t];
+            const float c[3] = { (a.x + b.x) * 0.5f, (a.y + b.y) * 0.5f, (a.z + b.z) * 0.5f };
+            const bool left = sahBinOf(c[axis], cminA, scaleA) <= plane;
+            validBits |= 1u << r;
+            leftBits |= left ? (1u << r) : 0u;
+            const int s2 = left ? 0 : 1;
+            for (int k = 0; k < 3; ++k) { clo[s2][k] = fminf(clo[s2][k], c[k]); chi[s2][k] = fmaxf(chi[s2][k], c[k]); }
+            myLeft += left ? 1 : 0; myRight += left ? 0 : 1;
+        }
+    }
+    // tile totals -> one pair of global atomics for the tile's two output ranges
+    int wl = myLeft, wr = myRight;
+    for (int o = 16; o > 0; o >>= 1) { wl += __shfl_xor_sync(0xffffffffu, wl, o); wr += __shfl_xor_sync(0xffffffffu, wr, o); }
+    for (int s2 = 0; s2 < 2; ++s2)
+        for (int k = 0; k < 3; ++k) { clo[s2][k] = warpMinF(clo[s2][k]); chi[s2][k] = warpMaxF(chi[s2][k]); }
+    if ((threadIdx.x & 31) == 0)
+    {
+        if (wl) atomicAdd(&sCount[0], wl);
+        if (wr) atomicAdd(&sCount[1], wr);
+        for (int s2 = 0; s2 < 2; ++s2)
+            for (int k = 0; k < 3; ++k) { atomicMin(&sClo[s2][k], floatToOrdered(clo[s2][k])); atomicMax(&sChi[s2][k], floatToOrdered(chi[s2][k])); }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        sBase[0] = nodeFirst + (sCount[0] ? atomicAdd(&n.curL, sCount[0]) : 0);
+        sBase[1] = nodeFirst + nLeft + (sCount[1] ? atomicAdd(&n.curR, sCount[1]) : 0);
+    }
+    if (threadIdx.x < 6)
+    {
+        const int s2 = threadIdx.x / 3, k = threadIdx.x % 3;
+        if (sCount[s2]) { atomicMin(&n.clo[s2][k], sClo[s2][k]); atomicMax(&n.chi[s2][k], sChi[s2][k]); }
+    }
+    __syncthreads();
+    // positions inside the tile's ranges: one shared atomic per warp and side
+    const int lane = threadIdx.x & 31;
+    #pragma unroll
+    for (int r = 0; r < kLargeItems; ++r)
+    {
+        const bool valid = (validBits >> r) & 1u, left = (leftBits >> r) & 1u;
+        const unsigned ml = __ballot_sync(0xffffffffu, valid && left), mr = __ballot_sync(0xffffffffu, valid && !left);
+        int bl = 0, br = 0;
+        if (lane == 0)
+        {
+            if (ml) bl = atomicAdd(&sFill[0], __popc(ml));
+            if (mr) br = atomicAdd(&sFill[1], __popc(mr));
+        }
+        bl = __shfl_sync(0xffffffffu, bl, 0); br = __shfl_sync(0xffffffffu, br, 0);
+        const unsigned lt = (1u << lane) - 1u;
+        if (valid) tmp[left ? (sBase[0] + bl + __popc(ml & lt)) : (sBase[1] + br + __popc(mr & lt))] = prim[r];
+    }
+}
+
+__global__ void __launch_bounds__(kLargeThreads) k_sahCopyLarge(const LargeNode* __restrict__ L, int nLarge, int* __restrict__ order,
+                                                                 const int* __restrict__ tmp, const uint32_t* __restrict__ counters)
+{
+    const int tile = blockIdx.x;
+    if (tile >= (int)counters[4]) return;
+    const int slot = largeSlotOfTile(L, nLarge, tile);
+    const LargeNode& n = L[slot];
+    if (n.axis < 0) return;
+    const int begin = n.first + (tile - n.tileStart) * kLargeTile, end = min(begin + kLargeTile, n.first + n.count);
+    for (int i = begin + threadIdx.x; i < end; i += kLargeThreads) order[i] = tmp[i];
+}
+
 struct CollapseWork { int32_t bin; uint32_t wide; };
 
 // counters: [0] wide nodes allocated, [1] triangles allocated, [2] next-level queue length
@@ -634,7 +980,7 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
     bool ok = devAlloc(leafLo, n) && devAlloc(leafHi, n) && devAlloc(lo, total) && devAlloc(hi, total) &&
               devAlloc(bounds, 12) && devAlloc(first, total) && devAlloc(last, total) && devAlloc(parent, total) &&
               devAlloc(visits, n) && devAlloc(keysA, n) && devAlloc(keysB, n) && devAlloc(valsA, n) &&
-              devAlloc(valsB, n) && devAlloc(hist, (size_t)256 * sortBlocks) && devAlloc(counters, 4) &&
+              devAlloc(valsB, n) && devAlloc(hist, (size_t)256 * sortBlocks) && devAlloc(counters, 8) &&
               devAlloc(q0, n) && devAlloc(q1, n) && devAlloc(out.nodes, n) && devAlloc(out.tris, n);
     const int blocks = (n + 255) / 256;
     if (ok)
@@ -654,6 +1000,47 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
             k_sahInit<<<blocks, 256, 0, stream>>>(T, n, bounds, order, sq[0], counters);
             g_counters.kernelLaunches += 1;
             int cur = 0;
+            int nSmall = n > kLeafMaxTris ? 1 : 0;      // k_sahInit queued the root for the warp-per-node kernel
+            if (ok && n > largeNodeMin())
+            {
+                // the large-node levels (see above); the warp-per-node queue fills up as nodes get small enough
+                const int maxLarge = n / std::max(largeNodeMin(), 1) + 2;
+                const unsigned maxTiles = (unsigned)(n / kLargeTile + maxLarge + 1);
+                LargeNode* dLarge[2] = { nullptr, nullptr };
+                SahBins* dBins = nullptr;
+                ok = devAlloc(dLarge[0], (size_t)maxLarge) && devAlloc(dLarge[1], (size_t)maxLarge) && devAlloc(dBins, (size_t)maxLarge);
+                LargeNode root;
+                memset(&root, 0, sizeof(root));
+                root.node = 0; root.first = 0; root.count = n; root.parent = -1;
+                const uint32_t init[5] = { 1u, 0u, 0u, 0u, 0u };
+                ok = ok && PT_CUDA(cudaMemcpyAsync(dLarge[0], &root, sizeof(root), cudaMemcpyHostToDevice, stream));
+                ok = ok && PT_CUDA(cudaMemcpyAsync(counters, init, sizeof(init), cudaMemcpyHostToDevice, stream));
+                int nLarge = 1, lcur = 0;
+                while (ok && nLarge > 0)
+                {
+                    k_sahPlanLarge<<<1, 256, 0, stream>>>(dLarge[lcur], nLarge, dLarge[lcur ^ 1], bounds, dBins, counters);
+                    k_sahBinLarge<<<maxTiles, kLargeThreads, 0, stream>>>(dLarge[lcur], nLarge, leafLo, leafHi, order, dBins, counters);
+                    k_sahPickLarge<<<(nLarge + kSahWarps - 1) / kSahWarps, kSahWarps * 32, 0, stream>>>(T, dLarge[lcur], nLarge, dBins,
+                                                                                                          dLarge[lcur ^ 1], sq[0], counters, largeNodeMin());
+                    k_sahPartitionLarge<<<maxTiles, kLargeThreads, 0, stream>>>(dLarge[lcur], nLarge, leafLo, leafHi, order, tmp, counters);
+                    k_sahCopyLarge<<<maxTiles, kLargeThreads, 0, stream>>>(dLarge[lcur], nLarge, order, tmp, counters);
+                    g_counters.kernelLaunches += 5;
+                    uint32_t h[4];
+                    ok = ok && PT_CUDA(cudaGetLastError());
+                    ok = ok && PT_CUDA(cudaMemcpyAsync(h, counters, sizeof(h), cudaMemcpyDeviceToHost, stream));
+                    ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
+                    if (!ok) break;
+                    nLarge = (int)h[2];
+                    nSmall = (int)h[3];
+                    ok = PT_CUDA(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), stream));
+                    lcur ^= 1;
+                    if (nLarge > maxLarge) { setError("buildBvh: large-node list overflow"); ok = false; }
+                }
+                cudaFree(dLarge[0]); cudaFree(dLarge[1]); cudaFree(dBins);
+                // hand over to the warp-per-node kernel: its input queue is sq[0], its level counter counters[1]
+                const uint32_t qlen = (uint32_t)nSmall;
+                ok = ok && PT_CUDA(cudaMemcpyAsync(counters + 1, &qlen, sizeof(qlen), cudaMemcpyHostToDevice, stream));
+            }
             for (;;)
             {
                 uint32_t h[2];

@@ -242,3 +242,25 @@ def test_lbvh_path_matches_sah_path(api, lut, oracle, monkeypatch):
     s.close()
     assert (a["iVert"] == b["iVert"]).all() and np.array_equal(a["wuvt"], b["wuvt"])
     assert (a["type"] != 0).mean() > 0.05
+
+
+def test_sah_large_node_levels_match_warp_per_node(api, lut, monkeypatch):
+    """The binned-SAH builder handles nodes above PT_SAH_LARGE_NODE primitives with many CTAs per node (tiles bin and
+    partition in parallel) and the rest with a warp per node. Both choose the same planes from the same bins, so with
+    the large-node levels switched off the tree has to come out the same: equal hits, equal node count, equal work
+    per ray."""
+    desc = scenes.random_soup(300_000, seed=5, extent=20.0)
+    desc.brdf_lut = lut
+    ro, rd = scenes.random_rays(100_000, seed=6, extent=20.0)
+    out = []
+    for large in (None, "1000000000"):
+        if large:
+            monkeypatch.setenv("PIMPT_SAH_LARGE_NODE", large)
+        s = api.Scene(desc)
+        out.append((s.intersect(ro, rd), s.stats.bvhNodeCount, s.fetch_counts(ro, rd), s.stats.phaseMs[1]))
+        s.close()
+    (a, nodes_a, cnt_a, ms_a), (b, nodes_b, cnt_b, ms_b) = out
+    assert (a["iVert"] == b["iVert"]).all() and np.array_equal(a["wuvt"], b["wuvt"])
+    assert (a["type"] != 0).mean() > 0.05
+    assert abs(nodes_a - nodes_b) <= 0.001 * nodes_b, (nodes_a, nodes_b)
+    assert abs(cnt_a[0] - cnt_b[0]) <= 0.01 * cnt_b[0] and abs(cnt_a[1] - cnt_b[1]) <= 0.01 * cnt_b[1], (cnt_a, cnt_b)
