@@ -169,19 +169,26 @@ def test_c4_lightmap_1024_wavefront_within_oracle_spread(api, oracle, c4_pack):
 
 # --------------------------------------------------------------------------- C3 / C5
 
-def _check_against_truth(got, hits, flags, exempt_floor=0.05):
+def _check_against_truth(got, hits, flags, ro, rd):
     hit = flags != 0
     tie = flags == 2
     assert (((got["type"] != 0) == hit) | tie).mean() >= AGREE
     same = hit & (got["iVert"] == hits["prim"] * 3)
     assert (same | tie | ~hit).mean() >= AGREE, (same | tie | ~hit).mean()
-    # hit distance: 1e-5 relative (north_star) wherever fp32 can deliver it. A distance is a difference of
-    # coordinates of magnitude |ro| + t: below t = exempt_floor the fp32 ulp of the coordinates is more than
-    # 1e-5 of t, so those rays are compared absolutely and counted
+    # hit distance: 1e-5 relative (north_star) on the rays where fp32 can deliver it. The fp32 test subtracts
+    # coordinates of magnitude M = max(|origin|, |hit point|) before anything else, so t carries an absolute error
+    # of a few ulp(M), magnified by 1 / cos(ray, normal) on grazing hits. A ray that misses 1e-5 t has to be
+    # within that floor (8 ulp); the share of rays that needed the floor is returned (the exempted set).
     t_gpu, t_ref = got["wuvt"][same, 3].astype(np.float64), hits["t"][same].astype(np.float64)
-    rel = np.abs(t_gpu - t_ref) / np.maximum(t_ref, exempt_floor)
-    assert rel.max() <= T_REL, rel.max()
-    return float((t_ref < exempt_floor).mean())
+    d = rd[same, :3].astype(np.float64); o = ro[same, :3].astype(np.float64)
+    ng = hits["ng"][same].astype(np.float64)
+    cos = np.abs((ng * d).sum(axis=1)) / np.maximum(np.linalg.norm(ng, axis=1), 1e-30)
+    scale = np.maximum(np.abs(o).max(axis=1), np.abs(o + d * t_ref[:, None]).max(axis=1))
+    fp32_floor = 8.0 * 2.0 ** -24 * scale / np.maximum(cos, 1e-6)
+    tol = np.maximum(T_REL * t_ref, fp32_floor)
+    err = np.abs(t_gpu - t_ref)
+    assert (err <= tol).all(), (err / tol).max()
+    return float((err > T_REL * t_ref).mean())
 
 
 def test_c3_interior_1m_scene_and_hits(api, lut):
@@ -207,7 +214,8 @@ def test_c3_interior_1m_scene_and_hits(api, lut):
     assert np.array_equal(bf, flags[sub]) and np.array_equal(bh["prim"], hits["prim"][sub]) and np.array_equal(bh["t"], hits["t"][sub])
     grid.close()
     assert (flags != 0).mean() > 0.5
-    _check_against_truth(got, hits, flags)
+    limited = _check_against_truth(got, hits, flags, ro, rd)
+    assert limited < 0.01, limited          # >= 99 % of the rays meet 1e-5 relative outright
     s.close()
 
 
@@ -231,7 +239,8 @@ def test_c5_soup_10m_closest_any_hit_and_persistent_wavefront(api, lut):
     bh, bf = truth.brute(verts, ro[sub], rd[sub])
     assert np.array_equal(bf, flags[sub]) and np.array_equal(bh["prim"], hits["prim"][sub]) and np.array_equal(bh["t"], hits["t"][sub])
     assert 0.2 < (flags != 0).mean() < 1.0
-    _check_against_truth(got, hits, flags)
+    limited = _check_against_truth(got, hits, flags, ro, rd)
+    assert limited < 0.01, limited          # coordinates up to 100 m (ulp 0.8e-5 m): still >= 99 % within 1e-5 relative
     # occlusion rays: tFar uniform in [1, 50]
     ro2, rd2 = scenes.random_rays(n, seed=13, occlusion=True)
     occ = s.occluded(ro2, rd2).astype(bool)
