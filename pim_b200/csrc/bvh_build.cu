@@ -24,10 +24,12 @@ constexpr int kSortThreads = 256;
 constexpr int kSortItems = 8;
 constexpr int kSortTile = kSortThreads * kSortItems;   // keys per block
 
-// up to this many triangles the tree is built top-down with binned SAH; above it with the
-// Morton-code radix tree (LBVH), whose build is one pass per level of the sort, not of the tree
+// up to this many triangles the tree is built top-down with binned SAH (the reference asks Embree for
+// RTC_BUILD_QUALITY_HIGH, path_tracer.c:627); above it with the Morton-code radix tree (LBVH), whose
+// build is one pass per level of the sort, not of the tree. With the many-CTA levels for large nodes
+// (below) the SAH build of the 10 M-triangle soup is fast enough to be the default there too.
 #ifndef PT_SAH_MAX_TRIS
-#define PT_SAH_MAX_TRIS (4 << 20)
+#define PT_SAH_MAX_TRIS (64 << 20)
 #endif
 constexpr int kSahMaxTris = PT_SAH_MAX_TRIS;
 
