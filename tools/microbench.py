@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1 << 24)
     ap.add_argument("--cpu-rays", type=int, default=0, help="rays for the CPU baseline and canonical fetch counts")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--extent", type=float, default=100.0)
     ap.add_argument("--coop", type=int, default=-1, help="eight lanes per ray: -1 by tree size, 0 off, 1 on")
     ap.add_argument("--extent", type=float, default=100.0)
     args = ap.parse_args()
