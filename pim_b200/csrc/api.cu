@@ -190,7 +190,6 @@ static bool ensureInit()
     if (n <= 0) { setError("no CUDA device: libpimpt has no CPU path"); return false; }
     if (const char* e = getenv("PIMPT_PERSISTENT")) g_persistentTraversal = atoi(e);   // tuning switches
     if (const char* e = getenv("PIMPT_FINISH")) g_finishThreshold = atoi(e);
-    if (const char* e = getenv("PIMPT_COOP")) g_coopTraversal = atoi(e);
     g_initialised = true;
     return true;
 }
@@ -405,7 +404,7 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
     const int32_t triCount = vertCount / 3;
     ok = ok && buildBvh(dPos, triCount, s->bvh, st);
     V.bvh.nodes = s->bvh.nodes; V.bvh.tris = s->bvh.tris; V.bvh.nodesF = s->bvh.nodesF;
-    V.bvh.nodeCount = s->bvh.nodeCount; V.bvh.triCount = s->bvh.triCount; V.bvh.depth = s->bvh.depth;
+    V.bvh.nodeCount = s->bvh.nodeCount; V.bvh.triCount = s->bvh.triCount;
 
     phase(1);
     // SetupEmissives (path_tracer.c:845-883): device pdf, ordered compaction
@@ -1581,7 +1580,6 @@ int32_t Pt_SetOption(const char* name, int32_t value)
     if (!ensureInit()) return -1;       // the environment's values are read first, then overridden here
     if (!strcmp(name, "persistent")) { g_persistentTraversal = value; return 0; }
     if (!strcmp(name, "finish")) { g_finishThreshold = value; return 0; }
-    if (!strcmp(name, "coop")) { g_coopTraversal = value; return 0; }
     setError("Pt_SetOption: unknown option '%s'", name);
     return -1;
 }

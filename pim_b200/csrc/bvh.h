@@ -63,7 +63,6 @@ struct Bvh
     int32_t nodeCount;
     int32_t triCount;
     const WideNodeF* nodesF;    // null above kFloatNodeMaxNodes nodes (or 2^24 triangles)
-    int32_t depth;              // levels of the wide tree: a traversal stack never holds more than 7 entries per level
 };
 
 struct Hit

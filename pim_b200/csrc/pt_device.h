@@ -33,8 +33,6 @@ extern int g_persistentTraversal;
 extern int g_finishThreshold;   // 0: one thread per ray, 1: persistent warps that refill idle lanes, -1: by BVH size
 bool usePersistent(int32_t bvhNodeCount);
 bool usePersistentBatch(int32_t bvhNodeCount);
-extern int g_coopTraversal;      // eight lanes per ray in the batch kernels: -1 by tree size, 0 never, 1 always
-bool useCoopBatch(int32_t bvhNodeCount);
 extern KernelStats g_kernelStats;
 
 constexpr int kSmCount = 148;           // B200: 2 dies x 74 SMs

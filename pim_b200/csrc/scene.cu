@@ -11,7 +11,6 @@
 //       brdfLutBake     BakeBrdfFn (src/math/lighting.c:31-86)
 #include "pt_device.h"
 #include "kernels_common.cuh"
-#include "traverse_coop.h"
 
 #include <algorithm>
 
@@ -181,83 +180,6 @@ __global__ void __launch_bounds__(kTravThreads) k_anyHitPersistent(DScene S, con
     }
 }
 
-// K3c / K4c: eight lanes per ray (traverse_coop.h). Persistent CTAs; a group claims kCoopChunk consecutive
-// rays per atomic. Every loop iteration is one wide node for each of the warp's four rays.
-template <bool kAnyHit>
-__global__ void __launch_bounds__(kCoopThreads) k_traceCoop(DScene S, const F4* __restrict__ ro, const F4* __restrict__ rd,
-                                                            float tNear, RayHitOut* __restrict__ out, uint8_t* __restrict__ occ,
-                                                            int64_t n, unsigned long long* cursor, int* overflow)
-{
-    __shared__ unsigned long long stackMem[kCoopGroups * kCoopStackDepth];
-    const int lane = threadIdx.x & 31, sub = lane & 7, gshift = lane & 24;
-    const unsigned gmask = 0xffu << gshift;
-    unsigned long long* st = stackMem + (threadIdx.x >> 3) * kCoopStackDepth;
-    CoopRay r;
-    r.haveCur = false; r.sp = 0; r.found = false;
-    bool active = false, exhausted = false;
-    long long idx = 0, chunkBase = 0;
-    int chunkLeft = 0;
-    for (;;)
-    {
-        __syncwarp();
-        // a group whose ray has no current node pops one; an empty stack ends the ray
-        bool done = false;
-        if (active && !r.haveCur && !coopPop(r, st)) done = true;
-        if (done)
-        {
-            if (sub == 0)
-            {
-                if (kAnyHit) occ[idx] = r.found ? 1 : 0;
-                else
-                {
-                    Hit th;
-                    th.t = r.tBest; th.u = r.bu; th.v = r.bv; th.prim = r.found ? (int32_t)r.bestPrim : -1;
-                    th.ng = v3(0.0f, 0.0f, 0.0f);
-                    if (r.found)
-                    {
-                        // the geometric normal of the winning triangle, as triTest computes it
-                        const int32_t iv = th.prim * 3;
-                        const V3 A = ld3(S.positions, iv), B = ld3(S.positions, iv + 1), C = ld3(S.positions, iv + 2);
-                        th.ng = crossr(v3(subr(B.x, A.x), subr(B.y, A.y), subr(B.z, A.z)), v3(subr(C.x, A.x), subr(C.y, A.y), subr(C.z, A.z)));
-                    }
-                    const RayHit h = finishHit(S, r.rd, th);
-                    U4* dst = reinterpret_cast<U4*>(out + idx);
-                    U4 a; a.x = f2u(h.w); a.y = f2u(h.u); a.z = f2u(h.v); a.w = f2u(h.t);
-                    U4 b; b.x = f2u(h.normal.x); b.y = f2u(h.normal.y); b.z = f2u(h.normal.z); b.w = 0;
-                    U4 c; c.x = (uint32_t)h.type; c.y = (uint32_t)h.iVert; c.z = h.flags; c.w = 0;
-                    dst[0] = a; dst[1] = b; dst[2] = c;
-                }
-            }
-            active = false;
-        }
-        // a group without a ray takes the next one
-        if (!active && !exhausted)
-        {
-            if (chunkLeft == 0)
-            {
-                unsigned long long base = 0;
-                if (sub == 0) base = atomicAdd(cursor, (unsigned long long)kCoopChunk);
-                base = __shfl_sync(gmask, base, gshift);
-                chunkBase = (long long)base; chunkLeft = kCoopChunk;
-            }
-            idx = chunkBase + (kCoopChunk - chunkLeft);
-            --chunkLeft;
-            if (idx < n)
-            {
-                const U4 o = ldg128(ro + idx), d = ldg128(rd + idx);
-                coopBegin(S.bvh, r, v3(u2f(o.x), u2f(o.y), u2f(o.z)), v3(u2f(d.x), u2f(d.y), u2f(d.z)), tNear, u2f(d.w));
-                active = true;
-            }
-            else exhausted = true;
-        }
-        if (__all_sync(0xffffffffu, !active && exhausted)) break;
-        if (active && r.haveCur)
-        {
-            if (coopNodeStep<kAnyHit>(S.bvh, r, st, sub, gmask, gshift, overflow)) { r.haveCur = false; r.sp = 0; }   // occluded: the ray ends at the next pop
-        }
-    }
-}
-
 __global__ void __launch_bounds__(kTravThreads) k_closestHitCount(DScene S, const F4* __restrict__ ro,
                                                                    const F4* __restrict__ rd, float tNear, int64_t n,
                                                                    unsigned long long* totals)
@@ -291,14 +213,7 @@ bool launchIntersect(const DScene& S, const F4* dRo, const F4* dRd, float tNear,
                      unsigned long long* dCursor, cudaStream_t stream)
 {
     if (n <= 0) return true;
-    if (useCoopBatch(S.bvh.nodeCount) && 7 * S.bvh.depth <= kCoopStackDepth && dCursor)
-    {
-        // cursor line: [0] ray cursor, [1] stack-overflow flag
-        if (!PT_CUDA(cudaMemsetAsync(dCursor, 0, 16, stream))) return false;
-        const unsigned grid = (unsigned)std::min<int64_t>(gridFor(n, kCoopGroups * kCoopChunk), kSmCount * 16);
-        k_traceCoop<false><<<grid, kCoopThreads, 0, stream>>>(S, dRo, dRd, tNear, dOut, nullptr, n, dCursor, (int*)(dCursor + 1));
-    }
-    else if (usePersistentBatch(S.bvh.nodeCount))
+    if (usePersistentBatch(S.bvh.nodeCount))
     {
         // the ray cursor belongs to this call alone (two batches in flight on different streams must
         // not share one: the other batch's claims would run this one's cursor past its rays)
@@ -318,13 +233,7 @@ bool launchOccluded(const DScene& S, const F4* dRo, const F4* dRd, float tNear, 
                     unsigned long long* dCursor, cudaStream_t stream)
 {
     if (n <= 0) return true;
-    if (useCoopBatch(S.bvh.nodeCount) && 7 * S.bvh.depth <= kCoopStackDepth && dCursor)
-    {
-        if (!PT_CUDA(cudaMemsetAsync(dCursor, 0, 16, stream))) return false;
-        const unsigned grid = (unsigned)std::min<int64_t>(gridFor(n, kCoopGroups * kCoopChunk), kSmCount * 16);
-        k_traceCoop<true><<<grid, kCoopThreads, 0, stream>>>(S, dRo, dRd, tNear, nullptr, dOut, n, dCursor, (int*)(dCursor + 1));
-    }
-    else if (usePersistentBatch(S.bvh.nodeCount))
+    if (usePersistentBatch(S.bvh.nodeCount))
     {
         if (!dCursor) { setError("launchOccluded: no cursor for the persistent kernel"); return false; }
         if (!PT_CUDA(cudaMemsetAsync(dCursor, 0, 8, stream))) return false;

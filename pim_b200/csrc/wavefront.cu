@@ -56,14 +56,6 @@ bool usePersistentBatch(int32_t bvhNodeCount)
     return bvhNodeCount >= 2048;
 }
 
-// Eight lanes per ray (traverse_coop.h) for the batch entry points: -1 by tree size, 0 never, 1 always
-int g_coopTraversal = -1;
-bool useCoopBatch(int32_t bvhNodeCount)
-{
-    if (g_coopTraversal >= 0) return g_coopTraversal != 0;
-    return bvhNodeCount >= 2048;
-}
-
 namespace {
 
 // shading kernels are latency bound (dependent loads through hit -> vertex -> material ->

@@ -264,33 +264,3 @@ def test_sah_large_node_levels_match_warp_per_node(api, lut, monkeypatch):
     assert (a["type"] != 0).mean() > 0.05
     assert abs(nodes_a - nodes_b) <= 0.001 * nodes_b, (nodes_a, nodes_b)
     assert abs(cnt_a[0] - cnt_b[0]) <= 0.01 * cnt_b[0] and abs(cnt_a[1] - cnt_b[1]) <= 0.01 * cnt_b[1], (cnt_a, cnt_b)
-
-
-def test_eight_lanes_per_ray_matches_one_thread_per_ray(api, lut):
-    """k_traceCoop (a group of eight lanes per ray, one child box per lane) against the one-thread-per-ray kernels:
-    same arithmetic per box and per triangle, minimum over (t, primitive id) either way, so closest hits are equal
-    bit for bit (all 48 bytes of every PtRayHit) and so are the occlusion flags; also with tNear > 0 and short tFar."""
-    cases = []
-    desc = scenes.cornell_box("spheres", brdf_lut=lut, seed=1)
-    ro, rd = parity.box_rays(300_000, seed=17)
-    cases.append((desc, ro, rd))
-    desc = scenes.random_soup(300_000, seed=5, extent=20.0)
-    desc.brdf_lut = lut
-    ro, rd = scenes.random_rays(300_000, seed=6, extent=20.0)
-    cases.append((desc, ro, rd))
-    try:
-        for desc, ro, rd in cases:
-            s = api.Scene(desc)
-            rd_short = rd.copy()
-            rd_short[:, 3] = np.random.default_rng(3).uniform(0.2, 6.0, len(rd))
-            got = []
-            for mode in (0, 1):
-                api.set_option("coop", mode)
-                got.append((s.intersect(ro, rd), s.intersect(ro, rd_short, t_near=0.1), s.occluded(ro, rd_short),
-                            s.occluded(ro, rd_short, t_near=0.1)))
-            for a, b in zip(*got):
-                assert a.tobytes() == b.tobytes()
-            assert 0.02 < (got[0][0]["type"] != 0).mean() and 0.02 < got[0][2].mean() < 0.98
-            s.close()
-    finally:
-        api.set_option("coop", -1)

@@ -27,14 +27,12 @@ def main():
     ap.add_argument("--cpu-rays", type=int, default=0, help="rays for the CPU baseline and canonical fetch counts")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--extent", type=float, default=100.0)
-    ap.add_argument("--coop", type=int, default=-1, help="eight lanes per ray: -1 by tree size, 0 off, 1 on")
     ap.add_argument("--extent", type=float, default=100.0)
     args = ap.parse_args()
 
     import torch
     from pim_b200 import api, scenes
     L = api.load()
-    api.set_option("coop", args.coop)
     dev = torch.device("cuda", 0)
     t0 = time.perf_counter()
     desc = scenes.random_soup(args.tris, seed=11, extent=args.extent)
@@ -43,7 +41,7 @@ def main():
     scene = api.Scene(desc)
     build_s = time.perf_counter() - t0
     out = {"tris": args.tris, "rays": args.rays, "scene_gen_s": gen_s, "scene_build_s": build_s,
-           "scene_build_ms_device": scene.stats.buildMs, "bvh_nodes": scene.stats.bvhNodeCount, "coop": args.coop,
+           "scene_build_ms_device": scene.stats.buildMs, "bvh_nodes": scene.stats.bvhNodeCount, 
            "build_phase_ms": dict(zip(["upload_flatten", "bvh", "emissive", "grid", "lut", "pool"], [round(x, 1) for x in scene.stats.phaseMs]))}
 
     batch = min(args.batch, args.rays)
