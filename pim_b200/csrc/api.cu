@@ -17,11 +17,13 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <thread>
+#include <string>
 
 namespace pt {
 
 static thread_local char t_error[512];
-LibCounters g_counters = { 0, 0, 0, 0, 0 };
+LibCounters g_counters;
 static float g_lastKernelMs = 0.0f;
 
 void setError(const char* fmt, ...)
@@ -88,6 +90,13 @@ struct PtScene_s
     static constexpr uint32_t kCursorRing = 64;
     unsigned long long* cursorRing = nullptr;
     unsigned long long* nextCursor() const;
+    // in-process multi-GPU (PtSys_SetDevices): full replicas of this scene on the other devices, and the
+    // buffers their partial results pass through. Growable, owned by the scene, freed with it.
+    std::vector<PtScene_s*> replicas;
+    float* partial[3] = { nullptr, nullptr, nullptr };  // replica: its partial sum images; primary: where a peer's arrive
+    size_t partialFloats = 0;
+    uint32_t* liveBase = nullptr;                       // light-learning counters before the call (replica: then its delta)
+    size_t liveWords = 0;
 };
 static std::atomic<uint32_t> g_cursorNext{ 0 };
 unsigned long long* PtScene_s::nextCursor() const
@@ -1542,7 +1551,10 @@ void Pt_GetCounters(PtCounters* out)
     out->paths = g_counters.paths; out->rays = g_counters.rays; out->occlusionRays = g_counters.occlusionRays;
     out->kernelLaunches = g_counters.kernelLaunches; out->iterations = g_counters.iterations;
 }
-void Pt_ResetCounters(void) { g_counters = LibCounters{ 0, 0, 0, 0, 0 }; }
+void Pt_ResetCounters(void)
+{
+    g_counters.paths = 0; g_counters.rays = 0; g_counters.occlusionRays = 0; g_counters.kernelLaunches = 0; g_counters.iterations = 0;
+}
 
 void Pt_SetKernelTiming(int32_t enable)
 {

@@ -4,6 +4,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -15,10 +16,11 @@ void setError(const char* fmt, ...);
 bool cudaOk(cudaError_t e, const char* what);
 #define PT_CUDA(call) ::pt::cudaOk((call), #call)
 
-struct LibCounters
+struct LibCounters      // bumped from every host thread that drives a device (in-process multi-GPU)
 {
-    unsigned long long paths, rays, occlusionRays, kernelLaunches, iterations;
+    std::atomic<unsigned long long> paths{ 0 }, rays{ 0 }, occlusionRays{ 0 }, kernelLaunches{ 0 }, iterations{ 0 };
 };
+extern thread_local bool t_workerThread;     // a replica's host thread: no per-kernel timing statistics from it
 extern LibCounters g_counters;
 
 // per-kernel CUDA-event timing of the wavefront (bench.py's roofline numbers)
@@ -186,7 +188,9 @@ enum WorkKind : int { Work_Camera = 0, Work_Rays = 1, Work_Sphere = 2 };
 struct WorkDesc
 {
     int32_t kind;
-    CamParams cam;          // Work_Camera: work item = sample * (w*h) + pixel
+    CamParams cam;          // Work_Camera: work item = sample * pixelCount + (pixel - pixelBegin)
+    int32_t pixelBegin;     // Work_Camera: the pixel range this call renders (a device's band of the frame);
+    int32_t pixelCount;     //              0 = the whole frame
     const F4* ro;           // Work_Rays: explicit rays, one path per item
     const F4* rd;
     const uint32_t* rngIds; // Work_Rays: optional RNG work-item id per ray (default: the ray's index)
@@ -236,6 +240,11 @@ bool launchLightmapScatter(const LightmapView& lm, const int32_t* dIdx, int32_t 
                            const float* dNrm3, const float* dCnt, cudaStream_t stream);
 bool launchLightmapGather(const LightmapView& lm, const int32_t* dIdx, int32_t count, F4* dProbes, float* dCnt,
                           cudaStream_t stream);
+
+// in-process multi-GPU: dst += src; dst = a - dst; dst += src
+bool launchAccumulate(float* dDst, const float* dSrc, int64_t n, cudaStream_t stream);
+bool launchU32Sub(uint32_t* dDst, const uint32_t* dA, int64_t n, cudaStream_t stream);
+bool launchU32Add(uint32_t* dDst, const uint32_t* dSrc, int64_t n, cudaStream_t stream);
 
 // image helpers
 bool launchResolve(float* dImage, const float* dSum, int64_t n, float prevCount, float addCount, cudaStream_t stream);

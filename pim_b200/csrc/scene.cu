@@ -38,6 +38,9 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHit(DScene S, const F4*
     dst[0] = a; dst[1] = b; dst[2] = c;
 }
 
+#ifndef PT_BATCH_REFILL
+#define PT_BATCH_REFILL 8
+#endif
 #ifndef PT_POSTPONED_LEAVES
 #define PT_POSTPONED_LEAVES 1
 #endif
@@ -61,7 +64,7 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHitPersistent(DScene S,
     for (;;)
     {
         const unsigned idle = __ballot_sync(0xffffffffu, !busy);
-        if (!exhausted && __popc(idle) >= 8)
+        if (!exhausted && __popc(idle) >= PT_BATCH_REFILL)
         {
             const int leader = __ffs((int)idle) - 1;
             unsigned long long base = 0;
@@ -140,7 +143,7 @@ __global__ void __launch_bounds__(kTravThreads) k_anyHitPersistent(DScene S, con
     for (;;)
     {
         const unsigned idle = __ballot_sync(0xffffffffu, !busy);
-        if (!exhausted && __popc(idle) >= 8)
+        if (!exhausted && __popc(idle) >= PT_BATCH_REFILL)
         {
             const int leader = __ffs((int)idle) - 1;
             unsigned long long base = 0;
@@ -573,6 +576,45 @@ __global__ void __launch_bounds__(256) k_lerp(float* __restrict__ image, const f
     if (i >= n) return;
     float a = image[i];
     image[i] = a + (sample[i] - a) * weight;      // f3_lerpvs, path_tracer.c:2550-2552
+}
+
+// element-wise helpers of the in-process multi-GPU mode: partial images and light-learning counters of the
+// replicas are brought to the primary device with peer copies and folded in there
+__global__ void __launch_bounds__(256) k_accumulate(float* __restrict__ dst, const float* __restrict__ src, int64_t n)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] += src[i];
+}
+__global__ void __launch_bounds__(256) k_u32Sub(uint32_t* __restrict__ dst, const uint32_t* __restrict__ a, int64_t n)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = a[i] - dst[i];          // dst held the values before the call: now what the call added
+}
+__global__ void __launch_bounds__(256) k_u32Add(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, int64_t n)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] += src[i];
+}
+bool launchAccumulate(float* dDst, const float* dSrc, int64_t n, cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    k_accumulate<<<gridFor(n, 256), 256, 0, stream>>>(dDst, dSrc, n);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+bool launchU32Sub(uint32_t* dDst, const uint32_t* dA, int64_t n, cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    k_u32Sub<<<gridFor(n, 256), 256, 0, stream>>>(dDst, dA, n);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+bool launchU32Add(uint32_t* dDst, const uint32_t* dSrc, int64_t n, cudaStream_t stream)
+{
+    if (n <= 0) return true;
+    k_u32Add<<<gridFor(n, 256), 256, 0, stream>>>(dDst, dSrc, n);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
 }
 
 bool launchResolve(float* dImage, const float* dSum, int64_t n, float prevCount, float addCount, cudaStream_t stream)

@@ -31,6 +31,7 @@
 namespace pt {
 
 bool g_kernelTiming = false;
+thread_local bool t_workerThread = false;
 int g_persistentTraversal = -1;   // -1: by scene size (see usePersistent)
 int g_finishThreshold = 131072;    // live paths at which the tail is finished in one launch; PIMPT_FINISH=n overrides, 0 disables
 KernelStats g_kernelStats = {};
@@ -237,8 +238,9 @@ __global__ void __launch_bounds__(128) k_wfRegen(DScene S, PoolView P, WorkDesc 
     Rng rng;
     if (W.kind == Work_Camera)
     {
-        const unsigned long long pixels = (unsigned long long)W.cam.width * (unsigned long long)W.cam.height;
-        const uint32_t pixel = (uint32_t)(item % pixels);
+        const unsigned long long pixels = W.pixelCount > 0 ? (unsigned long long)W.pixelCount
+                                                           : (unsigned long long)W.cam.width * (unsigned long long)W.cam.height;
+        const uint32_t pixel = (uint32_t)W.pixelBegin + (uint32_t)(item % pixels);
         const uint32_t sample = (uint32_t)(item / pixels);
         rng = seed_ctx(pixel, W.passBase + sample, W.seed, W.salt);
         cameraRay(W.cam, rng, (int)pixel, ro, rd);
@@ -673,7 +675,7 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     const bool persistent = usePersistent(S.bvh.nodeCount);
     const unsigned gridP = std::min<unsigned>(grid, (unsigned)(kSmCount * kPersistentBlocksPerSm));
     unsigned long long iterations = 0, consumed = 0, extendRays = 0, connectRays = 0;
-    const bool timing = g_kernelTiming;
+    const bool timing = g_kernelTiming && !t_workerThread;
     cudaEvent_t* done = pool.evDone;
     cudaEvent_t (*ev)[6] = pool.evKernel;
     if (timing && !ev[0][0])

@@ -27,7 +27,6 @@ def main():
     ap.add_argument("--cpu-rays", type=int, default=0, help="rays for the CPU baseline and canonical fetch counts")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--extent", type=float, default=100.0)
-    ap.add_argument("--extent", type=float, default=100.0)
     args = ap.parse_args()
 
     import torch
