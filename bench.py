@@ -500,6 +500,16 @@ def run_ours(args, rank, world, local_rank):
             extra[name] = r
         ctx.barrier()
 
+    if world > 1:
+        # the in-process form: rank 0 alone drives all the GPUs; the others wait on a host-side (gloo) barrier so
+        # that no NCCL kernel spins on their devices meanwhile
+        cpu_group = ctx.dist.new_group(backend="gloo")
+        if rank == 0:
+            try:
+                extra["inproc"] = extra_inproc(ctx)
+            except Exception as e:
+                extra["inproc"] = {"error": "%s: %s" % (type(e).__name__, e)}
+        ctx.dist.barrier(group=cpu_group)
     if rank == 0:
         line["extra"] = extra
         if not args.no_cpu_baseline and world == 1:
@@ -830,6 +840,34 @@ def extra_c5(ctx):
                                "sample": "2 M of the same rays against the same mesh, CPU BVH restatement of Embree's rtcIntersect1 / rtcOccluded (binary unavailable)",
                                "bvh_build_s": cpu_build, "agreement_with_gpu": float((gpu_prim == prim).mean())}
     return out
+
+
+def extra_inproc(ctx):
+    """The same step through the library's own multi-GPU mode (PtSys_SetDevices): ONE process drives all N devices
+    with a host thread each, the way a single-process engine would. Rank 0 runs it while the other ranks wait;
+    end to end with host PtTrace buffers (Pt_TraceSpp), N x 64 samples per pixel per call."""
+    api, scenes = ctx.api, ctx.scenes
+    n, spp = ctx.world, ctx.args.spp_per_step
+    api.set_devices(n)
+    try:
+        scene = api.Scene(scenes.cornell_box("boxes", brdf_lut=None, seed=1))
+        cam, dof = api.make_camera(EYE, AT, FOVY), api.default_dof(auto_focus=False)
+        trace = api.Trace(WIDTH, HEIGHT)
+        calls = max(2, min(ctx.args.steps, 8))
+        for i in range(2):
+            trace.trace_spp(scene, cam, dof, i * spp * n, spp * n)
+        t0 = time.perf_counter()
+        for i in range(calls):
+            trace.trace_spp(scene, cam, dof, (2 + i) * spp * n, spp * n)
+        dt = time.perf_counter() - t0
+        lum = float(trace.image("color").mean())
+        trace.close(); scene.close()
+    finally:
+        api.set_devices(1)
+    return {"workload": WORKLOAD + ", one process, PtSys_SetDevices(%d)" % n, "metric": "Msamples/s", "n_gpus": n,
+            "value": WIDTH * HEIGHT * spp * n * calls / dt / 1e6, "ms_per_call": dt / calls * 1e3, "mean_luminance": lum,
+            "how": "Pt_TraceSpp with host PtTrace buffers; samples sharded over the devices inside the library, partial sums "
+                   "to device 0 by peer copy, three images to the host"}
 
 
 def main():

@@ -179,6 +179,25 @@ void PtSys_Shutdown(void);
  * PtScene_NewFromDesc are never rebuilt; that call reads the description's arrays only
  * until it returns. */
 void PtSys_SetSceneDesc(const PtSceneDesc* desc);
+
+/* Multi-GPU inside the one process pim is (src/main.c:27-111 runs everything from a single loop; the
+ * reference has no counterpart, its parallel-for is Task_Run over host threads, threading/task.c:178-190).
+ * After PtSys_SetDevices(n) every scene built carries a full replica on each of devices 0..n-1 besides the
+ * one it is built on (the current device), and these calls spread their work, one host thread per device:
+ *   Pt_TraceSpp / Pt_TraceSpp_Device   by sample index (every device renders the whole frame for its
+ *                                      samples; the partial sums come to the scene's device by peer copy
+ *                                      and are added there), or by pixel band when there are fewer
+ *                                      samples than devices
+ *   Pt_Trace                           one sample per pixel: by pixel band
+ *   LmPack_BakeDesc / LmPack_Bake      contiguous ranges of the covered texels (never samples: the
+ *                                      spherical-gaussian fit is sequential per texel)
+ * A path's random stream is a function of (pixel or texel, sample, seed), and the light-learning counters
+ * every device adds during a call are summed and handed back to all of them afterwards, so results are those
+ * of one device up to the order of float additions. Everything else (ray batches, Pt_RayGen, cubemap bakes)
+ * runs on the scene's own device. Returns the count in effect, -1 on error; call it before PtScene_New. */
+int32_t PtSys_SetDevices(int32_t count);
+int32_t PtSys_GetDevices(void);
+
 PtScene* PtScene_New(void);
 PtScene* PtScene_NewFromDesc(const PtSceneDesc* desc);
 /* rebuild if the registered description changed, then relearn the light-grid distributions

@@ -145,7 +145,7 @@ EXPORTS = [
     "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
     "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap", "LmPack_EmbedDesc",
     "LmPack_BakeDesc_Device", "PtMediaParams_Default", "PtScene_SetMedia",
-    "Pt_RepackRome", "PtSys_SetLmPack", "LmPack_Bake", "Pt_PointQueryN", "Pt_SetOption",
+    "Pt_RepackRome", "PtSys_SetLmPack", "LmPack_Bake", "Pt_PointQueryN", "Pt_SetOption", "PtSys_SetDevices", "PtSys_GetDevices",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -227,6 +227,9 @@ def load():
     L.LmPack_BakeDesc_Device.restype = C.c_int32
     L.Pt_PointQueryN.argtypes = [vp, vp, vp, C.c_int64]
     L.Pt_PointQueryN.restype = C.c_int32
+    L.PtSys_SetDevices.argtypes = [C.c_int32]
+    L.PtSys_SetDevices.restype = C.c_int32
+    L.PtSys_GetDevices.restype = C.c_int32
     L.Pt_SetOption.argtypes = [C.c_char_p, C.c_int32]
     L.Pt_SetOption.restype = C.c_int32
     L.PtSys_SetLmPack.argtypes = [C.POINTER(PtLightmapDesc), C.c_int32, C.c_float]
@@ -273,6 +276,16 @@ def default_dof(auto_focus=True):
     load().DofInfo_New(C.byref(d))
     d.autoFocus = auto_focus
     return d
+
+
+def set_devices(count):
+    """PtSys_SetDevices: scenes built afterwards are replicated on devices 0..count-1 and the frame / bake calls shard"""
+    L = load()
+    L.PtSys_Init()
+    n = L.PtSys_SetDevices(int(count))
+    if n < 0:
+        raise PtError("PtSys_SetDevices failed: " + last_error())
+    return n
 
 
 def set_option(name, value):

@@ -181,6 +181,46 @@ static SceneDescCopy g_sceneDesc;
 static std::vector<PtLightmapDesc> g_lmPack;
 static float g_lmTexelsPerMeter = 0.0f;
 
+// In-process multi-GPU (PtSys_SetDevices): pim is one process, so the library itself can spread a call over
+// the first g_deviceCount devices: every scene built afterwards carries a full replica per extra device, one
+// host thread per device drives it, partial results come to the scene's own device by peer copy.
+static int g_deviceCount = 1;
+
+struct DeviceGuard
+{
+    int prev = 0;
+    explicit DeviceGuard(int d) { cudaGetDevice(&prev); if (d != prev) cudaSetDevice(d); }
+    ~DeviceGuard() { int cur = 0; cudaGetDevice(&cur); if (cur != prev) cudaSetDevice(prev); }
+};
+
+// runs fn(k) for k in [0, count): k = 0 on the calling thread, the others on a thread each; false (and the
+// first failing thread's message in Pt_LastError) when any of them failed
+template <class Fn>
+static bool forEachDevice(int count, Fn fn)
+{
+    if (count <= 1) return fn(0);
+    std::vector<std::thread> threads;
+    std::vector<int> okFlags((size_t)count, 1);
+    std::vector<std::string> errors((size_t)count);
+    for (int k = 1; k < count; ++k)
+    {
+        threads.emplace_back([&, k]()
+        {
+            t_workerThread = true;
+            t_error[0] = 0;
+            okFlags[(size_t)k] = fn(k) ? 1 : 0;
+            if (!okFlags[(size_t)k]) errors[(size_t)k] = t_error;
+        });
+    }
+    okFlags[0] = fn(0) ? 1 : 0;
+    for (std::thread& t : threads) t.join();
+    for (int k = 1; k < count; ++k)
+    {
+        if (!okFlags[(size_t)k]) { if (okFlags[0]) setError("device thread %d: %s", k, errors[(size_t)k].c_str()); okFlags[0] = 0; }
+    }
+    return okFlags[0] != 0;
+}
+
 template <class T>
 static bool sceneAlloc(PtScene* s, T*& p, size_t count)
 {
@@ -274,6 +314,11 @@ static CamParams makeCam(const Camera* camera, const PtDofInfo* dof, int w, int 
 static void sceneFree(PtScene* s)
 {
     if (!s) return;
+    for (PtScene_s* r : s->replicas) sceneFree(r);
+    s->replicas.clear();
+    DeviceGuard guard(s->device);
+    for (int k = 0; k < 3; ++k) if (s->partial[k]) cudaFree(s->partial[k]);
+    if (s->liveBase) cudaFree(s->liveBase);
     for (void* p : s->allocs) cudaFree(p);
     freeBvh(s->bvh);
     poolFree(s->pool);
@@ -286,7 +331,7 @@ static void sceneFree(PtScene* s)
     delete s;
 }
 
-static PtScene* sceneBuild(const PtSceneDesc* desc)
+static PtScene* sceneBuildOne(const PtSceneDesc* desc)
 {
     if (!ensureInit()) return nullptr;
     if (!desc) { setError("PtScene_NewFromDesc: null description"); return nullptr; }
@@ -492,6 +537,32 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
     return s;
 }
 
+// the scene on the current device plus, in multi-GPU mode, a replica on each of the other devices (the
+// build is deterministic, so the replicas hold the same tree and the same light grid)
+static PtScene* sceneBuild(const PtSceneDesc* desc)
+{
+    if (!ensureInit()) return nullptr;
+    int primary = 0;
+    if (!PT_CUDA(cudaGetDevice(&primary))) return nullptr;
+    std::vector<int> devices(1, primary);
+    for (int d = 0; d < g_deviceCount; ++d) if (d != primary) devices.push_back(d);
+    if (g_deviceCount <= 1) devices.resize(1);
+    std::vector<PtScene*> built(devices.size(), nullptr);
+    const bool ok = forEachDevice((int)devices.size(), [&](int k) -> bool
+    {
+        DeviceGuard guard(devices[(size_t)k]);
+        built[(size_t)k] = sceneBuildOne(desc);
+        return built[(size_t)k] != nullptr;
+    });
+    if (!ok)
+    {
+        for (PtScene* b : built) sceneFree(b);
+        return nullptr;
+    }
+    for (size_t k = 1; k < built.size(); ++k) built[0]->replicas.push_back(built[k]);
+    return built[0];
+}
+
 // ---- helpers for host <-> device batches ---------------------------------------
 
 // CUDA events around a call's kernels on their stream; stop() leaves the time in Pt_LastKernelMs().
@@ -535,24 +606,144 @@ static bool sceneRefresh(PtScene* scene, cudaStream_t st)
     return launchDistUpdate(scene->view, st);
 }
 
-static bool traceSppDevice(PtScene* scene, const Camera* camera, PtDofInfo* dof, int w, int h, int sppBegin, int sppCount,
-                           float* dColor, float* dAlbedo, float* dNormal, cudaStream_t st)
+template <class T>
+static bool growBuffer(T*& p, size_t& have, size_t need)
 {
-    const bool own = st == scene->stream;
-    if (!sceneRefresh(scene, st)) return false;       // PtScene_Update -> UpdateDists
-    if (own) st = scene->stream;
+    if (need <= have) return true;
+    if (p) cudaFree(p);
+    p = nullptr; have = 0;
+    if (!PT_CUDA(cudaMalloc((void**)&p, sizeof(T) * need))) return false;
+    have = need;
+    return true;
+}
+
+// one device's share of a Pt_Trace / Pt_TraceSpp call: samples [sppBegin, +sppCount) of pixels [pixelBegin, +pixelCount)
+struct TraceShare { int sppBegin, sppCount, pixelBegin, pixelCount; };
+
+static bool traceShare(PtScene* s, const Camera* camera, const PtDofInfo* dof, int w, int h, const TraceShare& sh,
+                       float* dColor, float* dAlbedo, float* dNormal, cudaStream_t st)
+{
+    if (sh.sppCount <= 0 || sh.pixelCount <= 0) return true;
     WorkDesc W; memset(&W, 0, sizeof(W));
     W.kind = Work_Camera;
     W.cam = makeCam(camera, dof, w, h);
-    W.count = (int64_t)w * h * sppCount;
-    W.passBase = (uint32_t)sppBegin;
-    W.seed = scene->config.seed;
+    W.pixelBegin = sh.pixelBegin; W.pixelCount = sh.pixelCount;
+    W.count = (int64_t)sh.pixelCount * sh.sppCount;
+    W.passBase = (uint32_t)sh.sppBegin;
+    W.seed = s->config.seed;
     W.salt = Salt_Trace;
     W.sumColor = dColor; W.sumAlbedo = dAlbedo; W.sumNormal = dNormal;
     W.accumulate = 1;
     float ms = 0.0f;
-    bool ok = runWavefront(scene->view, scene->pool, W, st, &ms);
-    g_lastKernelMs = ms;
+    const bool ok = runWavefront(s->view, s->pool, W, st, &ms);
+    if (!t_workerThread) g_lastKernelMs = ms;
+    return ok;
+}
+
+// The light-learning counters (Dist1D.live) of the replicas are kept equal to what one device tracing everything
+// would hold: every device notes its counters before the call, the replicas turn that into "what this call added",
+// the primary adds those and hands the totals back (all-reduce of the u32 counters per frame).
+static bool liveSnapshot(PtScene* s, cudaStream_t st)
+{
+    const size_t words = (size_t)s->gridCells * (size_t)s->view.emissiveCount;
+    if (words == 0) return true;
+    if (!growBuffer(s->liveBase, s->liveWords, words)) return false;
+    return PT_CUDA(cudaMemcpyAsync(s->liveBase, s->view.distLive, 4 * words, cudaMemcpyDeviceToDevice, st));
+}
+
+static bool liveMerge(PtScene* scene, cudaStream_t st)
+{
+    const size_t words = (size_t)scene->gridCells * (size_t)scene->view.emissiveCount;
+    if (words == 0 || scene->replicas.empty()) return true;
+    bool ok = true;
+    for (PtScene_s* r : scene->replicas)
+    {
+        // the replica's delta (left in its liveBase by its thread) arrives in the primary's liveBase, which the
+        // primary no longer needs once its own kernels are done
+        ok = ok && PT_CUDA(cudaMemcpyPeerAsync(scene->liveBase, scene->device, r->liveBase, r->device, 4 * words, st));
+        ok = ok && launchU32Add(scene->view.distLive, scene->liveBase, (int64_t)words, st);
+    }
+    for (PtScene_s* r : scene->replicas)
+        ok = ok && PT_CUDA(cudaMemcpyPeerAsync(r->view.distLive, r->device, scene->view.distLive, scene->device, 4 * words, st));
+    return ok;
+}
+
+static bool traceSppDevice(PtScene* scene, const Camera* camera, PtDofInfo* dof, int w, int h, int sppBegin, int sppCount,
+                           float* dColor, float* dAlbedo, float* dNormal, cudaStream_t st, bool refresh = true)
+{
+    const bool own = st == scene->stream;
+    if (refresh && !sceneRefresh(scene, st)) return false;       // PtScene_Update -> UpdateDists
+    if (own) st = scene->stream;
+    const int D = 1 + (int)scene->replicas.size();
+    const int pixels = w * h;
+    if (D == 1)
+    {
+        const TraceShare all = { sppBegin, sppCount, 0, pixels };
+        return traceShare(scene, camera, dof, w, h, all, dColor, dAlbedo, dNormal, st);
+    }
+    // Shares: by sample index when every device gets at least one sample of the frame (each renders the whole
+    // frame; the partial images are summed), else by pixel band (disjoint rows; a one-sample Pt_Trace frame)
+    std::vector<TraceShare> share((size_t)D);
+    const bool bySample = sppCount >= D;
+    for (int k = 0; k < D; ++k)
+    {
+        if (bySample)
+        {
+            const int base = sppCount / D, rem = sppCount % D;
+            share[(size_t)k] = { sppBegin + k * base + std::min(k, rem), base + (k < rem ? 1 : 0), 0, pixels };
+        }
+        else
+        {
+            const int rows = h / D, rem = h % D;
+            const int y0 = k * rows + std::min(k, rem), ny = rows + (k < rem ? 1 : 0);
+            share[(size_t)k] = { sppBegin, sppCount, y0 * w, ny * w };
+        }
+    }
+    const size_t n3 = (size_t)pixels * 3;
+    const int images = 1 + (dAlbedo ? 1 : 0) + (dNormal ? 1 : 0);
+    bool ok = forEachDevice(D, [&](int k) -> bool
+    {
+        if (k == 0) return liveSnapshot(scene, st) && traceShare(scene, camera, dof, w, h, share[0], dColor, dAlbedo, dNormal, st);
+        PtScene_s* r = scene->replicas[(size_t)k - 1];
+        DeviceGuard guard(r->device);
+        cudaStream_t rs = r->stream;
+        if (r->partialFloats < n3)
+        {
+            for (int i = 0; i < 3; ++i)
+            {
+                size_t have = 0;
+                if (r->partial[i]) { cudaFree(r->partial[i]); r->partial[i] = nullptr; }
+                if (!growBuffer(r->partial[i], have, n3)) { r->partialFloats = 0; return false; }
+            }
+            r->partialFloats = n3;
+        }
+        const TraceShare& sh = share[(size_t)k];
+        const size_t off = (size_t)sh.pixelBegin * 3, cnt = (size_t)sh.pixelCount * 3;
+        bool okr = launchDistUpdate(r->view, rs) && liveSnapshot(r, rs);
+        for (int i = 0; okr && i < images; ++i) okr = PT_CUDA(cudaMemsetAsync(r->partial[i] + off, 0, 4 * cnt, rs));
+        okr = okr && traceShare(r, camera, dof, w, h, sh, r->partial[0], dAlbedo ? r->partial[1] : nullptr, dNormal ? r->partial[2] : nullptr, rs);
+        const size_t words = (size_t)r->gridCells * (size_t)r->view.emissiveCount;
+        if (okr && words) okr = launchU32Sub(r->liveBase, r->view.distLive, (int64_t)words, rs);
+        return PT_CUDA(cudaStreamSynchronize(rs)) && okr;
+    });
+    // the partial images come to the primary by peer copy and are added (bands: only their rows)
+    float* dst[3] = { dColor, dAlbedo, dNormal };
+    for (int k = 1; ok && k < D; ++k)
+    {
+        PtScene_s* r = scene->replicas[(size_t)k - 1];
+        const TraceShare& sh = share[(size_t)k];
+        const size_t off = (size_t)sh.pixelBegin * 3, cnt = (size_t)sh.pixelCount * 3;
+        if (cnt == 0 || sh.sppCount <= 0) continue;
+        ok = growBuffer(scene->partial[0], scene->partialFloats, n3);
+        for (int i = 0; ok && i < 3; ++i)
+        {
+            if (!dst[i]) continue;
+            ok = PT_CUDA(cudaMemcpyPeerAsync(scene->partial[0], scene->device, r->partial[i] + off, r->device, 4 * cnt, st)) &&
+                 launchAccumulate(dst[i] + off, scene->partial[0], (int64_t)cnt, st);
+        }
+    }
+    ok = ok && liveMerge(scene, st);
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;      // the replicas' counters are current before the next call starts
     return ok;
 }
 
@@ -665,6 +856,32 @@ void PtSys_Shutdown(void)
 }
 
 void PtSys_SetSceneDesc(const PtSceneDesc* desc) { g_sceneDesc.assign(desc); }
+
+int32_t PtSys_SetDevices(int32_t count)
+{
+    if (!ensureInit()) return -1;
+    int have = 0;
+    if (!PT_CUDA(cudaGetDeviceCount(&have))) return -1;
+    if (count < 1) count = 1;
+    if (count > have || count > kMaxDevices) { setError("PtSys_SetDevices: %d devices asked for, %d present", count, have); return -1; }
+    // peer access both ways between the devices in use, where the hardware has it (NVLink / NVSwitch here);
+    // without it the peer copies still work, staged through the host by the driver
+    for (int a = 0; a < count; ++a)
+    {
+        DeviceGuard guard(a);
+        for (int b = 0; b < count; ++b)
+        {
+            int can = 0;
+            if (a == b || cudaDeviceCanAccessPeer(&can, a, b) != cudaSuccess || !can) continue;
+            const cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); }
+            else if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        }
+    }
+    g_deviceCount = count;
+    return count;
+}
+int32_t PtSys_GetDevices(void) { return g_deviceCount; }
 
 PtScene* PtScene_New(void)
 {
@@ -927,21 +1144,8 @@ void Pt_Trace(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera* came
     cudaStream_t st = scene->stream;
     bool ok = true;
     for (int k = 0; k < 3; ++k) ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[k], 0, sizeof(float) * n3, st));
-    {
-        // the CDFs were relearned just above: trace without a second PtScene_Update
-        WorkDesc W; memset(&W, 0, sizeof(W));
-        W.kind = Work_Camera;
-        W.cam = makeCam(camera, dof, w, h);
-        W.count = (int64_t)w * h;
-        W.passBase = scene->nextPass;
-        W.seed = scene->config.seed;
-        W.salt = Salt_Trace;
-        W.sumColor = im->sum[0]; W.sumAlbedo = im->sum[1]; W.sumNormal = im->sum[2];
-        W.accumulate = 1;
-        float ms = 0.0f;
-        ok = ok && runWavefront(scene->view, scene->pool, W, st, &ms);
-        g_lastKernelMs = ms;
-    }
+    // the CDFs were relearned just above: trace without a second PtScene_Update
+    ok = ok && traceSppDevice(scene, camera, dof, w, h, (int)scene->nextPass, 1, im->sum[0], im->sum[1], im->sum[2], st, false);
     scene->nextPass++;
     float* host[3] = { (float*)trace->color, (float*)trace->albedo, (float*)trace->normal };
     for (int k = 0; ok && k < 3; ++k)
@@ -1004,6 +1208,51 @@ static bool bakePageDevice(PtScene* scene, const LightmapView& view, float texel
                                        scene->config.seed, st);
 }
 
+// device side of one device's share of a host page (LmPack_BakeDesc): the full-size page and the compacted texels
+struct LmDeviceBuffers
+{
+    F4* probes = nullptr; float *pos = nullptr, *nrm = nullptr, *cnt = nullptr;                 // the full-size device page
+    int32_t* idx = nullptr; F4* cProbes = nullptr; float *cPos = nullptr, *cNrm = nullptr, *cCnt = nullptr;    // compacted
+};
+static void lmLeaseDevice(Lease& lease, LmDeviceBuffers& b, size_t texels)
+{
+    lease.dev(b.probes, 5 * texels).dev(b.pos, 3 * texels).dev(b.nrm, 3 * texels).dev(b.cnt, texels)
+         .dev(b.idx, texels).dev(b.cProbes, 5 * texels).dev(b.cPos, 3 * texels).dev(b.cNrm, 3 * texels).dev(b.cCnt, texels);
+}
+// covered texels [j0, j0 + count) of the page's m covered ones: up, scatter, bake, gather, down (into the same host
+// staging arrays, which are lobe-major over all m)
+static bool lmBakeShare(PtScene_s* s, const LmDeviceBuffers& b, size_t n, int32_t texelBase, int32_t j0, int32_t count, int32_t m,
+                        const int32_t* hIdx, F4* hCProbes, const float* hCPos, const float* hCNrm, float* hCCnt,
+                        float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass)
+{
+    if (count <= 0) return true;
+    cudaStream_t st = s->stream;
+    LightmapView view;
+    for (int k = 0; k < 5; ++k) view.probes[k] = b.probes + (size_t)k * n;
+    view.position = b.pos; view.normal = b.nrm; view.sampleCounts = b.cnt;
+    view.texelCount = (int32_t)n; view.texelBase = texelBase;
+    const size_t c = (size_t)count;
+    bool ok = PT_CUDA(cudaMemsetAsync(b.cnt, 0, sizeof(float) * n, st)) &&
+              PT_CUDA(cudaMemcpyAsync(b.idx, hIdx + j0, sizeof(int32_t) * c, cudaMemcpyHostToDevice, st));
+    for (int k = 0; ok && k < 5; ++k)
+        ok = PT_CUDA(cudaMemcpyAsync(b.cProbes + (size_t)k * c, hCProbes + (size_t)k * m + j0, sizeof(F4) * c, cudaMemcpyHostToDevice, st));
+    ok = ok && PT_CUDA(cudaMemcpyAsync(b.cPos, hCPos + 3 * (size_t)j0, 12 * c, cudaMemcpyHostToDevice, st)) &&
+         PT_CUDA(cudaMemcpyAsync(b.cNrm, hCNrm + 3 * (size_t)j0, 12 * c, cudaMemcpyHostToDevice, st)) &&
+         PT_CUDA(cudaMemcpyAsync(b.cCnt, hCCnt + j0, 4 * c, cudaMemcpyHostToDevice, st)) &&
+         launchLightmapScatter(view, b.idx, count, b.cProbes, b.cPos, b.cNrm, b.cCnt, st);
+    if (ok)
+    {
+        ok = s->config.bakeMode == PtBake_Sequential
+                 ? launchLightmapBake(s->view, view, 1.0f / texelsPerMeter, timeSlice, spp, pass, s->config.seed, st)
+                 : launchLightmapBakeWavefront(s->view, s->pool, view, 1.0f / texelsPerMeter, timeSlice, spp, pass, s->config.seed, st);
+    }
+    ok = ok && launchLightmapGather(view, b.idx, count, b.cProbes, b.cCnt, st);
+    for (int k = 0; ok && k < 5; ++k)
+        ok = PT_CUDA(cudaMemcpyAsync(hCProbes + (size_t)k * m + j0, b.cProbes + (size_t)k * c, sizeof(F4) * c, cudaMemcpyDeviceToHost, st));
+    ok = ok && PT_CUDA(cudaMemcpyAsync(hCCnt + j0, b.cCnt, 4 * c, cudaMemcpyDeviceToHost, st));
+    return PT_CUDA(cudaStreamSynchronize(st)) && ok;
+}
+
 // Host pages move sparsely. BakeFn skips every texel whose sampleCounts entry is 0 (lightmap.c:1145-1149)
 // — the texels no chart covers, usually most of an atlas page (cornell at 16 texels/m: 54 437 of 1 048 576)
 // — so only the covered texels' 108 bytes travel: the host compacts them into page-locked staging, one
@@ -1025,17 +1274,26 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
         maxTexels = std::max(maxTexels, (size_t)lm.size * (size_t)lm.size);
     }
     // worst case: every texel of the largest page is covered
-    F4* dProbes = nullptr; float *dPos = nullptr, *dNrm = nullptr, *dCnt = nullptr;          // the full-size device page
-    int32_t *dIdx = nullptr, *hIdx = nullptr;
-    F4 *dCProbes = nullptr, *hCProbes = nullptr;                                             // compacted staging, both sides
-    float *dCPos = nullptr, *hCPos = nullptr, *dCNrm = nullptr, *hCNrm = nullptr, *dCCnt = nullptr, *hCCnt = nullptr;
+    int32_t* hIdx = nullptr; F4* hCProbes = nullptr; float *hCPos = nullptr, *hCNrm = nullptr, *hCCnt = nullptr;
+    LmDeviceBuffers primary;
     Lease lease;
-    lease.dev(dProbes, 5 * maxTexels).dev(dPos, 3 * maxTexels).dev(dNrm, 3 * maxTexels).dev(dCnt, maxTexels)
-         .dev(dIdx, maxTexels).dev(dCProbes, 5 * maxTexels).dev(dCPos, 3 * maxTexels).dev(dCNrm, 3 * maxTexels).dev(dCCnt, maxTexels)
-         .host(hIdx, maxTexels).host(hCProbes, 5 * maxTexels).host(hCPos, 3 * maxTexels).host(hCNrm, 3 * maxTexels).host(hCCnt, maxTexels);
+    lmLeaseDevice(lease, primary, maxTexels);
+    lease.host(hIdx, maxTexels).host(hCProbes, 5 * maxTexels).host(hCPos, 3 * maxTexels).host(hCNrm, 3 * maxTexels).host(hCCnt, maxTexels);
     if (!lease.commit()) return -1;
     bool ok = sceneRefresh(scene, scene->stream);       // LmPack_Bake -> PtScene_Update (lightmap.c:1209)
-    cudaStream_t st = scene->stream;
+    const int D = 1 + (int)scene->replicas.size();
+    // the replicas relearn first (the primary did in sceneRefresh), then every device notes its light-learning
+    // counters so that what the bake adds on each can be merged afterwards (liveMerge)
+    if (D > 1)
+    {
+        ok = ok && forEachDevice(D, [&](int k) -> bool
+        {
+            PtScene_s* s = k == 0 ? scene : scene->replicas[(size_t)k - 1];
+            DeviceGuard guard(s->device);
+            bool okd = (k == 0 || launchDistUpdate(s->view, s->stream)) && liveSnapshot(s, s->stream);
+            return PT_CUDA(cudaStreamSynchronize(s->stream)) && okd;
+        });
+    }
     int32_t texelBase = 0;
     for (int32_t i = 0; ok && i < lmCount; ++i)
     {
@@ -1053,24 +1311,25 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
             hCNrm[3 * j] = nrm[3 * t]; hCNrm[3 * j + 1] = nrm[3 * t + 1]; hCNrm[3 * j + 2] = nrm[3 * t + 2];
             hCCnt[j] = lm.sampleCounts[t];
         }
-        LightmapView view;
-        for (int k = 0; k < 5; ++k) view.probes[k] = dProbes + (size_t)k * n;
-        view.position = dPos; view.normal = dNrm; view.sampleCounts = dCnt;
-        view.texelCount = (int32_t)n; view.texelBase = texelBase;
-        ok = PT_CUDA(cudaMemsetAsync(dCnt, 0, sizeof(float) * n, st));
-        if (ok && m > 0)
+        if (m > 0)
         {
-            ok = PT_CUDA(cudaMemcpyAsync(dIdx, hIdx, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, st)) &&
-                 PT_CUDA(cudaMemcpyAsync(dCProbes, hCProbes, sizeof(F4) * 5 * (size_t)m, cudaMemcpyHostToDevice, st)) &&
-                 PT_CUDA(cudaMemcpyAsync(dCPos, hCPos, 12 * (size_t)m, cudaMemcpyHostToDevice, st)) &&
-                 PT_CUDA(cudaMemcpyAsync(dCNrm, hCNrm, 12 * (size_t)m, cudaMemcpyHostToDevice, st)) &&
-                 PT_CUDA(cudaMemcpyAsync(dCCnt, hCCnt, 4 * (size_t)m, cudaMemcpyHostToDevice, st)) &&
-                 launchLightmapScatter(view, dIdx, m, dCProbes, dCPos, dCNrm, dCCnt, st);
-            ok = ok && bakePageDevice(scene, view, texelsPerMeter, timeSlice, spp, pass, st);
-            ok = ok && launchLightmapGather(view, dIdx, m, dCProbes, dCCnt, st);
-            ok = ok && PT_CUDA(cudaMemcpyAsync(hCProbes, dCProbes, sizeof(F4) * 5 * (size_t)m, cudaMemcpyDeviceToHost, st));
-            ok = ok && PT_CUDA(cudaMemcpyAsync(hCCnt, dCCnt, 4 * (size_t)m, cudaMemcpyDeviceToHost, st));
-            ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
+            // one contiguous range of the covered texels per device (the fit is sequential per texel, so texels,
+            // never samples, are what devices share out); a texel's random streams follow its index in the pack,
+            // so the result does not depend on how many devices baked it
+            ok = forEachDevice(D, [&](int k) -> bool
+            {
+                const int32_t base = m / D, rem = m % D;
+                const int32_t j0 = k * base + std::min(k, rem), cnt = base + (k < rem ? 1 : 0);
+                PtScene_s* s = k == 0 ? scene : scene->replicas[(size_t)k - 1];
+                if (k == 0) return lmBakeShare(s, primary, n, texelBase, j0, cnt, m, hIdx, hCProbes, hCPos, hCNrm, hCCnt,
+                                               texelsPerMeter, timeSlice, spp, pass);
+                DeviceGuard guard(s->device);
+                LmDeviceBuffers mine;
+                Lease own;                  // this device's arena
+                lmLeaseDevice(own, mine, std::max<size_t>(n, 1));
+                if (!own.commit()) return false;
+                return lmBakeShare(s, mine, n, texelBase, j0, cnt, m, hIdx, hCProbes, hCPos, hCNrm, hCCnt, texelsPerMeter, timeSlice, spp, pass);
+            });
             if (ok)
             {
                 for (int32_t j = 0; j < m; ++j)
@@ -1083,7 +1342,20 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
         }
         texelBase += (int32_t)n;
     }
-    if (!ok) cudaStreamSynchronize(st);
+    if (ok && D > 1)
+    {
+        ok = forEachDevice(D, [&](int k) -> bool
+        {
+            if (k == 0) return true;
+            PtScene_s* s = scene->replicas[(size_t)k - 1];
+            DeviceGuard guard(s->device);
+            const size_t words = (size_t)s->gridCells * (size_t)s->view.emissiveCount;
+            bool okd = words == 0 || launchU32Sub(s->liveBase, s->view.distLive, (int64_t)words, s->stream);
+            return PT_CUDA(cudaStreamSynchronize(s->stream)) && okd;
+        });
+        ok = ok && liveMerge(scene, scene->stream);
+    }
+    ok = PT_CUDA(cudaStreamSynchronize(scene->stream)) && ok;
     return ok ? 0 : -1;
 }
 
@@ -1317,6 +1589,7 @@ int32_t PtScene_SetMedia(PtScene* scene, const PtMediaParams* m)      // media_d
     d.rcpMajorant = 1.0f / f1_max(maj.x, f1_max(maj.y, maj.z));
     cudaStreamSynchronize(scene->stream);
     scene->view.media = d;
+    for (PtScene_s* r : scene->replicas) r->view.media = d;
     return 0;
 }
 
@@ -1507,6 +1780,11 @@ int32_t PtScene_GetDist(const PtScene* scene, int32_t cell, float* pdf, float* c
 int32_t PtScene_SetDist(PtScene* scene, int32_t cell, int32_t length, const float* pdf)
 {
     if (!scene || cell < 0 || cell >= scene->gridCells) return -1;
+    for (PtScene_s* r : scene->replicas)
+    {
+        DeviceGuard guard(r->device);
+        if (PtScene_SetDist(r, cell, length, pdf) != 0) return -1;
+    }
     const DScene& V = scene->view;
     const int32_t E = V.emissiveCount;
     if (length != 0 && length != E) { setError("PtScene_SetDist: length must be 0 or the emissive count"); return -1; }

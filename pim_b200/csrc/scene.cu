@@ -38,8 +38,10 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHit(DScene S, const F4*
     dst[0] = a; dst[1] = b; dst[2] = c;
 }
 
+// idle lanes at which a persistent warp fetches new rays (10 M-triangle soup, closest / any hit Mrays/s: 8 lanes
+// 334 / 638, 4 lanes 345 / 661)
 #ifndef PT_BATCH_REFILL
-#define PT_BATCH_REFILL 8
+#define PT_BATCH_REFILL 4
 #endif
 #ifndef PT_POSTPONED_LEAVES
 #define PT_POSTPONED_LEAVES 1

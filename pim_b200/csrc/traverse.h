@@ -54,23 +54,13 @@ struct TravCounters { uint32_t nodes, tris; };
 
 
 // byte `idx` (0..3) of `word` as a float: I2F.U8, 48 per wide node on the XU pipe (70 % busy in the
-// traversal kernels). Both ways around it measured slower on B200: splicing the byte into a float
-// mantissa with PRMT + FADD -4 %, and one dp4a per plane (2^23 + 128 q, folded into the fma) -4 %
-// on cornell and -18 % on the 10 M-triangle soup.
+// traversal kernels). Every way around it measured slower on B200: splicing the byte into a float
+// mantissa with PRMT + FADD -4 %; one dp4a per plane (2^23 + 128 q, folded into the fma) -4 %
+// on cornell and -18 % on the 10 M-triangle soup; PRMT into the mantissa of 32768.0f with the 32768 folded
+// into the fma's constant (no extra instruction, planes widened by 0.004 steps) 334 -> 320 Mrays/s on the
+// soup: the ALU pipe that takes the PRMTs is as busy as the XU pipe they leave.
 PT_D float byteToFloat(uint32_t word, int idx) { return (float)((word >> (8 * idx)) & 0xffu); }
 
-#ifndef PT_PRMT_PLANES
-#define PT_PRMT_PLANES 0
-#endif
-// 32768 + byte `idx` of `word`, exactly: the byte placed in bits 8..15 of 0x47000000 (= 32768.0f, whose ulp is 2^-8)
-PT_D float byteToFloat32768(uint32_t word, int idx)
-{
-#if defined(__CUDA_ARCH__)
-    return __uint_as_float(__byte_perm(word, 0x47000000u, 0x7404u | ((uint32_t)idx << 4)));
-#else
-    return 32768.0f + (float)((word >> (8 * idx)) & 0xffu);
-#endif
-}
 
 PT_D uint32_t max8(const uint32_t k[8])
 {
@@ -438,15 +428,6 @@ PT_D bool travNodeStepP(const Bvh& bvh, TravRay& r, Stack& st)
     const float bx = (u2f(n0.x) - r.ro.x) * r.idir.x;
     const float by = (u2f(n0.y) - r.ro.y) * r.idir.y;
     const float bz = (u2f(n0.z) - r.ro.z) * r.idir.z;
-#if PT_PRMT_PLANES
-    // plane byte -> float without the XU pipe: PRMT drops the byte into the mantissa of 32768.0f, which reads
-    // as 32768 + q exactly, and the 32768 is folded into the constant of the fma. The fold costs up to
-    // ~0.002 of a grid step of accuracy (rounding of 32768 * s), so the near planes move out by 0.004 steps
-    // and the far planes likewise: conservative, the hits are unchanged.
-    const float cnx = fmaf(-32768.0f, sx, bx) - 0.004f * fabsf(sx), cfx = fmaf(-32768.0f, sx, bx) + 0.004f * fabsf(sx);
-    const float cny = fmaf(-32768.0f, sy, by) - 0.004f * fabsf(sy), cfy = fmaf(-32768.0f, sy, by) + 0.004f * fabsf(sy);
-    const float cnz = fmaf(-32768.0f, sz, bz) - 0.004f * fabsf(sz), cfz = fmaf(-32768.0f, sz, bz) + 0.004f * fabsf(sz);
-#endif
     uint32_t nxw[2], fxw[2], nyw[2], fyw[2], nzw[2], fzw[2];
     nxw[0] = r.negx ? n3.z : n2.x; nxw[1] = r.negx ? n3.w : n2.y;
     fxw[0] = r.negx ? n2.x : n3.z; fxw[1] = r.negx ? n2.y : n3.w;
@@ -465,21 +446,12 @@ PT_D bool travNodeStepP(const Bvh& bvh, TravRay& r, Stack& st)
     for (int i = 0; i < 8; ++i)
     {
         const int w = i >> 2;
-#if PT_PRMT_PLANES
-        float tnx = byteToFloat32768(nxw[w], i & 3) * sx + cnx;
-        float tfx = byteToFloat32768(fxw[w], i & 3) * sx + cfx;
-        float tny = byteToFloat32768(nyw[w], i & 3) * sy + cny;
-        float tfy = byteToFloat32768(fyw[w], i & 3) * sy + cfy;
-        float tnz = byteToFloat32768(nzw[w], i & 3) * sz + cnz;
-        float tfz = byteToFloat32768(fzw[w], i & 3) * sz + cfz;
-#else
         float tnx = byteToFloat(nxw[w], i & 3) * sx + bx;
         float tfx = byteToFloat(fxw[w], i & 3) * sx + bx;
         float tny = byteToFloat(nyw[w], i & 3) * sy + by;
         float tfy = byteToFloat(fyw[w], i & 3) * sy + by;
         float tnz = byteToFloat(nzw[w], i & 3) * sz + bz;
         float tfz = byteToFloat(fzw[w], i & 3) * sz + bz;
-#endif
         float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tNear));
         float tmax = fminf(fminf(tfx, tfy), fminf(tfz, r.tBest));
         bool h = tmin <= tmax * 1.0000004f;
