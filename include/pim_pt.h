@@ -358,6 +358,27 @@ typedef struct PtEmbedMesh_s
 int32_t LmPack_EmbedDesc(const PtEmbedMesh* meshes, int32_t meshCount, PtLightmapDesc* lightmaps,
                          const int32_t* slotIndices, int32_t lmCount);
 
+/* The two data-parallel steps of LmPack_Pack before the embedding. Chart grouping (plane clustering, k-means split:
+ * chart_group, lightmap.c:563-642), chart_sort (:644-658) and chartnodes_assign (:867-935) stay host code around them.
+ * Charts are runs of nodes: chartFirstNode[c] .. chartFirstNode[c + 1] - 1; triCoords holds the three 2-D corners
+ * (chartnode_t.triCoord, texels) of every node, chart after chart.
+ *
+ * LmPack_ChartMasksDesc = ChartMaskFn (static, lightmap.c:527-561): moves every chart so that its lower corner is at
+ * (2, 2) (triCoords is rewritten), returns its bounds area and the size of its mask, and, where masksOut[c] is not
+ * NULL, the mask itself (maskSize.x * maskSize.y bytes, 0xff where a triangle of the chart lies within one texel of the
+ * texel centre: mask_tri :232-248).
+ *
+ * LmPack_AtlasDesc = atlases_create / AtlasFn / atlas_search (static, :680-721, :779-865) for charts in the order
+ * given (the caller has sorted them): rasterises the masks again on the device, then gives every chart the first
+ * position, rows first, of the first atlas where it overlaps nothing placed before, with the reference's row-skipping
+ * search state carried from chart to chart as in its single task chunk. atlasIndexOut[c], translationOut[2c..2c+1];
+ * *atlasCountOut = atlases in use. A chart that fits nowhere is an error (the reference searches forever). */
+int32_t LmPack_ChartMasksDesc(pim_float2* triCoords, const int32_t* chartFirstNode, int32_t chartCount, float* areaOut,
+                              int32_t* maskSizeOut, uint8_t* const* masksOut);
+int32_t LmPack_AtlasDesc(const pim_float2* triCoords, const int32_t* chartFirstNode, int32_t chartCount, const float* area,
+                         const int32_t* maskSize, int32_t atlasSize, int32_t* atlasIndexOut, int32_t* translationOut,
+                         int32_t* atlasCountOut);
+
 /* ---- callers either side of the path -------------------
  * The reference functions that feed the path tracer (sky) or consume Pt_TraceRay /
  * Pt_RayGen (cubemap and ambient-cube bakes) or its image (screenshot), same names and

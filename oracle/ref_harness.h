@@ -37,6 +37,9 @@ enum
 void oracle_set_threads(int n);
 int oracle_get_threads(void);
 void oracle_set_seed(uint32_t seed);
+/* 0: one call and one seeded random state per work item (parity); 1: the reference's chunking, task.c:35-64 (timing) */
+void oracle_set_task_mode(int mode);
+int oracle_get_task_mode(void);
 void oracle_begin(uint32_t stream, uint32_t pass);
 void oracle_frame_end(void);
 void oracle_set_pt_dist_meters(float v);
@@ -131,6 +134,14 @@ void oracle_lm_page(int i, float** probes5, float** position3, float** normal3, 
 void oracle_lm_embed(void);    /* EmbedAttributes alone, on the pack oracle_lm_pack left */
 int oracle_lm_slot(int i);      /* Lightmap.slot.index: what EmbedTaskFn matches texIndices.w against */
 void oracle_lm_bake(void* scene, float timeSlice, int spp, uint32_t pass);
+/* LmPack_Pack with its intermediate state recorded (ChartMaskFn's input and output, AtlasFn's input order and
+ * output): one task thread, the reference's chunking, so AtlasFn's row-skipping search state runs through all
+ * charts as it does in the engine's single chunk. Returns the chart count; the getters copy chart c. */
+int oracle_lm_pack_capture(int atlasSize, float texelsPerUnit, float distThresh, float degThresh);
+int oracle_lm_cap_atlas_count(void);
+int oracle_lm_cap_chart(int c, int* nodeCount, float* area, int* maskSize2, int* atlasIndex, int* translation2);
+void oracle_lm_cap_chart_data(int c, float* triBefore, float* triAfter, unsigned char* mask);
+int oracle_lm_cap_sorted_index(int c);
 
 /* SURVEY 8(f) rows (ref_cm_wrap.c). color: 6 x size*size float3; convolved: 6 x elemCount float4 */
 int oracle_cubemap_elem_count(int size);

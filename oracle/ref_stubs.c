@@ -99,6 +99,19 @@ static Prng s_prngs[kMaxThreads];
 
 static u32 s_seed = 1, s_pass = 0, s_stream = 0, s_call = 0;
 
+/* How Task_Run hands out work. 0 (default, parity runs): one fn(i, i + 1) call per item, each with its own
+ * seeded random state, so results do not depend on the thread count or on scheduling. 1 (timing runs, and
+ * code whose behaviour depends on the chunking, like AtlasFn's per-call search state): the reference's own rule,
+ * src/threading/task.c:35-64 — chunks of max(1, worksize / T^2) items claimed atomically, fn(begin, end) once per
+ * chunk, one random state per thread seeded at the start of the call. */
+static int s_taskMode = 0;
+void oracle_set_task_mode(int mode) { s_taskMode = mode; }
+int oracle_get_task_mode(void) { return s_taskMode; }
+
+/* test hook around every Task_Run: phase 0 before, 1 after (ref_lm_wrap.c captures the packer's intermediate state) */
+static void (*s_taskHook)(void* task, TaskExecuteFn fn, i32 worksize, int phase);
+void oracle_set_task_hook(void (*hook)(void*, TaskExecuteFn, i32, int)) { s_taskHook = hook; }
+
 void oracle_set_threads(int n)
 {
     if (n < 1) n = 1;
@@ -140,6 +153,7 @@ void oracle_counters_get(uint64_t* nodes, uint64_t* tris, uint64_t* rays)
 static void run_worker(RunCtx* r, i32 tid)
 {
     t_tid = tid;
+    if (s_taskMode == 1) seed_item(tid, 0x40000000u + (u32)tid, r->salt);     /* one stream per thread and call */
     cpubvh_counters_reset();
     _MM_SET_FLUSH_ZERO_MODE(_MM_FLUSH_ZERO_ON);          /* task.c:73-74 */
     _MM_SET_DENORMALS_ZERO_MODE(_MM_DENORMALS_ZERO_ON);
@@ -148,6 +162,11 @@ static void run_worker(RunCtx* r, i32 tid)
         i32 b = __atomic_fetch_add(&r->head, r->chunk, __ATOMIC_RELAXED);
         if (b >= r->worksize) break;
         i32 e = b + r->chunk; if (e > r->worksize) e = r->worksize;
+        if (s_taskMode == 1)
+        {
+            r->fn(r->task, b, e);
+            continue;
+        }
         for (i32 i = b; i < e; ++i)
         {
             seed_item(tid, (u32)i, r->salt);
@@ -171,6 +190,7 @@ static void* thread_main(void* p)
 void Task_Run(void* task, TaskExecuteFn fn, i32 worksize)
 {
     if (worksize <= 0) return;
+    if (s_taskHook) s_taskHook(task, fn, worksize, 0);
     RunCtx r;
     r.task = task; r.fn = fn; r.worksize = worksize; r.head = 0;
     r.salt = (s_stream << 4) | (s_call & 0xf);
@@ -196,6 +216,7 @@ void Task_Run(void* task, TaskExecuteFn fn, i32 worksize)
     }
     t_tid = savedTid;
     _mm_setcsr(savedCsr);
+    if (s_taskHook) s_taskHook(task, fn, worksize, 1);
 }
 
 /* Task_Submit + TaskSys_Schedule + Task_Await (cubemap.c:271-300 queues one task per mip):

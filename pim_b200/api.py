@@ -145,7 +145,7 @@ EXPORTS = [
     "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
     "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap", "LmPack_EmbedDesc",
     "LmPack_BakeDesc_Device", "PtMediaParams_Default", "PtScene_SetMedia",
-    "Pt_RepackRome", "PtSys_SetLmPack", "LmPack_Bake", "Pt_PointQueryN", "Pt_SetOption", "PtSys_SetDevices", "PtSys_GetDevices",
+    "Pt_RepackRome", "PtSys_SetLmPack", "LmPack_Bake", "Pt_PointQueryN", "Pt_SetOption", "PtSys_SetDevices", "PtSys_GetDevices", "LmPack_ChartMasksDesc", "LmPack_AtlasDesc",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -227,6 +227,10 @@ def load():
     L.LmPack_BakeDesc_Device.restype = C.c_int32
     L.Pt_PointQueryN.argtypes = [vp, vp, vp, C.c_int64]
     L.Pt_PointQueryN.restype = C.c_int32
+    L.LmPack_ChartMasksDesc.argtypes = [vp, vp, C.c_int32, vp, vp, vp]
+    L.LmPack_ChartMasksDesc.restype = C.c_int32
+    L.LmPack_AtlasDesc.argtypes = [vp, vp, C.c_int32, vp, vp, C.c_int32, vp, vp, C.POINTER(C.c_int32)]
+    L.LmPack_AtlasDesc.restype = C.c_int32
     L.PtSys_SetDevices.argtypes = [C.c_int32]
     L.PtSys_SetDevices.restype = C.c_int32
     L.PtSys_GetDevices.restype = C.c_int32
@@ -678,6 +682,40 @@ def lm_embed(meshes, slot_indices, size):
         out.append((position, normal, counts))
     _check(load().LmPack_EmbedDesc(arr, len(meshes), pages, slots.ctypes.data, len(slots)), "LmPack_EmbedDesc")
     return out
+
+
+def lm_chart_masks(tri_coords, first_node, want_masks=True):
+    """LmPack_ChartMasksDesc. tri_coords float32 [nodes, 3, 2] (chart after chart), first_node int32 [charts + 1].
+    Returns (moved tri_coords, area [charts], mask_size [charts, 2], masks: list of uint8 [h, w] or None)."""
+    tri = np.ascontiguousarray(tri_coords, np.float32).copy()
+    first = np.ascontiguousarray(first_node, np.int32)
+    n = len(first) - 1
+    area = np.zeros(n, np.float32); size = np.zeros((n, 2), np.int32)
+    L = load()
+    L.PtSys_Init()
+    _check(L.LmPack_ChartMasksDesc(tri.ctypes.data, first.ctypes.data, n, area.ctypes.data, size.ctypes.data, None), "LmPack_ChartMasksDesc")
+    masks = None
+    if want_masks:
+        # sizes are known now: a second call (the charts are already at (2, 2), moving them again changes nothing) fills the masks
+        masks = [np.zeros((int(size[c, 1]), int(size[c, 0])), np.uint8) for c in range(n)]
+        ptrs = (C.c_void_p * max(n, 1))(*[m.ctypes.data for m in masks])
+        again = tri.copy()
+        _check(L.LmPack_ChartMasksDesc(again.ctypes.data, first.ctypes.data, n, area.ctypes.data, size.ctypes.data, ptrs), "LmPack_ChartMasksDesc")
+    return tri, area, size, masks
+
+
+def lm_atlas(tri_coords, first_node, area, mask_size, atlas_size):
+    """LmPack_AtlasDesc: charts in the given order -> (atlas index [charts], translation [charts, 2], atlases in use)"""
+    tri = np.ascontiguousarray(tri_coords, np.float32)
+    first = np.ascontiguousarray(first_node, np.int32)
+    area = np.ascontiguousarray(area, np.float32); size = np.ascontiguousarray(mask_size, np.int32)
+    n = len(first) - 1
+    idx = np.zeros(n, np.int32); tr = np.zeros((n, 2), np.int32); count = C.c_int32()
+    L = load()
+    L.PtSys_Init()
+    _check(L.LmPack_AtlasDesc(tri.ctypes.data, first.ctypes.data, n, area.ctypes.data, size.ctypes.data, int(atlas_size), idx.ctypes.data,
+                              tr.ctypes.data, C.byref(count)), "LmPack_AtlasDesc")
+    return idx, tr, count.value
 
 
 def repack_rome(mr, occ, em, size):

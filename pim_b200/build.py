@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpimpt.so")
-SOURCES = ["api.cu", "bvh_build.cu", "scene.cu", "wavefront.cu", "pathkernels.cu", "bakes.cu"]
+SOURCES = ["api.cu", "bvh_build.cu", "scene.cu", "wavefront.cu", "pathkernels.cu", "bakes.cu", "lmpack.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
     # The reference is built -O3 -ffast-math with FTZ/DAZ (CMakeLists.txt:168, src/threading/task.c:73-74).

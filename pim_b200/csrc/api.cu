@@ -1663,6 +1663,81 @@ int32_t LmPack_EmbedDesc(const PtEmbedMesh* meshes, int32_t meshCount, PtLightma
     return ok ? 0 : -1;
 }
 
+int32_t LmPack_ChartMasksDesc(pim_float2* triCoords, const int32_t* chartFirstNode, int32_t chartCount, float* areaOut,
+                              int32_t* maskSizeOut, uint8_t* const* masksOut)
+{
+    if (!ensureInit()) return -1;
+    if (chartCount <= 0) return 0;
+    if (!triCoords || !chartFirstNode || !areaOut || !maskSizeOut) { setError("LmPack_ChartMasksDesc: null argument"); return -1; }
+    const size_t corners = 3 * (size_t)chartFirstNode[chartCount];
+    chartPrepare(reinterpret_cast<V2*>(triCoords), chartFirstNode, chartCount, areaOut, maskSizeOut);
+    if (!masksOut) return 0;            // the caller only wanted the moved charts, their areas and mask sizes
+    const size_t words = chartMaskWords(maskSizeOut, chartCount);
+    size_t maxTexels = 1;
+    for (int32_t c = 0; c < chartCount; ++c) maxTexels = std::max(maxTexels, (size_t)maskSizeOut[2 * c] * (size_t)std::max(maskSizeOut[2 * c + 1], 0));
+    V2* dTri = nullptr; uint32_t* dBits = nullptr; char* dCharts = nullptr; uint8_t* dBytes = nullptr;
+    Lease lease;
+    if (!lease.dev(dTri, corners).dev(dBits, words).dev(dCharts, chartInfoBytes() * (size_t)chartCount).dev(dBytes, maxTexels).commit()) return -1;
+    cudaStream_t st = nullptr;
+    std::vector<int32_t> wordBase;
+    bool ok = PT_CUDA(cudaMemcpyAsync(dTri, triCoords, sizeof(V2) * corners, cudaMemcpyHostToDevice, st));
+    KernelTimer timer(lease, st);
+    ok = ok && launchChartMasks(chartFirstNode, maskSizeOut, chartCount, dCharts, dTri, dBits, wordBase, st);
+    timer.stop();
+    for (int32_t c = 0; ok && c < chartCount; ++c)
+    {
+        const int32_t w = maskSizeOut[2 * c], h = maskSizeOut[2 * c + 1];
+        if (!masksOut[c] || w <= 0 || h <= 0) continue;
+        ok = launchMaskBytes(dCharts, c, w, h, dBits, dBytes, st) &&
+             PT_CUDA(cudaMemcpyAsync(masksOut[c], dBytes, (size_t)w * (size_t)h, cudaMemcpyDeviceToHost, st)) &&
+             PT_CUDA(cudaStreamSynchronize(st));
+    }
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
+    return ok ? 0 : -1;
+}
+
+int32_t LmPack_AtlasDesc(const pim_float2* triCoords, const int32_t* chartFirstNode, int32_t chartCount, const float* area,
+                         const int32_t* maskSize, int32_t atlasSize, int32_t* atlasIndexOut, int32_t* translationOut,
+                         int32_t* atlasCountOut)
+{
+    if (!ensureInit()) return -1;
+    if (atlasCountOut) *atlasCountOut = 0;
+    if (chartCount <= 0) return 0;
+    if (!triCoords || !chartFirstNode || !area || !maskSize || !atlasIndexOut || !translationOut || atlasSize <= 0 || atlasSize > 32768)
+    {
+        setError("LmPack_AtlasDesc: bad argument");
+        return -1;
+    }
+    // atlas_estimate (lightmap.c:825-842): enough atlases for the summed chart areas
+    long long areaRequired = 0;
+    for (int32_t c = 0; c < chartCount; ++c) areaRequired += (long long)ceilf(area[c]);
+    const long long perAtlas = (long long)atlasSize * atlasSize;
+    int32_t atlasCount = (int32_t)std::max<long long>(1, (areaRequired + perAtlas - 1) / perAtlas);
+    const size_t corners = 3 * (size_t)chartFirstNode[chartCount];
+    const size_t words = chartMaskWords(maskSize, chartCount);
+    const size_t atlasWords = (size_t)((atlasSize + 31) / 32) * (size_t)atlasSize * (size_t)atlasCount;
+    V2* dTri = nullptr; uint32_t *dBits = nullptr, *dAtlas = nullptr, *dBest = nullptr; char* dCharts = nullptr;
+    Lease lease;
+    if (!lease.dev(dTri, corners).dev(dBits, words).dev(dCharts, chartInfoBytes() * (size_t)chartCount).dev(dAtlas, atlasWords).dev(dBest, 64).commit()) return -1;
+    cudaStream_t st = nullptr;
+    std::vector<int32_t> wordBase;
+    bool ok = PT_CUDA(cudaMemcpyAsync(dTri, triCoords, sizeof(V2) * corners, cudaMemcpyHostToDevice, st)) &&
+              PT_CUDA(cudaMemsetAsync(dAtlas, 0, 4 * atlasWords, st));
+    KernelTimer timer(lease, st);
+    ok = ok && launchChartMasks(chartFirstNode, maskSize, chartCount, dCharts, dTri, dBits, wordBase, st);
+    ok = ok && placeCharts(chartFirstNode, maskSize, area, wordBase, chartCount, atlasSize, atlasCount, dAtlas, dBits, dBest,
+                           atlasIndexOut, translationOut, st);
+    timer.stop();
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
+    if (ok && atlasCountOut)
+    {
+        int32_t used = 0;
+        for (int32_t c = 0; c < chartCount; ++c) used = std::max(used, atlasIndexOut[c] + 1);
+        *atlasCountOut = used;
+    }
+    return ok ? 0 : -1;
+}
+
 int32_t Pt_BakeSky(Cubemap* cm, const SkyMedium* sky, pim_float3 sunDir, float sunLum, int32_t steps)
 {
     if (!ensureInit()) return -1;

@@ -241,6 +241,17 @@ bool launchLightmapScatter(const LightmapView& lm, const int32_t* dIdx, int32_t 
 bool launchLightmapGather(const LightmapView& lm, const int32_t* dIdx, int32_t count, F4* dProbes, float* dCnt,
                           cudaStream_t stream);
 
+// ------------------------------------------------------------------ lmpack.cu (chart masks, atlas placement)
+void chartPrepare(V2* tri, const int32_t* firstNode, int32_t chartCount, float* areaOut, int32_t* maskSizeOut);
+size_t chartMaskWords(const int32_t* maskSize, int32_t chartCount);
+size_t chartInfoBytes();
+bool launchChartMasks(const int32_t* firstNode, const int32_t* maskSize, int32_t chartCount, void* dCharts, const V2* dTri,
+                      uint32_t* dBits, std::vector<int32_t>& wordBaseOut, cudaStream_t stream);
+bool launchMaskBytes(const void* dCharts, int32_t chart, int32_t w, int32_t h, const uint32_t* dBits, uint8_t* dBytes, cudaStream_t stream);
+bool placeCharts(const int32_t* firstNode, const int32_t* maskSize, const float* area, const std::vector<int32_t>& wordBase,
+                 int32_t chartCount, int32_t atlasSize, int32_t atlasCount, uint32_t* dAtlas, const uint32_t* dBits, uint32_t* dBest,
+                 int32_t* atlasIndexOut, int32_t* translationOut, cudaStream_t stream);
+
 // in-process multi-GPU: dst += src; dst = a - dst; dst += src
 bool launchAccumulate(float* dDst, const float* dSrc, int64_t n, cudaStream_t stream);
 bool launchU32Sub(uint32_t* dDst, const uint32_t* dA, int64_t n, cudaStream_t stream);

@@ -370,3 +370,25 @@ def lm_bake(scene, time_slice, spp, pass_index):
     L = lib()
     L.oracle_lm_bake.argtypes = [C.c_void_p, C.c_float, C.c_int, C.c_uint32]
     L.oracle_lm_bake(scene.h, time_slice, spp, pass_index)
+
+
+def lm_pack_capture(atlas_size, texels_per_unit, dist_thresh=0.1, deg_thresh=15.0):
+    """LmPack_Pack on one task thread with ChartMaskFn's and AtlasFn's inputs and outputs recorded. Returns a list of
+    charts in chart_group's order: dict(tri_before [n,3,2], tri_after, area, mask [h,w] uint8, atlas, translation (x, y),
+    sorted_index = the chart's position in AtlasFn's order) and the number of atlases the reference estimated."""
+    L = lib()
+    L.oracle_lm_pack_capture.argtypes = [C.c_int, C.c_float, C.c_float, C.c_float]
+    L.oracle_lm_cap_chart.argtypes = [C.c_int, i32p, f32p, i32p, i32p, i32p]
+    L.oracle_lm_cap_chart_data.argtypes = [C.c_int, f32p, f32p, C.c_void_p]
+    n = L.oracle_lm_pack_capture(atlas_size, texels_per_unit, dist_thresh, deg_thresh)
+    charts = []
+    for c in range(n):
+        nc = np.zeros(1, np.int32); area = np.zeros(1, np.float32); ms = np.zeros(2, np.int32)
+        ai = np.zeros(1, np.int32); tr = np.zeros(2, np.int32)
+        L.oracle_lm_cap_chart(c, _ptr(nc, i32p), _ptr(area), _ptr(ms, i32p), _ptr(ai, i32p), _ptr(tr, i32p))
+        before = np.zeros((int(nc[0]), 3, 2), np.float32); after = np.zeros_like(before)
+        mask = np.zeros((int(ms[1]), int(ms[0])), np.uint8)
+        L.oracle_lm_cap_chart_data(c, _ptr(before), _ptr(after), mask.ctypes.data)
+        charts.append({"tri_before": before, "tri_after": after, "area": float(area[0]), "mask": mask, "atlas": int(ai[0]),
+                       "translation": (int(tr[0]), int(tr[1])), "sorted_index": L.oracle_lm_cap_sorted_index(c)})
+    return charts, L.oracle_lm_cap_atlas_count()

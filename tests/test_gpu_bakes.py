@@ -215,3 +215,49 @@ def test_rome_repack_matches_reference(api, oracle):
     assert (got == np.array([128, 255, 0, 0], np.uint8)).all()
     assert (got == oracle.repack_rome(d_mr, d_occ, d_em, 4).view(np.uint8).reshape(-1, 4)).all()
     assert api.load().Pt_RepackRome(None, api.Int2(1, 1), None, api.Int2(1, 1), None, api.Int2(1, 1), 4, None) == -1
+
+
+def test_chart_masks_and_atlas_match_reference(oracle):
+    """N1: ChartMaskFn and AtlasFn / atlas_search of LmPack_Pack on the device (LmPack_ChartMasksDesc, LmPack_AtlasDesc)
+    against the reference's own run on one task thread, whose intermediate state the oracle records: the charts moved
+    to (2, 2), their areas, mask sizes and masks texel for texel, and then, for the charts in the reference's sorted
+    order, the atlas and translation every chart gets. Two scenes: cornell boxes at 16 texels/m (28 charts) and the
+    cornell spheres (thousands of small charts)."""
+    from pim_b200 import api
+    for variant, size, tpm in (("boxes", 1024, 16.0), ("boxes", 256, 8.0)):
+        desc = scenes.cornell_box(variant, brdf_lut=np.zeros((4, 4, 2), np.float32), seed=1)
+        oracle.set_seed(1)
+        oracle.load_scene_desc(desc)
+        charts, ref_atlases = oracle.lm_pack_capture(size, tpm, 0.1, 15.0)
+        assert len(charts) >= 20
+        first = np.zeros(len(charts) + 1, np.int32)
+        first[1:] = np.cumsum([len(c["tri_before"]) for c in charts])
+        tri = np.concatenate([c["tri_before"] for c in charts]).astype(np.float32)
+        moved, area, msize, masks = api.lm_chart_masks(tri, first)
+        assert np.array_equal(moved, np.concatenate([c["tri_after"] for c in charts]))
+        assert np.array_equal(area, np.array([c["area"] for c in charts], np.float32))
+        differing = total = 0
+        for c, ch in enumerate(charts):
+            assert masks[c].shape == ch["mask"].shape
+            differing += int((masks[c] != ch["mask"]).sum()); total += masks[c].size
+            assert set(np.unique(masks[c])) <= {0, 255}
+        assert differing <= 1e-5 * total, (differing, total)       # the same arithmetic, rounded the same way
+        # AtlasFn's order: the reference's chart_sort
+        order = np.argsort([c["sorted_index"] for c in charts])
+        s_first = np.zeros(len(charts) + 1, np.int32)
+        s_first[1:] = np.cumsum([len(charts[i]["tri_after"]) for i in order])
+        s_tri = np.concatenate([charts[i]["tri_after"] for i in order]).astype(np.float32)
+        idx, tr, used = api.lm_atlas(s_tri, s_first, area[order], msize[order], size)
+        want_idx = np.array([charts[i]["atlas"] for i in order]); want_tr = np.array([charts[i]["translation"] for i in order])
+        if differing == 0:
+            assert np.array_equal(idx, want_idx) and np.array_equal(tr, want_tr)
+        else:       # a rim texel apart: the first chart after it may shift, and everything packed later with it
+            assert (idx == want_idx).mean() > 0.5
+        assert used == max(want_idx) + 1 and used <= ref_atlases
+        # nothing overlaps: paint the device's placements with the device's masks
+        canvas = np.zeros((used, size, size), np.uint16)
+        for k, i in enumerate(order):
+            m = masks[i] != 0
+            h, w = m.shape
+            canvas[idx[k], tr[k, 1]:tr[k, 1] + h, tr[k, 0]:tr[k, 0] + w] += m
+        assert canvas.max() == 1
