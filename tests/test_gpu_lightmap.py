@@ -119,3 +119,48 @@ def test_device_resident_bake_equals_host_form(oracle):
                 x, y = d_probes[k].cpu().numpy()[h_cnt > 0], h_probes[k][h_cnt > 0]
                 assert np.abs(x.mean(axis=0) - y.mean(axis=0)).max() <= 0.02 * np.abs(y.mean(axis=0)).max()
         a.close(); b.close()
+
+
+def test_bake_writes_the_block_lmpack_save_stores(oracle):
+    """LmPack_Save (lightmap.c:1225-1262) writes each lightmap as ONE blob: bytesPerLightmap = 108 * size^2 bytes from
+    probes[0], i.e. Lightmap_New's allocation [5 x N float4 probes][N float3 position][N float3 normal][N float counts]
+    (lightmap.c:81-109). The bake works in place on arrays laid out like that: here the page is one such block (a byte
+    copy of the reference's), the PtLightmapDesc pointers are Lightmap_New's offsets into it, and after the same bake on
+    both sides the two blobs are compared region by region — what LmPack_Save would store is the reference's file."""
+    import ctypes as C
+    from pim_b200 import api
+    desc = scenes.cornell_box("boxes", brdf_lut=parity.reference_lut(), seed=1)
+    desc.bake_mode = 1
+    oracle.set_seed(1)
+    oracle.load_scene_desc(desc)
+    size = 256
+    assert oracle.lm_pack(size, 4.0) == 1
+    probes, pos, nrm, cnt = oracle.lm_page(0)
+    n = size * size
+    # the reference's own block: its five probe arrays, position, normal and counts are consecutive
+    base = probes[0].ctypes.data
+    assert [p.ctypes.data - base for p in probes] == [16 * n * k for k in range(5)]
+    assert pos.ctypes.data - base == 80 * n and nrm.ctypes.data - base == 92 * n and cnt.ctypes.data - base == 104 * n
+    bytes_per_lightmap = 108 * n                      # DiskLmPack.bytesPerLightmap
+    ref_blob = np.ctypeslib.as_array(C.cast(base, C.POINTER(C.c_uint8)), (bytes_per_lightmap,))
+    blob = ref_blob.copy()
+    f = blob.view(np.float32)
+    views = ([f[4 * n * k:4 * n * (k + 1)].reshape(n, 4) for k in range(5)], f[20 * n:23 * n].reshape(n, 3),
+             f[23 * n:26 * n].reshape(n, 3), f[26 * n:27 * n])
+    ref = oracle.Scene()
+    s = api.Scene(desc)
+    for c in range(int(np.prod(s.grid_size))):
+        k, pdf, _, _ = ref.dist(c)
+        if k:
+            s.set_dist(c, pdf)
+    oracle.lm_bake(ref, 1.0, 4, 0)
+    s.bake_lightmap(views[0], views[1], views[2], views[3], 4.0, 1.0, 4, 0)
+    ref.close(); s.close()
+    # position, normal and sample counts: byte for byte the reference's blob
+    assert np.array_equal(blob[80 * n:], ref_blob[80 * n:])
+    # probes: the uncovered texels byte for byte, the covered ones texel for texel within the bake's tolerance
+    covered = views[3] > 0
+    got = blob[:80 * n].view(np.float32).reshape(5, n, 4); want = ref_blob[:80 * n].view(np.float32).reshape(5, n, 4)
+    assert np.array_equal(got[:, ~covered], want[:, ~covered])
+    close = np.abs(got[:, covered] - want[:, covered]).max(axis=2) <= 1e-3 * (np.abs(want[:, covered]).max(axis=2) + 1e-2)
+    assert close.mean() >= 0.95
