@@ -39,7 +39,8 @@ WORKLOAD = "cornell_box boxes 1920x1080 progressive accumulation (BASELINE confi
 TRAVERSAL_COUNTS = os.path.join(ROOT, "baseline", "traversal_counts.json")
 TRAFFIC = os.path.join(ROOT, "profiles", "r02_traffic.json")
 DEFAULT_EXTRAS = "c1,c3,c4,c5"
-BACKEND = "reference path_tracer.c over the CPU BVH restatement (Embree 3.13.5 binary unavailable)"
+BACKEND = ("reference path_tracer.c over the CPU BVH restatement (Embree 3.13.5 binary unavailable), "
+           "work chunked as threading/task.c:35-64 does")
 
 
 def parse_args():
@@ -137,6 +138,7 @@ def _oracle():
 def _oracle_cornell(O, seed=1, lut_samples=1024):
     from pim_b200 import scenes
     O.set_threads(host_cores())
+    O.set_task_mode(1)          # timing runs: work handed out as the reference's task.c does (chunks of N / T^2, no per-item reseed)
     O.set_seed(seed)
     lut = O.bake_brdf_lut(128, lut_samples)
     desc = scenes.cornell_box("boxes", brdf_lut=lut, seed=seed)
@@ -624,7 +626,7 @@ def extra_c3(ctx):
     if ctx.world == 1 and not ctx.args.no_cpu_baseline:
         O = _oracle()
         if O.available():
-            O.set_threads(host_cores()); O.set_seed(1)
+            O.set_threads(host_cores()); O.set_task_mode(1); O.set_seed(1)
             desc.brdf_lut = lut
             t0 = time.perf_counter()
             O.load_scene_desc(desc)

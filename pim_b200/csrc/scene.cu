@@ -52,7 +52,10 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHit(DScene S, const F4*
 constexpr int kLeafVotes = PT_LEAF_VOTES;
 
 // persistent form: warps refill finished lanes with the next rays of the batch (one atomic per warp)
-__global__ void __launch_bounds__(kTravThreads) k_closestHitPersistent(DScene S, const F4* __restrict__ ro,
+#ifndef PT_PERSIST_MIN_BLOCKS
+#define PT_PERSIST_MIN_BLOCKS 1
+#endif
+__global__ void __launch_bounds__(kTravThreads, PT_PERSIST_MIN_BLOCKS) k_closestHitPersistent(DScene S, const F4* __restrict__ ro,
                                                                         const F4* __restrict__ rd, float tNear,
                                                                         RayHitOut* __restrict__ out, int64_t n,
                                                                         unsigned long long* cursor)

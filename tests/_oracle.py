@@ -97,6 +97,12 @@ def set_threads(n):
     lib().oracle_set_threads(int(n))
 
 
+def set_task_mode(mode):
+    """0: one call and one seeded random state per work item (parity runs, the default); 1: the reference's own
+    chunking, threading/task.c:35-64 — chunks of worksize / T^2 items per call, one random state per thread (timing)"""
+    lib().oracle_set_task_mode(int(mode))
+
+
 def set_seed(seed):
     lib().oracle_set_seed(int(seed))
 
