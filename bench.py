@@ -392,6 +392,9 @@ def run_ours(args, rank, world, local_rank):
 
     def step(i):
         begin, _ = mg.sample_range(i, rank, world, spp)
+        if world == 1:
+            ctx.trace(scene, cam, dof, WIDTH, HEIGHT, begin, spp, total)     # one rank: straight into the frame's total
+            return
         for t in sums:
             t.zero_()
         ctx.trace(scene, cam, dof, WIDTH, HEIGHT, begin, spp, sums)

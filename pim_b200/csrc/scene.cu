@@ -4,7 +4,7 @@
 //   K4  anyHit          RtcOccluded16 over a ray batch (path_tracer.c:524-553)
 //   K0  flatten         FlattenDrawables (path_tracer.c:692-782)
 //   K9  emissionPdf     CalcEmissionPdfFn / EmissionPdf (path_tracer.c:784-843)
-//   K10 lightGrid       SetupLightGridFn (path_tracer.c:891-990): point query,
+//   K10 lightGridCells / Pairs / Bake   SetupLightGridFn (path_tracer.c:891-990): point query,
 //                       16 probe rays, cells x emissives x 16 occlusion rays,
 //                       then Dist1D_Bake (dist1d.c:33-73)
 //   K11 distUpdate      Dist1D_Update (dist1d.c:128-163) per cell
@@ -52,8 +52,10 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHit(DScene S, const F4*
 constexpr int kLeafVotes = PT_LEAF_VOTES;
 
 // persistent form: warps refill finished lanes with the next rays of the batch (one atomic per warp)
+// registers: 70 per thread when left to the compiler (43 % occupancy); capped at 64 for 8 CTAs per SM the 10 M-triangle
+// soup goes from 345 to 370 Mrays/s, at 48 (10 CTAs, spills) down to 299
 #ifndef PT_PERSIST_MIN_BLOCKS
-#define PT_PERSIST_MIN_BLOCKS 1
+#define PT_PERSIST_MIN_BLOCKS 8
 #endif
 __global__ void __launch_bounds__(kTravThreads, PT_PERSIST_MIN_BLOCKS) k_closestHitPersistent(DScene S, const F4* __restrict__ ro,
                                                                         const F4* __restrict__ rd, float tNear,
@@ -409,7 +411,17 @@ __device__ void distBake(const DScene& S, int cell)      // Dist1D_Bake, dist1d.
     }
 }
 
-__global__ void __launch_bounds__(kTravThreads) k_lightGrid(DScene S, float metersPerCell, uint32_t seed)
+// SetupLightGridFn (path_tracer.c:891-990) in three kernels. The reference walks a cell's emissive triangles in
+// order with ONE random stream per cell (a hash chain: no skipping ahead), which is why a thread per cell was the
+// first form — and the slow one: the 1 M-triangle interior has 1875 cells x 648 emissives x 16 rays, and 15 CTAs
+// of cells ran for 317 ms at 5.6 % occupancy. Now
+//   cells   a thread per cell: the surface test (point query, probe rays), and for a cell that is kept the random
+//           stream stepped through all its emissives with the state at the start of each one saved (16 B per pair);
+//   pairs   a thread per (cell, emissive): its 16 visibility rays from the saved state -> pdf;
+//   bake    a thread per cell: Dist1D_Bake.
+// Same draws, same ray set-up, same any-hit decisions as before: the pdfs are unchanged.
+__global__ void __launch_bounds__(kTravThreads) k_lightGridCells(DScene S, float metersPerCell, uint32_t seed, Rng* __restrict__ states,
+                                                                  uint8_t* __restrict__ keep)
 {
     PT_DECLARE_STACK(st);
     const int cell = blockIdx.x * blockDim.x + threadIdx.x;
@@ -418,6 +430,7 @@ __global__ void __launch_bounds__(kTravThreads) k_lightGrid(DScene S, float mete
     const V3 position = Grid_Position(S.grid, cell);
     S.distLength[cell] = 0;
     S.distSum[cell] = 0;
+    keep[cell] = 0;
     {
         float dist = pointQuery(S.bvh, position, radius + 0.01f * kMilli, st);
         if (dist > radius)
@@ -435,53 +448,89 @@ __global__ void __launch_bounds__(kTravThreads) k_lightGrid(DScene S, float mete
     }
     const int E = S.emissiveCount;
     if (E <= 0) return;
+    keep[cell] = 1;
     Rng rng = seed_prng((uint32_t)cell, 0u, seed, Salt_LightGrid);
-    float* pdf = S.distPdf + (size_t)cell * E;
-    uint32_t* live = S.distLive + (size_t)cell * E;
     for (int iEmit = 0; iEmit < E; ++iEmit)
     {
-        const int iVert = S.emitToVert[iEmit];
-        const V3 A = ld3(S.positions, iVert), B = ld3(S.positions, iVert + 1), C = ld3(S.positions, iVert + 2);
-        int hits = 0;
-        for (int k = 0; k < 16; ++k)
-        {
-            // ray setup without fused multiply-adds: same roundings as the reference's CPU code,
-            // so the any-hit decisions (and with them the k/16 pdfs) come out the same
-            F4 r4 = rng_f4(rng);
-            V3 t = v3(mulr(addr(-1.5f, mulr(r4.x, 3.0f)), radius), mulr(addr(-1.5f, mulr(r4.y, 3.0f)), radius),
-                      mulr(addr(-1.5f, mulr(r4.z, 3.0f)), radius));
-            V3 ro = v3(addr(position.x, t.x), addr(position.y, t.y), addr(position.z, t.z));
-            V3 wuv = SampleBaryCoord(rng_f2(rng));
-            V3 at = v3(addr(addr(mulr(A.x, wuv.x), mulr(B.x, wuv.y)), mulr(C.x, wuv.z)),
-                       addr(addr(mulr(A.y, wuv.x), mulr(B.y, wuv.y)), mulr(C.y, wuv.z)),
-                       addr(addr(mulr(A.z, wuv.x), mulr(B.z, wuv.y)), mulr(C.z, wuv.z)));
-            V3 rd = v3(subr(at.x, ro.x), subr(at.y, ro.y), subr(at.z, ro.z));
-            float dist = sqrtr(dotr(rd, rd));
-            rd = v3(divr(rd.x, dist), divr(rd.y, dist), divr(rd.z, dist));
-            float tFar = dist - 0.01f * kMilli;
-            bool visible = false;
-            if (tFar > 0.0f)
-            {
-                Hit hit;
-                visible = !traverse<true, false>(S.bvh, ro, rd, 0.0f, tFar, hit, st, (TravCounters*)nullptr);
-            }
-            hits += visible ? 1 : 0;
-        }
-        pdf[iEmit] = (float)hits / 16.0f;
-        live[iEmit] = 0;
+        states[(size_t)cell * E + iEmit] = rng;
+        for (int k = 0; k < 16; ++k) { rng_f4(rng); rng_f2(rng); }      // the draws of this emissive's 16 rays
     }
+}
+
+__global__ void __launch_bounds__(kTravThreads) k_lightGridPairs(DScene S, float metersPerCell, const Rng* __restrict__ states,
+                                                                  const uint8_t* __restrict__ keep, long long pairs)
+{
+    PT_DECLARE_STACK(st);
+    const long long pair = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= pairs) return;
+    const int E = S.emissiveCount;
+    const int cell = (int)(pair / E), iEmit = (int)(pair % E);
+    if (!keep[cell]) return;
+    const float radius = metersPerCell * 0.666f;
+    const V3 position = Grid_Position(S.grid, cell);
+    Rng rng = states[pair];
+    const int iVert = S.emitToVert[iEmit];
+    const V3 A = ld3(S.positions, iVert), B = ld3(S.positions, iVert + 1), C = ld3(S.positions, iVert + 2);
+    int hits = 0;
+    for (int k = 0; k < 16; ++k)
+    {
+        // ray setup without fused multiply-adds: same roundings as the reference's CPU code,
+        // so the any-hit decisions (and with them the k/16 pdfs) come out the same
+        F4 r4 = rng_f4(rng);
+        V3 t = v3(mulr(addr(-1.5f, mulr(r4.x, 3.0f)), radius), mulr(addr(-1.5f, mulr(r4.y, 3.0f)), radius),
+                  mulr(addr(-1.5f, mulr(r4.z, 3.0f)), radius));
+        V3 ro = v3(addr(position.x, t.x), addr(position.y, t.y), addr(position.z, t.z));
+        V3 wuv = SampleBaryCoord(rng_f2(rng));
+        V3 at = v3(addr(addr(mulr(A.x, wuv.x), mulr(B.x, wuv.y)), mulr(C.x, wuv.z)),
+                   addr(addr(mulr(A.y, wuv.x), mulr(B.y, wuv.y)), mulr(C.y, wuv.z)),
+                   addr(addr(mulr(A.z, wuv.x), mulr(B.z, wuv.y)), mulr(C.z, wuv.z)));
+        V3 rd = v3(subr(at.x, ro.x), subr(at.y, ro.y), subr(at.z, ro.z));
+        float dist = sqrtr(dotr(rd, rd));
+        rd = v3(divr(rd.x, dist), divr(rd.y, dist), divr(rd.z, dist));
+        float tFar = dist - 0.01f * kMilli;
+        bool visible = false;
+        if (tFar > 0.0f)
+        {
+            Hit hit;
+            visible = !traverse<true, false>(S.bvh, ro, rd, 0.0f, tFar, hit, st, (TravCounters*)nullptr);
+        }
+        hits += visible ? 1 : 0;
+    }
+    S.distPdf[pair] = (float)hits / 16.0f;
+    S.distLive[pair] = 0;
+}
+
+__global__ void __launch_bounds__(128) k_lightGridBake(DScene S, const uint8_t* __restrict__ keep)
+{
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= Grid_Len(S.grid) || !keep[cell]) return;
     distBake(S, cell);
-    S.distLength[cell] = E;
+    S.distLength[cell] = S.emissiveCount;
 }
 
 bool launchLightGrid(const DScene& S, float ptDistMeters, uint32_t seed, cudaStream_t stream)
 {
     int cells = Grid_Len(S.grid);
     if (cells <= 0) return true;
-    k_lightGrid<<<gridFor(cells, kTravThreads), kTravThreads, 0, stream>>>(S, ptDistMeters, seed);
-    g_counters.kernelLaunches++;
-    g_counters.occlusionRays += (unsigned long long)cells * (unsigned long long)S.emissiveCount * 16ull;
-    return PT_CUDA(cudaGetLastError());
+    const long long pairs = (long long)cells * (long long)std::max(S.emissiveCount, 0);
+    Rng* dStates = nullptr; uint8_t* dKeep = nullptr;
+    bool ok = PT_CUDA(cudaMalloc((void**)&dStates, sizeof(Rng) * (size_t)std::max<long long>(pairs, 1))) &&
+              PT_CUDA(cudaMalloc((void**)&dKeep, (size_t)cells));
+    if (ok)
+    {
+        k_lightGridCells<<<gridFor(cells, kTravThreads), kTravThreads, 0, stream>>>(S, ptDistMeters, seed, dStates, dKeep);
+        if (pairs > 0)
+        {
+            k_lightGridPairs<<<gridFor(pairs, kTravThreads), kTravThreads, 0, stream>>>(S, ptDistMeters, dStates, dKeep, pairs);
+            k_lightGridBake<<<gridFor(cells, 128), 128, 0, stream>>>(S, dKeep);
+        }
+        g_counters.kernelLaunches += 3;
+        g_counters.occlusionRays += (unsigned long long)pairs * 16ull;
+        ok = PT_CUDA(cudaGetLastError()) && PT_CUDA(cudaStreamSynchronize(stream));
+    }
+    if (dStates) cudaFree(dStates);
+    if (dKeep) cudaFree(dKeep);
+    return ok;
 }
 
 __global__ void __launch_bounds__(128) k_distUpdate(DScene S)     // Dist1D_Update, dist1d.c:128-163
