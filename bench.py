@@ -334,6 +334,34 @@ def dominant_kernel_roofline(ctx, kstats, counters):
                               if traffic is not None else None}
 
 
+def traversal_roofline(ctx, kstats):
+    """k_wfExtend by the bytes-per-ray definition of SURVEY.md 8(d). The 19-node cornell tree is served from L1 / L2,
+    so the HBM fraction is a normalised ray rate that may exceed 1; the honest bound for it is the L2: the kernel's
+    measured L2 traffic per ray (lts__t_sectors.sum x 32 B from the committed ncu capture) at this run's ray rate,
+    against the L2 read bandwidth measured live with a read-only sweep of a 32 MB buffer (Pt_MeasureL2ReadGBs)."""
+    tc = traversal_counts("cornell_boxes_camera_paths")
+    b_ray = bytes_per_ray(tc)
+    ext = kstats["extend"]
+    launches = max(ext["launches"], 1)
+    rays = kstats["extendRays"] / launches
+    avg_s = ext["ms"] * 1e-3 / launches
+    achieved = rays * b_ray / max(avg_s, 1e-12) / 1e9
+    out = {"bound": "hbm", "kernel": "k_wfExtend", "bytes_per_ray": b_ray, "rays_per_launch": rays, "avg_launch_ms": avg_s * 1e3,
+           "achieved": achieved, "peak": ctx.peak, "unit": "GB/s", "frac": achieved / ctx.peak,
+           "note": "108-triangle BVH is L1/L2 resident: algorithmic bytes never reach HBM, so frac can exceed 1 (SURVEY.md 8(d))"}
+    l2_peak = float(ctx.L.Pt_MeasureL2ReadGBs(32 << 20, 64))
+    if l2_peak > 0 and os.path.exists(TRAFFIC):
+        with open(TRAFFIC) as f:
+            tj = json.load(f)
+        per_ray = tj.get("k_wfExtend", {}).get("l2_bytes_per_slot")
+        if per_ray:
+            l2_gbs = per_ray * rays / max(avg_s, 1e-12) / 1e9
+            out["l2"] = {"achieved": l2_gbs, "peak": l2_peak, "unit": "GB/s", "frac": l2_gbs / l2_peak, "bytes_per_ray": per_ray,
+                         "peak_source": "Pt_MeasureL2ReadGBs: 64 read-only sweeps of a 32 MB buffer, measured in this run",
+                         "traffic_source": "profiles/r02_traffic.json"}
+    return out
+
+
 def verify_ranks(ctx, scene_desc_fn):
     """The N-rank image against the 1-rank image over the same (pixel, sample) set: 32 samples per pixel of the 1080p
     frame, split by sample index over the ranks (fresh replicas, so every rank samples the light grid as built),
@@ -482,6 +510,7 @@ def run_ours(args, rank, world, local_rank):
                     "d2h_bytes_per_step": 3 * n3 * 4, "steps": e2e_steps, "mean_luminance": e2e_lum, "how": e2e_how},
             "roofline": dominant_kernel_roofline(ctx, kstats, counters),
             "roofline_sample": sample_roofline(ctx, value / world, "cornell_boxes_camera_paths", kstats, counters),
+            "roofline_traversal": traversal_roofline(ctx, kstats),
             "kernels": kernel_table(api, kstats),
             "clocks": clocks,
             "verify": verify,

@@ -489,6 +489,11 @@ void Pt_GetKernelStats(PtKernelStats* out);
 int32_t Pt_IntersectCountN(const PtScene* scene, const pim_float4* ro, const pim_float4* rd, float tNear,
                            int64_t n, uint64_t* nodeFetches, uint64_t* triFetches);
 
+/* Read bandwidth of the L2 cache as this library's kernels see it: `reps` read-only sweeps (128-bit loads) over a
+ * buffer of `bytes` that was just brought into L2; GB/s, negative on error. bench.py uses it as the denominator of
+ * the L2 roofline of the configs whose BVH never leaves the caches. */
+float Pt_MeasureL2ReadGBs(int64_t bytes, int32_t reps);
+
 /* Tuning switches, also readable from the environment at PtSys_Init (PIMPT_PERSISTENT, PIMPT_FINISH):
  *   "persistent"  -1 choose the traversal kernels by BVH size (default), 0 one thread per ray, 1 persistent
  *                 warps with postponed leaves

@@ -145,7 +145,7 @@ EXPORTS = [
     "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
     "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap", "LmPack_EmbedDesc",
     "LmPack_BakeDesc_Device", "PtMediaParams_Default", "PtScene_SetMedia",
-    "Pt_RepackRome", "PtSys_SetLmPack", "LmPack_Bake", "Pt_PointQueryN", "Pt_SetOption", "PtSys_SetDevices", "PtSys_GetDevices", "LmPack_ChartMasksDesc", "LmPack_AtlasDesc",
+    "Pt_RepackRome", "PtSys_SetLmPack", "LmPack_Bake", "Pt_PointQueryN", "Pt_SetOption", "PtSys_SetDevices", "PtSys_GetDevices", "LmPack_ChartMasksDesc", "LmPack_AtlasDesc", "Pt_MeasureL2ReadGBs",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -231,6 +231,8 @@ def load():
     L.LmPack_ChartMasksDesc.restype = C.c_int32
     L.LmPack_AtlasDesc.argtypes = [vp, vp, C.c_int32, vp, vp, C.c_int32, vp, vp, C.POINTER(C.c_int32)]
     L.LmPack_AtlasDesc.restype = C.c_int32
+    L.Pt_MeasureL2ReadGBs.argtypes = [C.c_int64, C.c_int32]
+    L.Pt_MeasureL2ReadGBs.restype = C.c_float
     L.PtSys_SetDevices.argtypes = [C.c_int32]
     L.PtSys_SetDevices.restype = C.c_int32
     L.PtSys_GetDevices.restype = C.c_int32

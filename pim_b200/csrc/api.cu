@@ -1939,6 +1939,22 @@ int32_t Pt_IntersectCountN(const PtScene* scene, const pim_float4* ro, const pim
 }
 float Pt_LastKernelMs(void) { return g_lastKernelMs; }
 
+float Pt_MeasureL2ReadGBs(int64_t bytes, int32_t reps)
+{
+    if (!ensureInit() || bytes < 4096 || reps < 1) return -1.0f;
+    char* buf = nullptr; unsigned* sink = nullptr;
+    Lease lease;
+    if (!lease.dev(buf, (size_t)bytes).dev(sink, 64).commit()) return -1.0f;
+    cudaStream_t st = nullptr;
+    bool ok = PT_CUDA(cudaMemsetAsync(buf, 1, (size_t)bytes, st)) && launchL2Read(buf, (size_t)bytes, 2, sink, st);    // warm: the buffer is in L2
+    KernelTimer timer(lease, st);
+    ok = ok && launchL2Read(buf, (size_t)bytes, reps, sink, st);
+    timer.stop();
+    ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
+    if (!ok || g_lastKernelMs <= 0.0f) return -1.0f;
+    return (float)((double)bytes * reps / (g_lastKernelMs * 1e-3) / 1e9);
+}
+
 int32_t Pt_SetOption(const char* name, int32_t value)
 {
     if (!name) return -1;

@@ -257,6 +257,8 @@ bool launchAccumulate(float* dDst, const float* dSrc, int64_t n, cudaStream_t st
 bool launchU32Sub(uint32_t* dDst, const uint32_t* dA, int64_t n, cudaStream_t stream);
 bool launchU32Add(uint32_t* dDst, const uint32_t* dSrc, int64_t n, cudaStream_t stream);
 
+bool launchL2Read(const void* dBuf, size_t bytes, int reps, unsigned* dSink, cudaStream_t stream);
+
 // image helpers
 bool launchResolve(float* dImage, const float* dSum, int64_t n, float prevCount, float addCount, cudaStream_t stream);
 bool launchLerp(float* dImage, const float* dSample, int64_t n, float weight, cudaStream_t stream);

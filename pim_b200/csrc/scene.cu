@@ -671,6 +671,30 @@ bool launchU32Add(uint32_t* dDst, const uint32_t* dSrc, int64_t n, cudaStream_t 
     return PT_CUDA(cudaGetLastError());
 }
 
+// read-only sweep of a buffer that fits in L2, for the L2 roofline of the cache-resident configs: every thread
+// streams 16-byte loads through the whole buffer `reps` times; the xor keeps the loads alive
+__global__ void __launch_bounds__(256) k_l2Read(const uint4* __restrict__ buf, size_t n16, int reps, unsigned* sink)
+{
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    unsigned acc = 0;
+    for (int r = 0; r < reps; ++r)
+    {
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride)
+        {
+            uint4 v;
+            asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(buf + i));
+            acc ^= v.x ^ v.y ^ v.z ^ v.w;
+        }
+    }
+    if (acc == 0x12345678u) *sink = acc;
+}
+bool launchL2Read(const void* dBuf, size_t bytes, int reps, unsigned* dSink, cudaStream_t stream)
+{
+    k_l2Read<<<kSmCount * 8, 256, 0, stream>>>((const uint4*)dBuf, bytes / 16, reps, dSink);
+    g_counters.kernelLaunches++;
+    return PT_CUDA(cudaGetLastError());
+}
+
 bool launchResolve(float* dImage, const float* dSum, int64_t n, float prevCount, float addCount, cudaStream_t stream)
 {
     if (n <= 0) return true;

@@ -85,6 +85,42 @@ def test_c1_cornell_320x180_64spp(api, lut, oracle):
     assert abs(oracle.stddev(got) - sds.mean()) <= 1.5 * (sds.max() - sds.min()), (oracle.stddev(got), sds)
 
 
+def test_c1_cornell_320x180_1024spp_converged(api, lut, oracle):
+    """The same frame at 1024 samples per pixel (SURVEY.md 8(c) golden-image list): two oracle seeds of 1024 frames
+    give the noise floor at that depth, the GPU image (Pt_TraceSpp, 16 calls of 64 spp) has to be as close to each
+    of them as they are to each other (1.5x), in per-channel RMSE and in mean luminance."""
+    W, H, spp = 320, 180, 1024
+    desc = scenes.cornell_box("boxes", brdf_lut=lut, seed=1)
+    ocam, odof = oracle.camera_lookat([-4, 0, 4], [0, -1, 0]), oracle.default_dof()
+    odof.autoFocus = 0
+    imgs = []
+    for seed in (1, 2):
+        oracle.set_seed(seed)
+        oracle.load_scene_desc(desc)
+        ref = oracle.Scene()
+        col = np.zeros((H, W, 3), np.float32); alb = col.copy(); nor = col.copy()
+        for p in range(spp):
+            ref.trace(col, alb, nor, 1.0 / (p + 1), ocam, odof, p)
+        ref.close()
+        imgs.append(col)
+    oracle.set_seed(1)
+    s = api.Scene(scenes.cornell_box("boxes", brdf_lut=lut, seed=5))
+    cam, dof = api.make_camera([-4, 0, 4], [0, -1, 0]), api.default_dof(auto_focus=False)
+    tr = api.Trace(W, H)
+    for begin in range(0, spp, 64):
+        tr.trace_spp(s, cam, dof, begin, 64)
+    got = tr.image("color").copy()
+    tr.close(); s.close()
+
+    def rmse(a, b):
+        return np.sqrt(np.mean((np.minimum(a, 4.0) - np.minimum(b, 4.0)) ** 2, axis=(0, 1)))
+    floor = rmse(imgs[0], imgs[1])
+    for ref_img in imgs:
+        assert (rmse(got, ref_img) <= 1.5 * floor).all(), (rmse(got, ref_img), floor)
+    m0, m1 = imgs[0].mean(), imgs[1].mean()
+    assert abs(got.mean() - 0.5 * (m0 + m1)) <= 1.5 * abs(m0 - m1) + 2e-3 * m0, (got.mean(), m0, m1)
+
+
 # --------------------------------------------------------------------------- C4
 
 @pytest.fixture(scope="module")
