@@ -364,6 +364,12 @@ __global__ void __launch_bounds__(128) k_emissionPdf(DScene S, int triCount, uin
     if (mat.flags & MatFlag_Sky) { pdfs[tri] = 1.0f; return; }
     if (mat.rome < 0) { pdfs[tri] = 0.0f; return; }
     const DTexture tex = S.textures[mat.rome];
+    if (tex.w == 1 && tex.h == 1)
+    {
+        // a flat texture: all 1000 probes of EmissionPdf (path_tracer.c:784-822) read the same texel
+        pdfs[tri] = (tex.texels[0] >> 24) ? 1.0f : 0.0f;
+        return;
+    }
     const V2 UA = S.uvs[iVert], UB = S.uvs[iVert + 1], UC = S.uvs[iVert + 2];
     Rng rng = seed_prng((uint32_t)tri, 0u, seed, Salt_Emission);
     const int attempts = 1000;

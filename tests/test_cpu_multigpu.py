@@ -68,3 +68,40 @@ def test_texel_ranges_partition():
                 assert b == pos
                 pos += n
             assert pos == count
+
+
+def _texel_worker(rank, world, port, covered, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # bench.py's C4 sharding: contiguous ranges of the covered texels, padded slabs gathered on rank 0
+    begin, count = multigpu.texel_range(covered, rank, world)
+    m = (covered + world - 1) // world
+    slab = torch.zeros((m, 2), dtype=torch.float64)
+    slab[:count, 0] = torch.arange(begin, begin + count, dtype=torch.float64)        # "baked" value = the texel's own index
+    slab[:count, 1] = 1.0
+    parts = [torch.zeros_like(slab) for _ in range(world)] if rank == 0 else None
+    dist.gather(slab, parts, dst=0)
+    if rank == 0:
+        page = torch.full((covered,), -1.0, dtype=torch.float64)
+        for r, part in enumerate(parts):
+            b, c = multigpu.texel_range(covered, r, world)
+            page[b:b + c] = part[:c, 0]
+            assert float(part[:c, 1].sum()) == c
+        out.put(page.numpy())
+    dist.destroy_process_group()
+
+
+def test_two_rank_texel_ranges_gather_to_one_page():
+    world, covered = 2, 54437
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_texel_worker, args=(r, world, port, covered, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    page = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert np.array_equal(page, np.arange(covered, dtype=np.float64))      # every covered texel exactly once, in place

@@ -142,3 +142,72 @@ def test_oracle_cubemap_convolve_of_a_constant_is_the_constant(oracle):
     assert np.allclose(conv[:, :n - 1, 3], 1.0, atol=1e-5)
     # the 1x1 mip: Cubemap_CalcDir divides by size - 1 = 0, the direction is NaN, no sample passes NoL > 0
     assert (conv[:, n - 1] == 0).all()
+
+
+def test_fp64_grid_ground_truth_equals_all_triangles_loop():
+    """oracle/cpu_bvh.c f64grid_*: the uniform-grid fp64 ground truth the full-size GPU tests use must give, ray for
+    ray, what the all-triangles fp64 loop gives (hit flag incl. ties, primitive, t bit for bit), for long rays and for
+    occlusion-length rays; and the CPU BVH's occlusion query must agree with both."""
+    import truth
+    from pim_b200 import scenes
+    desc = scenes.random_soup(100_000, seed=5, extent=20.0)
+    verts = desc.entities[0].positions
+    grid = truth.Grid(verts, 1.0)
+    bvh = truth.CpuBvh(verts)
+    for occlusion in (False, True):
+        ro, rd = scenes.random_rays(1500, seed=6, extent=20.0, occlusion=occlusion)
+        bh, bf = truth.brute(verts, ro, rd)
+        gh, gf = grid.intersect(ro, rd)
+        assert np.array_equal(bf, gf) and np.array_equal(bh["prim"], gh["prim"]) and np.array_equal(bh["t"], gh["t"])
+        assert 0.05 < (bf != 0).mean() < 0.95
+        if occlusion:
+            assert np.array_equal(bvh.occluded(ro, rd).astype(bool), bf != 0)
+        else:
+            prim, nodes, tris = bvh.intersect(ro, rd)
+            assert ((prim == bh["prim"]) | (bf == 2)).all() and nodes > 0 and tris > 0
+    grid.close(); bvh.close()
+
+
+def test_lm_pack_capture_is_repeatable(oracle):
+    """the packer's recorded intermediate state (one task thread, the reference's chunking) is the same on every run:
+    what makes it usable as the expected value of the device's chart masks and atlas placement"""
+    from pim_b200 import scenes
+    desc = scenes.cornell_box("boxes", brdf_lut=np.zeros((4, 4, 2), np.float32), seed=1)
+    runs = []
+    for _ in range(2):
+        oracle.set_seed(1)
+        oracle.load_scene_desc(desc)
+        charts, atlases = oracle.lm_pack_capture(256, 8.0, 0.1, 15.0)
+        runs.append((charts, atlases))
+    (a, na), (b, nb) = runs
+    assert na == nb and len(a) == len(b) and len(a) >= 20
+    for x, y in zip(a, b):
+        assert np.array_equal(x["tri_after"], y["tri_after"]) and np.array_equal(x["mask"], y["mask"])
+        assert x["atlas"] == y["atlas"] and x["translation"] == y["translation"] and x["sorted_index"] == y["sorted_index"]
+    # every chart sits at (2, 2) after ChartMaskFn and got a place
+    assert all(abs(c["tri_after"].reshape(-1, 2).min(axis=0) - 2.0).max() < 1e-3 for c in a)
+    assert all(c["atlas"] >= 0 for c in a) and max(c["atlas"] for c in a) == 1
+
+
+def test_reference_chunking_gives_the_same_estimate(oracle):
+    """task mode 1 (threading/task.c's chunks, one random stream per thread: the timing arm) renders the same
+    estimator as task mode 0 (one seeded stream per pixel: the parity arm): equal mean luminance within noise"""
+    from pim_b200 import scenes
+    desc = scenes.cornell_box("boxes", brdf_lut=oracle.bake_brdf_lut(128, 256), seed=1)
+    cam, dof = oracle.camera_lookat([-4, 0, 4], [0, -1, 0]), oracle.default_dof()
+    dof.autoFocus = 0
+    means = []
+    try:
+        for mode in (0, 1):
+            oracle.set_task_mode(mode)
+            oracle.set_seed(1)
+            oracle.load_scene_desc(desc)
+            ref = oracle.Scene()
+            col = np.zeros((90, 160, 3), np.float32); alb = col.copy(); nor = col.copy()
+            for p in range(16):
+                ref.trace(col, alb, nor, 1.0 / (p + 1), cam, dof, p)
+            ref.close()
+            means.append(float(np.minimum(col, 4.0).mean()))
+    finally:
+        oracle.set_task_mode(0)
+    assert abs(means[0] - means[1]) <= 0.05 * means[0], means
