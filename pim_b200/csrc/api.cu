@@ -651,6 +651,30 @@ static bool liveSnapshot(PtScene* s, cudaStream_t st)
     return PT_CUDA(cudaMemcpyAsync(s->liveBase, s->view.distLive, 4 * words, cudaMemcpyDeviceToDevice, st));
 }
 
+// Before a call is shared out, every replica takes the primary's light grid as it is now (pdf, cdf, counters, sums,
+// lengths): the primary has just relearned (PtScene_Update), and calls that run on the primary alone (Pt_RayGen,
+// cubemap bakes, ray batches that feed LightOnHit) have moved its counters since the last shared call.
+static bool lightGridToReplicas(PtScene* scene, cudaStream_t st)
+{
+    const size_t cells = (size_t)scene->gridCells, E = (size_t)scene->view.emissiveCount;
+    if (cells == 0 || scene->replicas.empty()) return true;
+    bool ok = true;
+    const DScene& P = scene->view;
+    for (PtScene_s* r : scene->replicas)
+    {
+        const DScene& R = r->view;
+        if (E > 0)
+        {
+            ok = ok && PT_CUDA(cudaMemcpyPeerAsync(R.distPdf, r->device, P.distPdf, scene->device, 4 * cells * E, st)) &&
+                 PT_CUDA(cudaMemcpyPeerAsync(R.distCdf, r->device, P.distCdf, scene->device, 4 * cells * (E + 1), st)) &&
+                 PT_CUDA(cudaMemcpyPeerAsync(R.distLive, r->device, P.distLive, scene->device, 4 * cells * E, st));
+        }
+        ok = ok && PT_CUDA(cudaMemcpyPeerAsync(R.distLength, r->device, P.distLength, scene->device, 4 * cells, st)) &&
+             PT_CUDA(cudaMemcpyPeerAsync(R.distSum, r->device, P.distSum, scene->device, 4 * cells, st));
+    }
+    return PT_CUDA(cudaStreamSynchronize(st)) && ok;
+}
+
 static bool liveMerge(PtScene* scene, cudaStream_t st)
 {
     const size_t words = (size_t)scene->gridCells * (size_t)scene->view.emissiveCount;
@@ -701,7 +725,8 @@ static bool traceSppDevice(PtScene* scene, const Camera* camera, PtDofInfo* dof,
     }
     const size_t n3 = (size_t)pixels * 3;
     const int images = 1 + (dAlbedo ? 1 : 0) + (dNormal ? 1 : 0);
-    bool ok = forEachDevice(D, [&](int k) -> bool
+    bool ok = lightGridToReplicas(scene, st);
+    ok = ok && forEachDevice(D, [&](int k) -> bool
     {
         if (k == 0) return liveSnapshot(scene, st) && traceShare(scene, camera, dof, w, h, share[0], dColor, dAlbedo, dNormal, st);
         PtScene_s* r = scene->replicas[(size_t)k - 1];
@@ -719,7 +744,7 @@ static bool traceSppDevice(PtScene* scene, const Camera* camera, PtDofInfo* dof,
         }
         const TraceShare& sh = share[(size_t)k];
         const size_t off = (size_t)sh.pixelBegin * 3, cnt = (size_t)sh.pixelCount * 3;
-        bool okr = launchDistUpdate(r->view, rs) && liveSnapshot(r, rs);
+        bool okr = liveSnapshot(r, rs);
         for (int i = 0; okr && i < images; ++i) okr = PT_CUDA(cudaMemsetAsync(r->partial[i] + off, 0, 4 * cnt, rs));
         okr = okr && traceShare(r, camera, dof, w, h, sh, r->partial[0], dAlbedo ? r->partial[1] : nullptr, dNormal ? r->partial[2] : nullptr, rs);
         const size_t words = (size_t)r->gridCells * (size_t)r->view.emissiveCount;
@@ -1282,15 +1307,16 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
     if (!lease.commit()) return -1;
     bool ok = sceneRefresh(scene, scene->stream);       // LmPack_Bake -> PtScene_Update (lightmap.c:1209)
     const int D = 1 + (int)scene->replicas.size();
-    // the replicas relearn first (the primary did in sceneRefresh), then every device notes its light-learning
-    // counters so that what the bake adds on each can be merged afterwards (liveMerge)
+    // the replicas take the primary's light grid (it relearned in sceneRefresh), then every device notes its
+    // light-learning counters so that what the bake adds on each can be merged afterwards (liveMerge)
     if (D > 1)
     {
+        ok = ok && lightGridToReplicas(scene, scene->stream);
         ok = ok && forEachDevice(D, [&](int k) -> bool
         {
             PtScene_s* s = k == 0 ? scene : scene->replicas[(size_t)k - 1];
             DeviceGuard guard(s->device);
-            bool okd = (k == 0 || launchDistUpdate(s->view, s->stream)) && liveSnapshot(s, s->stream);
+            const bool okd = liveSnapshot(s, s->stream);
             return PT_CUDA(cudaStreamSynchronize(s->stream)) && okd;
         });
     }
