@@ -417,6 +417,23 @@ __device__ void distBake(const DScene& S, int cell)      // Dist1D_Bake, dist1d.
     }
 }
 
+// Grid_Position (grid.h:24-39) and SampleBaryCoord (sampling.h:120-128) with IEEE division / square root and
+// unfused products, as the reference's CPU build rounds them: the light-grid rays start and end where the
+// reference's do, to the bit (the library's --use_fast_math forms differ by an ulp, which flips grazing rays)
+__device__ __forceinline__ V3 gridPositionR(const Grid& g, int index)
+{
+    const float metersPerCell = divr(1.0f, g.cellsPerMeter);
+    const int ix = index % g.sx, iy = (index / g.sx) % g.sy, iz = index / (g.sx * g.sy);
+    return v3(addr(g.lo.x, mulr((float)ix + 0.5f, metersPerCell)), addr(g.lo.y, mulr((float)iy + 0.5f, metersPerCell)),
+              addr(g.lo.z, mulr((float)iz + 0.5f, metersPerCell)));
+}
+__device__ __forceinline__ V3 sampleBaryCoordR(V2 Xi)
+{
+    const float r1 = sqrtr(f1_max(Xi.x, kEpsilonSq)), r2 = Xi.y;
+    const float u = mulr(r1, subr(1.0f, r2)), v = mulr(r2, r1);
+    return v3(subr(1.0f, addr(u, v)), u, v);
+}
+
 // SetupLightGridFn (path_tracer.c:891-990) in three kernels. The reference walks a cell's emissive triangles in
 // order with ONE random stream per cell (a hash chain: no skipping ahead), which is why a thread per cell was the
 // first form — and the slow one: the 1 M-triangle interior has 1875 cells x 648 emissives x 16 rays, and 15 CTAs
@@ -473,7 +490,7 @@ __global__ void __launch_bounds__(kTravThreads) k_lightGridPairs(DScene S, float
     const int cell = (int)(pair / E), iEmit = (int)(pair % E);
     if (!keep[cell]) return;
     const float radius = metersPerCell * 0.666f;
-    const V3 position = Grid_Position(S.grid, cell);
+    const V3 position = gridPositionR(S.grid, cell);
     Rng rng = states[pair];
     const int iVert = S.emitToVert[iEmit];
     const V3 A = ld3(S.positions, iVert), B = ld3(S.positions, iVert + 1), C = ld3(S.positions, iVert + 2);
@@ -486,13 +503,15 @@ __global__ void __launch_bounds__(kTravThreads) k_lightGridPairs(DScene S, float
         V3 t = v3(mulr(addr(-1.5f, mulr(r4.x, 3.0f)), radius), mulr(addr(-1.5f, mulr(r4.y, 3.0f)), radius),
                   mulr(addr(-1.5f, mulr(r4.z, 3.0f)), radius));
         V3 ro = v3(addr(position.x, t.x), addr(position.y, t.y), addr(position.z, t.z));
-        V3 wuv = SampleBaryCoord(rng_f2(rng));
+        V3 wuv = sampleBaryCoordR(rng_f2(rng));
         V3 at = v3(addr(addr(mulr(A.x, wuv.x), mulr(B.x, wuv.y)), mulr(C.x, wuv.z)),
                    addr(addr(mulr(A.y, wuv.x), mulr(B.y, wuv.y)), mulr(C.y, wuv.z)),
                    addr(addr(mulr(A.z, wuv.x), mulr(B.z, wuv.y)), mulr(C.z, wuv.z)));
         V3 rd = v3(subr(at.x, ro.x), subr(at.y, ro.y), subr(at.z, ro.z));
         float dist = sqrtr(dotr(rd, rd));
-        rd = v3(divr(rd.x, dist), divr(rd.y, dist), divr(rd.z, dist));
+        // f4_divvs under the reference's -ffast-math: one reciprocal, three products
+        const float rcpDist = divr(1.0f, dist);
+        rd = v3(mulr(rd.x, rcpDist), mulr(rd.y, rcpDist), mulr(rd.z, rcpDist));
         float tFar = dist - 0.01f * kMilli;
         bool visible = false;
         if (tFar > 0.0f)

@@ -88,14 +88,18 @@ def test_light_grid_matches_golden(boxes):
             pdf[c] = p
             assert abs(cdf[-1] - 1.0) < 1e-5 and (np.diff(cdf) >= 0).all()
     assert (lens == g["lens"]).all()
-    # One of a cell's 16-trial visibility counts may flip when a ray grazes an edge (the ray
-    # setup rounds differently under fma contraction); a flip rescales that cell's whole pdf.
+    # The rays are the reference's to the bit (same draws, IEEE-rounded set-up); what can differ is the any-hit decision
+    # of a ray that grazes a silhouette edge, where the two BVHs' box tests (each with its own rounding) decide
+    # whether the edge's triangle is tested at all: the exact-edge ties north_star excepts. Measured: 24 of the 65 856
+    # rays (0.04 %), never two in one entry. A flip rescales its cell's whole pdf, so count entries in units of trials.
     same_cell = (np.abs(pdf - g["pdf"]) <= 1e-5).all(axis=1)
-    assert same_cell.mean() >= 0.9, same_cell.mean()
+    assert same_cell.mean() >= 0.93, same_cell.mean()
     raw_g = g["pdf"] / np.maximum(g["pdf"].max(axis=1, keepdims=True), 1e-20)
     raw = pdf / np.maximum(pdf.max(axis=1, keepdims=True), 1e-20)
-    assert np.abs(raw - raw_g).max() <= 0.26          # at most a couple of the 16 trials of an entry
-    assert np.abs(pdf - g["pdf"]).mean() <= 5e-3
+    trials = np.abs(raw - raw_g) * 16.0                 # visibility counts are k / 16 of the cell's largest
+    assert (trials > 0.5).mean() <= 0.01, (trials > 0.5).mean()
+    assert np.abs(raw - raw_g).max() <= 0.26            # at most a couple of the 16 trials of an entry
+    assert np.abs(pdf - g["pdf"]).mean() <= 3e-3
 
 
 def test_brdf_lut_device_bake(api):
