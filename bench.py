@@ -417,6 +417,7 @@ def run_ours(args, rank, world, local_rank):
     n3 = WIDTH * HEIGHT * 3
     sums = ctx.images(WIDTH, HEIGHT)                 # this step's samples of this rank
     total = ctx.images(WIDTH, HEIGHT) if rank == 0 else None     # rank 0: everything rendered so far, all ranks
+    counters_sync = mg.LightCounterSync(scene, ctx.dev, ctx.stream)   # N > 1: all replicas learn from all ranks' paths
 
     def step(i):
         begin, _ = mg.sample_range(i, rank, world, spp)
@@ -425,7 +426,9 @@ def run_ours(args, rank, world, local_rank):
             return
         for t in sums:
             t.zero_()
+        counters_sync.before()
         ctx.trace(scene, cam, dof, WIDTH, HEIGHT, begin, spp, sums)
+        counters_sync.after()                        # all-reduce of the light-learning counters the call added (16 KB)
         mg.reduce_sums(sums, dst=0)                  # per-step sums, not running totals
         if rank == 0:
             for a, b in zip(total, sums):
@@ -499,7 +502,8 @@ def run_ours(args, rank, world, local_rank):
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "spp_per_step": spp, "width": WIDTH, "height": HEIGHT,
-                       "sharding": "sample index per rank, scene replicated, NCCL reduce of the per-step sums to rank 0",
+                       "sharding": "sample index per rank, scene replicated, NCCL reduce of the per-step sums to rank 0, "
+                                   "all-reduce of the light-learning counters each step adds",
                        "l2": "256 MB buffer written between timed steps (L2 flush)",
                        "path_pool_slots": args.pool or (1 << 23)},
             "mrays_per_s": value * total_rays / paths,      # all ranks, from rank 0's rays per sample

@@ -457,6 +457,12 @@ int32_t PtScene_Download(const PtScene* scene, pim_float4* positions, pim_float4
 /* light-grid cell: returns the cell's distribution length (0 = none) */
 int32_t PtScene_GetDist(const PtScene* scene, int32_t cell, float* pdf, float* cdf, uint32_t* live);
 int32_t PtScene_SetDist(PtScene* scene, int32_t cell, int32_t length, const float* pdf);
+/* The light-learning counters of the whole grid (Dist1D.live of every cell, path_tracer.c:1709-1733: cells x emissives
+ * uint32, cell-major) copied device to device on `stream`: toScene = 0 reads them into dCounters, 1 writes them back.
+ * Returns the number of counters (also with dCounters = NULL), -1 on error. One process per GPU uses it to sum what
+ * every rank's call added (an all-reduce of the differences) so that all replicas relearn from the same counts, as
+ * SURVEY.md 8(e) describes; the in-process multi-GPU mode does the same inside the library. */
+int64_t PtScene_LightCounters(PtScene* scene, void* dCounters, int32_t toScene, void* stream);
 /* BRDF LUT actually in use (lutWidth*lutHeight float2) */
 int32_t PtScene_GetBrdfLut(const PtScene* scene, float* texels, int32_t* width, int32_t* height);
 

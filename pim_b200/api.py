@@ -145,7 +145,7 @@ EXPORTS = [
     "Cubemap_New", "Cubemap_Del", "Cubemap_Bake", "Cubemap_Convolve", "Cubemap_BakePass", "Cubemap_ConvolvePass",
     "AmbCube_Bake", "Pt_BakeSky", "Pt_Tonemap", "LmPack_EmbedDesc",
     "LmPack_BakeDesc_Device", "PtMediaParams_Default", "PtScene_SetMedia",
-    "Pt_RepackRome", "PtSys_SetLmPack", "LmPack_Bake", "Pt_PointQueryN", "Pt_SetOption", "PtSys_SetDevices", "PtSys_GetDevices", "LmPack_ChartMasksDesc", "LmPack_AtlasDesc", "Pt_MeasureL2ReadGBs",
+    "Pt_RepackRome", "PtSys_SetLmPack", "LmPack_Bake", "Pt_PointQueryN", "Pt_SetOption", "PtSys_SetDevices", "PtSys_GetDevices", "LmPack_ChartMasksDesc", "LmPack_AtlasDesc", "Pt_MeasureL2ReadGBs", "PtScene_LightCounters",
 ]
 
 NOALLOC_MAX_PATHS = 32768
@@ -231,6 +231,8 @@ def load():
     L.LmPack_ChartMasksDesc.restype = C.c_int32
     L.LmPack_AtlasDesc.argtypes = [vp, vp, C.c_int32, vp, vp, C.c_int32, vp, vp, C.POINTER(C.c_int32)]
     L.LmPack_AtlasDesc.restype = C.c_int32
+    L.PtScene_LightCounters.argtypes = [vp, vp, C.c_int32, vp]
+    L.PtScene_LightCounters.restype = C.c_int64
     L.Pt_MeasureL2ReadGBs.argtypes = [C.c_int64, C.c_int32]
     L.Pt_MeasureL2ReadGBs.restype = C.c_float
     L.PtSys_SetDevices.argtypes = [C.c_int32]
@@ -458,6 +460,13 @@ class Scene:
     def set_dist(self, cell, pdf):
         pdf = np.ascontiguousarray(pdf, np.float32)
         _check(load().PtScene_SetDist(self.h, cell, len(pdf), pdf.ctypes.data), "PtScene_SetDist")
+
+    def light_counters(self, d_ptr=None, to_scene=False, stream=None):
+        """PtScene_LightCounters: number of counters; with a device pointer also copies them out of / into the scene"""
+        n = load().PtScene_LightCounters(self.h, d_ptr, 1 if to_scene else 0, stream)
+        if n < 0:
+            raise PtError("PtScene_LightCounters failed: " + last_error())
+        return int(n)
 
     def brdf_lut(self):
         w, h = C.c_int32(), C.c_int32()

@@ -1915,6 +1915,17 @@ int32_t PtScene_SetDist(PtScene* scene, int32_t cell, int32_t length, const floa
     return ok ? 0 : -1;
 }
 
+int64_t PtScene_LightCounters(PtScene* scene, void* dCounters, int32_t toScene, void* stream)
+{
+    if (!scene) { setError("PtScene_LightCounters: null scene"); return -1; }
+    const size_t words = (size_t)scene->gridCells * (size_t)scene->view.emissiveCount;
+    if (!dCounters || words == 0) return (int64_t)words;
+    cudaStream_t st = stream ? (cudaStream_t)stream : scene->stream;
+    const bool ok = toScene ? PT_CUDA(cudaMemcpyAsync(scene->view.distLive, dCounters, 4 * words, cudaMemcpyDeviceToDevice, st))
+                            : PT_CUDA(cudaMemcpyAsync(dCounters, scene->view.distLive, 4 * words, cudaMemcpyDeviceToDevice, st));
+    return ok ? (int64_t)words : -1;
+}
+
 int32_t PtScene_GetBrdfLut(const PtScene* scene, float* texels, int32_t* width, int32_t* height)
 {
     if (!scene) return -1;

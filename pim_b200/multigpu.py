@@ -40,3 +40,31 @@ def max_over_ranks(value, device):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
     return float(value)
+
+
+class LightCounterSync:
+    """Keeps the adaptive light grid of every rank's replica learning from ALL ranks' paths: note the
+    counters before a call, and after it all-reduce what the call added and write base + sum back. Integer adds, so the
+    replicas hold exactly the counters one device tracing every rank's samples would hold."""
+
+    def __init__(self, scene, device, stream=None):
+        self.scene, self.stream = scene, stream
+        n = scene.light_counters()
+        self.base = torch.zeros(max(n, 1), dtype=torch.int32, device=device)
+        self.live = torch.zeros_like(self.base)
+        self.n = n
+
+    def _s(self):
+        return self.stream.cuda_stream if self.stream is not None else None
+
+    def before(self):
+        if self.n:
+            self.scene.light_counters(self.base.data_ptr(), False, self._s())
+
+    def after(self):
+        if self.n and dist.is_initialized() and dist.get_world_size() > 1:
+            self.scene.light_counters(self.live.data_ptr(), False, self._s())
+            self.live -= self.base
+            dist.all_reduce(self.live, op=dist.ReduceOp.SUM)
+            self.live += self.base
+            self.scene.light_counters(self.live.data_ptr(), True, self._s())

@@ -179,3 +179,56 @@ def test_occluded_and_point_query_match_reference(api, oracle):
         assert np.abs(d_got[~none] - d_want[~none]).max() <= 1e-5, name
         assert 0.05 < none.mean() < 0.95 or name == "spheres"
         ref.close(); s.close()
+
+
+def test_light_counters_summed_over_two_replicas_equal_one_scene(api):
+    """PtScene_LightCounters, the hook one process per GPU uses to keep its replicas learning as one (SURVEY.md 8(e),
+    Dist1D.live path_tracer.c:1709-1733): two scenes stand in for two ranks, each renders its own sample indices from
+    the same light grid, and base + (what A added) + (what B added) equals, counter for counter, what ONE scene
+    rendering both ranges in a single call holds. Written back, both replicas carry exactly those counters."""
+    import torch
+    L = api.load()
+    dev = torch.device("cuda", 0)
+    w, h, spp = 192, 128, 4
+    cam = api.make_camera([-4.0, 0.0, 4.0], [0.0, -1.0, 0.0], 90.0)
+    dof = api.default_dof(auto_focus=False)
+
+    def scene():
+        return api.Scene(scenes.cornell_box("boxes", brdf_lut=parity.reference_lut(), seed=1))
+
+    def trace(s, begin, count):
+        img = [torch.zeros(w * h * 3, dtype=torch.float32, device=dev) for _ in range(3)]
+        assert L.Pt_TraceSpp_Device(s.h, C.byref(cam), C.byref(dof), w, h, begin, count,
+                                    img[0].data_ptr(), img[1].data_ptr(), img[2].data_ptr(), None) == 0, api.last_error()
+        torch.cuda.synchronize()
+        return img
+
+    def counters(s):
+        t = torch.zeros(s.light_counters(), dtype=torch.int32, device=dev)
+        assert s.light_counters(t.data_ptr(), False) == t.numel()
+        torch.cuda.synchronize()
+        return t
+
+    a, b, one = scene(), scene(), scene()
+    n = a.light_counters()
+    assert n == one.light_counters() and n > 0
+    base = counters(a)
+    assert torch.equal(base, counters(b)) and torch.equal(base, counters(one))
+    img_a = trace(a, 0, spp); img_b = trace(b, spp, spp); img_one = trace(one, 0, 2 * spp)
+    da, db = counters(a) - base, counters(b) - base
+    assert int(da.sum()) > 0 and int(db.sum()) > 0 and not torch.equal(da, db)
+    merged = base + da + db
+    assert torch.equal(merged, counters(one))
+    for s in (a, b):
+        assert s.light_counters(merged.data_ptr(), True) == n
+        assert torch.equal(counters(s), merged)
+    # the two halves are the one call's paths: same light grid during the call, disjoint sample indices
+    for k in range(3):
+        assert torch.allclose(img_a[k] + img_b[k], img_one[k], rtol=1e-5, atol=1e-5)
+    # and from here on the replicas pick lights exactly as the one scene does
+    nxt_a, nxt_one = trace(a, 2 * spp, spp), trace(one, 2 * spp, spp)
+    for k in range(3):
+        assert torch.allclose(nxt_a[k], nxt_one[k], rtol=1e-5, atol=1e-5)
+    assert torch.equal(counters(a), counters(one))
+    for s in (a, b, one):
+        s.close()
