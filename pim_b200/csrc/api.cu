@@ -7,6 +7,8 @@
 #include "../../include/pim_pt.h"
 #include "pt_device.h"
 #include "arena.h"
+#include "hostpool.h"
+#include "hostcopy.h"
 
 #include <atomic>
 #include <chrono>
@@ -363,7 +365,7 @@ static PtScene* sceneBuildOne(const PtSceneDesc* desc)
         uint32_t* d = nullptr;
         size_t n = (size_t)t.width * (size_t)t.height;
         ok = sceneAlloc(s, d, n);
-        ok = ok && PT_CUDA(cudaMemcpyAsync(d, t.texels, n * 4, cudaMemcpyHostToDevice, st));
+        ok = ok && copyIn(d, t.texels, n * 4, st);
         texTable[i].texels = d; texTable[i].w = t.width; texTable[i].h = t.height;
     }
     DTexture* dTex = nullptr;
@@ -411,9 +413,9 @@ static PtScene* sceneBuildOne(const PtSceneDesc* desc)
             if (done[e.positions]) continue;
             done[e.positions] = true;
             const size_t bytes = sizeof(F4) * (size_t)e.length;
-            ok = ok && PT_CUDA(cudaMemcpyAsync(dSrcPos + ents[i].srcOffset, e.positions, bytes, cudaMemcpyHostToDevice, st));
-            ok = ok && PT_CUDA(cudaMemcpyAsync(dSrcNrm + ents[i].srcOffset, e.normals, bytes, cudaMemcpyHostToDevice, st));
-            ok = ok && PT_CUDA(cudaMemcpyAsync(dSrcUv + ents[i].srcOffset, e.uvs, bytes, cudaMemcpyHostToDevice, st));
+            ok = ok && copyIn(dSrcPos + ents[i].srcOffset, e.positions, bytes, st);
+            ok = ok && copyIn(dSrcNrm + ents[i].srcOffset, e.normals, bytes, st);
+            ok = ok && copyIn(dSrcUv + ents[i].srcOffset, e.uvs, bytes, st);
         }
     }
     EntityUpload* dEnts = nullptr;
@@ -440,7 +442,7 @@ static PtScene* sceneBuildOne(const PtSceneDesc* desc)
     {
         float* dSky = nullptr;
         size_t n = (size_t)6 * desc->skySize * desc->skySize * 3;
-        ok = sceneAlloc(s, dSky, n) && PT_CUDA(cudaMemcpyAsync(dSky, desc->skyFaces, n * 4, cudaMemcpyHostToDevice, st));
+        ok = sceneAlloc(s, dSky, n) && copyIn(dSky, desc->skyFaces, n * 4, st);
         V.sky = dSky; V.skySize = desc->skySize;
     }
     {
@@ -868,13 +870,17 @@ void PtSys_Shutdown(void)
         for (int d = 0; d < count && d < kMaxDevices; ++d)
         {
             Arena& A = stagingArena(d);
+            CopyRing& R = copyRing(d);
             std::lock_guard<std::mutex> lock(A.mutex);
-            if (!A.dev && !A.host && !A.evA) continue;
+            std::lock_guard<std::mutex> ringLock(R.mutex);
+            if (!A.dev && !A.host && !A.evA && !R.slots[0]) continue;
             cudaSetDevice(d);
             A.release();
+            R.release();
         }
         cudaSetDevice(cur);
     }
+    HostPool::get().stop();
     g_sceneDesc.clear();
     g_lmPack.clear();
     g_initialised = false;
@@ -995,10 +1001,10 @@ int32_t Pt_IntersectN(const PtScene* scene, const pim_float4* ro, const pim_floa
     for (int64_t base = 0; base < n; base += chunk)
     {
         const int64_t c = std::min(chunk, n - base);
-        bool ok = PT_CUDA(cudaMemcpyAsync(dRo, ro + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
-                  PT_CUDA(cudaMemcpyAsync(dRd, rd + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+        bool ok = copyIn(dRo, ro + base, sizeof(F4) * c, st) &&
+                  copyIn(dRd, rd + base, sizeof(F4) * c, st) &&
                   launchIntersect(scene->view, dRo, dRd, tNear, dOut, c, scene->nextCursor(), st) &&
-                  PT_CUDA(cudaMemcpyAsync(hitsOut + base, dOut, sizeof(RayHitOut) * c, cudaMemcpyDeviceToHost, st)) &&
+                  copyOut(hitsOut + base, dOut, sizeof(RayHitOut) * c, st) &&
                   PT_CUDA(cudaStreamSynchronize(st));
         if (!ok) { cudaStreamSynchronize(st); return -1; }
     }
@@ -1019,10 +1025,10 @@ int32_t Pt_OccludedN(const PtScene* scene, const pim_float4* ro, const pim_float
     for (int64_t base = 0; base < n; base += chunk)
     {
         const int64_t c = std::min(chunk, n - base);
-        bool ok = PT_CUDA(cudaMemcpyAsync(dRo, ro + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
-                  PT_CUDA(cudaMemcpyAsync(dRd, rd + base, sizeof(F4) * c, cudaMemcpyHostToDevice, st)) &&
+        bool ok = copyIn(dRo, ro + base, sizeof(F4) * c, st) &&
+                  copyIn(dRd, rd + base, sizeof(F4) * c, st) &&
                   launchOccluded(scene->view, dRo, dRd, tNear, dOut, c, scene->nextCursor(), st) &&
-                  PT_CUDA(cudaMemcpyAsync(occludedOut + base, dOut, c, cudaMemcpyDeviceToHost, st)) &&
+                  copyOut(occludedOut + base, dOut, c, st) &&
                   PT_CUDA(cudaStreamSynchronize(st));
         if (!ok) { cudaStreamSynchronize(st); return -1; }
     }
@@ -1037,9 +1043,9 @@ int32_t Pt_PointQueryN(const PtScene* scene, const pim_float4* points, float* di
     Lease lease;
     if (!lease.dev(dPts, (size_t)n).dev(dDist, (size_t)n).commit()) return -1;
     cudaStream_t st = scene->stream;
-    bool ok = PT_CUDA(cudaMemcpyAsync(dPts, points, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
+    bool ok = copyIn(dPts, points, sizeof(F4) * n, st) &&
               launchPointQuery(scene->view, dPts, dDist, n, st) &&
-              PT_CUDA(cudaMemcpyAsync(distanceOut, dDist, sizeof(float) * n, cudaMemcpyDeviceToHost, st));
+              copyOut(distanceOut, dDist, sizeof(float) * n, st);
     ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
 }
@@ -1066,8 +1072,8 @@ int32_t Pt_TraceRayN(PtScene* scene, const pim_float4* ro, const pim_float4* rd,
     if (!small) lease.dev(c, 3 * (size_t)n).dev(a, 3 * (size_t)n).dev(nr, 3 * (size_t)n);
     if (!lease.commit()) return -1;
     cudaStream_t st = scene->stream;
-    bool ok = PT_CUDA(cudaMemcpyAsync(dRo, ro, sizeof(F4) * n, cudaMemcpyHostToDevice, st)) &&
-              PT_CUDA(cudaMemcpyAsync(dRd, rd, sizeof(F4) * n, cudaMemcpyHostToDevice, st));
+    bool ok = copyIn(dRo, ro, sizeof(F4) * n, st) &&
+              copyIn(dRd, rd, sizeof(F4) * n, st);
     if (ok && small)
     {
         ok = launchTraceRays(scene->view, dRo, dRd, n, pass, scene->config.seed, dOut, st);
@@ -1087,7 +1093,7 @@ int32_t Pt_TraceRayN(PtScene* scene, const pim_float4* ro, const pim_float4* rd,
         ok = ok && PT_CUDA(cudaMemcpy2DAsync(dOut + 3, 36, a, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
         ok = ok && PT_CUDA(cudaMemcpy2DAsync(dOut + 6, 36, nr, 12, 12, (size_t)n, cudaMemcpyDeviceToDevice, st));
     }
-    ok = ok && PT_CUDA(cudaMemcpyAsync(resultsOut, dOut, sizeof(float) * 9 * n, cudaMemcpyDeviceToHost, st));
+    ok = ok && copyOut(resultsOut, dOut, sizeof(float) * 9 * n, st);
     ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
 }
@@ -1233,22 +1239,20 @@ static bool bakePageDevice(PtScene* scene, const LightmapView& view, float texel
                                        scene->config.seed, st);
 }
 
-// device side of one device's share of a host page (LmPack_BakeDesc): the full-size page and the compacted texels
+// device side of one device's share of a host page (LmPack_BakeDesc): the full-size page and the covered texels' records
 struct LmDeviceBuffers
 {
     F4* probes = nullptr; float *pos = nullptr, *nrm = nullptr, *cnt = nullptr;                 // the full-size device page
-    int32_t* idx = nullptr; F4* cProbes = nullptr; float *cPos = nullptr, *cNrm = nullptr, *cCnt = nullptr;    // compacted
+    LmTexelRecord* records = nullptr;
 };
 static void lmLeaseDevice(Lease& lease, LmDeviceBuffers& b, size_t texels)
 {
-    lease.dev(b.probes, 5 * texels).dev(b.pos, 3 * texels).dev(b.nrm, 3 * texels).dev(b.cnt, texels)
-         .dev(b.idx, texels).dev(b.cProbes, 5 * texels).dev(b.cPos, 3 * texels).dev(b.cNrm, 3 * texels).dev(b.cCnt, texels);
+    lease.dev(b.probes, 5 * texels).dev(b.pos, 3 * texels).dev(b.nrm, 3 * texels).dev(b.cnt, texels).dev(b.records, texels);
 }
-// covered texels [j0, j0 + count) of the page's m covered ones: up, scatter, bake, gather, down (into the same host
-// staging arrays, which are lobe-major over all m)
-static bool lmBakeShare(PtScene_s* s, const LmDeviceBuffers& b, size_t n, int32_t texelBase, int32_t j0, int32_t count, int32_t m,
-                        const int32_t* hIdx, F4* hCProbes, const float* hCPos, const float* hCNrm, float* hCCnt,
-                        float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass)
+// covered texels [j0, j0 + count) of the page: up in one copy, scatter, bake, gather, down in one copy (into the
+// same page-locked records)
+static bool lmBakeShare(PtScene_s* s, const LmDeviceBuffers& b, size_t n, int32_t texelBase, int32_t j0, int32_t count,
+                        LmTexelRecord* hRecords, float texelsPerMeter, float timeSlice, int32_t spp, uint32_t pass)
 {
     if (count <= 0) return true;
     cudaStream_t st = s->stream;
@@ -1256,25 +1260,18 @@ static bool lmBakeShare(PtScene_s* s, const LmDeviceBuffers& b, size_t n, int32_
     for (int k = 0; k < 5; ++k) view.probes[k] = b.probes + (size_t)k * n;
     view.position = b.pos; view.normal = b.nrm; view.sampleCounts = b.cnt;
     view.texelCount = (int32_t)n; view.texelBase = texelBase;
-    const size_t c = (size_t)count;
+    const size_t bytes = sizeof(LmTexelRecord) * (size_t)count;
     bool ok = PT_CUDA(cudaMemsetAsync(b.cnt, 0, sizeof(float) * n, st)) &&
-              PT_CUDA(cudaMemcpyAsync(b.idx, hIdx + j0, sizeof(int32_t) * c, cudaMemcpyHostToDevice, st));
-    for (int k = 0; ok && k < 5; ++k)
-        ok = PT_CUDA(cudaMemcpyAsync(b.cProbes + (size_t)k * c, hCProbes + (size_t)k * m + j0, sizeof(F4) * c, cudaMemcpyHostToDevice, st));
-    ok = ok && PT_CUDA(cudaMemcpyAsync(b.cPos, hCPos + 3 * (size_t)j0, 12 * c, cudaMemcpyHostToDevice, st)) &&
-         PT_CUDA(cudaMemcpyAsync(b.cNrm, hCNrm + 3 * (size_t)j0, 12 * c, cudaMemcpyHostToDevice, st)) &&
-         PT_CUDA(cudaMemcpyAsync(b.cCnt, hCCnt + j0, 4 * c, cudaMemcpyHostToDevice, st)) &&
-         launchLightmapScatter(view, b.idx, count, b.cProbes, b.cPos, b.cNrm, b.cCnt, st);
+              PT_CUDA(cudaMemcpyAsync(b.records, hRecords + j0, bytes, cudaMemcpyHostToDevice, st)) &&
+              launchLightmapScatter(view, b.records, count, st);
     if (ok)
     {
         ok = s->config.bakeMode == PtBake_Sequential
                  ? launchLightmapBake(s->view, view, 1.0f / texelsPerMeter, timeSlice, spp, pass, s->config.seed, st)
                  : launchLightmapBakeWavefront(s->view, s->pool, view, 1.0f / texelsPerMeter, timeSlice, spp, pass, s->config.seed, st);
     }
-    ok = ok && launchLightmapGather(view, b.idx, count, b.cProbes, b.cCnt, st);
-    for (int k = 0; ok && k < 5; ++k)
-        ok = PT_CUDA(cudaMemcpyAsync(hCProbes + (size_t)k * m + j0, b.cProbes + (size_t)k * c, sizeof(F4) * c, cudaMemcpyDeviceToHost, st));
-    ok = ok && PT_CUDA(cudaMemcpyAsync(hCCnt + j0, b.cCnt, 4 * c, cudaMemcpyDeviceToHost, st));
+    ok = ok && launchLightmapGather(view, b.records, count, st) &&
+         PT_CUDA(cudaMemcpyAsync(hRecords + j0, b.records, bytes, cudaMemcpyDeviceToHost, st));
     return PT_CUDA(cudaStreamSynchronize(st)) && ok;
 }
 
@@ -1284,7 +1281,7 @@ static bool lmBakeShare(PtScene_s* s, const LmDeviceBuffers& b, size_t n, int32_
 // copy takes them to the device, a kernel scatters them into a full-size device page whose sampleCounts
 // were zeroed, the bake runs on that page exactly as it would on a resident one, and probes + counts of
 // the same texels come back the same way. A dense page costs the same bytes as a plain copy plus 4 B of
-// index per texel; the cornell page costs 5.9 MB each way instead of 113 MB.
+// index per texel; the cornell page costs 6.1 MB each way instead of 113 MB.
 int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCount, float texelsPerMeter, float timeSlice,
                         int32_t spp, uint32_t pass)
 {
@@ -1299,11 +1296,11 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
         maxTexels = std::max(maxTexels, (size_t)lm.size * (size_t)lm.size);
     }
     // worst case: every texel of the largest page is covered
-    int32_t* hIdx = nullptr; F4* hCProbes = nullptr; float *hCPos = nullptr, *hCNrm = nullptr, *hCCnt = nullptr;
+    LmTexelRecord* hRecords = nullptr; int32_t* hIdx = nullptr;
     LmDeviceBuffers primary;
     Lease lease;
     lmLeaseDevice(lease, primary, maxTexels);
-    lease.host(hIdx, maxTexels).host(hCProbes, 5 * maxTexels).host(hCPos, 3 * maxTexels).host(hCNrm, 3 * maxTexels).host(hCCnt, maxTexels);
+    lease.host(hRecords, maxTexels).host(hIdx, maxTexels);
     if (!lease.commit()) return -1;
     bool ok = sceneRefresh(scene, scene->stream);       // LmPack_Bake -> PtScene_Update (lightmap.c:1209)
     const int D = 1 + (int)scene->replicas.size();
@@ -1325,18 +1322,46 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
     {
         PtLightmapDesc& lm = lightmaps[i];
         const size_t n = (size_t)lm.size * (size_t)lm.size;
-        // covered texels, compacted on the host
-        int32_t m = 0;
-        for (size_t t = 0; t < n; ++t) if (lm.sampleCounts[t] != 0.0f) hIdx[m++] = (int32_t)t;
+        // covered texels, compacted on the host by the resident host threads in three steps: every thread counts
+        // the covered texels of its slice of the page; writes their indices (a dense int array) behind those of
+        // the slices before it; then packs an equal share of the covered texels' records (charts cluster in the
+        // atlas: packing by slice left nearly all of the records, 6 MB of cache lines, to one or two threads)
+        HostPool& hostPool = HostPool::get();
+        hostPool.start();
         const float* pos = (const float*)lm.position; const float* nrm = (const float*)lm.normal;
-        for (int32_t j = 0; j < m; ++j)
+        std::vector<int32_t> sliceCount((size_t)hostPool.workers() + 1, 0);
+        hostPool.run([&](int w, int workers)
         {
-            const size_t t = (size_t)hIdx[j];
-            for (int k = 0; k < 5; ++k) hCProbes[(size_t)k * m + j] = *(const F4*)&lm.probes[k][t];
-            hCPos[3 * j] = pos[3 * t]; hCPos[3 * j + 1] = pos[3 * t + 1]; hCPos[3 * j + 2] = pos[3 * t + 2];
-            hCNrm[3 * j] = nrm[3 * t]; hCNrm[3 * j + 1] = nrm[3 * t + 1]; hCNrm[3 * j + 2] = nrm[3 * t + 2];
-            hCCnt[j] = lm.sampleCounts[t];
-        }
+            size_t t0, t1; hostShare(n, w, workers, t0, t1);
+            int32_t c = 0;
+            for (size_t t = t0; t < t1; ++t) c += lm.sampleCounts[t] != 0.0f ? 1 : 0;
+            sliceCount[(size_t)w + 1] = c;
+        });
+        for (size_t w = 1; w < sliceCount.size(); ++w) sliceCount[w] += sliceCount[w - 1];
+        const int32_t m = sliceCount.back();
+        hostPool.run([&](int w, int workers)
+        {
+            size_t t0, t1; hostShare(n, w, workers, t0, t1);
+            int32_t j = sliceCount[(size_t)w];
+            for (size_t t = t0; t < t1; ++t) if (lm.sampleCounts[t] != 0.0f) hIdx[j++] = (int32_t)t;
+        });
+        hostPool.run([&](int w, int workers)
+        {
+            size_t j0, j1; hostShare((size_t)m, w, workers, j0, j1);
+            for (size_t j = j0; j < j1; ++j)
+            {
+                alignas(16) LmTexelRecord r;
+                const size_t t = (size_t)hIdx[j];
+                r.idx = hIdx[j];
+                for (int k = 0; k < 5; ++k) r.probes[k] = *(const F4*)&lm.probes[k][t];
+                r.pos[0] = pos[3 * t]; r.pos[1] = pos[3 * t + 1]; r.pos[2] = pos[3 * t + 2];
+                r.nrm[0] = nrm[3 * t]; r.nrm[1] = nrm[3 * t + 1]; r.nrm[2] = nrm[3 * t + 2];
+                r.cnt = lm.sampleCounts[t];
+                // non-temporal stores: the DMA engine reads the records next, and lines left dirty in eight cores'
+                // caches made that copy 6.6x slower (6.1 MB: 0.81 ms against 0.12 ms)
+                streamStore16(&hRecords[j], &r, sizeof(LmTexelRecord));
+            }
+        });
         if (m > 0)
         {
             // one contiguous range of the covered texels per device (the fit is sequential per texel, so texels,
@@ -1347,23 +1372,27 @@ int32_t LmPack_BakeDesc(PtScene* scene, PtLightmapDesc* lightmaps, int32_t lmCou
                 const int32_t base = m / D, rem = m % D;
                 const int32_t j0 = k * base + std::min(k, rem), cnt = base + (k < rem ? 1 : 0);
                 PtScene_s* s = k == 0 ? scene : scene->replicas[(size_t)k - 1];
-                if (k == 0) return lmBakeShare(s, primary, n, texelBase, j0, cnt, m, hIdx, hCProbes, hCPos, hCNrm, hCCnt,
-                                               texelsPerMeter, timeSlice, spp, pass);
+                if (k == 0) return lmBakeShare(s, primary, n, texelBase, j0, cnt, hRecords, texelsPerMeter, timeSlice, spp, pass);
                 DeviceGuard guard(s->device);
                 LmDeviceBuffers mine;
                 Lease own;                  // this device's arena
                 lmLeaseDevice(own, mine, std::max<size_t>(n, 1));
                 if (!own.commit()) return false;
-                return lmBakeShare(s, mine, n, texelBase, j0, cnt, m, hIdx, hCProbes, hCPos, hCNrm, hCCnt, texelsPerMeter, timeSlice, spp, pass);
+                return lmBakeShare(s, mine, n, texelBase, j0, cnt, hRecords, texelsPerMeter, timeSlice, spp, pass);
             });
             if (ok)
             {
-                for (int32_t j = 0; j < m; ++j)
+                hostPool.run([&](int w, int workers)
                 {
-                    const size_t t = (size_t)hIdx[j];
-                    for (int k = 0; k < 5; ++k) *(F4*)&lm.probes[k][t] = hCProbes[(size_t)k * m + j];
-                    lm.sampleCounts[t] = hCCnt[j];
-                }
+                    size_t j0, j1; hostShare((size_t)m, w, workers, j0, j1);
+                    for (size_t j = j0; j < j1; ++j)
+                    {
+                        const LmTexelRecord& r = hRecords[j];
+                        const size_t t = (size_t)r.idx;
+                        for (int k = 0; k < 5; ++k) *(F4*)&lm.probes[k][t] = r.probes[k];
+                        lm.sampleCounts[t] = r.cnt;
+                    }
+                });
             }
         }
         texelBase += (int32_t)n;
@@ -1474,8 +1503,8 @@ static bool cubeUpload(const Cubemap* cm, float* dColor, float* dConv, cudaStrea
     bool ok = true;
     for (int f = 0; ok && f < 6; ++f)
     {
-        if (dColor) ok = PT_CUDA(cudaMemcpyAsync(dColor + 3 * len * f, cm->color[f], 12 * len, cudaMemcpyHostToDevice, st));
-        if (ok && dConv) ok = PT_CUDA(cudaMemcpyAsync(dConv + 4 * elemCount * f, cm->convolved[f], 16 * elemCount, cudaMemcpyHostToDevice, st));
+        if (dColor) ok = copyIn(dColor + 3 * len * f, cm->color[f], 12 * len, st);
+        if (ok && dConv) ok = copyIn(dConv + 4 * elemCount * f, cm->convolved[f], 16 * elemCount, st);
     }
     return ok;
 }
@@ -1485,8 +1514,8 @@ static bool cubeDownload(Cubemap* cm, const float* dColor, const float* dConv, c
     bool ok = true;
     for (int f = 0; ok && f < 6; ++f)
     {
-        if (dColor) ok = PT_CUDA(cudaMemcpyAsync(cm->color[f], dColor + 3 * len * f, 12 * len, cudaMemcpyDeviceToHost, st));
-        if (ok && dConv) ok = PT_CUDA(cudaMemcpyAsync(cm->convolved[f], dConv + 4 * elemCount * f, 16 * elemCount, cudaMemcpyDeviceToHost, st));
+        if (dColor) ok = copyOut(cm->color[f], dColor + 3 * len * f, 12 * len, st);
+        if (ok && dConv) ok = copyOut(cm->convolved[f], dConv + 4 * elemCount * f, 16 * elemCount, st);
     }
     return ok && PT_CUDA(cudaStreamSynchronize(st));
 }
@@ -1665,9 +1694,9 @@ int32_t LmPack_EmbedDesc(const PtEmbedMesh* meshes, int32_t meshCount, PtLightma
             page[(size_t)(base + t)] = p;
         }
         const size_t bytes = 16 * 3 * (size_t)nt, off = 3 * (size_t)base;
-        ok = PT_CUDA(cudaMemcpyAsync(dPos + off, m.positions, bytes, cudaMemcpyHostToDevice, st)) &&
-             PT_CUDA(cudaMemcpyAsync(dNor + off, m.normals, bytes, cudaMemcpyHostToDevice, st)) &&
-             PT_CUDA(cudaMemcpyAsync(dUv + off, m.uvs, bytes, cudaMemcpyHostToDevice, st));
+        ok = copyIn(dPos + off, m.positions, bytes, st) &&
+             copyIn(dNor + off, m.normals, bytes, st) &&
+             copyIn(dUv + off, m.uvs, bytes, st);
         base += nt;
     }
     ok = ok && PT_CUDA(cudaMemcpyAsync(dPage, page.data(), 4 * (size_t)triCount, cudaMemcpyHostToDevice, st));
@@ -1681,9 +1710,9 @@ int32_t LmPack_EmbedDesc(const PtEmbedMesh* meshes, int32_t meshCount, PtLightma
     const size_t n = (size_t)lmSize * lmSize;
     for (int32_t k = 0; ok && k < lmCount; ++k)
     {
-        ok = PT_CUDA(cudaMemcpyAsync((void*)lightmaps[k].position, dOutPos + 3 * n * k, 12 * n, cudaMemcpyDeviceToHost, st)) &&
-             PT_CUDA(cudaMemcpyAsync((void*)lightmaps[k].normal, dOutNor + 3 * n * k, 12 * n, cudaMemcpyDeviceToHost, st)) &&
-             PT_CUDA(cudaMemcpyAsync(lightmaps[k].sampleCounts, dOutCnt + n * k, 4 * n, cudaMemcpyDeviceToHost, st));
+        ok = copyOut((void*)lightmaps[k].position, dOutPos + 3 * n * k, 12 * n, st) &&
+             copyOut((void*)lightmaps[k].normal, dOutNor + 3 * n * k, 12 * n, st) &&
+             copyOut(lightmaps[k].sampleCounts, dOutCnt + n * k, 4 * n, st);
     }
     ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
@@ -1715,7 +1744,7 @@ int32_t LmPack_ChartMasksDesc(pim_float2* triCoords, const int32_t* chartFirstNo
         const int32_t w = maskSizeOut[2 * c], h = maskSizeOut[2 * c + 1];
         if (!masksOut[c] || w <= 0 || h <= 0) continue;
         ok = launchMaskBytes(dCharts, c, w, h, dBits, dBytes, st) &&
-             PT_CUDA(cudaMemcpyAsync(masksOut[c], dBytes, (size_t)w * (size_t)h, cudaMemcpyDeviceToHost, st)) &&
+             copyOut(masksOut[c], dBytes, (size_t)w * (size_t)h, st) &&
              PT_CUDA(cudaStreamSynchronize(st));
     }
     ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
@@ -1794,11 +1823,11 @@ int32_t Pt_Tonemap(const pim_float4* light, int64_t count, float exposure, uint3
     Lease lease;
     if (!lease.dev(dLight, (size_t)count).dev(dOut, (size_t)count).commit()) return -1;
     cudaStream_t st = nullptr;
-    bool ok = PT_CUDA(cudaMemcpyAsync(dLight, light, 16 * (size_t)count, cudaMemcpyHostToDevice, st));
+    bool ok = copyIn(dLight, light, 16 * (size_t)count, st);
     KernelTimer timer(lease, st);
     ok = ok && launchTonemap(dLight, count, exposure, pass, seed, dOut, st);
     timer.stop();
-    ok = ok && PT_CUDA(cudaMemcpyAsync(rgba8Out, dOut, 4 * (size_t)count, cudaMemcpyDeviceToHost, st));
+    ok = ok && copyOut(rgba8Out, dOut, 4 * (size_t)count, st);
     ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
 }
@@ -1819,13 +1848,13 @@ int32_t Pt_RepackRome(const pim_float4* mr, pim_int2 mrSize, const pim_float4* o
     Lease lease;
     if (!lease.dev(dMr, nMr).dev(dOcc, nOcc).dev(dEm, nEm).dev(dOut, n).commit()) return -1;
     cudaStream_t st = nullptr;
-    bool ok = PT_CUDA(cudaMemcpyAsync(dMr, mr, 16 * nMr, cudaMemcpyHostToDevice, st)) &&
-              PT_CUDA(cudaMemcpyAsync(dOcc, occ, 16 * nOcc, cudaMemcpyHostToDevice, st)) &&
-              PT_CUDA(cudaMemcpyAsync(dEm, em, 16 * nEm, cudaMemcpyHostToDevice, st));
+    bool ok = copyIn(dMr, mr, 16 * nMr, st) &&
+              copyIn(dOcc, occ, 16 * nOcc, st) &&
+              copyIn(dEm, em, 16 * nEm, st);
     KernelTimer timer(lease, st);
     ok = ok && launchRepackRome(dMr, mrSize.x, mrSize.y, dOcc, occSize.x, occSize.y, dEm, emSize.x, emSize.y, size, dOut, st);
     timer.stop();
-    ok = ok && PT_CUDA(cudaMemcpyAsync(romeOut, dOut, 4 * n, cudaMemcpyDeviceToHost, st));
+    ok = ok && copyOut(romeOut, dOut, 4 * n, st);
     ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
     return ok ? 0 : -1;
 }

@@ -100,48 +100,44 @@ bool launchLightmapBake(const DScene& S, const LightmapView& lm, float metersPer
 }
 
 // ---------------------------------------------------------------- sparse page transfer
-// LmPack_BakeDesc moves only the texels a chart covers (sampleCounts != 0): idx[j] is the texel of
-// compact entry j; probes are lobe-major (5 x count), positions and normals float3, counts float.
+// LmPack_BakeDesc moves only the texels a chart covers (sampleCounts != 0), one 112-byte LmTexelRecord each
+// (five lobes, position, normal, sample count, texel index), so that any range of them is one copy each way.
 
-__global__ void __launch_bounds__(256) k_lmScatter(LightmapView lm, const int32_t* __restrict__ idx, int count,
-                                                   const F4* __restrict__ probes, const float* __restrict__ pos3,
-                                                   const float* __restrict__ nrm3, const float* __restrict__ cnt)
+__global__ void __launch_bounds__(256) k_lmScatter(LightmapView lm, const LmTexelRecord* __restrict__ rec, int count)
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= count) return;
-    const int t = idx[j];
-    for (int k = 0; k < 5; ++k) lm.probes[k][t] = probes[(size_t)k * count + j];
+    const LmTexelRecord r = rec[j];
+    const int t = r.idx;
+    for (int k = 0; k < 5; ++k) lm.probes[k][t] = r.probes[k];
     float* p = const_cast<float*>(lm.position) + 3 * (size_t)t;
     float* n = const_cast<float*>(lm.normal) + 3 * (size_t)t;
-    p[0] = pos3[3 * j]; p[1] = pos3[3 * j + 1]; p[2] = pos3[3 * j + 2];
-    n[0] = nrm3[3 * j]; n[1] = nrm3[3 * j + 1]; n[2] = nrm3[3 * j + 2];
-    lm.sampleCounts[t] = cnt[j];
+    p[0] = r.pos[0]; p[1] = r.pos[1]; p[2] = r.pos[2];
+    n[0] = r.nrm[0]; n[1] = r.nrm[1]; n[2] = r.nrm[2];
+    lm.sampleCounts[t] = r.cnt;
 }
 
-__global__ void __launch_bounds__(256) k_lmGather(LightmapView lm, const int32_t* __restrict__ idx, int count,
-                                                  F4* __restrict__ probes, float* __restrict__ cnt)
+__global__ void __launch_bounds__(256) k_lmGather(LightmapView lm, LmTexelRecord* __restrict__ rec, int count)
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= count) return;
-    const int t = idx[j];
-    for (int k = 0; k < 5; ++k) probes[(size_t)k * count + j] = lm.probes[k][t];
-    cnt[j] = lm.sampleCounts[t];
+    const int t = rec[j].idx;
+    for (int k = 0; k < 5; ++k) rec[j].probes[k] = lm.probes[k][t];
+    rec[j].cnt = lm.sampleCounts[t];
 }
 
-bool launchLightmapScatter(const LightmapView& lm, const int32_t* dIdx, int32_t count, const F4* dProbes, const float* dPos3,
-                           const float* dNrm3, const float* dCnt, cudaStream_t stream)
+bool launchLightmapScatter(const LightmapView& lm, const LmTexelRecord* dRecords, int32_t count, cudaStream_t stream)
 {
     if (count <= 0) return true;
-    k_lmScatter<<<(count + 255) / 256, 256, 0, stream>>>(lm, dIdx, count, dProbes, dPos3, dNrm3, dCnt);
+    k_lmScatter<<<(count + 255) / 256, 256, 0, stream>>>(lm, dRecords, count);
     g_counters.kernelLaunches++;
     return PT_CUDA(cudaGetLastError());
 }
 
-bool launchLightmapGather(const LightmapView& lm, const int32_t* dIdx, int32_t count, F4* dProbes, float* dCnt,
-                          cudaStream_t stream)
+bool launchLightmapGather(const LightmapView& lm, LmTexelRecord* dRecords, int32_t count, cudaStream_t stream)
 {
     if (count <= 0) return true;
-    k_lmGather<<<(count + 255) / 256, 256, 0, stream>>>(lm, dIdx, count, dProbes, dCnt);
+    k_lmGather<<<(count + 255) / 256, 256, 0, stream>>>(lm, dRecords, count);
     g_counters.kernelLaunches++;
     return PT_CUDA(cudaGetLastError());
 }

@@ -236,10 +236,11 @@ bool launchLightmapBakeWavefront(const DScene& S, PathPool& pool, const Lightmap
                                  float timeSlice, int32_t spp, uint32_t pass, uint32_t seed, cudaStream_t stream);
 
 // covered texels of a host page to / from a full-size device page (LmPack_BakeDesc)
-bool launchLightmapScatter(const LightmapView& lm, const int32_t* dIdx, int32_t count, const F4* dProbes, const float* dPos3,
-                           const float* dNrm3, const float* dCnt, cudaStream_t stream);
-bool launchLightmapGather(const LightmapView& lm, const int32_t* dIdx, int32_t count, F4* dProbes, float* dCnt,
-                          cudaStream_t stream);
+// one covered texel of a host lightmap page on its way to the device and back (LmPack_BakeDesc)
+struct LmTexelRecord { F4 probes[5]; float pos[3]; float nrm[3]; float cnt; int32_t idx; };
+static_assert(sizeof(LmTexelRecord) == 112, "LmTexelRecord is seven 16-byte pieces");
+bool launchLightmapScatter(const LightmapView& lm, const LmTexelRecord* dRecords, int32_t count, cudaStream_t stream);
+bool launchLightmapGather(const LightmapView& lm, LmTexelRecord* dRecords, int32_t count, cudaStream_t stream);
 
 // ------------------------------------------------------------------ lmpack.cu (chart masks, atlas placement)
 void chartPrepare(V2* tri, const int32_t* firstNode, int32_t chartCount, float* areaOut, int32_t* maskSizeOut);
