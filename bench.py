@@ -780,7 +780,7 @@ def extra_c4(ctx):
                 scene.bake_lightmap(g_probes, h_pos, h_nrm, g_cnt, tpm, 1.0, spp, 51 + p)
             dt = (time.perf_counter() - t0) / reps
             out["e2e"] = {"value": covered * spp / dt / 1e6, "unit": "M texel-samples/s", "how": "LmPack_BakeDesc with the host page",
-                          "h2d_bytes_per_step": covered * 112, "d2h_bytes_per_step": covered * 84}
+                          "h2d_bytes_per_step": covered * 112, "d2h_bytes_per_step": covered * 112}
             if not ctx.args.no_cpu_baseline:
                 ref = O.Scene()
                 O.lm_bake(ref, 1.0, 1, 0)
@@ -851,10 +851,13 @@ def extra_c5(ctx):
                                 "frac": anyhit * 1e6 * b_any / 1e9 / ctx.peak}}
     # end to end with host rays and host hits (Pt_IntersectN): 32 B in, 48 B out per ray over PCIe
     n_e2e = 1 << 22
-    scene.intersect(ro[:1 << 16], rd[:1 << 16])
-    t0 = time.perf_counter()
-    scene.intersect(ro[:n_e2e], rd[:n_e2e])
-    dt = time.perf_counter() - t0
+    h_hits = np.zeros(n_e2e, api.HIT_DTYPE)           # the caller's result buffer, reused from call to call
+    scene.intersect(ro[:n_e2e], rd[:n_e2e], out=h_hits)
+    dt = 1e30
+    for _ in range(3):
+        t0 = time.perf_counter()
+        scene.intersect(ro[:n_e2e], rd[:n_e2e], out=h_hits)
+        dt = min(dt, time.perf_counter() - t0)
     out["e2e"] = {"value": n_e2e / dt / 1e6, "unit": "Mrays/s", "how": "Pt_IntersectN, 4.2 M host rays in, PtRayHit out",
                   "h2d_bytes_per_step": n_e2e * 32, "d2h_bytes_per_step": n_e2e * 48}
     scene.close()

@@ -477,9 +477,12 @@ class Scene:
         return out
 
     # ---- ray batches -----------------------------------------------------------
-    def intersect(self, ro, rd, t_near=0.0):
+    def intersect(self, ro, rd, t_near=0.0, out=None):
+        """Pt_IntersectN with host arrays; `out` (HIT_DTYPE, len(ro)) lets a caller reuse its result buffer"""
         ro = np.ascontiguousarray(ro, np.float32); rd = np.ascontiguousarray(rd, np.float32)
-        out = np.zeros(len(ro), HIT_DTYPE)
+        if out is None:
+            out = np.zeros(len(ro), HIT_DTYPE)
+        assert out.dtype == HIT_DTYPE and len(out) == len(ro) and out.flags.c_contiguous
         _check(load().Pt_IntersectN(self.h, ro.ctypes.data, rd.ctypes.data, t_near, out.ctypes.data, len(ro)), "Pt_IntersectN")
         return out
 
