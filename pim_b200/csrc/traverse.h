@@ -454,10 +454,9 @@ PT_D bool travNodeStepP(const Bvh& bvh, TravRay& r, Stack& st)
         float tfz = byteToFloat(fzw[w], i & 3) * sz + bz;
         float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tNear));
         float tmax = fminf(fminf(tfx, tfy), fminf(tfz, r.tBest));
-        bool h = tmin <= tmax * 1.0000004f;
-        // a leaf slot with no triangles (an empty slot let through by the slack) is dropped here
-        const uint32_t m = (metaw[w] >> (8 * (i & 3))) & 0xffu;
-        h = h && (((imask >> i) & 1u) || (m >> 5) != 0u);
+        // (an empty slot holds an inverted box and misses by itself; inside a node of no extent at all the slack can
+        // let it through, and it then travels as a leaf entry of zero triangles, which the leaf step skips)
+        const bool h = tmin <= tmax * 1.0000004f;
         keys[i] = h ? (((f2u(tmin) & ~7u) | (uint32_t)i) + 8u) : 0xffffffffu;
         nearest = keys[i] < nearest ? keys[i] : nearest;
         hitMask |= h ? (1u << i) : 0u;
