@@ -232,3 +232,37 @@ def test_light_counters_summed_over_two_replicas_equal_one_scene(api):
     assert torch.equal(counters(a), counters(one))
     for s in (a, b, one):
         s.close()
+
+
+def test_pageable_host_buffers_through_the_copy_ring_equal_the_direct_forms(api):
+    """Host-buffer calls with pageable arrays of 2 MB or more go through the page-locked ring (hostcopy.h: parallel
+    streaming memcpy into two slots, graded chunk sizes); page-locked arrays and device pointers do not. Same bytes
+    either way: an odd-sized ray batch against the device form, a screenshot against the same call on page-locked
+    memory, and sizes around the ring's threshold and slot size."""
+    import torch
+    L = api.load()
+    dev = torch.device("cuda", 0)
+    s = api.Scene(scenes.cornell_box("spheres", brdf_lut=parity.reference_lut(), seed=1))
+    n = 3_000_001                                    # 48 MB of origins, 144 MB of hits: several slots, a ragged tail
+    ro, rd = parity.box_rays(n, seed=77)
+    got = s.intersect(ro, rd)
+    d_ro, d_rd = torch.from_numpy(ro).to(dev), torch.from_numpy(rd).to(dev)
+    d_hits = torch.zeros((n, 12), dtype=torch.float32, device=dev)
+    assert L.Pt_IntersectN_Device(s.h, d_ro.data_ptr(), d_rd.data_ptr(), 0.0, d_hits.data_ptr(), n, None) == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(got.view(np.uint32).reshape(n, 12), d_hits.cpu().numpy().view(np.uint32))
+    occ = s.occluded(ro, rd)
+    d_occ = torch.zeros(n, dtype=torch.uint8, device=dev)
+    assert L.Pt_OccludedN_Device(s.h, d_ro.data_ptr(), d_rd.data_ptr(), 0.0, d_occ.data_ptr(), n, None) == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(occ, d_occ.cpu().numpy())
+    s.close()
+    # tonemap: pageable numpy arrays against page-locked torch tensors, sizes around 2 MB (threshold) and 8 MB (slot)
+    rng = np.random.default_rng(5)
+    for pixels in (131_071, 131_072, 131_073, 524_288 + 3, 1920 * 1080, 2_097_152 + 5):
+        light = (rng.random((pixels, 4), np.float32) * 4.0).astype(np.float32)
+        out = np.zeros(pixels, np.uint32)
+        assert L.Pt_Tonemap(light.ctypes.data, pixels, 1.0, 1, 0, out.ctypes.data) == 0, api.last_error()
+        p_light = torch.from_numpy(light).pin_memory(); p_out = torch.zeros(pixels, dtype=torch.int32).pin_memory()
+        assert L.Pt_Tonemap(p_light.data_ptr(), pixels, 1.0, 1, 0, p_out.data_ptr()) == 0, api.last_error()
+        assert np.array_equal(out, p_out.numpy().view(np.uint32)), pixels
