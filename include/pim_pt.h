@@ -448,6 +448,7 @@ typedef struct PtSceneStats_s
     int32_t bvhNodeCount, bvhTriCount;
     float buildMs;
     float phaseMs[6];       /* upload+flatten, BVH, emissive pdf, light grid, BRDF LUT, pool */
+    int32_t bvhRefitted;    /* 1: the tree was taken over from the scene this one replaced and refitted ("refit" option) */
 } PtSceneStats;
 
 int32_t PtScene_GetStats(const PtScene* scene, PtSceneStats* stats);
@@ -504,7 +505,13 @@ float Pt_MeasureL2ReadGBs(int64_t bytes, int32_t reps);
  *   "persistent"  -1 choose the traversal kernels by BVH size (default), 0 one thread per ray, 1 persistent
  *                 warps with postponed leaves
  *   "finish"      live paths below which the tail of a wavefront call finishes in one launch (0 = never)
- * Results do not depend on either. 0 on success. */
+ *   "refit"       1: when PtScene_Update / Pt_Trace / LmPack_Bake find a newer registered description whose
+ *                 geometry has the shape of the old one (same entities, same vertex counts), the scene keeps its
+ *                 BVH topology: packed triangles and node boxes are recomputed bottom up from the moved vertices
+ *                 instead of a new SAH build. 0 (default): always rebuild, as the reference
+ *                 does (path_tracer.c:1028-1032). Hits are the same either way; a refitted tree gets slower the
+ *                 further the geometry has moved from the pose it was built for.
+ * Results do not depend on any of them. 0 on success. */
 int32_t Pt_SetOption(const char* name, int32_t value);
 
 const char* Pt_LastError(void);

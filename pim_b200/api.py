@@ -102,7 +102,7 @@ class PtSceneStats(C.Structure):
     _fields_ = [("vertCount", C.c_int32), ("matCount", C.c_int32), ("emissiveCount", C.c_int32),
                 ("gridSize", C.c_int32 * 3), ("gridLo", C.c_float * 4), ("gridHi", C.c_float * 4),
                 ("cellsPerMeter", C.c_float), ("bvhNodeCount", C.c_int32), ("bvhTriCount", C.c_int32),
-                ("buildMs", C.c_float), ("phaseMs", C.c_float * 6)]
+                ("buildMs", C.c_float), ("phaseMs", C.c_float * 6), ("bvhRefitted", C.c_int32)]
 
 
 class PtCounters(C.Structure):

@@ -87,6 +87,8 @@ struct PtScene_s
     int rayGenFlip = 0;
     int device = 0;                 // the CUDA device the scene lives on (current when it was built)
     uint64_t descVersion = 0;       // PtSys_SetSceneDesc generation the scene was built from (0: an explicit description)
+    std::vector<int32_t> entityLengths;     // vertices per entity, in order: the shape a refit must find again
+    bool refitted = false;          // the tree was refitted from the scene this one replaced, not built
     // ray cursors of the persistent batch kernels: one 128-byte line per call in flight, handed out
     // round robin, so two batches on different streams never share a cursor
     static constexpr uint32_t kCursorRing = 64;
@@ -187,6 +189,7 @@ static float g_lmTexelsPerMeter = 0.0f;
 // the first g_deviceCount devices: every scene built afterwards carries a full replica per extra device, one
 // host thread per device drives it, partial results come to the scene's own device by peer copy.
 static int g_deviceCount = 1;
+static bool g_refitOnUpdate = false;    // Pt_SetOption("refit"): PtScene_Update refits the tree when the geometry kept its shape
 
 struct DeviceGuard
 {
@@ -333,7 +336,9 @@ static void sceneFree(PtScene* s)
     delete s;
 }
 
-static PtScene* sceneBuildOne(const PtSceneDesc* desc)
+// reuse: the tree of the scene this one replaces, refitted to the new vertices when the geometry still has its
+// shape (same triangle count, same entity lengths), else dropped
+static PtScene* sceneBuildOne(const PtSceneDesc* desc, PtScene* reuse = nullptr)
 {
     if (!ensureInit()) return nullptr;
     if (!desc) { setError("PtScene_NewFromDesc: null description"); return nullptr; }
@@ -458,7 +463,15 @@ static PtScene* sceneBuildOne(const PtSceneDesc* desc)
     phase(4);
     // BVH (RtcNewScene)
     const int32_t triCount = vertCount / 3;
-    ok = ok && buildBvh(dPos, triCount, s->bvh, st);
+    for (int i = 0; i < desc->entityCount; ++i) s->entityLengths.push_back(desc->entities[i].length);
+    if (ok && reuse && reuse->bvh.triCount == triCount && reuse->bvh.nodes && reuse->entityLengths == s->entityLengths)
+    {
+        s->bvh = std::move(reuse->bvh);
+        reuse->bvh = BvhBuffers();
+        ok = refitBvh(dPos, triCount, s->bvh, st);
+        s->refitted = true;
+    }
+    else ok = ok && buildBvh(dPos, triCount, s->bvh, st);
     V.bvh.nodes = s->bvh.nodes; V.bvh.tris = s->bvh.tris; V.bvh.nodesF = s->bvh.nodesF;
     V.bvh.nodeCount = s->bvh.nodeCount; V.bvh.triCount = s->bvh.triCount;
 
@@ -534,14 +547,19 @@ static PtScene* sceneBuildOne(const PtSceneDesc* desc)
     if (dSrcNrm) cudaFree(dSrcNrm);
     if (dSrcUv) cudaFree(dSrcUv);
     if (dEnts) cudaFree(dEnts);
-    if (!ok) { sceneFree(s); return nullptr; }
+    if (!ok)
+    {
+        if (s->refitted && reuse) { reuse->bvh = std::move(s->bvh); s->bvh = BvhBuffers(); }     // the tree goes back with its owner
+        sceneFree(s);
+        return nullptr;
+    }
     s->buildMs = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return s;
 }
 
 // the scene on the current device plus, in multi-GPU mode, a replica on each of the other devices (the
 // build is deterministic, so the replicas hold the same tree and the same light grid)
-static PtScene* sceneBuild(const PtSceneDesc* desc)
+static PtScene* sceneBuild(const PtSceneDesc* desc, PtScene* reuse = nullptr)
 {
     if (!ensureInit()) return nullptr;
     int primary = 0;
@@ -553,7 +571,11 @@ static PtScene* sceneBuild(const PtSceneDesc* desc)
     const bool ok = forEachDevice((int)devices.size(), [&](int k) -> bool
     {
         DeviceGuard guard(devices[(size_t)k]);
-        built[(size_t)k] = sceneBuildOne(desc);
+        PtScene* old = nullptr;         // the replaced scene's tree on the same device
+        if (reuse && k == 0 && reuse->device == devices[0]) old = reuse;
+        else if (reuse && k > 0 && (size_t)k <= reuse->replicas.size() && reuse->replicas[(size_t)k - 1]->device == devices[(size_t)k])
+            old = reuse->replicas[(size_t)k - 1];
+        built[(size_t)k] = sceneBuildOne(desc, old);
         return built[(size_t)k] != nullptr;
     });
     if (!ok)
@@ -586,8 +608,6 @@ struct KernelTimer
     }
 };
 
-static PtScene* sceneBuild(const PtSceneDesc* desc);
-
 // PtScene_Update (path_tracer.c:1024-1037): a scene built from the registered description is rebuilt in
 // place when the description has changed since (the reference compares Entities_Get()->modtime), then
 // the light-grid distributions relearn (UpdateDists)
@@ -595,11 +615,13 @@ static bool sceneRefresh(PtScene* scene, cudaStream_t st)
 {
     if (scene->descVersion != 0 && g_sceneDesc.valid && scene->descVersion != g_sceneDesc.version)
     {
-        PtScene* fresh = sceneBuild(&g_sceneDesc.desc);
+        // Pt_SetOption("refit", 1): keep the tree's topology and refit it when the geometry has the same shape
+        for (PtScene* r : scene->replicas) { DeviceGuard guard(r->device); cudaStreamSynchronize(r->stream); }
+        cudaStreamSynchronize(scene->stream);
+        PtScene* fresh = sceneBuild(&g_sceneDesc.desc, g_refitOnUpdate ? scene : nullptr);
         if (!fresh) return false;
         fresh->descVersion = g_sceneDesc.version;
         fresh->nextPass = scene->nextPass;
-        cudaStreamSynchronize(scene->stream);
         const bool ownStream = st == scene->stream;
         std::swap(*scene, *fresh);          // the caller's handle now owns the new scene
         sceneFree(fresh);
@@ -1872,6 +1894,7 @@ int32_t PtScene_GetStats(const PtScene* scene, PtSceneStats* stats)
     stats->bvhNodeCount = V.bvh.nodeCount; stats->bvhTriCount = V.bvh.triCount;
     stats->buildMs = scene->buildMs;
     for (int k = 0; k < 6; ++k) stats->phaseMs[k] = scene->phaseMs[k];
+    stats->bvhRefitted = scene->refitted ? 1 : 0;
     return 0;
 }
 
@@ -2027,6 +2050,7 @@ int32_t Pt_SetOption(const char* name, int32_t value)
     if (!ensureInit()) return -1;       // the environment's values are read first, then overridden here
     if (!strcmp(name, "persistent")) { g_persistentTraversal = value; return 0; }
     if (!strcmp(name, "finish")) { g_finishThreshold = value; return 0; }
+    if (!strcmp(name, "refit")) { g_refitOnUpdate = value != 0; return 0; }
     setError("Pt_SetOption: unknown option '%s'", name);
     return -1;
 }

@@ -226,6 +226,15 @@ PT_HD uint32_t quantExp(float extent)
     return (uint32_t)e;
 }
 
+// [a, b] on the grid org + q * scale: the largest q at or below a, the smallest at or above b (0 .. 255)
+PT_HD void quantRange(float a, float b, float org, float scale, int& ql, int& qh)
+{
+    float q = floorf((a - org) / scale); ql = (int)f1_clamp(q, 0.0f, 255.0f);
+    while (ql > 0 && org + (float)ql * scale > a) --ql;
+    q = ceilf((b - org) / scale); qh = (int)f1_clamp(q, 0.0f, 255.0f);
+    while (qh < 255 && org + (float)qh * scale < b) ++qh;
+}
+
 PT_HD void setByte(uint32_t w[2], int i, uint32_t v)
 {
     w[i >> 2] |= (v & 0xffu) << (8 * (i & 3));

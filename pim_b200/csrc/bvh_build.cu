@@ -957,7 +957,128 @@ __global__ void __launch_bounds__(256) k_expandNodes(const WideNode* __restrict_
     out[i] = f;
 }
 
+// ---- refit ------------------------------------------------------------------
+
+// the packed triangles again, from the new positions, in the leaf order the build gave them
+__global__ void __launch_bounds__(256) k_refitTris(const F4* __restrict__ pos, int32_t n, PackedTri* __restrict__ tris)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint32_t t = tris[j].prim;
+    const U4 a = ldg128(pos + 3 * (size_t)t), b = ldg128(pos + 3 * (size_t)t + 1), c = ldg128(pos + 3 * (size_t)t + 2);
+    PackedTri pt;
+    pt.v0x = u2f(a.x); pt.v0y = u2f(a.y); pt.v0z = u2f(a.z); pt.prim = t;
+    pt.e1x = u2f(b.x) - u2f(a.x); pt.e1y = u2f(b.y) - u2f(a.y); pt.e1z = u2f(b.z) - u2f(a.z); pt.pad0 = 0;
+    pt.e2x = u2f(c.x) - u2f(a.x); pt.e2y = u2f(c.y) - u2f(a.y); pt.e2z = u2f(c.z) - u2f(a.z); pt.pad1 = 0;
+    tris[j] = pt;
+}
+
+// one level of wide nodes, the levels below it done: child boxes from the leaves' vertices or the inner children's
+// frames (boxLo / boxHi), then the node's own frame and plane bytes exactly as encodeWideNode makes them
+__global__ void __launch_bounds__(128) k_refitLevel(WideNode* __restrict__ nodes, int32_t begin, int32_t end,
+                                                    const PackedTri* __restrict__ tris, const F4* __restrict__ pos,
+                                                    F4* __restrict__ boxLo, F4* __restrict__ boxHi)
+{
+    const int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= end) return;
+    WideNode w = nodes[i];
+    const uint32_t imask = w.exyzImask >> 24;
+    F4 clo[8], chi[8];
+    F4 lo = f4(3.0e38f, 3.0e38f, 3.0e38f, 0), hi = f4(-3.0e38f, -3.0e38f, -3.0e38f, 0);
+    uint32_t present = 0;
+    for (int c = 0; c < 8; ++c)
+    {
+        const uint32_t m = (w.meta[c >> 2] >> (8 * (c & 3))) & 0xffu;
+        if (m == 0u) continue;
+        F4 a = f4(3.0e38f, 3.0e38f, 3.0e38f, 0), b = f4(-3.0e38f, -3.0e38f, -3.0e38f, 0);
+        if ((imask >> c) & 1u)
+        {
+            const uint32_t child = w.childBase + (uint32_t)__popc(imask & ((1u << c) - 1u));
+            a = boxLo[child]; b = boxHi[child];
+        }
+        else
+        {
+            const uint32_t first = w.triBase + (m & 31u), count = m >> 5;
+            for (uint32_t j = 0; j < count; ++j)
+            {
+                const uint32_t t = tris[first + j].prim;
+                for (int v = 0; v < 3; ++v)
+                {
+                    const U4 p = ldg128(pos + 3 * (size_t)t + v);
+                    a.x = fminf(a.x, u2f(p.x)); a.y = fminf(a.y, u2f(p.y)); a.z = fminf(a.z, u2f(p.z));
+                    b.x = fmaxf(b.x, u2f(p.x)); b.y = fmaxf(b.y, u2f(p.y)); b.z = fmaxf(b.z, u2f(p.z));
+                }
+            }
+        }
+        clo[c] = a; chi[c] = b;
+        present |= 1u << c;
+        lo.x = fminf(lo.x, a.x); lo.y = fminf(lo.y, a.y); lo.z = fminf(lo.z, a.z);
+        hi.x = fmaxf(hi.x, b.x); hi.y = fmaxf(hi.y, b.y); hi.z = fmaxf(hi.z, b.z);
+    }
+    boxLo[i] = lo; boxHi[i] = hi;
+    const uint32_t ex = quantExp(hi.x - lo.x), ey = quantExp(hi.y - lo.y), ez = quantExp(hi.z - lo.z);
+    const float sx = u2f(ex << 23), sy = u2f(ey << 23), sz = u2f(ez << 23);
+    w.ox = lo.x; w.oy = lo.y; w.oz = lo.z;
+    w.exyzImask = ex | (ey << 8) | (ez << 16) | (imask << 24);
+    w.qlox[0] = w.qlox[1] = w.qloy[0] = w.qloy[1] = w.qloz[0] = w.qloz[1] = 0;
+    w.qhix[0] = w.qhix[1] = w.qhiy[0] = w.qhiy[1] = w.qhiz[0] = w.qhiz[1] = 0;
+    for (int c = 0; c < 8; ++c)
+    {
+        if (!((present >> c) & 1u))
+        {
+            setByte(w.qlox, c, 255); setByte(w.qloy, c, 255); setByte(w.qloz, c, 255);     // empty slot: inverted box
+            continue;
+        }
+        int ql, qh;
+        quantRange(clo[c].x, chi[c].x, w.ox, sx, ql, qh); setByte(w.qlox, c, (uint32_t)ql); setByte(w.qhix, c, (uint32_t)qh);
+        quantRange(clo[c].y, chi[c].y, w.oy, sy, ql, qh); setByte(w.qloy, c, (uint32_t)ql); setByte(w.qhiy, c, (uint32_t)qh);
+        quantRange(clo[c].z, chi[c].z, w.oz, sz, ql, qh); setByte(w.qloz, c, (uint32_t)ql); setByte(w.qhiz, c, (uint32_t)qh);
+    }
+    nodes[i] = w;
+}
+
 } // namespace
+
+bool refitBvh(const F4* dPositions, int32_t triCount, BvhBuffers& b, cudaStream_t stream)
+{
+    if (triCount != b.triCount || b.nodeCount <= 0 || b.levelEnd.empty() || b.levelEnd.back() != b.nodeCount)
+    {
+        setError("refitBvh: the tree does not match the geometry (%d triangles against %d, %d nodes)", triCount, b.triCount, b.nodeCount);
+        return false;
+    }
+    F4 *boxLo = nullptr, *boxHi = nullptr;
+    bool ok = devAlloc(boxLo, (size_t)b.nodeCount) && devAlloc(boxHi, (size_t)b.nodeCount);
+    if (ok)
+    {
+        k_refitTris<<<(triCount + 255) / 256, 256, 0, stream>>>(dPositions, triCount, b.tris);
+        g_counters.kernelLaunches++;
+        for (int l = (int)b.levelEnd.size() - 1; l >= 0; --l)
+        {
+            const int32_t begin = l == 0 ? 0 : b.levelEnd[(size_t)l - 1], end = b.levelEnd[(size_t)l];
+            if (end <= begin) continue;
+            k_refitLevel<<<(end - begin + 127) / 128, 128, 0, stream>>>(b.nodes, begin, end, b.tris, dPositions, boxLo, boxHi);
+            g_counters.kernelLaunches++;
+        }
+        if (b.nodesF)
+        {
+            k_expandNodes<<<(b.nodeCount + 255) / 256, 256, 0, stream>>>(b.nodes, b.nodeCount, b.nodesF);
+            g_counters.kernelLaunches++;
+        }
+        F4 root[2];
+        ok = PT_CUDA(cudaGetLastError()) &&
+             PT_CUDA(cudaMemcpyAsync(&root[0], boxLo, sizeof(F4), cudaMemcpyDeviceToHost, stream)) &&
+             PT_CUDA(cudaMemcpyAsync(&root[1], boxHi, sizeof(F4), cudaMemcpyDeviceToHost, stream)) &&
+             PT_CUDA(cudaStreamSynchronize(stream));
+        if (ok)
+        {
+            b.sceneLo[0] = root[0].x; b.sceneLo[1] = root[0].y; b.sceneLo[2] = root[0].z;
+            b.sceneHi[0] = root[1].x; b.sceneHi[1] = root[1].y; b.sceneHi[2] = root[1].z;
+        }
+    }
+    cudaFree(boxLo); cudaFree(boxHi);
+    return ok;
+}
+
 
 void freeBvh(BvhBuffers& b)
 {
@@ -1090,6 +1211,8 @@ bool buildBvh(const F4* dPositions, int32_t n, BvhBuffers& out, cudaStream_t str
             ok = ok && PT_CUDA(cudaStreamSynchronize(stream));
             levelCount = (int)h[2];
             out.depth++;
+            if (out.levelEnd.empty()) out.levelEnd.push_back(1);       // the root
+            if (levelCount > 0) out.levelEnd.push_back((int32_t)h[0]);
             out.nodeCount = (int32_t)h[0];
             out.triCount = (int32_t)h[1];
             ok = ok && PT_CUDA(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), stream));

@@ -48,10 +48,16 @@ struct BvhBuffers
     int32_t nodeCount = 0;
     int32_t triCount = 0;
     int32_t depth = 0;              // levels of the wide tree (the traversal stack holds at most 7 entries per level)
+    std::vector<int32_t> levelEnd;  // the collapse is breadth first: level l is nodes [levelEnd[l-1], levelEnd[l])
     float sceneLo[3] = { 0, 0, 0 }, sceneHi[3] = { 0, 0, 0 };   // bounds of all vertices
 };
 // positions: device float4[3*triCount]. Allocates nodes/tris with cudaMalloc.
 bool buildBvh(const F4* dPositions, int32_t triCount, BvhBuffers& out, cudaStream_t stream);
+// Same topology, moved vertices ("refit path for unchanged topology"): the packed triangles are
+// rewritten from the new positions in their leaf order and every wide node's frame and child boxes are recomputed
+// bottom up, level by level. Hits are those of a fresh build (the closest hit does not depend on the tree); how
+// fast they are found depends on how far the geometry moved.
+bool refitBvh(const F4* dPositions, int32_t triCount, BvhBuffers& bvh, cudaStream_t stream);
 void freeBvh(BvhBuffers& b);
 
 // LSD radix sort of (64-bit key, 32-bit value) pairs (bvh_build.cu); hist holds 256 * radixSortBlocks(n) words

@@ -266,3 +266,61 @@ def test_pageable_host_buffers_through_the_copy_ring_equal_the_direct_forms(api)
         p_light = torch.from_numpy(light).pin_memory(); p_out = torch.zeros(pixels, dtype=torch.int32).pin_memory()
         assert L.Pt_Tonemap(p_light.data_ptr(), pixels, 1.0, 1, 0, p_out.data_ptr()) == 0, api.last_error()
         assert np.array_equal(out, p_out.numpy().view(np.uint32)), pixels
+
+
+def test_refit_on_update_returns_the_hits_of_a_fresh_build(api):
+    """Pt_SetOption("refit", 1) ("refit path for unchanged topology"): after the entities moved,
+    PtScene_Update keeps the tree's topology, rewrites the packed triangles and refits the node boxes level by level.
+    Closest hits do not depend on the tree, so they must equal, bit for bit, those of a scene built from the moved
+    description; a description of another shape falls back to the rebuild."""
+    L = api.load()
+    lut = parity.reference_lut()
+
+    def moved(step):
+        d = scenes.cornell_box("spheres", brdf_lut=lut, seed=1)
+        rng = np.random.default_rng(100 + step)
+        for k, e in enumerate(d.entities):
+            m = np.array(e.matrix, np.float32).copy()
+            if step and len(e.positions) > 600:         # the spheres: move them about, the second one a lot
+                m[12:15] += np.float32(0.35 * step) * rng.uniform(-1.0, 1.0, 3).astype(np.float32)
+            e.matrix = m
+            if step:                                    # and every vertex of every entity a little
+                e.positions = e.positions.copy()
+                e.positions[:, :3] += rng.uniform(-0.01, 0.01, (len(e.positions), 3)).astype(np.float32)
+        return d
+
+    ro, rd = parity.box_rays(400_000, seed=21)
+    assert L.Pt_SetOption(b"refit", 1) == 0
+    try:
+        api.set_scene_desc(moved(0))
+        s = api.Scene()
+        assert s.stats.bvhRefitted == 0
+        first = s.intersect(ro, rd)
+        nodes = s.stats.bvhNodeCount
+        for step in (1, 2, 0):                          # moved, moved further, back where it was built
+            d = moved(step)
+            api.set_scene_desc(d)
+            st = s.update()
+            assert st.bvhRefitted == 1 and st.bvhNodeCount == nodes
+            fresh = api.Scene(d)
+            assert fresh.stats.bvhRefitted == 0
+            got, want = s.intersect(ro, rd), fresh.intersect(ro, rd)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), step
+            assert np.array_equal(s.occluded(ro, rd), fresh.occluded(ro, rd)), step
+            if step == 0:
+                assert np.array_equal(got.view(np.uint32), first.view(np.uint32))
+            fresh.close()
+        # a frame after the refit: the light grid, emissive tables and pool were set up anew around the kept tree
+        tr = api.Trace(96, 54)
+        cam, dof = api.make_camera([-4, 0, 4], [0, -1, 0]), api.default_dof(auto_focus=False)
+        tr.trace(s, cam, dof, 1.0)
+        assert np.isfinite(tr.image("color")).all() and tr.image("color").mean() > 0.0
+        tr.close()
+        # another shape: rebuilt, not refitted
+        api.set_scene_desc(scenes.cornell_box("boxes", brdf_lut=lut, seed=1))
+        st = s.update()
+        assert st.bvhRefitted == 0 and st.bvhNodeCount != nodes
+        s.close()
+    finally:
+        L.Pt_SetOption(b"refit", 0)
+        api.set_scene_desc(None)

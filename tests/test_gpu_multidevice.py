@@ -82,3 +82,37 @@ def test_two_devices_bake_what_one_bakes(api, oracle):
         assert np.array_equal(c1, c2) and (c1[start[3] > 0] == start[3][start[3] > 0] + 8).all()
         for k in range(5):
             assert np.array_equal(p1[k], p2[k]), (mode, k)
+
+
+def test_refit_on_update_with_a_replica_per_device(api):
+    """The "refit" option in multi-GPU mode: every replica keeps its own tree and refits it on its own device; a frame
+    spread over the two devices afterwards equals the frame of a scene built from the moved description."""
+    lut = parity.reference_lut()
+
+    def desc(shift):
+        d = scenes.cornell_box("spheres", brdf_lut=lut, seed=1)
+        for e in d.entities:
+            if len(e.positions) > 600:
+                m = np.array(e.matrix, np.float32).copy(); m[12] += np.float32(shift); e.matrix = m
+        return d
+
+    api.set_devices(2)
+    api.set_option("refit", 1)
+    try:
+        api.set_scene_desc(desc(0.0))
+        s = api.Scene()
+        api.set_scene_desc(desc(0.3))
+        assert s.update().bvhRefitted == 1
+        fresh = api.Scene(desc(0.3))
+        cam, dof = api.make_camera([-4, 0, 4], [0, -1, 0]), api.default_dof(auto_focus=False)
+        a, b = api.Trace(160, 90), api.Trace(160, 90)
+        a.trace_spp(s, cam, dof, 0, 1, sums=True)            # one sample per pixel: equal bit for bit
+        b.trace_spp(fresh, cam, dof, 0, 1, sums=True)
+        assert np.array_equal(a.image("color"), b.image("color")) and a.image("color").mean() > 0.0
+        a.trace_spp(s, cam, dof, 1, 4, sums=True)            # by sample index over the two devices
+        b.trace_spp(fresh, cam, dof, 1, 4, sums=True)
+        assert np.allclose(a.image("color"), b.image("color"), rtol=1e-5, atol=1e-5)
+        a.close(); b.close(); fresh.close(); s.close()
+    finally:
+        api.set_option("refit", 0)
+        api.set_scene_desc(None)
