@@ -5,6 +5,7 @@
 #pragma once
 
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 #if defined(__SSE2__)
 #include <emmintrin.h>
@@ -64,6 +65,7 @@ public:
         started_ = true;
         unsigned hw = std::thread::hardware_concurrency();
         int n = hw == 0 ? 1 : (int)(hw > 8 ? 8 : hw);
+        if (const char* e = getenv("PIMPT_HOST_THREADS")) { const int v = atoi(e); if (v >= 1 && v <= 64) n = v; }
         unsigned long long seen;
         { std::lock_guard<std::mutex> lock(mutex_); seen = generation_; }      // runs before this start are not theirs
         for (int w = 1; w < n; ++w) threads_.emplace_back([this, w, seen] { loop(w, seen); });
