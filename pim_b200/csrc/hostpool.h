@@ -7,6 +7,7 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 #if defined(__SSE2__)
 #include <emmintrin.h>
 #endif
@@ -28,30 +29,34 @@ public:
     // fn(w, workers()) once per worker, w = 0 on the caller; returns when all are done. One run at a time.
     void run(const std::function<void(int, int)>& fn)
     {
-        std::lock_guard<std::mutex> serial(runMutex_);
+        afterFork();
+        Sync& S = *sync_;
+        std::lock_guard<std::mutex> serial(S.runMutex);
         if (threads_.empty()) { fn(0, 1); return; }
         {
-            std::lock_guard<std::mutex> lock(mutex_);
+            std::lock_guard<std::mutex> lock(S.mutex);
             fn_ = &fn;
             pending_ = (int)threads_.size();
             ++generation_;
         }
-        wake_.notify_all();
+        S.wake.notify_all();
         fn(0, workers());
-        std::unique_lock<std::mutex> lock(mutex_);
-        done_.wait(lock, [&] { return pending_ == 0; });
+        std::unique_lock<std::mutex> lock(S.mutex);
+        S.done.wait(lock, [&] { return pending_ == 0; });
         fn_ = nullptr;
     }
 
-    // joins the threads (PtSys_Shutdown); the next run() starts them again
+    // joins the threads (PtSys_Shutdown); the next start() starts them again
     void stop()
     {
-        std::lock_guard<std::mutex> serial(runMutex_);
+        afterFork();
+        Sync& S = *sync_;
+        std::lock_guard<std::mutex> serial(S.runMutex);
         {
-            std::lock_guard<std::mutex> lock(mutex_);
+            std::lock_guard<std::mutex> lock(S.mutex);
             quit_ = true;
         }
-        wake_.notify_all();
+        S.wake.notify_all();
         for (std::thread& t : threads_) t.join();
         threads_.clear();
         quit_ = false;
@@ -60,30 +65,47 @@ public:
 
     void start()
     {
-        std::lock_guard<std::mutex> serial(runMutex_);
+        afterFork();
+        Sync& S = *sync_;
+        std::lock_guard<std::mutex> serial(S.runMutex);
         if (started_) return;
         started_ = true;
         unsigned hw = std::thread::hardware_concurrency();
         int n = hw == 0 ? 1 : (int)(hw > 8 ? 8 : hw);
         if (const char* e = getenv("PIMPT_HOST_THREADS")) { const int v = atoi(e); if (v >= 1 && v <= 64) n = v; }
         unsigned long long seen;
-        { std::lock_guard<std::mutex> lock(mutex_); seen = generation_; }      // runs before this start are not theirs
-        for (int w = 1; w < n; ++w) threads_.emplace_back([this, w, seen] { loop(w, seen); });
+        { std::lock_guard<std::mutex> lock(S.mutex); seen = generation_; }      // runs before this start are not theirs
+        for (int w = 1; w < n; ++w) threads_.emplace_back([this, w, seen, &S] { loop(S, w, seen); });
     }
 
 private:
-    HostPool() = default;
-    ~HostPool() { stop(); }
+    // the locks and condition variables live in a block of their own: a forked child inherits them in whatever
+    // state the parent's threads left them (waiters that do not exist in the child), so it drops the block,
+    // lets go of the thread handles and starts over
+    struct Sync { std::mutex runMutex, mutex; std::condition_variable wake, done; };
 
-    void loop(int w, unsigned long long seen)
+    HostPool() : sync_(new Sync()), ownerPid_((long)getpid()) {}
+    ~HostPool() { if (ownerPid_ == (long)getpid()) { stop(); delete sync_; } else abandon(); }
+
+    void abandon()
+    {
+        for (std::thread& t : threads_) { try { t.detach(); } catch (...) {} }
+        threads_.clear();
+        sync_ = new Sync();         // the old block is left alone on purpose
+        started_ = false; quit_ = false; pending_ = 0; fn_ = nullptr;
+        ownerPid_ = (long)getpid();
+    }
+    void afterFork() { if (ownerPid_ != (long)getpid()) abandon(); }
+
+    void loop(Sync& S, int w, unsigned long long seen)
     {
         for (;;)
         {
             const std::function<void(int, int)>* fn = nullptr;
             int total = 0;
             {
-                std::unique_lock<std::mutex> lock(mutex_);
-                wake_.wait(lock, [&] { return quit_ || generation_ != seen; });
+                std::unique_lock<std::mutex> lock(S.mutex);
+                S.wake.wait(lock, [&] { return quit_ || generation_ != seen; });
                 if (quit_) return;
                 seen = generation_;
                 fn = fn_;
@@ -91,19 +113,19 @@ private:
             }
             (*fn)(w, total);
             {
-                std::lock_guard<std::mutex> lock(mutex_);
-                if (--pending_ == 0) done_.notify_one();
+                std::lock_guard<std::mutex> lock(S.mutex);
+                if (--pending_ == 0) S.done.notify_one();
             }
         }
     }
 
-    std::mutex runMutex_, mutex_;
-    std::condition_variable wake_, done_;
+    Sync* sync_;
     std::vector<std::thread> threads_;
     const std::function<void(int, int)>* fn_ = nullptr;
     unsigned long long generation_ = 0;
     int pending_ = 0;
     bool quit_ = false, started_ = false;
+    long ownerPid_ = 0;
 };
 
 // [begin, end) of worker w's share of n items

@@ -42,3 +42,23 @@ extern "C" void hp_touch(int32_t* visits, int64_t n)
 
 extern "C" void hp_copy(void* dst, const void* src, int64_t bytes) { pt::hostCopyParallel(dst, src, (size_t)bytes); }
 extern "C" void hp_stream_copy(void* dst, const void* src, int64_t bytes) { pt::streamCopy((char*)dst, (const char*)src, (size_t)bytes); }
+
+#include <sys/wait.h>
+// fork after the pool has started: the child starts its own threads, runs, and exits cleanly (exit code 0)
+extern "C" int hp_fork_child_runs(void)
+{
+    pt::HostPool::get().start();
+    const pid_t pid = fork();
+    if (pid == 0)
+    {
+        int32_t visits[64] = {};
+        pt::HostPool::get().run([&](int w, int workers) { size_t a, b; pt::hostShare(64, w, workers, a, b); for (size_t i = a; i < b; ++i) visits[i] += 1; });
+        int bad = 0;
+        for (int i = 0; i < 64; ++i) bad += visits[i] != 1;
+        pt::HostPool::get().stop();
+        _exit(bad ? 3 : 0);
+    }
+    int status = -1;
+    if (pid < 0 || waitpid(pid, &status, 0) != pid) return -1;
+    return WIFEXITED(status) ? WEXITSTATUS(status) : -2;
+}

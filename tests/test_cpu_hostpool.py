@@ -63,3 +63,11 @@ def test_parallel_streaming_copy_is_a_memcpy(hp):
                 fn(dst.ctypes.data + 16 + dst_off, src.ctypes.data + src_off, n)
                 assert np.array_equal(dst[16 + dst_off:16 + dst_off + n], src[src_off:src_off + n]), (n, src_off, dst_off)
                 assert (dst[:16 + dst_off] == 0xAB).all() and (dst[16 + dst_off + n:] == 0xAB).all()
+
+
+def test_pool_after_fork(hp):
+    """A forked child holds the parent's thread handles but not its threads: start() lets go of them and starts anew"""
+    assert hp.hp_fork_child_runs() == 0
+    visits = np.zeros(100, np.int32)
+    hp.hp_touch(visits.ctypes.data, 100)          # the parent's pool still works
+    assert (visits == 1).all()
