@@ -68,8 +68,10 @@ constexpr int kShadeThreads = PT_SHADE_THREADS;
 #ifndef PT_SHADE_BLOCKS_A
 #define PT_SHADE_BLOCKS_A 8
 #endif
+// stage B, cornell 1080p, us per full-pool launch at 4 / 5 / 6 / 7 / 8 CTAs per SM (128 / 96 / 80 / 72 / 64 registers):
+// 583 / 509 / 490 / 496 / 523; stage A at 6 / 7 / 8 / 9 / 10: 402 / 378 / 364 / 414 / 424
 #ifndef PT_SHADE_BLOCKS_B
-#define PT_SHADE_BLOCKS_B 5
+#define PT_SHADE_BLOCKS_B 6
 #endif
 
 // What stage A leaves for stage B. rd2.w holds flag bits: the low two are Pend_None (shade
