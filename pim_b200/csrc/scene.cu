@@ -39,9 +39,9 @@ __global__ void __launch_bounds__(kTravThreads) k_closestHit(DScene S, const F4*
 }
 
 // idle lanes at which a persistent warp fetches new rays (10 M-triangle soup, closest / any hit Mrays/s: 8 lanes
-// 334 / 638, 4 lanes 345 / 661)
+// 334 / 638, 4 lanes 345 / 661; on the final code at 9 CTAs per SM: 4 lanes 376 / 675, 3 lanes 378 / 678, 2 lanes 378 / 675)
 #ifndef PT_BATCH_REFILL
-#define PT_BATCH_REFILL 4
+#define PT_BATCH_REFILL 3
 #endif
 #ifndef PT_POSTPONED_LEAVES
 #define PT_POSTPONED_LEAVES 1
@@ -53,9 +53,9 @@ constexpr int kLeafVotes = PT_LEAF_VOTES;
 
 // persistent form: warps refill finished lanes with the next rays of the batch (one atomic per warp)
 // registers: 70 per thread when left to the compiler (43 % occupancy); capped at 64 for 8 CTAs per SM the 10 M-triangle
-// soup goes from 345 to 370 Mrays/s, at 48 (10 CTAs, spills) down to 299
+// soup goes from 345 to 370 Mrays/s, at 56 (9 CTAs) to 376, at 48 (10 CTAs, spills) down to 299; 72 (7 CTAs) 347
 #ifndef PT_PERSIST_MIN_BLOCKS
-#define PT_PERSIST_MIN_BLOCKS 8
+#define PT_PERSIST_MIN_BLOCKS 9
 #endif
 __global__ void __launch_bounds__(kTravThreads, PT_PERSIST_MIN_BLOCKS) k_closestHitPersistent(DScene S, const F4* __restrict__ ro,
                                                                         const F4* __restrict__ rd, float tNear,
