@@ -33,7 +33,12 @@ namespace pt {
 bool g_kernelTiming = false;
 thread_local bool t_workerThread = false;
 int g_persistentTraversal = -1;   // -1: by scene size (see usePersistent)
-int g_finishThreshold = 131072;    // live paths at which the tail is finished in one launch; PIMPT_FINISH=n overrides, 0 disables
+constexpr int kSmallCallPaths = 131072;   // a call with no more paths than this skips the wavefront altogether
+// live paths at which the tail is finished in one launch; PIMPT_FINISH=n overrides, 0 disables. Msamples/s at
+// 128 K / 512 K / 2 M: cornell boxes 1080p 2454 / 2455 / 2466, 320x180 x 64 spp 1454 / 1503 / 1569, its lightmap bake
+// 1231 / 1289 / 1326 (M texel-samples/s), 1 M-triangle interior 1266 / 1273 / 1277, but cornell spheres (glass: long,
+// uneven paths) 740 / 739 / 676: 512 K is the largest that costs no scene anything
+int g_finishThreshold = 524288;
 KernelStats g_kernelStats = {};
 
 // Refilling idle lanes pays off only when rays take very many steps: +22 % on the 10 M-triangle
@@ -721,7 +726,7 @@ bool runWavefront(const DScene& S, PathPool& pool, const WorkDesc& work, cudaStr
     while (ok && !finished)
     {
         const int r = (int)(iterations % kRing);
-        const bool smallCall = iterations == 0 && work.count <= (int64_t)g_finishThreshold && work.count <= (int64_t)cap;
+        const bool smallCall = iterations == 0 && work.count <= (int64_t)std::min(g_finishThreshold, kSmallCallPaths) && work.count <= (int64_t)cap;
         if ((!workLeft && bound <= g_finishThreshold) || smallCall)
         {
             // the few paths still alive (after the iterations already queued) finish in one launch;
