@@ -816,14 +816,13 @@ static bool dofUpdate(PtScene* scene, PtDofInfo* dof, const Camera* camera)
     return true;
 }
 
+// the six images are one allocation: image[0..2] then sum[0..2], each w*h*3 floats, so that a frame zeroes the
+// sums with one memset, folds them with one launch and, when the host images are adjacent too (PtTrace_New
+// makes them so), copies them back with one copy
 static void freeImages(DeviceImages& im)
 {
-    for (int k = 0; k < 3; ++k)
-    {
-        if (im.image[k]) cudaFree(im.image[k]);
-        if (im.sum[k]) cudaFree(im.sum[k]);
-        im.image[k] = im.sum[k] = nullptr;
-    }
+    if (im.image[0]) cudaFree(im.image[0]);
+    for (int k = 0; k < 3; ++k) im.image[k] = im.sum[k] = nullptr;
 }
 
 // The running-mean images of a PtTrace live on the device (the host arrays are refreshed from
@@ -837,16 +836,11 @@ static DeviceImages* traceImages(PtTrace* trace)
     if (it != g_traces.end()) { freeImages(it->second); g_traces.erase(it); }      // the image size changed
     DeviceImages im;
     im.texels = texels;
-    for (int k = 0; k < 3; ++k)
-    {
-        if (!PT_CUDA(cudaMalloc((void**)&im.image[k], sizeof(float) * 3 * texels)) ||
-            !PT_CUDA(cudaMalloc((void**)&im.sum[k], sizeof(float) * 3 * texels)) ||
-            !PT_CUDA(cudaMemset(im.image[k], 0, sizeof(float) * 3 * texels)))
-        {
-            freeImages(im);
-            return nullptr;
-        }
-    }
+    float* block = nullptr;
+    const size_t n3 = 3 * (size_t)texels;
+    if (!PT_CUDA(cudaMalloc((void**)&block, sizeof(float) * 6 * n3))) return nullptr;
+    if (!PT_CUDA(cudaMemset(block, 0, sizeof(float) * 3 * n3))) { cudaFree(block); return nullptr; }
+    for (int k = 0; k < 3; ++k) { im.image[k] = block + (size_t)k * n3; im.sum[k] = block + (size_t)(3 + k) * n3; }
     g_traces[trace] = im;
     return &g_traces[trace];
 }
@@ -961,22 +955,20 @@ void PtTrace_New(PtTrace* trace, pim_int2 imageSize)      // path_tracer.c:1117-
     trace->imageSize = imageSize;
     trace->sampleWeight = 1.0f;
     if (!ensureInit() || texels == 0) return;
+    // one page-locked block, carved into the four images (color is its base: PtTrace_Del frees that)
     const size_t bytes = sizeof(float) * 3 * texels;
-    bool ok = PT_CUDA(cudaMallocHost((void**)&trace->color, bytes)) && PT_CUDA(cudaMallocHost((void**)&trace->albedo, bytes)) &&
-              PT_CUDA(cudaMallocHost((void**)&trace->normal, bytes)) && PT_CUDA(cudaMallocHost((void**)&trace->denoised, bytes));
-    if (!ok) { PtTrace_Del(trace); return; }
-    memset(trace->color, 0, bytes); memset(trace->albedo, 0, bytes);
-    memset(trace->normal, 0, bytes); memset(trace->denoised, 0, bytes);
+    char* block = nullptr;
+    if (!PT_CUDA(cudaMallocHost((void**)&block, 4 * bytes))) return;
+    memset(block, 0, 4 * bytes);
+    trace->color = (pim_float3*)block; trace->albedo = (pim_float3*)(block + bytes);
+    trace->normal = (pim_float3*)(block + 2 * bytes); trace->denoised = (pim_float3*)(block + 3 * bytes);
 }
 
 void PtTrace_Del(PtTrace* trace)
 {
     if (!trace) return;
     releaseImages(trace);
-    if (trace->color) cudaFreeHost(trace->color);
-    if (trace->albedo) cudaFreeHost(trace->albedo);
-    if (trace->normal) cudaFreeHost(trace->normal);
-    if (trace->denoised) cudaFreeHost(trace->denoised);
+    if (trace->color) cudaFreeHost(trace->color);       // the base of the block PtTrace_New carved the four images from
     memset(trace, 0, sizeof(*trace));
 }
 
@@ -1164,7 +1156,7 @@ int32_t Pt_TraceSpp(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera
     const int w = trace->imageSize.x, h = trace->imageSize.y;
     const int64_t n3 = im->texels * 3;
     bool ok = true;
-    for (int k = 0; k < 3; ++k) ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[k], 0, sizeof(float) * n3, scene->stream));
+    ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[0], 0, sizeof(float) * 3 * n3, scene->stream));      // the three sums are adjacent
     ok = ok && traceSppDevice(scene, camera, dof, w, h, sppBegin, sppCount, im->sum[0], im->sum[1], im->sum[2], scene->stream);
     cudaStream_t st = scene->stream;
     float* host[3] = { (float*)trace->color, (float*)trace->albedo, (float*)trace->normal };
@@ -1196,16 +1188,16 @@ void Pt_Trace(PtTrace* trace, PtDofInfo* dof, PtScene* scene, const Camera* came
     if (!dofUpdate(scene, dof, camera)) return;
     cudaStream_t st = scene->stream;
     bool ok = true;
-    for (int k = 0; k < 3; ++k) ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[k], 0, sizeof(float) * n3, st));
+    ok = ok && PT_CUDA(cudaMemsetAsync(im->sum[0], 0, sizeof(float) * 3 * n3, st));      // the three sums are adjacent
     // the CDFs were relearned just above: trace without a second PtScene_Update
     ok = ok && traceSppDevice(scene, camera, dof, w, h, (int)scene->nextPass, 1, im->sum[0], im->sum[1], im->sum[2], st, false);
     scene->nextPass++;
     float* host[3] = { (float*)trace->color, (float*)trace->albedo, (float*)trace->normal };
-    for (int k = 0; ok && k < 3; ++k)
-    {
-        ok = launchLerp(im->image[k], im->sum[k], n3, trace->sampleWeight, st);
-        ok = ok && PT_CUDA(cudaMemcpyAsync(host[k], im->image[k], sizeof(float) * n3, cudaMemcpyDeviceToHost, st));
-    }
+    ok = ok && launchLerp(im->image[0], im->sum[0], 3 * n3, trace->sampleWeight, st);           // and so are the three means
+    if (ok && host[1] == host[0] + n3 && host[2] == host[1] + n3)
+        ok = PT_CUDA(cudaMemcpyAsync(host[0], im->image[0], sizeof(float) * 3 * n3, cudaMemcpyDeviceToHost, st));
+    else
+        for (int k = 0; ok && k < 3; ++k) ok = PT_CUDA(cudaMemcpyAsync(host[k], im->image[k], sizeof(float) * n3, cudaMemcpyDeviceToHost, st));
     ok = PT_CUDA(cudaStreamSynchronize(st)) && ok;
 }
 
